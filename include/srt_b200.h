@@ -1,0 +1,131 @@
+/* srt_b200.h -- C-ABI of the B200 path-tracing hot path (libsrt_b200.so).
+ *
+ * The reference has no FFI layer: its boundary around the hot path is the set of OpenGL calls the host
+ * makes around glDispatchCompute.  Each entry point below replaces one of those call
+ * sites (cited as file:line in /root/reference) and takes exactly the host data that call site hands
+ * to GL -- plain pointers and sizes in the layouts of srt_types.h, no CUDA or torch types.
+ *
+ * Conventions: every function returns 0 on success, non-zero on error (srt_last_error gives the
+ * text).  Host arrays stay owned by the caller and are copied; device memory is owned by the context
+ * and released by srt_destroy.  Calls on one context must be serialised by the caller (the reference is
+ * single-threaded on its GL context thread).  There is NO CPU fallback: without a usable CUDA device
+ * srt_create fails.
+ */
+#ifndef SRT_B200_H_
+#define SRT_B200_H_
+
+#include "srt_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct srt_ctx srt_ctx;
+
+/* Counters of the work done by srt_render since the last srt_reset_counters (device-side counts). */
+typedef struct srt_counters {
+  uint64_t segments;     /* CheckHit calls of the path loop (raytrace_compute.glsl:225): primary + bounce rays */
+  uint64_t shadow_rays;  /* CheckHit calls of CheckLightOccluded (raytrace_compute.glsl:174) */
+  uint64_t paths;        /* pixel samples started */
+  uint64_t capped_paths; /* paths cut by the 1024-iteration decree (Q9) */
+  uint64_t kernel_launches; /* kernels launched by this context (all kinds) */
+  uint64_t nodes;        /* BVH nodes box-tested   (only counted when SRT_FLAG_COUNT_TRAVERSAL is set) */
+  uint64_t tris;         /* triangles tested       (only counted when SRT_FLAG_COUNT_TRAVERSAL is set) */
+} srt_counters;
+
+/* srt_set_option keys */
+#define SRT_OPT_TRAVERSAL 1      /* 0 = reference visiting order (bit-exact by construction)
+                                    1 = near-child-first ordered traversal (default; same hits bar documented ties) */
+#define SRT_OPT_COUNT_TRAVERSAL 2 /* 1 = count nodes/tris (slower; for the roofline figures) */
+#define SRT_OPT_L2_PERSIST 3     /* 1 = pin BVH top levels + noise tables in L2 with an access-policy window (default 1) */
+#define SRT_OPT_BLOCK_THREADS 4  /* threads per block of the path kernel (multiple of 32) */
+
+/* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
+ * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */
+int srt_create(srt_ctx** out, int device);
+/* glDeleteProgram / end of process. */
+void srt_destroy(srt_ctx* ctx);
+/* glGetError-style text of the last failure on this context (ctx may be NULL for srt_create failures). */
+const char* srt_last_error(const srt_ctx* ctx);
+
+/* Run on an existing CUDA stream (a cudaStream_t passed as void*); NULL = the context's own stream. */
+int srt_set_stream(srt_ctx* ctx, void* cuda_stream);
+int srt_set_option(srt_ctx* ctx, int key, int value);
+
+/* AssetUtils::UploadModelDataToGPU  (src/asset_utils/gpu_loader.cpp:135-182): the five SSBOs at
+ * binding_offset+0..4, whole-buffer upload; may be called again to replace the scene. */
+int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* nodes, uint32_t n_nodes,
+                     const srt_material* materials, uint32_t n_materials, const srt_triangle* triangles,
+                     uint32_t n_triangles, const srt_vertex* vertices, uint32_t n_vertices);
+
+/* AssetUtils::UpdateModelMatrix  (src/asset_utils/gpu_loader.cpp:185-196): glBufferSubData of bvhs[index].frame,
+ * 16 floats column-major. */
+int srt_update_frame(srt_ctx* ctx, uint32_t index, const float* mat4_column_major);
+
+/* UpdateNoiseTex  (src/main.cpp:281-296): the two RGB32F texture buffers, count texels of 3 floats each.
+ * count must equal width*height of the render (the shader indexes them modulo Width*Height). */
+int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const float* uniform_vec3, uint32_t count);
+
+/* lights SSBO at binding 4 + SetInt("lightCount")  (src/main.cpp:684,688-692).  count <= SRT_MAX_LIGHTS. */
+int srt_set_lights(srt_ctx* ctx, const srt_light* lights, int32_t count);
+
+/* Compute::SetBool/SetInt/SetUInt/SetVec3  (src/main.cpp:668-685): the per-frame uniforms.  light_count is
+ * taken from srt_set_lights when params->light_count < 0. */
+int srt_set_params(srt_ctx* ctx, const srt_params* params);
+
+/* Texture::getTextureHandle / Texture32::getTextureHandle  (src/graphics/texture.cpp:50-97,142-186): allocate
+ * the RGBA8 output image and the RGBA32F accumulation image (zero-initialised, decree Q8).
+ * width and height must be multiples of 8 (src/main.cpp:706 dispatches W/8 x H/8 groups unguarded). */
+int srt_resize(srt_ctx* ctx, int32_t width, int32_t height);
+
+/* Restrict rendering to rows [y0, y1) (multiples of 8) -- the image-tile half of the multi-GPU split.
+ * Default is the whole image. */
+int srt_set_rows(srt_ctx* ctx, int32_t y0, int32_t y1);
+
+/* glDispatchCompute(W/8,H/8,1) + glMemoryBarrier + glFinish  (src/main.cpp:706-718), n_frames times:
+ * renders frames accum_frames .. accum_frames+n_frames-1 (1 sample per pixel each), accumulating in
+ * frame order, then advances params.accum_frames by n_frames.  With params.reset_accum set it clears the
+ * accumulation image instead (raytrace_compute.glsl:390-393).  Returns after the work completed. */
+int srt_render(srt_ctx* ctx, int32_t n_frames);
+/* Same, without the trailing synchronisation (work is queued on the context's stream). */
+int srt_render_async(srt_ctx* ctx, int32_t n_frames);
+int srt_sync(srt_ctx* ctx);
+
+/* Texture::updateImageDataFromGPU / Texture32::updateImageDataFromGPU  (src/graphics/texture.cpp:99-106,192-200). */
+int srt_read_output(srt_ctx* ctx, uint8_t* rgba8 /* W*H*4 */);
+int srt_read_accum(srt_ctx* ctx, float* rgba32f /* W*H*4 */);
+/* Replace the accumulation image (resume from a checkpoint / install a reduced multi-GPU sum). */
+int srt_write_accum(srt_ctx* ctx, const float* rgba32f /* W*H*4 */);
+/* Re-run only the tonemap (raytrace_compute.glsl:412-413) from the current accumulation image with
+ * divisor accum_frames; used after a multi-GPU reduce. */
+int srt_tonemap(srt_ctx* ctx, int32_t accum_frames);
+/* Device address of the RGBA32F accumulation image (W*H*4 floats) so that a collective (NCCL through
+ * torch.distributed) can reduce it in place.  Owned by the context. */
+int srt_accum_device_ptr(srt_ctx* ctx, void** device_ptr, uint64_t* n_floats);
+
+/* Parity aid: primary-hit primitive per pixel of the last frame rendered (sphere index or global triangle
+ * index, SRT_NO_HIT for a miss).  Recording is switched on by the first call with enable=1. */
+int srt_enable_primary_ids(srt_ctx* ctx, int enable);
+int srt_read_primary_ids(srt_ctx* ctx, uint32_t* ids /* W*H */);
+
+/* AssetUtils::UpdateRays + the test kernel of ray_intersects.glsl:135-161  (src/asset_utils/gpu_loader.cpp:198-210,
+ * include/compute/tests/BVH_intergration_tests.cpp:69-94): closest hit of each ray against the first bvh_count
+ * BVHs; hit_tri[i] = global triangle index or SRT_NO_HIT, hit_t[i] = final intersection_distance (may be NULL). */
+int srt_trace_rays(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, uint32_t bvh_count, uint32_t* hit_tri,
+                   float* hit_t);
+
+int srt_get_counters(srt_ctx* ctx, srt_counters* out);
+int srt_reset_counters(srt_ctx* ctx);
+
+/* Device-side evaluation of the numeric decree (srt_detmath.h), for bit-for-bit checks against the host:
+ * which: 0 = sin, 1 = cos, 2 = pow(x, 1/2.4), 3 = randFloat(x, y[i]) (y required), 4 = linearToSrgb. */
+int srt_eval_detmath(srt_ctx* ctx, int which, const float* x, const float* y, float* out, uint32_t n);
+
+/* Library/build identification, e.g. "srt_b200 0.1 sm_100a". */
+const char* srt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* SRT_B200_H_ */
