@@ -1,0 +1,222 @@
+"""Python view of libsrt_b200.so (the C-ABI of include/srt_b200.h) through ctypes.
+
+This is plumbing for tests/, bench.py and __graft_entry__.py: it only marshals numpy arrays into the C-ABI
+calls a C++ host (simple-ray-tracer_b200/host) makes.  There is no Python or CPU rendering path here; if the
+shared library is missing or no B200 is visible the calls fail loudly.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsrt_b200.so")
+
+OPT_TRAVERSAL, OPT_COUNT_TRAVERSAL, OPT_L2_PERSIST, OPT_BLOCK_THREADS = 1, 2, 3, 4
+TRAV_REFERENCE, TRAV_ORDERED = 0, 1
+NO_HIT = 0xFFFFFFFF
+MAX_LIGHTS = 10
+
+BVH_DT = np.dtype([("first_index", "<u4"), ("count", "<u4"), ("_pad", "<u4", 2), ("frame", "<f4", 16)])
+NODE_DT = np.dtype([("min", "<f4", 3), ("index", "<u4"), ("max", "<f4", 3), ("count", "<u4")])
+MAT_DT = np.dtype([("diffuse", "<f4", 3), ("specular_ex", "<f4"), ("specular", "<f4", 3), ("use_texture", "<u4"),
+                   ("handle", "<u4", 2), ("_pad", "<u4", 2)])
+TRI_DT = np.dtype([("v", "<u4", 3), ("material", "<u4")])
+VERT_DT = np.dtype([("vertex", "<f4", 3), ("_pad0", "<f4"), ("texture", "<f4", 2), ("_pad1", "<f4", 2)])
+LIGHT_DT = np.dtype([("position", "<f4", 3), ("intensity", "<f4"), ("color", "<f4", 3), ("pad1", "<f4")])
+RAY_DT = np.dtype([("origin", "<f4", 3), ("_pad0", "<f4"), ("direction", "<f4", 3), ("dist", "<f4")])
+
+EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt_set_option", "srt_upload_scene",
+           "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows",
+           "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
+           "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays",
+           "srt_get_counters", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
+
+
+class Params(C.Structure):  # srt_params, include/srt_types.h
+    _fields_ = [("show_model", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
+                ("accum_frames", C.c_int32), ("reset_accum", C.c_int32),
+                ("camera_origin", C.c_float * 3), ("camera_direction", C.c_float * 3),
+                ("camera_up", C.c_float * 3), ("camera_right", C.c_float * 3),
+                ("light_count", C.c_int32), ("bvh_count", C.c_uint32), ("max_depth", C.c_int32)]
+
+
+class Counters(C.Structure):  # srt_counters, include/srt_b200.h
+    _fields_ = [("segments", C.c_uint64), ("shadow_rays", C.c_uint64), ("paths", C.c_uint64),
+                ("capped_paths", C.c_uint64), ("kernel_launches", C.c_uint64), ("nodes", C.c_uint64),
+                ("tris", C.c_uint64)]
+
+
+def build():
+    """Compiles libsrt_b200.so for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    subprocess.run(["make", "-s", "-C", HERE, "libsrt_b200.so"], check=True)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libsrt_b200.so is not built (run __graft_entry__.build()); there is no fallback path")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.srt_last_error.restype = C.c_char_p
+        _lib.srt_last_error.argtypes = [C.c_void_p]
+        _lib.srt_version.restype = C.c_char_p
+        _lib.srt_destroy.restype = None
+        _lib.srt_destroy.argtypes = [C.c_void_p]
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class SrtError(RuntimeError):
+    pass
+
+
+class Context:
+    """One srt_ctx: the stand-in for the reference's GL context + compute program + bound buffers."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        self._lib = lib()
+        if self._lib.srt_create(C.byref(self._h), C.c_int(device)) != 0:
+            raise SrtError(self._lib.srt_last_error(None).decode())
+        self.width = self.height = 0
+
+    def close(self):
+        if self._h:
+            self._lib.srt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise SrtError(self._lib.srt_last_error(self._h).decode())
+
+    def set_option(self, key, value):
+        self._ck(self._lib.srt_set_option(self._h, C.c_int(key), C.c_int(value)))
+
+    def set_stream(self, cuda_stream_ptr):
+        self._ck(self._lib.srt_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
+
+    def upload_scene(self, scene):
+        a = {k: np.ascontiguousarray(scene[k]) for k in ("bvhs", "nodes", "materials", "triangles", "vertices")}
+        assert a["bvhs"].dtype.itemsize == 80 and a["nodes"].dtype.itemsize == 32 and a["materials"].dtype.itemsize == 48
+        assert a["triangles"].dtype.itemsize == 16 and a["vertices"].dtype.itemsize == 32
+        self._ck(self._lib.srt_upload_scene(self._h, _p(a["bvhs"]), C.c_uint32(len(a["bvhs"])), _p(a["nodes"]),
+                                            C.c_uint32(len(a["nodes"])), _p(a["materials"]),
+                                            C.c_uint32(len(a["materials"])), _p(a["triangles"]),
+                                            C.c_uint32(len(a["triangles"])), _p(a["vertices"]),
+                                            C.c_uint32(len(a["vertices"]))))
+
+    def update_frame(self, index, mat4_column_major):
+        m = np.ascontiguousarray(mat4_column_major, np.float32).reshape(16)
+        self._ck(self._lib.srt_update_frame(self._h, C.c_uint32(index), _p(m)))
+
+    def upload_noise(self, unit, uniform):
+        unit = np.ascontiguousarray(unit, np.float32)
+        uniform = np.ascontiguousarray(uniform, np.float32)
+        assert unit.shape == uniform.shape and unit.shape[-1] == 3
+        self._ck(self._lib.srt_upload_noise(self._h, _p(unit), _p(uniform), C.c_uint32(unit.size // 3)))
+
+    def set_lights(self, lights):
+        lights = np.ascontiguousarray(lights)
+        assert lights.dtype.itemsize == 32
+        self._ck(self._lib.srt_set_lights(self._h, _p(lights), C.c_int32(len(lights))))
+
+    def set_params(self, params):
+        self._ck(self._lib.srt_set_params(self._h, C.byref(params)))
+
+    def resize(self, width, height):
+        self._ck(self._lib.srt_resize(self._h, C.c_int32(width), C.c_int32(height)))
+        self.width, self.height = width, height
+
+    def set_rows(self, y0, y1):
+        self._ck(self._lib.srt_set_rows(self._h, C.c_int32(y0), C.c_int32(y1)))
+
+    def render(self, n_frames=1):
+        self._ck(self._lib.srt_render(self._h, C.c_int32(n_frames)))
+
+    def render_async(self, n_frames=1):
+        self._ck(self._lib.srt_render_async(self._h, C.c_int32(n_frames)))
+
+    def sync(self):
+        self._ck(self._lib.srt_sync(self._h))
+
+    def read_output(self, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.uint8)
+        self._ck(self._lib.srt_read_output(self._h, _p(out)))
+        return out
+
+    def read_accum(self, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.float32)
+        self._ck(self._lib.srt_read_accum(self._h, _p(out)))
+        return out
+
+    def write_accum(self, accum):
+        accum = np.ascontiguousarray(accum, np.float32)
+        assert accum.size == self.width * self.height * 4
+        self._ck(self._lib.srt_write_accum(self._h, _p(accum)))
+
+    def tonemap(self, accum_frames):
+        self._ck(self._lib.srt_tonemap(self._h, C.c_int32(accum_frames)))
+
+    def accum_device_ptr(self):
+        ptr, n = C.c_void_p(), C.c_uint64()
+        self._ck(self._lib.srt_accum_device_ptr(self._h, C.byref(ptr), C.byref(n)))
+        return ptr.value, n.value
+
+    def enable_primary_ids(self, enable=True):
+        self._ck(self._lib.srt_enable_primary_ids(self._h, C.c_int(int(enable))))
+
+    def read_primary_ids(self):
+        ids = np.empty((self.height, self.width), np.uint32)
+        self._ck(self._lib.srt_read_primary_ids(self._h, _p(ids)))
+        return ids
+
+    def trace_rays(self, rays, bvh_count=1):
+        rays = np.ascontiguousarray(rays)
+        assert rays.dtype.itemsize == 32
+        hit = np.empty(len(rays), np.uint32)
+        t = np.empty(len(rays), np.float32)
+        self._ck(self._lib.srt_trace_rays(self._h, _p(rays), C.c_uint32(len(rays)), C.c_uint32(bvh_count), _p(hit), _p(t)))
+        return hit, t
+
+    def counters(self):
+        c = Counters()
+        self._ck(self._lib.srt_get_counters(self._h, C.byref(c)))
+        return {k: int(getattr(c, k)) for k, _ in Counters._fields_}
+
+    def reset_counters(self):
+        self._ck(self._lib.srt_reset_counters(self._h))
+
+    def eval_detmath(self, which, x, y=None):
+        x = np.ascontiguousarray(x, np.float32)
+        y = np.ascontiguousarray(y, np.float32) if y is not None else None
+        out = np.empty_like(x)
+        self._ck(self._lib.srt_eval_detmath(self._h, C.c_int(which), _p(x), _p(y), _p(out), C.c_uint32(x.size)))
+        return out
+
+
+def make_params(width, height, cam, show_model, accum_frames=1, light_count=-1, bvh_count=1, max_depth=0, reset=0):
+    p = Params()
+    p.show_model, p.width, p.height = int(show_model), width, height
+    p.accum_frames, p.reset_accum = accum_frames, reset
+    p.camera_origin[:] = cam["origin"]
+    p.camera_direction[:] = cam["direction"]
+    p.camera_up[:] = cam["up"]
+    p.camera_right[:] = cam["right"]
+    p.light_count, p.bvh_count, p.max_depth = light_count, bvh_count, max_depth
+    return p

@@ -1,0 +1,634 @@
+// srt_api.cu -- the C-ABI of include/srt_b200.h: context, uploads, device re-layout, launches, readback.
+//
+// Each entry point stands in for the OpenGL call site of the reference named in srt_b200.h.  No torch, no
+// CPU rendering path: every result comes from the kernels in srt_kernels.cu.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "srt_b200.h"
+#include "srt_kernels.h"
+
+using namespace srt;
+
+struct srt_ctx {
+  int device = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  std::string error;
+
+  // host copies of what the reference keeps in its file-static vectors (gpu_loader.cpp:44-52)
+  std::vector<srt_bvh> h_bvhs;
+  std::vector<BvhRecord> h_bvh_records;
+  uint32_t n_nodes = 0, n_tris = 0, n_mats = 0;
+  int tree_depth = 0;
+  bool have_scene = false;
+
+  // device scene
+  NodePair* d_pairs = nullptr;
+  uint2* d_leaves = nullptr;
+  TriRecord* d_tris = nullptr;
+  MatRecord* d_mats = nullptr;
+  BvhRecord* d_bvhs = nullptr;
+  float2* d_noise_xy = nullptr;
+  float* d_noise_x = nullptr;
+  uint32_t noise_count = 0;
+
+  // images
+  int width = 0, height = 0;
+  float4* d_accum = nullptr;
+  uchar4* d_out = nullptr;
+  uint32_t* d_ids = nullptr;
+  bool ids_enabled = false;
+  int row0 = 0, row1 = 0;
+
+  // uniforms + lights
+  srt_params params;
+  bool have_params = false;
+  srt_light lights[SRT_MAX_LIGHTS];
+  int light_count = 0;
+
+  // options
+  int traversal = TRAV_ORDERED;
+  bool count_traversal = false;
+  bool l2_persist = true;
+  int block_threads = 64;
+
+  DeviceCounters* d_counters = nullptr;
+  uint64_t kernel_launches = 0;
+};
+
+static thread_local std::string g_create_error;
+
+static int fail(srt_ctx* ctx, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->error = buf; else g_create_error = buf;
+  return 1;
+}
+
+#define CU(ctx, call)                                                                       \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) return fail(ctx, "%s: %s", #call, cudaGetErrorString(e_));       \
+  } while (0)
+
+template <class T>
+static void dfree(T*& p) {
+  if (p) cudaFree(p);
+  p = nullptr;
+}
+
+extern "C" const char* srt_version(void) { return "srt_b200 0.1 sm_100a"; }
+
+extern "C" const char* srt_last_error(const srt_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+extern "C" int srt_create(srt_ctx** out, int device) {
+  if (!out) return fail(nullptr, "srt_create: out is NULL");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return fail(nullptr, "srt_create: no CUDA device (%s); this library has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  if (device < 0 || device >= n) return fail(nullptr, "srt_create: device %d out of range (0..%d)", device, n - 1);
+  cudaDeviceProp prop;
+  CU(nullptr, cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return fail(nullptr, "srt_create: device %d is sm_%d%d; kernels are built for sm_100a only", device, prop.major,
+                prop.minor);
+  CU(nullptr, cudaSetDevice(device));
+  srt_ctx* ctx = new srt_ctx();
+  ctx->device = device;
+  memset(&ctx->params, 0, sizeof ctx->params);
+  memset(ctx->lights, 0, sizeof ctx->lights);
+  if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaMalloc(&ctx->d_counters, sizeof(DeviceCounters)) != cudaSuccess ||
+      cudaMemset(ctx->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess) {
+    fail(nullptr, "srt_create: %s", cudaGetErrorString(cudaGetLastError()));
+    delete ctx;
+    return 1;
+  }
+  ctx->stream = ctx->own_stream;
+  *out = ctx;
+  return 0;
+}
+
+extern "C" void srt_destroy(srt_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris); dfree(ctx->d_mats); dfree(ctx->d_bvhs);
+  dfree(ctx->d_noise_xy); dfree(ctx->d_noise_x); dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
+  dfree(ctx->d_counters);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+}
+
+extern "C" int srt_set_stream(srt_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return 1;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+  return 0;
+}
+
+extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
+  if (!ctx) return 1;
+  switch (key) {
+    case SRT_OPT_TRAVERSAL:
+      if (value != TRAV_REFERENCE && value != TRAV_ORDERED) return fail(ctx, "SRT_OPT_TRAVERSAL: 0 or 1");
+      ctx->traversal = value;
+      return 0;
+    case SRT_OPT_COUNT_TRAVERSAL: ctx->count_traversal = value != 0; return 0;
+    case SRT_OPT_L2_PERSIST: ctx->l2_persist = value != 0; return 0;
+    case SRT_OPT_BLOCK_THREADS:
+      if (value < 32 || value > SRT_MAX_BLOCK_THREADS || value % 32) return fail(ctx, "SRT_OPT_BLOCK_THREADS: 32..%d, multiple of 32", SRT_MAX_BLOCK_THREADS);
+      ctx->block_threads = value;
+      return 0;
+  }
+  return fail(ctx, "srt_set_option: unknown key %d", key);
+}
+
+// ---- scene upload: reference layouts -> device layouts ----------------------------------------
+namespace {
+
+struct Relayout {
+  std::vector<NodePair> pairs;
+  std::vector<uint2> leaves;
+  std::vector<BvhRecord> bvhs;
+  std::vector<uint32_t> rank;  // per triangle: position in the shader's visiting order
+  int depth = 0;
+};
+
+// Walks every BVH from its root in the reference's numbering (children at idx, idx+1;
+// ray_intersects.glsl:126-127) and emits NodePair / leaf records in depth-first order.
+bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* nodes, uint32_t n_nodes,
+              uint32_t n_tris, Relayout& out) {
+  out.rank.assign(n_tris, 0xFFFFFFFFu);
+  uint32_t next_rank = 0;
+  std::vector<uint32_t> seen(n_nodes, 0);  // BVH (1-based) that reached the node
+  struct Item { uint32_t node; uint32_t slot; int depth; };  // slot: where to write this node's reference
+  for (uint32_t b = 0; b < n_bvhs; ++b) {
+    uint32_t root = bvhs[b].first_index;
+    if (root >= n_nodes) return fail(ctx, "bvh %u: first_index %u >= node count %u", b, root, n_nodes), false;
+    BvhRecord rec;
+    memset(&rec, 0, sizeof rec);
+    memcpy(rec.frame, bvhs[b].frame, sizeof rec.frame);
+    memcpy(rec.root_min, nodes[root].min_bounds, 12);
+    memcpy(rec.root_max, nodes[root].max_bounds, 12);
+    // refs[] collects (slot -> ref); slot 0xFFFFFFFF = the root reference of this BVH
+    std::vector<Item> stack;
+    stack.push_back({root, 0xFFFFFFFFu, 0});
+    while (!stack.empty()) {
+      Item it = stack.back();
+      stack.pop_back();
+      if (seen[it.node] == b + 1) return fail(ctx, "bvh %u: node %u reached twice (not a tree)", b, it.node), false;
+      seen[it.node] = b + 1;
+      if (it.depth > out.depth) out.depth = it.depth;
+      const srt_bvh_node& n = nodes[it.node];
+      uint32_t ref;
+      if (n.prim_count > 0) {
+        if ((uint64_t)n.first_child_or_prim_index + n.prim_count > n_tris)
+          return fail(ctx, "node %u: triangles [%u,+%u) out of range", it.node, n.first_child_or_prim_index, n.prim_count), false;
+        ref = SRT_LEAF_BIT | (uint32_t)out.leaves.size();
+        out.leaves.push_back(make_uint2(n.first_child_or_prim_index, n.prim_count));
+      } else {
+        uint32_t c = n.first_child_or_prim_index;
+        if ((uint64_t)c + 1 >= n_nodes) return fail(ctx, "node %u: children %u,%u out of range", it.node, c, c + 1), false;
+        ref = (uint32_t)out.pairs.size();
+        if (ref >= SRT_LEAF_BIT) return fail(ctx, "too many inner nodes"), false;
+        const srt_bvh_node &l = nodes[c], &r = nodes[c + 1];
+        NodePair p;
+        p.a = make_float4(l.min_bounds[0], l.min_bounds[1], l.min_bounds[2], l.max_bounds[0]);
+        p.b = make_float4(l.max_bounds[1], l.max_bounds[2], r.min_bounds[0], r.min_bounds[1]);
+        p.c = make_float4(r.min_bounds[2], r.max_bounds[0], r.max_bounds[1], r.max_bounds[2]);
+        p.d = make_uint4(0, 0, 0, 0);
+        out.pairs.push_back(p);
+        // left subtree first so that records of a subtree are contiguous
+        stack.push_back({c + 1, ref * 2 + 1, it.depth + 1});
+        stack.push_back({c, ref * 2 + 0, it.depth + 1});
+      }
+      if (it.slot == 0xFFFFFFFFu) rec.root_ref = ref;
+      else if (it.slot & 1) out.pairs[it.slot >> 1].d.y = ref;
+      else out.pairs[it.slot >> 1].d.x = ref;
+    }
+    // rank = order in which the shader's traversal (right child popped first) meets the triangles
+    std::vector<uint32_t> order;
+    order.push_back(root);
+    while (!order.empty()) {
+      uint32_t i = order.back();
+      order.pop_back();
+      const srt_bvh_node& n = nodes[i];
+      if (n.prim_count > 0) {
+        for (uint32_t k = 0; k < n.prim_count; ++k) out.rank[n.first_child_or_prim_index + k] = next_rank++;
+      } else {
+        order.push_back(n.first_child_or_prim_index);      // left pushed first
+        order.push_back(n.first_child_or_prim_index + 1);  // right popped first
+      }
+    }
+    out.bvhs.push_back(rec);
+  }
+  return true;
+}
+
+template <class T>
+int upload_vec(srt_ctx* ctx, T*& dst, const std::vector<T>& src) {
+  dfree(dst);
+  size_t bytes = (src.size() ? src.size() : 1) * sizeof(T);
+  CU(ctx, cudaMalloc(&dst, bytes));
+  if (!src.empty()) CU(ctx, cudaMemcpyAsync(dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* nodes,
+                                uint32_t n_nodes, const srt_material* materials, uint32_t n_materials,
+                                const srt_triangle* triangles, uint32_t n_triangles, const srt_vertex* vertices,
+                                uint32_t n_vertices) {
+  if (!ctx) return 1;
+  if (!bvhs || !nodes || !materials || !triangles || !vertices) return fail(ctx, "srt_upload_scene: NULL array");
+  if (n_bvhs == 0 || n_bvhs > SRT_MAX_BVHS) return fail(ctx, "srt_upload_scene: n_bvhs must be 1..%d", SRT_MAX_BVHS);
+  CU(ctx, cudaSetDevice(ctx->device));
+  Relayout rl;
+  if (!relayout(ctx, bvhs, n_bvhs, nodes, n_nodes, n_triangles, rl)) return 1;
+  if (rl.depth > SRT_STACK_SIZE - 1)
+    return fail(ctx, "srt_upload_scene: BVH depth %d overflows the shader's %d-entry traversal stack "
+                "(ray_intersects.glsl:100)", rl.depth, SRT_STACK_SIZE);
+
+  std::vector<TriRecord> tris(n_triangles);
+  for (uint32_t i = 0; i < n_triangles; ++i) {
+    const srt_triangle& t = triangles[i];
+    if (t.v0_idx >= n_vertices || t.v1_idx >= n_vertices || t.v2_idx >= n_vertices)
+      return fail(ctx, "triangle %u: vertex index out of range", i);
+    if (t.material_idx >= n_materials) return fail(ctx, "triangle %u: material index out of range", i);
+    const float *v0 = vertices[t.v0_idx].vertex, *v1 = vertices[t.v1_idx].vertex, *v2 = vertices[t.v2_idx].vertex;
+    TriRecord r;
+    // edge_1 = v1 - v0, edge_2 = v2 - v0 (ray_intersects.glsl:69-70): IEEE subtractions, same bits as on the device
+    r.v0 = make_float4(v0[0], v0[1], v0[2], u2f(t.material_idx));
+    r.e1 = make_float4(v1[0] - v0[0], v1[1] - v0[1], v1[2] - v0[2], u2f(rl.rank[i]));
+    r.e2 = make_float4(v2[0] - v0[0], v2[1] - v0[1], v2[2] - v0[2], 0.0f);
+    tris[i] = r;
+  }
+  std::vector<MatRecord> mats(n_materials);
+  for (uint32_t i = 0; i < n_materials; ++i) {
+    const srt_material& m = materials[i];
+    // raytrace_utils.glsl:171: roughness = 1 / (Ns + 1e-7); albedo = Kd (decree Q7)
+    float roughness = 1.0f / (m.specular_ex + 0.0000001f);
+    mats[i].a = make_float4(m.diffuse[0], m.diffuse[1], m.diffuse[2], roughness);
+    mats[i].b = make_float4(m.specular[0], m.specular[1], m.specular[2], 0.0f);
+  }
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  if (upload_vec(ctx, ctx->d_pairs, rl.pairs) || upload_vec(ctx, ctx->d_leaves, rl.leaves) ||
+      upload_vec(ctx, ctx->d_tris, tris) || upload_vec(ctx, ctx->d_mats, mats) || upload_vec(ctx, ctx->d_bvhs, rl.bvhs))
+    return 1;
+  CU(ctx, cudaStreamSynchronize(ctx->stream));  // host vectors go out of scope
+  ctx->h_bvhs.assign(bvhs, bvhs + n_bvhs);
+  ctx->h_bvh_records = rl.bvhs;
+  ctx->n_nodes = n_nodes;
+  ctx->n_tris = n_triangles;
+  ctx->n_mats = n_materials;
+  ctx->tree_depth = rl.depth;
+  ctx->have_scene = true;
+  return 0;
+}
+
+extern "C" int srt_update_frame(srt_ctx* ctx, uint32_t index, const float* m) {
+  if (!ctx || !m) return 1;
+  if (!ctx->have_scene || index >= ctx->h_bvhs.size()) return fail(ctx, "srt_update_frame: index %u out of range", index);
+  CU(ctx, cudaSetDevice(ctx->device));
+  memcpy(ctx->h_bvhs[index].frame, m, 64);
+  memcpy(ctx->h_bvh_records[index].frame, m, 64);
+  CU(ctx, cudaMemcpyAsync(ctx->d_bvhs + index, &ctx->h_bvh_records[index], 64, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- noise, lights, uniforms, images -----------------------------------------------------------
+extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const float* uniform_vec3, uint32_t count) {
+  if (!ctx) return 1;
+  if (!unit_vec3 || !uniform_vec3 || count == 0) return fail(ctx, "srt_upload_noise: NULL table or count 0");
+  CU(ctx, cudaSetDevice(ctx->device));
+  // the shader reads noiseTex.xy (raytrace_utils.glsl:15) and noiseUniformTex.x (:52) only: keep those, packed
+  std::vector<float2> xy(count);
+  std::vector<float> x(count);
+  for (uint32_t i = 0; i < count; ++i) {
+    xy[i] = make_float2(unit_vec3[3 * (size_t)i], unit_vec3[3 * (size_t)i + 1]);
+    x[i] = uniform_vec3[3 * (size_t)i];
+  }
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  if (upload_vec(ctx, ctx->d_noise_xy, xy) || upload_vec(ctx, ctx->d_noise_x, x)) return 1;
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->noise_count = count;
+  return 0;
+}
+
+extern "C" int srt_set_lights(srt_ctx* ctx, const srt_light* lights, int32_t count) {
+  if (!ctx) return 1;
+  if (count < 0 || count > SRT_MAX_LIGHTS) return fail(ctx, "srt_set_lights: count %d not in 0..%d", count, SRT_MAX_LIGHTS);
+  if (count > 0 && !lights) return fail(ctx, "srt_set_lights: NULL lights");
+  memset(ctx->lights, 0, sizeof ctx->lights);  // decree Q2: zero-padded to MAX_LIGHTS
+  if (count > 0) memcpy(ctx->lights, lights, (size_t)count * sizeof(srt_light));
+  ctx->light_count = count;
+  return 0;
+}
+
+extern "C" int srt_set_params(srt_ctx* ctx, const srt_params* p) {
+  if (!ctx || !p) return 1;
+  if (p->width <= 0 || p->height <= 0 || (p->width % 8) || (p->height % 8))
+    return fail(ctx, "srt_set_params: Width/Height must be positive multiples of 8 (src/main.cpp:706), got %dx%d", p->width, p->height);
+  if ((int64_t)p->width * p->height >= (1 << 30)) return fail(ctx, "srt_set_params: Width*Height must be < 2^30");
+  if (p->accum_frames < 1 && !p->reset_accum) return fail(ctx, "srt_set_params: accumFrames must be >= 1");
+  if (p->max_depth < 0) return fail(ctx, "srt_set_params: max_depth < 0");
+  ctx->params = *p;
+  ctx->have_params = true;
+  return 0;
+}
+
+extern "C" int srt_resize(srt_ctx* ctx, int32_t width, int32_t height) {
+  if (!ctx) return 1;
+  if (width <= 0 || height <= 0 || (width % 8) || (height % 8))
+    return fail(ctx, "srt_resize: width/height must be positive multiples of 8, got %dx%d", width, height);
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
+  size_t n = (size_t)width * height;
+  CU(ctx, cudaMalloc(&ctx->d_accum, n * sizeof(float4)));
+  CU(ctx, cudaMalloc(&ctx->d_out, n * sizeof(uchar4)));
+  CU(ctx, cudaMemsetAsync(ctx->d_accum, 0, n * sizeof(float4), ctx->stream));  // decree Q8
+  CU(ctx, cudaMemsetAsync(ctx->d_out, 0, n * sizeof(uchar4), ctx->stream));
+  if (ctx->ids_enabled) {
+    CU(ctx, cudaMalloc(&ctx->d_ids, n * sizeof(uint32_t)));
+    CU(ctx, cudaMemsetAsync(ctx->d_ids, 0xFF, n * sizeof(uint32_t), ctx->stream));
+  }
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->width = width;
+  ctx->height = height;
+  ctx->row0 = 0;
+  ctx->row1 = height;
+  return 0;
+}
+
+extern "C" int srt_set_rows(srt_ctx* ctx, int32_t y0, int32_t y1) {
+  if (!ctx) return 1;
+  if (y0 < 0 || y1 > ctx->height || y0 > y1 || (y0 % 8) || (y1 % 8))
+    return fail(ctx, "srt_set_rows: [%d,%d) must be multiples of 8 inside 0..%d", y0, y1, ctx->height);
+  ctx->row0 = y0;
+  ctx->row1 = y1;
+  return 0;
+}
+
+extern "C" int srt_enable_primary_ids(srt_ctx* ctx, int enable) {
+  if (!ctx) return 1;
+  CU(ctx, cudaSetDevice(ctx->device));
+  ctx->ids_enabled = enable != 0;
+  if (ctx->ids_enabled && !ctx->d_ids && ctx->width > 0) {
+    size_t n = (size_t)ctx->width * ctx->height;
+    CU(ctx, cudaMalloc(&ctx->d_ids, n * sizeof(uint32_t)));
+    CU(ctx, cudaMemsetAsync(ctx->d_ids, 0xFF, n * sizeof(uint32_t), ctx->stream));
+  }
+  return 0;
+}
+
+// ---- dispatch -------------------------------------------------------------------------------
+namespace {
+
+DeviceScene device_scene(const srt_ctx* ctx) {
+  DeviceScene sc;
+  sc.pairs = ctx->d_pairs; sc.leaves = ctx->d_leaves; sc.tris = ctx->d_tris; sc.mats = ctx->d_mats;
+  sc.bvhs = ctx->d_bvhs; sc.noise_unit_xy = ctx->d_noise_xy; sc.noise_uniform_x = ctx->d_noise_x;
+  return sc;
+}
+
+V3 ld3(const float* p) { return v3(p[0], p[1], p[2]); }
+
+// GetCamera (raytrace_compute.glsl:47-76) + the settings of main() (:366-384), evaluated once on the host with
+// the decree's operations instead of once per pixel.
+void fill_frame_params(const srt_ctx* ctx, int n_frames, FrameParams& fp) {
+  const srt_params& p = ctx->params;
+  memset(&fp, 0, sizeof fp);
+  fp.width = p.width;
+  fp.height = p.height;
+  fp.n_texels = p.width * p.height;
+  fp.width_f = (float)p.width;
+  fp.height_f = (float)p.height;
+  fp.accum_frames = p.accum_frames;
+  fp.n_frames = n_frames;
+  fp.y0 = ctx->row0;
+  fp.y1 = ctx->row1;
+  fp.light_count = p.light_count < 0 ? ctx->light_count : p.light_count;
+  fp.light_count_f = (float)fp.light_count;
+  fp.bvh_count = p.bvh_count;
+  fp.max_depth = p.max_depth > 0 ? p.max_depth : 5;  // raytrace_compute.glsl:370
+  int cap = ctx->tree_depth + 1;
+  fp.stack_cap = cap < 2 ? 2 : cap;
+
+  const float focus_dist = 1.0f;                                  // :384
+  float aspect = (float)p.width / (float)p.height;                // :368
+  int cam_h = f2i_((float)p.width / aspect);                      // :50
+  cam_h = cam_h < 1 ? 1 : cam_h;                                  // :51
+  V3 center = ld3(p.camera_origin);                               // :55
+  V3 w = -ld3(p.camera_direction), u = ld3(p.camera_right), v = ld3(p.camera_up);  // :58-60
+  V3 view_u = u * focus_dist, view_v = v * focus_dist;            // :62-63
+  fp.delta_u = view_u / (float)p.width;                           // :65
+  fp.delta_v = view_v / (float)cam_h;                             // :66
+  V3 lower_left = center - (focus_dist * w) - view_u / 2.0f - view_v / 2.0f;  // :68
+  fp.pixel00 = lower_left + 0.5f * (fp.delta_u + fp.delta_v);     // :69
+  fp.center = center;
+  for (int i = 0; i < SRT_MAX_LIGHTS; ++i) {
+    const srt_light& l = ctx->lights[i];
+    DeviceLight d = {l.position[0], l.position[1], l.position[2], l.intensity, l.color[0], l.color[1], l.color[2], 0.0f};
+    fp.lights[i] = d;
+  }
+}
+
+int check_ready(srt_ctx* ctx) {
+  const srt_params& p = ctx->params;
+  if (!ctx->have_params) return fail(ctx, "srt_render: srt_set_params has not been called");
+  if (!ctx->d_accum || ctx->width != p.width || ctx->height != p.height)
+    return fail(ctx, "srt_render: images are %dx%d but Width/Height are %dx%d (call srt_resize)", ctx->width,
+                ctx->height, p.width, p.height);
+  if (p.reset_accum) return 0;
+  if (ctx->noise_count != (uint32_t)(p.width * p.height))
+    return fail(ctx, "srt_render: noise tables hold %u texels, Width*Height is %d", ctx->noise_count, p.width * p.height);
+  int lc = p.light_count < 0 ? ctx->light_count : p.light_count;
+  if (lc > SRT_MAX_LIGHTS) return fail(ctx, "srt_render: lightCount %d > MAX_LIGHTS", lc);
+  if (p.show_model) {
+    if (!ctx->have_scene) return fail(ctx, "srt_render: showModel set but no scene uploaded");
+    if (p.bvh_count > ctx->h_bvhs.size())  // decree Q1
+      return fail(ctx, "srt_render: bvh_count %u exceeds the %zu uploaded BVHs", p.bvh_count, ctx->h_bvhs.size());
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
+  if (!ctx) return 1;
+  if (n_frames < 0) return fail(ctx, "srt_render: n_frames < 0");
+  if (check_ready(ctx)) return 1;
+  CU(ctx, cudaSetDevice(ctx->device));
+  if (ctx->params.reset_accum) {
+    CU(ctx, launch_clear(ctx->d_accum, ctx->width, ctx->row0, ctx->row1, ctx->stream));
+    ctx->kernel_launches++;
+    return 0;
+  }
+  if (n_frames == 0 || ctx->row1 == ctx->row0) return 0;
+  FrameParams fp;
+  fill_frame_params(ctx, n_frames, fp);
+  CU(ctx, launch_pathtrace(device_scene(ctx), fp, ctx->params.show_model != 0, ctx->traversal, ctx->count_traversal,
+                           ctx->d_accum, ctx->d_out, ctx->ids_enabled ? ctx->d_ids : nullptr, ctx->d_counters,
+                           ctx->block_threads, ctx->stream));
+  ctx->kernel_launches++;
+  ctx->params.accum_frames += n_frames;
+  return 0;
+}
+
+extern "C" int srt_sync(srt_ctx* ctx) {
+  if (!ctx) return 1;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int srt_render(srt_ctx* ctx, int32_t n_frames) {
+  if (srt_render_async(ctx, n_frames)) return 1;
+  return srt_sync(ctx);
+}
+
+extern "C" int srt_tonemap(srt_ctx* ctx, int32_t accum_frames) {
+  if (!ctx || !ctx->d_accum) return 1;
+  if (accum_frames < 1) return fail(ctx, "srt_tonemap: accum_frames < 1");
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, launch_tonemap(ctx->d_accum, ctx->d_out, (size_t)ctx->width * ctx->height, (float)accum_frames, ctx->stream));
+  ctx->kernel_launches++;
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- readback / checkpoint / collectives ------------------------------------------------------
+extern "C" int srt_read_output(srt_ctx* ctx, uint8_t* rgba8) {
+  if (!ctx || !rgba8) return 1;
+  if (!ctx->d_out) return fail(ctx, "srt_read_output: no image (call srt_resize)");
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(rgba8, ctx->d_out, (size_t)ctx->width * ctx->height * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int srt_read_accum(srt_ctx* ctx, float* rgba32f) {
+  if (!ctx || !rgba32f) return 1;
+  if (!ctx->d_accum) return fail(ctx, "srt_read_accum: no image (call srt_resize)");
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(rgba32f, ctx->d_accum, (size_t)ctx->width * ctx->height * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int srt_write_accum(srt_ctx* ctx, const float* rgba32f) {
+  if (!ctx || !rgba32f) return 1;
+  if (!ctx->d_accum) return fail(ctx, "srt_write_accum: no image (call srt_resize)");
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(ctx->d_accum, rgba32f, (size_t)ctx->width * ctx->height * 16, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int srt_accum_device_ptr(srt_ctx* ctx, void** device_ptr, uint64_t* n_floats) {
+  if (!ctx || !device_ptr) return 1;
+  if (!ctx->d_accum) return fail(ctx, "srt_accum_device_ptr: no image (call srt_resize)");
+  *device_ptr = ctx->d_accum;
+  if (n_floats) *n_floats = (uint64_t)ctx->width * ctx->height * 4;
+  return 0;
+}
+
+extern "C" int srt_read_primary_ids(srt_ctx* ctx, uint32_t* ids) {
+  if (!ctx || !ids) return 1;
+  if (!ctx->d_ids) return fail(ctx, "srt_read_primary_ids: recording is off (srt_enable_primary_ids)");
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(ids, ctx->d_ids, (size_t)ctx->width * ctx->height * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int srt_trace_rays(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, uint32_t bvh_count, uint32_t* hit_tri,
+                              float* hit_t) {
+  if (!ctx) return 1;
+  if (!ctx->have_scene) return fail(ctx, "srt_trace_rays: no scene uploaded");
+  if (bvh_count > ctx->h_bvhs.size()) return fail(ctx, "srt_trace_rays: bvh_count %u exceeds the uploaded BVHs", bvh_count);
+  if (n_rays == 0) return 0;
+  if (!rays || !hit_tri) return fail(ctx, "srt_trace_rays: NULL array");
+  CU(ctx, cudaSetDevice(ctx->device));
+  srt_ray* d_rays = nullptr;
+  uint32_t* d_hit = nullptr;
+  float* d_t = nullptr;
+  int rc = 0;
+  cudaError_t e;
+  if ((e = cudaMalloc(&d_rays, (size_t)n_rays * sizeof(srt_ray))) != cudaSuccess ||
+      (e = cudaMalloc(&d_hit, (size_t)n_rays * 4)) != cudaSuccess || (e = cudaMalloc(&d_t, (size_t)n_rays * 4)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(d_rays, rays, (size_t)n_rays * sizeof(srt_ray), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) {
+    rc = fail(ctx, "srt_trace_rays: %s", cudaGetErrorString(e));
+  } else {
+    int cap = ctx->tree_depth + 1 < 2 ? 2 : ctx->tree_depth + 1;
+    e = launch_trace_rays(device_scene(ctx), ctx->traversal, cap, d_rays, n_rays, bvh_count, d_hit, d_t, ctx->stream);
+    ctx->kernel_launches++;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(hit_tri, d_hit, (size_t)n_rays * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && hit_t) e = cudaMemcpyAsync(hit_t, d_t, (size_t)n_rays * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) rc = fail(ctx, "srt_trace_rays: %s", cudaGetErrorString(e));
+  }
+  cudaFree(d_rays); cudaFree(d_hit); cudaFree(d_t);
+  return rc;
+}
+
+extern "C" int srt_get_counters(srt_ctx* ctx, srt_counters* out) {
+  if (!ctx || !out) return 1;
+  CU(ctx, cudaSetDevice(ctx->device));
+  DeviceCounters h;
+  CU(ctx, cudaMemcpyAsync(&h, ctx->d_counters, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  out->segments = h.segments; out->shadow_rays = h.shadow_rays; out->paths = h.paths;
+  out->capped_paths = h.capped_paths; out->kernel_launches = ctx->kernel_launches;
+  out->nodes = h.nodes; out->tris = h.tris;
+  return 0;
+}
+
+extern "C" int srt_reset_counters(srt_ctx* ctx) {
+  if (!ctx) return 1;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(DeviceCounters), ctx->stream));
+  ctx->kernel_launches = 0;
+  return 0;
+}
+
+extern "C" int srt_eval_detmath(srt_ctx* ctx, int which, const float* x, const float* y, float* out, uint32_t n) {
+  if (!ctx) return 1;
+  if (n == 0) return 0;
+  if (!x || !out || (which == 3 && !y)) return fail(ctx, "srt_eval_detmath: NULL array");
+  CU(ctx, cudaSetDevice(ctx->device));
+  float *dx = nullptr, *dy = nullptr, *dout = nullptr;
+  int rc = 0;
+  cudaError_t e;
+  if ((e = cudaMalloc(&dx, (size_t)n * 4)) != cudaSuccess || (e = cudaMalloc(&dy, (size_t)n * 4)) != cudaSuccess ||
+      (e = cudaMalloc(&dout, (size_t)n * 4)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(dx, x, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
+      (y && (e = cudaMemcpyAsync(dy, y, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)) {
+    rc = fail(ctx, "srt_eval_detmath: %s", cudaGetErrorString(e));
+  } else {
+    e = launch_detmath(which, dx, dy, dout, n, ctx->stream);
+    ctx->kernel_launches++;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) rc = fail(ctx, "srt_eval_detmath: %s", cudaGetErrorString(e));
+  }
+  cudaFree(dx); cudaFree(dy); cudaFree(dout);
+  return rc;
+}

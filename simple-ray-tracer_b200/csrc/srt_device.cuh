@@ -1,0 +1,101 @@
+// srt_device.cuh -- device-side data layout of the B200 path tracer (private to libsrt_b200.so).
+//
+// The C-ABI takes the reference's std430 arrays (include/srt_types.h); srt_api.cu re-lays them out once
+// per upload into the gather-friendly forms below.  Every record is a multiple of 16 B and is read with
+// 128-bit __ldg loads (ld.global.nc.v4).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "srt_detmath.h"
+#include "srt_types.h"
+
+namespace srt {
+
+// One record per INNER node of the reference BVH (raytrace_types.glsl:41-46), holding the boxes of both
+// children so that a single 64 B fetch decides both box tests (the reference fetches the child nodes one at
+// a time, ray_intersects.glsl:107).  Child references:
+//   bit 31 clear: index of the child's own NodePair record (child is an inner node)
+//   bit 31 set  : index into the leaf table (child is a leaf)
+struct NodePair {
+  float4 a;  // L.min.xyz, L.max.x
+  float4 b;  // L.max.yz,  R.min.xy
+  float4 c;  // R.min.z,   R.max.xyz
+  uint4 d;   // L.ref, R.ref, unused, unused
+};
+static_assert(sizeof(NodePair) == 64, "NodePair is one 64 B fetch");
+
+#define SRT_LEAF_BIT 0x80000000u
+
+// One record per triangle in the reference's triangle order (= BVH leaf order, bvh.h:66-72), positions
+// pre-gathered through the index record (the reference does 4 dependent gathers per triangle,
+// ray_intersects.glsl:114-118).  e1/e2 are the IEEE differences v1-v0, v2-v0 the shader recomputes per test
+// (ray_intersects.glsl:69-70) -- same bits, computed once.
+struct TriRecord {
+  float4 v0;  // v0.xyz, bits: material index
+  float4 e1;  // edge_1.xyz, bits: rank in the reference's visiting order (tie-break key)
+  float4 e2;  // edge_2.xyz, unused
+};
+static_assert(sizeof(TriRecord) == 48, "TriRecord is three 16 B fetches");
+
+// MaterialFromOBJ (raytrace_types.glsl:19-27) after TriangleToSupportedMat (raytrace_utils.glsl:140-175).
+struct MatRecord {
+  float4 a;  // albedo (= Kd, decree Q7), roughness = 1/(Ns+1e-7)
+  float4 b;  // specular (= Ks), unused
+};
+
+// BVH (raytrace_types.glsl:32-38) plus the root's own box (the reference box-tests the root when it pops
+// it, ray_intersects.glsl:102-110).
+struct BvhRecord {
+  float frame[16];
+  float root_min[3];
+  uint32_t root_ref;
+  float root_max[3];
+  uint32_t _pad;
+};
+
+// SRT_OPT_TRAVERSAL values (srt_b200.h)
+enum { TRAV_REFERENCE = 0, TRAV_ORDERED = 1 };
+
+#define SRT_MAX_BVHS 64
+
+struct DeviceScene {
+  const NodePair* pairs;
+  const uint2* leaves;     // (first triangle, count) per leaf
+  const TriRecord* tris;
+  const MatRecord* mats;
+  const BvhRecord* bvhs;
+  const float2* noise_unit_xy;  // noiseTex.xy   (raytrace_utils.glsl:15)
+  const float* noise_uniform_x; // noiseUniformTex.x (raytrace_utils.glsl:52)
+};
+
+struct DeviceLight {
+  float px, py, pz, intensity;
+  float cx, cy, cz, pad;
+};
+
+// Everything a frame needs that is not a big array: the uniform block (raytrace_compute.glsl:18-31,39), the
+// camera GetCamera derives from it (raytrace_compute.glsl:47-76, hoisted to the host: same IEEE ops, once per
+// launch instead of once per pixel) and the padded light list (decree Q2).
+struct FrameParams {
+  int width, height;
+  int n_texels;          // Width*Height
+  float width_f, height_f;
+  int accum_frames;      // accumFrames of the first frame of this launch
+  int n_frames;          // frames rendered by this launch
+  int y0, y1;            // row range
+  int light_count;
+  float light_count_f;
+  uint32_t bvh_count;
+  int max_depth;
+  int stack_cap;         // entries per thread in the shared-memory traversal stack
+  V3 center, pixel00, delta_u, delta_v;
+  DeviceLight lights[SRT_MAX_LIGHTS];
+};
+
+struct DeviceCounters {
+  unsigned long long segments, shadow_rays, paths, capped_paths, nodes, tris;
+};
+
+}  // namespace srt

@@ -1,0 +1,207 @@
+// srt_kernels.cu -- the sm_100a kernels of the path-tracing hot path and their launchers.
+//
+// pathtrace_kernel replaces one or more glDispatchCompute(W/8, H/8, 1) calls of the reference frame loop
+// (src/main.cpp:706; shader entry shaders/raytrace_compute.glsl:296-414).  One thread owns one pixel and
+// runs the launch's frames in order, so the fp32 accumulation order of a pixel is the shader's
+// (prev + c1) + c2 + ... (raytrace_compute.glsl:404-406) and the accumulation image is read and written once
+// per launch instead of once per frame.  A warp covers an 8x4 pixel tile (primary rays stay coherent; the
+// reference's work group is 8x8, raytrace_compute.glsl:12).
+#include "srt_kernels.h"
+#include "srt_path.cuh"
+
+namespace srt {
+
+template <bool MODEL, int MODE, bool COUNT>
+__global__ void __launch_bounds__(SRT_MAX_BLOCK_THREADS)
+pathtrace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, float4* __restrict__ accum,
+                 uchar4* __restrict__ out, uint32_t* __restrict__ primary_ids, DeviceCounters* __restrict__ counters) {
+  extern __shared__ uint2 s_stack_all[];
+  uint2* s_stack = s_stack_all + threadIdx.x;
+  const int stride = blockDim.x;
+
+  const int lane = threadIdx.x & 31;
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int tiles_x = fp.width >> 3;
+  const int n_tiles = tiles_x * ((fp.y1 - fp.y0) >> 2);
+  if (warp_global >= n_tiles) return;
+  const int x = ((warp_global % tiles_x) << 3) + (lane & 7);
+  const int y = fp.y0 + ((warp_global / tiles_x) << 2) + (lane >> 3);
+  const int pix = y * fp.height + x;  // Q4
+  const size_t texel = (size_t)y * fp.width + x;
+
+  float4 prev = accum[texel];
+  V3 acc = v3(prev.x, prev.y, prev.z);
+  PathStats st;
+  st.segments = st.shadow_rays = st.capped = 0;
+  st.trav.nodes = st.trav.tris = 0;
+  uint32_t primary = SRT_NO_HIT;
+
+  for (int f = 0; f < fp.n_frames; ++f) {
+    int frames = fp.accum_frames + f;
+    int samp = frames % fp.n_texels;
+    // GetRay + SampleSquare (raytrace_compute.glsl:78-90, raytrace_utils.glsl:10-17)
+    int idx = (pix + samp) % fp.n_texels;
+    float2 jit = __ldg(sc.noise_unit_xy + idx);
+    float ox = jit.x - 0.5f, oy = jit.y - 0.5f;
+    V3 pixel_sample = fp.pixel00 + (((float)x + ox) * fp.delta_u) + (((float)y + oy) * fp.delta_v);
+    V3 dir = pixel_sample - fp.center;
+    V3 c = trace_path<MODEL, MODE, COUNT>(sc, fp, pix, fp.center, dir, s_stack, stride, st, primary);
+    V3 pixel_color = v3(0.0f) + c;
+    acc = acc + pixel_color;
+  }
+
+  accum[texel] = make_float4(acc.x, acc.y, acc.z, 1.0f);
+  V3 lin = acc / (float)(fp.accum_frames + fp.n_frames - 1);
+  out[texel] = make_uchar4(to_unorm8(linear_to_srgb(lin.x)), to_unorm8(linear_to_srgb(lin.y)),
+                           to_unorm8(linear_to_srgb(lin.z)), 255);
+  if (primary_ids) primary_ids[texel] = primary;
+
+  // per-warp totals, one atomic per counter per warp
+  unsigned int seg = st.segments, sh = st.shadow_rays, cap = st.capped, nd = st.trav.nodes, tr = st.trav.tris;
+  __syncwarp();
+  const unsigned int active = 0xFFFFFFFFu;  // the early exit above is warp-uniform
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    seg += __shfl_down_sync(active, seg, o);
+    sh += __shfl_down_sync(active, sh, o);
+    cap += __shfl_down_sync(active, cap, o);
+    if (COUNT) {
+      nd += __shfl_down_sync(active, nd, o);
+      tr += __shfl_down_sync(active, tr, o);
+    }
+  }
+  if (lane == 0) {
+    atomicAdd(&counters->segments, (unsigned long long)seg);
+    atomicAdd(&counters->shadow_rays, (unsigned long long)sh);
+    atomicAdd(&counters->paths, (unsigned long long)(32 * fp.n_frames));
+    if (cap) atomicAdd(&counters->capped_paths, (unsigned long long)cap);
+    if (COUNT) {
+      atomicAdd(&counters->nodes, (unsigned long long)nd);
+      atomicAdd(&counters->tris, (unsigned long long)tr);
+    }
+  }
+}
+
+// resetAccumBuffer branch of the shader (raytrace_compute.glsl:390-393)
+__global__ void clear_accum_kernel(float4* __restrict__ accum, int width, int y0, int y1) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t n = (size_t)(y1 - y0) * width;
+  if (i < n) accum[(size_t)y0 * width + i] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+}
+
+// raytrace_compute.glsl:412-413 alone (after a multi-GPU reduce of the accumulation image)
+__global__ void tonemap_kernel(const float4* __restrict__ accum, uchar4* __restrict__ out, size_t n, float frames) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float4 a = accum[i];
+  V3 lin = v3(a.x, a.y, a.z) / frames;
+  out[i] = make_uchar4(to_unorm8(linear_to_srgb(lin.x)), to_unorm8(linear_to_srgb(lin.y)),
+                       to_unorm8(linear_to_srgb(lin.z)), 255);
+}
+
+// the disabled test kernel of ray_intersects.glsl:135-161
+template <int MODE>
+__global__ void trace_rays_kernel(const DeviceScene sc, const srt_ray* __restrict__ rays, uint32_t n_rays,
+                                  uint32_t bvh_count, uint32_t* __restrict__ hit_tri, float* __restrict__ hit_t) {
+  extern __shared__ uint2 s_stack_all[];
+  uint2* s_stack = s_stack_all + threadIdx.x;
+  uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_rays) return;
+  srt_ray ray = rays[r];
+  float best = ray.intersection_distance;
+  uint32_t out = SRT_NO_HIT;
+  TravCount tc;
+  tc.nodes = tc.tris = 0;
+  for (uint32_t i = 0; i < bvh_count; ++i) {
+    const BvhRecord* bvh = sc.bvhs + i;
+    V3 o = mat4_mul_(bvh->frame, v3(ray.origin[0], ray.origin[1], ray.origin[2]), 1.0f);
+    V3 d = mat4_mul_(bvh->frame, v3(ray.direction[0], ray.direction[1], ray.direction[2]), 0.0f);
+    uint32_t h = traverse<MODE, false, false>(sc, bvh, o, d, best, s_stack, blockDim.x, tc);
+    if (h != SRT_NO_HIT) out = h;
+  }
+  hit_tri[r] = out;
+  if (hit_t) hit_t[r] = best;
+}
+
+__global__ void detmath_kernel(int which, const float* __restrict__ x, const float* __restrict__ y,
+                               float* __restrict__ out, uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float v;
+  switch (which) {
+    case 0: v = sin_(x[i]); break;
+    case 1: v = cos_(x[i]); break;
+    case 2: v = pow_(x[i], div_(1.0f, 2.4f)); break;
+    case 3: v = fract_(sin_(dot2_(x[i], y[i], 12.9898f, 78.233f)) * 43758.5453f); break;
+    default: v = linear_to_srgb(x[i]); break;
+  }
+  out[i] = v;
+}
+
+// ---- launchers --------------------------------------------------------------------------------
+template <bool MODEL, int MODE, bool COUNT>
+static cudaError_t launch_path(const DeviceScene& sc, const FrameParams& fp, float4* accum, uchar4* out,
+                               uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
+  int n_tiles = (fp.width / 8) * ((fp.y1 - fp.y0) / 4);
+  int warps_per_block = block / 32;
+  int grid = (n_tiles + warps_per_block - 1) / warps_per_block;
+  size_t smem = MODEL ? (size_t)fp.stack_cap * block * sizeof(uint2) : 0;
+  auto k = pathtrace_kernel<MODEL, MODE, COUNT>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  k<<<grid, block, smem, stream>>>(sc, fp, accum, out, ids, counters);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool model, int mode, bool count,
+                             float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters, int block,
+                             cudaStream_t stream) {
+  if (!model) return launch_path<false, TRAV_REFERENCE, false>(sc, fp, accum, out, ids, counters, block, stream);
+  if (mode == TRAV_REFERENCE) {
+    return count ? launch_path<true, TRAV_REFERENCE, true>(sc, fp, accum, out, ids, counters, block, stream)
+                 : launch_path<true, TRAV_REFERENCE, false>(sc, fp, accum, out, ids, counters, block, stream);
+  }
+  return count ? launch_path<true, TRAV_ORDERED, true>(sc, fp, accum, out, ids, counters, block, stream)
+               : launch_path<true, TRAV_ORDERED, false>(sc, fp, accum, out, ids, counters, block, stream);
+}
+
+cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream) {
+  size_t n = (size_t)(y1 - y0) * width;
+  if (n == 0) return cudaSuccess;
+  clear_accum_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(accum, width, y0, y1);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tonemap(const float4* accum, uchar4* out, size_t n, float frames, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  tonemap_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(accum, out, n, frames);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_trace_rays(const DeviceScene& sc, int mode, int stack_cap, const srt_ray* rays, uint32_t n_rays,
+                              uint32_t bvh_count, uint32_t* hit_tri, float* hit_t, cudaStream_t stream) {
+  if (n_rays == 0) return cudaSuccess;
+  const int block = 64;
+  size_t smem = (size_t)stack_cap * block * sizeof(uint2);
+  unsigned grid = (n_rays + block - 1) / block;
+  if (mode == TRAV_REFERENCE) {
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(trace_rays_kernel<TRAV_REFERENCE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    trace_rays_kernel<TRAV_REFERENCE><<<grid, block, smem, stream>>>(sc, rays, n_rays, bvh_count, hit_tri, hit_t);
+  } else {
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(trace_rays_kernel<TRAV_ORDERED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    trace_rays_kernel<TRAV_ORDERED><<<grid, block, smem, stream>>>(sc, rays, n_rays, bvh_count, hit_tri, hit_t);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_detmath(int which, const float* x, const float* y, float* out, uint32_t n, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  detmath_kernel<<<(n + 255) / 256, 256, 0, stream>>>(which, x, y, out, n);
+  return cudaGetLastError();
+}
+
+}  // namespace srt

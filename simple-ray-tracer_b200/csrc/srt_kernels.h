@@ -1,0 +1,21 @@
+// srt_kernels.h -- launchers of the sm_100a kernels (srt_kernels.cu), called by the C-ABI (srt_api.cu).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "srt_device.cuh"
+
+#define SRT_MAX_BLOCK_THREADS 128
+
+namespace srt {
+
+cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool model, int mode, bool count,
+                             float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters, int block,
+                             cudaStream_t stream);
+cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream);
+cudaError_t launch_tonemap(const float4* accum, uchar4* out, size_t n, float frames, cudaStream_t stream);
+cudaError_t launch_trace_rays(const DeviceScene& sc, int mode, int stack_cap, const srt_ray* rays, uint32_t n_rays,
+                              uint32_t bvh_count, uint32_t* hit_tri, float* hit_t, cudaStream_t stream);
+cudaError_t launch_detmath(int which, const float* x, const float* y, float* out, uint32_t n, cudaStream_t stream);
+
+}  // namespace srt
