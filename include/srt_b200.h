@@ -34,8 +34,9 @@ typedef struct srt_counters {
 } srt_counters;
 
 /* srt_set_option keys */
-#define SRT_OPT_TRAVERSAL 1      /* 0 = reference visiting order (bit-exact by construction)
-                                    1 = near-child-first ordered traversal (default; same hits bar documented ties) */
+#define SRT_OPT_TRAVERSAL 1      /* 0 = the shader's visiting order everywhere (bit-exact by construction)
+                                    1 = nearer child first where neither child's box contains the ray origin, the
+                                        shader's order elsewhere (default; same hits bar documented grazing ties) */
 #define SRT_OPT_COUNT_TRAVERSAL 2 /* 1 = count nodes/tris (slower; for the roofline figures) */
 #define SRT_OPT_L2_PERSIST 3     /* 1 = pin BVH top levels + noise tables in L2 with an access-policy window (default 1) */
 #define SRT_OPT_BLOCK_THREADS 4  /* threads per block of the path kernel (multiple of 32) */
@@ -81,6 +82,9 @@ int srt_resize(srt_ctx* ctx, int32_t width, int32_t height);
 /* Restrict rendering to rows [y0, y1) (multiples of 8) -- the image-tile half of the multi-GPU split.
  * Default is the whole image. */
 int srt_set_rows(srt_ctx* ctx, int32_t y0, int32_t y1);
+/* Of the 8-row bands inside the row range, render only those with band % world == rank (interleaved bands keep
+ * the ranks' loads even when the model covers part of the picture).  Default rank 0 of world 1. */
+int srt_set_stripe(srt_ctx* ctx, int32_t rank, int32_t world);
 
 /* glDispatchCompute(W/8,H/8,1) + glMemoryBarrier + glFinish  (src/main.cpp:706-718), n_frames times:
  * renders frames accum_frames .. accum_frames+n_frames-1 (1 sample per pixel each), accumulating in

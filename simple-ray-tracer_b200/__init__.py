@@ -28,7 +28,7 @@ LIGHT_DT = np.dtype([("position", "<f4", 3), ("intensity", "<f4"), ("color", "<f
 RAY_DT = np.dtype([("origin", "<f4", 3), ("_pad0", "<f4"), ("direction", "<f4", 3), ("dist", "<f4")])
 
 EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt_set_option", "srt_upload_scene",
-           "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows",
+           "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
            "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays",
            "srt_get_counters", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
@@ -143,6 +143,9 @@ class Context:
 
     def set_rows(self, y0, y1):
         self._ck(self._lib.srt_set_rows(self._h, C.c_int32(y0), C.c_int32(y1)))
+
+    def set_stripe(self, rank, world):
+        self._ck(self._lib.srt_set_stripe(self._h, C.c_int32(rank), C.c_int32(world)))
 
     def render(self, n_frames=1):
         self._ck(self._lib.srt_render(self._h, C.c_int32(n_frames)))

@@ -45,6 +45,7 @@ struct srt_ctx {
   uint32_t* d_ids = nullptr;
   bool ids_enabled = false;
   int row0 = 0, row1 = 0;
+  int stripe_rank = 0, stripe_world = 1;
 
   // uniforms + lights
   srt_params params;
@@ -386,6 +387,14 @@ extern "C" int srt_set_rows(srt_ctx* ctx, int32_t y0, int32_t y1) {
   return 0;
 }
 
+extern "C" int srt_set_stripe(srt_ctx* ctx, int32_t rank, int32_t world) {
+  if (!ctx) return 1;
+  if (world < 1 || rank < 0 || rank >= world) return fail(ctx, "srt_set_stripe: rank %d of world %d", rank, world);
+  ctx->stripe_rank = rank;
+  ctx->stripe_world = world;
+  return 0;
+}
+
 extern "C" int srt_enable_primary_ids(srt_ctx* ctx, int enable) {
   if (!ctx) return 1;
   CU(ctx, cudaSetDevice(ctx->device));
@@ -424,6 +433,8 @@ void fill_frame_params(const srt_ctx* ctx, int n_frames, FrameParams& fp) {
   fp.n_frames = n_frames;
   fp.y0 = ctx->row0;
   fp.y1 = ctx->row1;
+  fp.stripe_rank = ctx->stripe_rank;
+  fp.stripe_world = ctx->stripe_world;
   fp.light_count = p.light_count < 0 ? ctx->light_count : p.light_count;
   fp.light_count_f = (float)fp.light_count;
   fp.bvh_count = p.bvh_count;

@@ -85,6 +85,7 @@ struct FrameParams {
   int accum_frames;      // accumFrames of the first frame of this launch
   int n_frames;          // frames rendered by this launch
   int y0, y1;            // row range
+  int stripe_rank, stripe_world;  // of the 8-row bands inside [y0,y1) this launch renders those with band % world == rank
   int light_count;
   float light_count_f;
   uint32_t bvh_count;

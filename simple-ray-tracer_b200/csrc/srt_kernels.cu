@@ -22,10 +22,14 @@ pathtrace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, f
   const int lane = threadIdx.x & 31;
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int tiles_x = fp.width >> 3;
-  const int n_tiles = tiles_x * ((fp.y1 - fp.y0) >> 2);
+  const int n_bands = (fp.y1 - fp.y0) >> 3;
+  const int my_bands = (n_bands - fp.stripe_rank + fp.stripe_world - 1) / fp.stripe_world;
+  const int n_tiles = tiles_x * (my_bands << 1);
   if (warp_global >= n_tiles) return;
+  const int tile_row = warp_global / tiles_x;  // two 4-row tiles per 8-row band
+  const int band = (tile_row >> 1) * fp.stripe_world + fp.stripe_rank;
   const int x = ((warp_global % tiles_x) << 3) + (lane & 7);
-  const int y = fp.y0 + ((warp_global / tiles_x) << 2) + (lane >> 3);
+  const int y = fp.y0 + (band << 3) + ((tile_row & 1) << 2) + (lane >> 3);
   const int pix = y * fp.height + x;  // Q4
   const size_t texel = (size_t)y * fp.width + x;
 
@@ -142,7 +146,10 @@ __global__ void detmath_kernel(int which, const float* __restrict__ x, const flo
 template <bool MODEL, int MODE, bool COUNT>
 static cudaError_t launch_path(const DeviceScene& sc, const FrameParams& fp, float4* accum, uchar4* out,
                                uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
-  int n_tiles = (fp.width / 8) * ((fp.y1 - fp.y0) / 4);
+  int n_bands = (fp.y1 - fp.y0) / 8;
+  int my_bands = (n_bands - fp.stripe_rank + fp.stripe_world - 1) / fp.stripe_world;
+  int n_tiles = (fp.width / 8) * my_bands * 2;
+  if (n_tiles <= 0) return cudaSuccess;
   int warps_per_block = block / 32;
   int grid = (n_tiles + warps_per_block - 1) / warps_per_block;
   size_t smem = MODEL ? (size_t)fp.stack_cap * block * sizeof(uint2) : 0;

@@ -12,9 +12,14 @@
 //     exactly the test the shader performs when it pops a node (ray_intersects.glsl:109-110)
 //   * TRAV_REFERENCE visits children in the shader's order (left pushed first, right visited first,
 //     ray_intersects.glsl:126-127) => bit-identical hits by construction
-//   * TRAV_ORDERED visits the nearer child first and breaks exact distance ties by the triangle's rank in
-//     the shader's visiting order => same hit unless a box distance and a triangle distance that differ by
-//     rounding straddle the running closest hit (the documented grazing ties)
+//   * TRAV_ORDERED: IntersectsBox returns the EXIT distance for a box that contains the ray origin
+//     (ray_intersects.glsl:57), so the shader culls such a box whenever an earlier hit is nearer than its far
+//     side -- its result depends on the visiting order wherever the origin is inside a box.  Children are
+//     therefore visited in the shader's order whenever either child's box contains the origin, and
+//     nearer-child-first only when neither does (then both subtrees see entry distances only and the closest
+//     hit does not depend on their order).  Exact distance ties are broken by the triangle's rank in the
+//     shader's visiting order.  Same hit as TRAV_REFERENCE unless a box distance and a triangle distance that
+//     differ by rounding straddle the running closest hit (the documented grazing ties)
 //   * shadow rays (CheckLightOccluded only reads rec.hit, raytrace_compute.glsl:174-175) stop at the first
 //     accepted triangle: until one is accepted the shader's running distance is the constant light distance,
 //     so "some triangle is accepted" does not depend on the visiting order.
@@ -32,11 +37,12 @@ struct TravCount {
 
 // IntersectsBox (ray_intersects.glsl:49-58) with inv_dir hoisted.  GLSL min/max semantics (decree Q17).
 __device__ __forceinline__ float box_distance(V3 o, V3 inv, float mnx, float mny, float mnz, float mxx, float mxy,
-                                              float mxz) {
+                                              float mxz, bool& origin_inside) {
   float t0x = (mnx - o.x) * inv.x, t0y = (mny - o.y) * inv.y, t0z = (mnz - o.z) * inv.z;
   float t1x = (mxx - o.x) * inv.x, t1y = (mxy - o.y) * inv.y, t1z = (mxz - o.z) * inv.z;
   float t_near = max_(max_(min_(t0x, t1x), min_(t0y, t1y)), min_(t0z, t1z));
   float t_far = min_(min_(max_(t0x, t1x), max_(t0y, t1y)), max_(t0z, t1z));
+  origin_inside = (t_near <= t_far) && !(t_near >= 0.0f);
   return t_near <= t_far ? ((t_near >= 0.0f) ? t_near : t_far) : inf_();
 }
 
@@ -86,8 +92,9 @@ __device__ __forceinline__ uint32_t traverse(const DeviceScene& sc, const BvhRec
   uint32_t best_rank = 0xFFFFFFFFu;
 
   // the root is popped and box-tested like any other node
+  bool in_l, in_r;
   float d_root = box_distance(o, inv, bvh->root_min[0], bvh->root_min[1], bvh->root_min[2], bvh->root_max[0],
-                              bvh->root_max[1], bvh->root_max[2]);
+                              bvh->root_max[1], bvh->root_max[2], in_l);
   if (COUNT) cnt.nodes++;
   if (!(d_root < best) || isinf_(d_root)) return hit;
 
@@ -98,14 +105,14 @@ __device__ __forceinline__ uint32_t traverse(const DeviceScene& sc, const BvhRec
       const float4* p = reinterpret_cast<const float4*>(sc.pairs + cur);
       float4 na = __ldg(p), nb = __ldg(p + 1), nc = __ldg(p + 2);
       uint4 nd = __ldg(reinterpret_cast<const uint4*>(p + 3));
-      float dl = box_distance(o, inv, na.x, na.y, na.z, na.w, nb.x, nb.y);
-      float dr = box_distance(o, inv, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w);
+      float dl = box_distance(o, inv, na.x, na.y, na.z, na.w, nb.x, nb.y, in_l);
+      float dr = box_distance(o, inv, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, in_r);
       if (COUNT) cnt.nodes += 2;
       // a child whose box distance is already >= best would fail the shader's test when popped (best only shrinks)
       bool pl = (dl < best) && !isinf_(dl);
       bool pr = (dr < best) && !isinf_(dr);
       if (pl && pr) {
-        bool right_first = (MODE == TRAV_REFERENCE) ? true : !(dl < dr);
+        bool right_first = (MODE == TRAV_REFERENCE || in_l || in_r) ? true : !(dl < dr);
         uint32_t first = right_first ? nd.y : nd.x, second = right_first ? nd.x : nd.y;
         float d_second = right_first ? dl : dr;
         s_stack[sp * stack_stride] = make_uint2(second, __float_as_uint(d_second));
