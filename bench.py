@@ -163,8 +163,10 @@ def run_gpu(args):
     mode = pkg.TRAV_REFERENCE if args.traversal == "reference" else pkg.TRAV_ORDERED
 
     ctx = pkg.Context(local)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()  # a real (non-NULL) stream: kernels, events and NCCL ordering all go through it
+    torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
+    ctx.set_option(pkg.OPT_SCHEDULE, pkg.SCHED_REGEN if args.schedule == "regen" else pkg.SCHED_PER_PATH)
     ctx.set_option(pkg.OPT_TRAVERSAL, mode)
     ctx.set_option(pkg.OPT_BLOCK_THREADS, args.block)
 
@@ -318,7 +320,7 @@ def run_gpu(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": inp["desc"], "traversal": args.traversal, "block_threads": args.block,
+        "config": {"workload": inp["desc"], "traversal": args.traversal, "schedule": args.schedule, "block_threads": args.block,
                    "split": "interleaved 8-row bands over %d GPU(s), NCCL reduce of the fp32 accumulation image to rank 0" % world
                             if world > 1 else "single GPU",
                    "l2": "512 MB device buffer rewritten between timed steps (L2 flush)",
@@ -344,6 +346,7 @@ def main():
     ap.add_argument("--workload", default="rubik", choices=sorted(WORKLOADS))
     ap.add_argument("--traversal", default="ordered", choices=["ordered", "reference"])
     ap.add_argument("--block", type=int, default=64)
+    ap.add_argument("--schedule", default="regen", choices=["regen", "per-path"])
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the workload the CPU baseline renders")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

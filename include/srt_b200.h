@@ -40,6 +40,9 @@ typedef struct srt_counters {
 #define SRT_OPT_COUNT_TRAVERSAL 2 /* 1 = count nodes/tris (slower; for the roofline figures) */
 #define SRT_OPT_L2_PERSIST 3     /* 1 = pin BVH top levels + noise tables in L2 with an access-policy window (default 1) */
 #define SRT_OPT_BLOCK_THREADS 4  /* threads per block of the path kernel (multiple of 32) */
+#define SRT_OPT_SCHEDULE 5       /* 0 = one path at a time per lane (the shader's schedule)
+                                    1 = per-lane state machine with path regeneration + warp-synchronous traversal
+                                        (default; same results, different lane schedule) */
 
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */

@@ -8,11 +8,11 @@ unit, uniform = scenes.noise_tables(W, H)
 scene = scenes.rubik_scene()
 ctx.upload_scene(scene); ctx.upload_noise(unit, uniform); ctx.set_lights(scenes.model_lights()); ctx.resize(W, H)
 for mode in (0, 1):
-    for block in (64, 128):
-        ctx.set_option(pkg.OPT_TRAVERSAL, mode); ctx.set_option(pkg.OPT_BLOCK_THREADS, block)
+    for sched, block in ((0, 64), (1, 64), (1, 128)):
+        ctx.set_option(pkg.OPT_TRAVERSAL, mode); ctx.set_option(pkg.OPT_BLOCK_THREADS, block); ctx.set_option(pkg.OPT_SCHEDULE, sched)
         ctx.set_params(pkg.make_params(W, H, scenes.reset_camera(True), True, accum_frames=1, bvh_count=1))
         ctx.render(2)
         ctx.reset_counters()
         t = time.time(); ctx.render(16); dt = time.time() - t
         c = ctx.counters()
-        print("mode", mode, "block", block, "16spp ms", dt * 1e3, "Mseg/s", c["segments"] / dt / 1e6, "Mrays/s", (c["segments"] + c["shadow_rays"]) / dt / 1e6, c)
+        print("mode", mode, "sched", sched, "block", block, "16spp ms", dt * 1e3, "Mseg/s", c["segments"] / dt / 1e6, "Mrays/s", (c["segments"] + c["shadow_rays"]) / dt / 1e6, c)

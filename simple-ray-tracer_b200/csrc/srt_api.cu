@@ -58,6 +58,7 @@ struct srt_ctx {
   bool count_traversal = false;
   bool l2_persist = true;
   int block_threads = 64;
+  int schedule = SCHED_REGEN;
 
   DeviceCounters* d_counters = nullptr;
   uint64_t kernel_launches = 0;
@@ -154,6 +155,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
       if (value < 32 || value > SRT_MAX_BLOCK_THREADS || value % 32) return fail(ctx, "SRT_OPT_BLOCK_THREADS: 32..%d, multiple of 32", SRT_MAX_BLOCK_THREADS);
       ctx->block_threads = value;
       return 0;
+  }
+  if (key == SRT_OPT_SCHEDULE) {
+    if (value != SCHED_PER_PATH && value != SCHED_REGEN) return fail(ctx, "SRT_OPT_SCHEDULE: 0 or 1");
+    ctx->schedule = value;
+    return 0;
   }
   return fail(ctx, "srt_set_option: unknown key %d", key);
 }
@@ -495,7 +501,7 @@ extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
   if (n_frames == 0 || ctx->row1 == ctx->row0) return 0;
   FrameParams fp;
   fill_frame_params(ctx, n_frames, fp);
-  CU(ctx, launch_pathtrace(device_scene(ctx), fp, ctx->params.show_model != 0, ctx->traversal, ctx->count_traversal,
+  CU(ctx, launch_pathtrace(device_scene(ctx), fp, ctx->params.show_model != 0, ctx->traversal, ctx->count_traversal, ctx->schedule,
                            ctx->d_accum, ctx->d_out, ctx->ids_enabled ? ctx->d_ids : nullptr, ctx->d_counters,
                            ctx->block_threads, ctx->stream));
   ctx->kernel_launches++;

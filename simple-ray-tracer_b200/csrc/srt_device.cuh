@@ -57,6 +57,8 @@ struct BvhRecord {
 
 // SRT_OPT_TRAVERSAL values (srt_b200.h)
 enum { TRAV_REFERENCE = 0, TRAV_ORDERED = 1 };
+// SRT_OPT_SCHEDULE values (srt_b200.h)
+enum { SCHED_PER_PATH = 0, SCHED_REGEN = 1 };
 
 #define SRT_MAX_BVHS 64
 

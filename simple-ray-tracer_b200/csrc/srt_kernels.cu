@@ -8,10 +8,11 @@
 // reference's work group is 8x8, raytrace_compute.glsl:12).
 #include "srt_kernels.h"
 #include "srt_path.cuh"
+#include "srt_regen.cuh"
 
 namespace srt {
 
-template <bool MODEL, int MODE, bool COUNT>
+template <bool MODEL, int MODE, bool COUNT, int SCHED>
 __global__ void __launch_bounds__(SRT_MAX_BLOCK_THREADS)
 pathtrace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, float4* __restrict__ accum,
                  uchar4* __restrict__ out, uint32_t* __restrict__ primary_ids, DeviceCounters* __restrict__ counters) {
@@ -40,6 +41,9 @@ pathtrace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, f
   st.trav.nodes = st.trav.tris = 0;
   uint32_t primary = SRT_NO_HIT;
 
+  if (SCHED == SCHED_REGEN) {
+    render_pixel_regen<MODEL, MODE, COUNT>(sc, fp, x, y, acc, s_stack, stride, st, primary);
+  } else
   for (int f = 0; f < fp.n_frames; ++f) {
     int frames = fp.accum_frames + f;
     int samp = frames % fp.n_texels;
@@ -143,7 +147,7 @@ __global__ void detmath_kernel(int which, const float* __restrict__ x, const flo
 }
 
 // ---- launchers --------------------------------------------------------------------------------
-template <bool MODEL, int MODE, bool COUNT>
+template <bool MODEL, int MODE, bool COUNT, int SCHED>
 static cudaError_t launch_path(const DeviceScene& sc, const FrameParams& fp, float4* accum, uchar4* out,
                                uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
   int n_bands = (fp.y1 - fp.y0) / 8;
@@ -153,7 +157,7 @@ static cudaError_t launch_path(const DeviceScene& sc, const FrameParams& fp, flo
   int warps_per_block = block / 32;
   int grid = (n_tiles + warps_per_block - 1) / warps_per_block;
   size_t smem = MODEL ? (size_t)fp.stack_cap * block * sizeof(uint2) : 0;
-  auto k = pathtrace_kernel<MODEL, MODE, COUNT>;
+  auto k = pathtrace_kernel<MODEL, MODE, COUNT, SCHED>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -162,16 +166,24 @@ static cudaError_t launch_path(const DeviceScene& sc, const FrameParams& fp, flo
   return cudaGetLastError();
 }
 
-cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool model, int mode, bool count,
+template <bool MODEL, int MODE, bool COUNT>
+static cudaError_t launch_path_sched(int sched, const DeviceScene& sc, const FrameParams& fp, float4* accum, uchar4* out,
+                                     uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
+  return sched == SCHED_REGEN
+             ? launch_path<MODEL, MODE, COUNT, SCHED_REGEN>(sc, fp, accum, out, ids, counters, block, stream)
+             : launch_path<MODEL, MODE, COUNT, SCHED_PER_PATH>(sc, fp, accum, out, ids, counters, block, stream);
+}
+
+cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool model, int mode, bool count, int sched,
                              float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters, int block,
                              cudaStream_t stream) {
-  if (!model) return launch_path<false, TRAV_REFERENCE, false>(sc, fp, accum, out, ids, counters, block, stream);
+  if (!model) return launch_path_sched<false, TRAV_REFERENCE, false>(sched, sc, fp, accum, out, ids, counters, block, stream);
   if (mode == TRAV_REFERENCE) {
-    return count ? launch_path<true, TRAV_REFERENCE, true>(sc, fp, accum, out, ids, counters, block, stream)
-                 : launch_path<true, TRAV_REFERENCE, false>(sc, fp, accum, out, ids, counters, block, stream);
+    return count ? launch_path_sched<true, TRAV_REFERENCE, true>(sched, sc, fp, accum, out, ids, counters, block, stream)
+                 : launch_path_sched<true, TRAV_REFERENCE, false>(sched, sc, fp, accum, out, ids, counters, block, stream);
   }
-  return count ? launch_path<true, TRAV_ORDERED, true>(sc, fp, accum, out, ids, counters, block, stream)
-               : launch_path<true, TRAV_ORDERED, false>(sc, fp, accum, out, ids, counters, block, stream);
+  return count ? launch_path_sched<true, TRAV_ORDERED, true>(sched, sc, fp, accum, out, ids, counters, block, stream)
+               : launch_path_sched<true, TRAV_ORDERED, false>(sched, sc, fp, accum, out, ids, counters, block, stream);
 }
 
 cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream) {

@@ -9,7 +9,7 @@
 
 namespace srt {
 
-cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool model, int mode, bool count,
+cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool model, int mode, bool count, int sched,
                              float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters, int block,
                              cudaStream_t stream);
 cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream);

@@ -14,11 +14,12 @@ pytestmark = pytest.mark.gpu
 
 
 def gpu_render(pkg, ctx, W, H, show_model, n_frames, traversal, scene=None, lights=None, cam=None, first_frame=1,
-               max_depth=0, noise=None, rows=None):
+               max_depth=0, noise=None, rows=None, schedule=1):
     unit, uniform = noise if noise is not None else scenes.noise_tables(W, H)
     lights = lights if lights is not None else (scenes.model_lights() if show_model else scenes.sphere_lights())
     cam = cam or scenes.reset_camera(show_model)
     ctx.set_option(pkg.OPT_TRAVERSAL, traversal)
+    ctx.set_option(pkg.OPT_SCHEDULE, schedule)
     if scene is not None:
         ctx.upload_scene(scene)
     ctx.upload_noise(unit, uniform)
@@ -78,9 +79,10 @@ def test_detmath_bitwise(pkg, ctx, oracle):
     assert np.array_equal(canon(got), canon(ref))
 
 
-def test_c1_spheres_640x480_1spp_bit_exact(pkg, ctx, oracle):
+@pytest.mark.parametrize("schedule", [0, 1])
+def test_c1_spheres_640x480_1spp_bit_exact(pkg, ctx, oracle, schedule):
     """BASELINE.json configs[0]: built-in spheres, 640x480, 1 spp."""
-    acc, out, ids, cnt = gpu_render(pkg, ctx, 640, 480, False, 1, pkg.TRAV_REFERENCE)
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 640, 480, False, 1, pkg.TRAV_REFERENCE, schedule=schedule)
     oacc, oout, oids, ocnt = cpu_render(oracle, 640, 480, False, 1)
     assert np.array_equal(ids, oids)
     assert_bit_exact(acc, oacc)
@@ -99,10 +101,11 @@ def test_spheres_multi_frame_bit_exact(pkg, ctx, oracle, frames):
     assert np.array_equal(out, oout)
 
 
-def test_rubik_reference_order_bit_exact(pkg, ctx, oracle):
+@pytest.mark.parametrize("schedule", [0, 1])
+def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     """C2's scene at a size the oracle finishes in seconds; reference visiting order => bit-exact."""
     scene = scenes.rubik_scene()
-    acc, out, ids, cnt = gpu_render(pkg, ctx, 640, 360, True, 4, pkg.TRAV_REFERENCE, scene=scene)
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 640, 360, True, 4, pkg.TRAV_REFERENCE, scene=scene, schedule=schedule)
     oacc, oout, oids, ocnt = cpu_render(oracle, 640, 360, True, 4, scene=scene)
     assert np.array_equal(ids, oids)
     assert_bit_exact(acc, oacc)
@@ -111,11 +114,12 @@ def test_rubik_reference_order_bit_exact(pkg, ctx, oracle):
     assert ocnt["capped_paths"] == 0 and cnt["capped_paths"] == 0
 
 
-def test_rubik_ordered_traversal_matches_bar_ties(pkg, ctx, oracle):
+@pytest.mark.parametrize("schedule", [0, 1])
+def test_rubik_ordered_traversal_matches_bar_ties(pkg, ctx, oracle, schedule):
     """Ordered traversal: same image except documented grazing ties (budget: 1e-4 of the pixels; ids identical
     on every pixel outside that budget, radiance bit-exact there too)."""
     scene = scenes.rubik_scene()
-    acc, out, ids, cnt = gpu_render(pkg, ctx, 640, 360, True, 4, pkg.TRAV_ORDERED, scene=scene)
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 640, 360, True, 4, pkg.TRAV_ORDERED, scene=scene, schedule=schedule)
     oacc, oout, oids, ocnt = cpu_render(oracle, 640, 360, True, 4, scene=scene)
     bad = (acc.view(np.uint32) != oacc.view(np.uint32)).any(axis=2)
     assert bad.mean() <= 1e-4, "ordered traversal differs on %d pixels" % bad.sum()
