@@ -166,7 +166,7 @@ def run_gpu(args):
     stream = torch.cuda.Stream()  # a real (non-NULL) stream: kernels, events and NCCL ordering all go through it
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
-    ctx.set_option(pkg.OPT_SCHEDULE, pkg.SCHED_REGEN if args.schedule == "regen" else pkg.SCHED_PER_PATH)
+    ctx.set_option(pkg.OPT_SCHEDULE, {"persistent": pkg.SCHED_PERSISTENT, "regen": pkg.SCHED_REGEN, "per-path": pkg.SCHED_PER_PATH}[args.schedule])
     ctx.set_option(pkg.OPT_TRAVERSAL, mode)
     ctx.set_option(pkg.OPT_BLOCK_THREADS, args.block)
 
@@ -346,7 +346,7 @@ def main():
     ap.add_argument("--workload", default="rubik", choices=sorted(WORKLOADS))
     ap.add_argument("--traversal", default="ordered", choices=["ordered", "reference"])
     ap.add_argument("--block", type=int, default=64)
-    ap.add_argument("--schedule", default="regen", choices=["regen", "per-path"])
+    ap.add_argument("--schedule", default="persistent", choices=["persistent", "regen", "per-path"])
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the workload the CPU baseline renders")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

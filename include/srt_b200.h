@@ -42,7 +42,8 @@ typedef struct srt_counters {
 #define SRT_OPT_BLOCK_THREADS 4  /* threads per block of the path kernel (multiple of 32) */
 #define SRT_OPT_SCHEDULE 5       /* 0 = one path at a time per lane (the shader's schedule)
                                     1 = per-lane state machine with path regeneration + warp-synchronous traversal
-                                        (default; same results, different lane schedule) */
+                                    2 = persistent warps over 8x4 tiles, traversal state kept across refills of idle
+                                        lanes (default for models; same results, different lane schedule) */
 
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */

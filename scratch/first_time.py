@@ -8,7 +8,7 @@ unit, uniform = scenes.noise_tables(W, H)
 scene = scenes.rubik_scene()
 ctx.upload_scene(scene); ctx.upload_noise(unit, uniform); ctx.set_lights(scenes.model_lights()); ctx.resize(W, H)
 for mode in (0, 1):
-    for sched, block in ((0, 64), (1, 64), (1, 128)):
+    for sched, block in ((1, 64), (2, 64), (2, 128)):
         ctx.set_option(pkg.OPT_TRAVERSAL, mode); ctx.set_option(pkg.OPT_BLOCK_THREADS, block); ctx.set_option(pkg.OPT_SCHEDULE, sched)
         ctx.set_params(pkg.make_params(W, H, scenes.reset_camera(True), True, accum_frames=1, bvh_count=1))
         ctx.render(2)

@@ -58,7 +58,7 @@ struct srt_ctx {
   bool count_traversal = false;
   bool l2_persist = true;
   int block_threads = 64;
-  int schedule = SCHED_REGEN;
+  int schedule = SCHED_PERSISTENT;
 
   DeviceCounters* d_counters = nullptr;
   uint64_t kernel_launches = 0;
@@ -157,7 +157,7 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
       return 0;
   }
   if (key == SRT_OPT_SCHEDULE) {
-    if (value != SCHED_PER_PATH && value != SCHED_REGEN) return fail(ctx, "SRT_OPT_SCHEDULE: 0 or 1");
+    if (value < SCHED_PER_PATH || value > SCHED_PERSISTENT) return fail(ctx, "SRT_OPT_SCHEDULE: 0, 1 or 2");
     ctx->schedule = value;
     return 0;
   }
@@ -502,7 +502,7 @@ extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
   FrameParams fp;
   fill_frame_params(ctx, n_frames, fp);
   CU(ctx, launch_pathtrace(device_scene(ctx), fp, ctx->params.show_model != 0, ctx->traversal, ctx->count_traversal, ctx->schedule,
-                           ctx->d_accum, ctx->d_out, ctx->ids_enabled ? ctx->d_ids : nullptr, ctx->d_counters,
+                           ctx->d_accum, ctx->d_out, ctx->ids_enabled ? ctx->d_ids : nullptr, ctx->d_counters, &ctx->d_counters->next_tile,
                            ctx->block_threads, ctx->stream));
   ctx->kernel_launches++;
   ctx->params.accum_frames += n_frames;

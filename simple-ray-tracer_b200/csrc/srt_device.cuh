@@ -58,7 +58,7 @@ struct BvhRecord {
 // SRT_OPT_TRAVERSAL values (srt_b200.h)
 enum { TRAV_REFERENCE = 0, TRAV_ORDERED = 1 };
 // SRT_OPT_SCHEDULE values (srt_b200.h)
-enum { SCHED_PER_PATH = 0, SCHED_REGEN = 1 };
+enum { SCHED_PER_PATH = 0, SCHED_REGEN = 1, SCHED_PERSISTENT = 2 };
 
 #define SRT_MAX_BVHS 64
 
@@ -99,6 +99,8 @@ struct FrameParams {
 
 struct DeviceCounters {
   unsigned long long segments, shadow_rays, paths, capped_paths, nodes, tris;
+  unsigned int next_tile;  // work counter of the persistent kernel (zeroed before each launch)
+  unsigned int _pad;
 };
 
 }  // namespace srt

@@ -9,6 +9,7 @@
 #include "srt_kernels.h"
 #include "srt_path.cuh"
 #include "srt_regen.cuh"
+#include "srt_persistent.cuh"
 
 namespace srt {
 
@@ -82,6 +83,48 @@ pathtrace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, f
     atomicAdd(&counters->segments, (unsigned long long)seg);
     atomicAdd(&counters->shadow_rays, (unsigned long long)sh);
     atomicAdd(&counters->paths, (unsigned long long)(32 * fp.n_frames));
+    if (cap) atomicAdd(&counters->capped_paths, (unsigned long long)cap);
+    if (COUNT) {
+      atomicAdd(&counters->nodes, (unsigned long long)nd);
+      atomicAdd(&counters->tris, (unsigned long long)tr);
+    }
+  }
+}
+
+// Persistent warps over the tiles of the image (srt_persistent.cuh).  next_tile must be 0 at launch.
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(SRT_MAX_BLOCK_THREADS)
+pathtrace_persistent_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, float4* __restrict__ accum,
+                            uchar4* __restrict__ out, uint32_t* __restrict__ primary_ids,
+                            DeviceCounters* __restrict__ counters, unsigned int* __restrict__ next_tile) {
+  extern __shared__ uint2 s_stack_all[];
+  uint2* s_stack = s_stack_all + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int n_bands = (fp.y1 - fp.y0) >> 3;
+  const int my_bands = (n_bands - fp.stripe_rank + fp.stripe_world - 1) / fp.stripe_world;
+  const uint32_t n_tiles = (uint32_t)((fp.width >> 3) * (my_bands << 1));
+  PathStats st;
+  st.segments = st.shadow_rays = st.capped = 0;
+  st.trav.nodes = st.trav.tris = 0;
+  unsigned int tiles_done = 0;
+  persistent_warp_loop<MODE, COUNT>(sc, fp, accum, out, primary_ids, next_tile, n_tiles, s_stack, blockDim.x, st,
+                                    tiles_done);
+  unsigned int seg = st.segments, sh = st.shadow_rays, cap = st.capped, nd = st.trav.nodes, tr = st.trav.tris;
+  __syncwarp();
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    seg += __shfl_down_sync(0xFFFFFFFFu, seg, o);
+    sh += __shfl_down_sync(0xFFFFFFFFu, sh, o);
+    cap += __shfl_down_sync(0xFFFFFFFFu, cap, o);
+    if (COUNT) {
+      nd += __shfl_down_sync(0xFFFFFFFFu, nd, o);
+      tr += __shfl_down_sync(0xFFFFFFFFu, tr, o);
+    }
+  }
+  if (lane == 0) {
+    atomicAdd(&counters->segments, (unsigned long long)seg);
+    atomicAdd(&counters->shadow_rays, (unsigned long long)sh);
+    atomicAdd(&counters->paths, (unsigned long long)tiles_done * 32ull * (unsigned long long)fp.n_frames);
     if (cap) atomicAdd(&counters->capped_paths, (unsigned long long)cap);
     if (COUNT) {
       atomicAdd(&counters->nodes, (unsigned long long)nd);
@@ -166,6 +209,33 @@ static cudaError_t launch_path(const DeviceScene& sc, const FrameParams& fp, flo
   return cudaGetLastError();
 }
 
+template <int MODE, bool COUNT>
+static cudaError_t launch_persistent(const DeviceScene& sc, const FrameParams& fp, float4* accum, uchar4* out,
+                                     uint32_t* ids, DeviceCounters* counters, unsigned int* next_tile, int block,
+                                     cudaStream_t stream) {
+  int n_bands = (fp.y1 - fp.y0) / 8;
+  int my_bands = (n_bands - fp.stripe_rank + fp.stripe_world - 1) / fp.stripe_world;
+  long n_tiles = (long)(fp.width / 8) * my_bands * 2;
+  if (n_tiles <= 0) return cudaSuccess;
+  size_t smem = (size_t)fp.stack_cap * block * sizeof(uint2);
+  auto k = pathtrace_persistent_kernel<MODE, COUNT>;
+  cudaError_t e;
+  if (smem > 48 * 1024 && (e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+    return e;
+  int dev = 0, sms = 0, per_sm = 0;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, block, smem)) != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  long warps_per_block = block / 32;
+  long grid = (long)sms * per_sm;  // every resident slot of all SMs, once
+  long need = (n_tiles + warps_per_block - 1) / warps_per_block;
+  if (grid > need) grid = need;
+  if ((e = cudaMemsetAsync(next_tile, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
+  k<<<(unsigned)grid, block, smem, stream>>>(sc, fp, accum, out, ids, counters, next_tile);
+  return cudaGetLastError();
+}
+
 template <bool MODEL, int MODE, bool COUNT>
 static cudaError_t launch_path_sched(int sched, const DeviceScene& sc, const FrameParams& fp, float4* accum, uchar4* out,
                                      uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
@@ -175,9 +245,16 @@ static cudaError_t launch_path_sched(int sched, const DeviceScene& sc, const Fra
 }
 
 cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool model, int mode, bool count, int sched,
-                             float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters, int block,
-                             cudaStream_t stream) {
+                             float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters,
+                             unsigned int* next_tile, int block, cudaStream_t stream) {
   if (!model) return launch_path_sched<false, TRAV_REFERENCE, false>(sched, sc, fp, accum, out, ids, counters, block, stream);
+  if (sched == SCHED_PERSISTENT) {
+    if (mode == TRAV_REFERENCE)
+      return count ? launch_persistent<TRAV_REFERENCE, true>(sc, fp, accum, out, ids, counters, next_tile, block, stream)
+                   : launch_persistent<TRAV_REFERENCE, false>(sc, fp, accum, out, ids, counters, next_tile, block, stream);
+    return count ? launch_persistent<TRAV_ORDERED, true>(sc, fp, accum, out, ids, counters, next_tile, block, stream)
+                 : launch_persistent<TRAV_ORDERED, false>(sc, fp, accum, out, ids, counters, next_tile, block, stream);
+  }
   if (mode == TRAV_REFERENCE) {
     return count ? launch_path_sched<true, TRAV_REFERENCE, true>(sched, sc, fp, accum, out, ids, counters, block, stream)
                  : launch_path_sched<true, TRAV_REFERENCE, false>(sched, sc, fp, accum, out, ids, counters, block, stream);

@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 
 
 def gpu_render(pkg, ctx, W, H, show_model, n_frames, traversal, scene=None, lights=None, cam=None, first_frame=1,
-               max_depth=0, noise=None, rows=None, schedule=1):
+               max_depth=0, noise=None, rows=None, schedule=2):
     unit, uniform = noise if noise is not None else scenes.noise_tables(W, H)
     lights = lights if lights is not None else (scenes.model_lights() if show_model else scenes.sphere_lights())
     cam = cam or scenes.reset_camera(show_model)
@@ -101,7 +101,7 @@ def test_spheres_multi_frame_bit_exact(pkg, ctx, oracle, frames):
     assert np.array_equal(out, oout)
 
 
-@pytest.mark.parametrize("schedule", [0, 1])
+@pytest.mark.parametrize("schedule", [0, 1, 2])
 def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     """C2's scene at a size the oracle finishes in seconds; reference visiting order => bit-exact."""
     scene = scenes.rubik_scene()
@@ -114,7 +114,7 @@ def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     assert ocnt["capped_paths"] == 0 and cnt["capped_paths"] == 0
 
 
-@pytest.mark.parametrize("schedule", [0, 1])
+@pytest.mark.parametrize("schedule", [0, 1, 2])
 def test_rubik_ordered_traversal_matches_bar_ties(pkg, ctx, oracle, schedule):
     """Ordered traversal: same image except documented grazing ties (budget: 1e-4 of the pixels; ids identical
     on every pixel outside that budget, radiance bit-exact there too)."""
