@@ -1,0 +1,189 @@
+// headless_main.cpp -- the reference's frame loop without the window (reference: src/main.cpp:381-779, compute branch
+// :464-496 set-up, :600-725 per frame).  Same sequence of calls on the same classes -- camera Reset, Compute(path) +
+// Init, output/accumulation textures, noise tables, LoadObject + UploadModelDataToGPU, then per frame:
+// accumFrames++, the eleven uniforms, the lights buffer, one dispatch of (W/8, H/8, 1) groups -- with the GLFW
+// window, input polling and blit quad left out.  Writes the final picture as PPM (P3) and prints one JSON line
+// with the measured rates.
+//
+//   srt_headless [--spheres | --model NAME] [--objects DIR] [--width W] [--height H] [--frames N] [--batch B]
+//                [--out FILE.ppm] [--device D] [--seed S] [--max-depth D] [--pose x y z yaw pitch]
+//                [--noise FILE]   raw fp32: W*H unit vectors (xyz) then W*H uniform triples, instead of std::rand()
+//                [--accum FILE]   also write the RGBA32F accumulation image as raw fp32
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <exception>
+#include <memory>
+#include <stdexcept>
+#include <algorithm>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "asset_utils/gpu_loader.h"
+#include "asset_utils/model_loader.h"
+#include "common/utils.h"
+#include "graphics/shader.h"
+#include "graphics/texture.h"
+#include "raytracer/camera.h"
+#include "raytracer/light.h"
+#include "raytracer/raytracer.h"
+
+namespace {
+// the reference's compile-time flags (src/main.cpp:133-139) as run-time defaults
+struct Options {
+  bool show_model = true;
+  std::string model = "Rubik";
+  std::string objects = "./objects/";
+  int width = 1000, height = 800, frames = 60, batch = 1, device = 0, max_depth = 0;
+  unsigned seed = 1;  // std::rand() is never seeded by the reference, i.e. srand(1)
+  std::string out = "out.ppm";
+  std::string noise_file, accum_file;
+  bool pose = false;
+  float px = 0, py = 0, pz = 0, yaw = -90, pitch = 0;
+};
+}  // namespace
+
+int main(int argc, char** argv) {
+  Options o;
+  for (int i = 1; i < argc; ++i) {
+    const std::string a = argv[i];
+    const auto val = [&](int k = 1) -> const char* {
+      if (i + k >= argc) {
+        std::fprintf(stderr, "%s needs %d value(s)\n", a.c_str(), k);
+        std::exit(2);
+      }
+      return argv[i + k];
+    };
+    if (a == "--spheres") o.show_model = false;
+    else if (a == "--model") { o.model = val(); o.show_model = true; ++i; }
+    else if (a == "--objects") { o.objects = val(); ++i; }
+    else if (a == "--width") { o.width = std::atoi(val()); ++i; }
+    else if (a == "--height") { o.height = std::atoi(val()); ++i; }
+    else if (a == "--frames") { o.frames = std::atoi(val()); ++i; }
+    else if (a == "--batch") { o.batch = std::atoi(val()); ++i; }
+    else if (a == "--device") { o.device = std::atoi(val()); ++i; }
+    else if (a == "--seed") { o.seed = static_cast<unsigned>(std::atoi(val())); ++i; }
+    else if (a == "--max-depth") { o.max_depth = std::atoi(val()); ++i; }
+    else if (a == "--out") { o.out = val(); ++i; }
+    else if (a == "--noise") { o.noise_file = val(); ++i; }
+    else if (a == "--accum") { o.accum_file = val(); ++i; }
+    else if (a == "--pose") {
+      o.pose = true;
+      o.px = std::atof(val(1)); o.py = std::atof(val(2)); o.pz = std::atof(val(3));
+      o.yaw = std::atof(val(4)); o.pitch = std::atof(val(5));
+      i += 5;
+    } else {
+      std::fprintf(stderr, "unknown option %s\n", a.c_str());
+      return 2;
+    }
+  }
+  if (o.batch < 1) o.batch = 1;
+
+  try {
+    RayTracer::CameraSettings settings;
+    settings.width = static_cast<RayTracer::uint>(o.width);
+    settings.aspect = static_cast<float>(o.width) / static_cast<float>(o.height);
+    RayTracer::Camera camera(settings);
+    camera.Initialize(o.show_model);
+    camera.Reset();
+    if (o.pose) camera.SetPose(glm::vec3(o.px, o.py, o.pz), o.yaw, o.pitch);
+
+    Graphics::Compute compute("./shaders/raytrace_compute.glsl", o.device);
+    compute.Init();
+    compute.Use();
+
+    Graphics::Texture texture;
+    texture.setWidth(o.width);
+    texture.setHeight(o.height);
+    texture.getTextureHandle(0, 0, true);
+    Graphics::Texture32 accum;
+    accum.setWidth(o.width);
+    accum.setHeight(o.height);
+    accum.getTextureHandle(3, 3, true);
+
+    const std::size_t texels = static_cast<std::size_t>(o.width) * o.height;
+    std::vector<glm::vec3> noise(texels), noise_uniform(texels);
+    if (!o.noise_file.empty()) {
+      std::FILE* f = std::fopen(o.noise_file.c_str(), "rb");
+      if (!f || std::fread(noise.data(), 12, texels, f) != texels || std::fread(noise_uniform.data(), 12, texels, f) != texels)
+        throw std::runtime_error("cannot read 2 x W*H x 3 floats from " + o.noise_file);
+      std::fclose(f);
+    } else {
+      // UpdateNoiseTex (src/main.cpp:269-279): every unit vector first, then every uniform triple
+      std::srand(o.seed);
+      for (glm::vec3& v : noise) v = Common::randomUnitVector();
+      for (glm::vec3& v : noise_uniform) v = Common::randomVec3(0.0f, 1.0f);
+    }
+    compute.UploadNoise(noise.data(), noise_uniform.data(), static_cast<Graphics::uint>(texels));
+
+    std::unique_ptr<AssetUtils::Model> model;
+    double load_s = 0.0;
+    if (o.show_model) {
+      const auto t0 = std::chrono::steady_clock::now();
+      AssetUtils::SetObjectFolder(o.objects);
+      model = AssetUtils::LoadObject(o.model);
+      std::vector<AssetUtils::Model*> models{model.get()};
+      AssetUtils::UploadModelDataToGPU(models, 5);
+      load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+
+    std::vector<RayTracer::PointLight> lights;
+    if (o.show_model) {
+      lights.emplace_back(glm::vec3(1.0f, 10.0f, 10.0f), glm::vec3(1.0f, 1.0f, 1.0f), 50.0f);
+      lights.emplace_back(glm::vec3(-5.0f, 15.0f, 10.0f), glm::vec3(1.0f, 0.2f, 0.2f), 15.0f);
+      lights.emplace_back(glm::vec3(5.0f, 15.0f, 10.0f), glm::vec3(0.2f, 1.0f, 0.2f), 15.0f);
+      lights.emplace_back(glm::vec3(-5.0f, 5.0f, 10.0f), glm::vec3(0.2f, 0.2f, 1.0f), 15.0f);
+      lights.emplace_back(glm::vec3(5.0f, 5.0f, 10.0f), glm::vec3(1.0f, 1.0f, 0.1f), 15.0f);
+      lights.emplace_back(glm::vec3(0.0f, 21.0f, 17.0f), glm::vec3(1.0f, 1.0f, 1.0f), 50.0f);
+    } else {
+      lights.emplace_back(glm::vec3(1.0f, 2.0f, 0.0f), glm::vec3(1.0f, 1.0f, 1.0f), 10.0f);
+      lights.emplace_back(glm::vec3(-2.5f, 2.0f, 0.0f), glm::vec3(1.0f, 1.0f, 1.0f), 3.0f);
+    }
+
+    srt_reset_counters(compute.GetProgram());
+    int accumFrames = 0;
+    const auto t0 = std::chrono::steady_clock::now();
+    while (accumFrames < o.frames) {
+      const int n = std::min(o.batch, o.frames - accumFrames);
+      compute.Use();
+      compute.SetBool("resetAccumBuffer", false);
+      compute.SetVec3("cameraOrigin", camera.getOrigin());
+      compute.SetVec3("cameraDirection", camera.getForward());
+      compute.SetVec3("cameraUp", camera.getUpVector());
+      compute.SetVec3("cameraRight", camera.getRightVector());
+      compute.SetInt("accumFrames", accumFrames + 1);
+      compute.SetInt("Width", o.width);
+      compute.SetInt("Height", o.height);
+      compute.SetUInt("bvh_count", o.show_model ? 1u : 0u);  // models in scene (decree Q1; the reference passes 2)
+      compute.SetInt("lightCount", static_cast<int>(lights.size()));
+      compute.SetBool("showModel", o.show_model);
+      if (o.max_depth > 0) compute.SetInt("maxDepth", o.max_depth);
+      compute.SetLights(lights.data(), static_cast<Graphics::uint>(lights.size()));
+      compute.DispatchFrames(o.width / 8, o.height / 8, n);
+      accumFrames += n;
+    }
+    const double render_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+
+    texture.updateImageDataFromGPU();
+    RayTracer::WritePPM(o.out, texture.getImageData(), o.width, o.height);
+    if (!o.accum_file.empty()) {
+      accum.updateImageDataFromGPU();
+      std::FILE* f = std::fopen(o.accum_file.c_str(), "wb");
+      if (!f || std::fwrite(accum.getImageData(), 16, texels, f) != texels) throw std::runtime_error("cannot write " + o.accum_file);
+      std::fclose(f);
+    }
+    srt_counters c;
+    srt_get_counters(compute.GetProgram(), &c);
+    std::printf("{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"frames\": %d, \"ms_per_frame\": %.4f, "
+                "\"segments\": %llu, \"shadow_rays\": %llu, \"mseg_per_s\": %.2f, \"load_s\": %.3f, \"out\": \"%s\"}\n",
+                o.show_model ? o.model.c_str() : "spheres", o.width, o.height, o.frames, render_s * 1e3 / o.frames,
+                (unsigned long long)c.segments, (unsigned long long)c.shadow_rays, c.segments / render_s / 1e6, load_s,
+                o.out.c_str());
+  } catch (const std::exception& e) {
+    std::fprintf(stderr, "srt_headless: %s\n", e.what());
+    return 1;
+  }
+  return 0;
+}
