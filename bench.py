@@ -166,9 +166,11 @@ def run_gpu(args):
     stream = torch.cuda.Stream()  # a real (non-NULL) stream: kernels, events and NCCL ordering all go through it
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
-    ctx.set_option(pkg.OPT_SCHEDULE, {"persistent": pkg.SCHED_PERSISTENT, "regen": pkg.SCHED_REGEN, "per-path": pkg.SCHED_PER_PATH}[args.schedule])
+    ctx.set_option(pkg.OPT_SCHEDULE, {"wavefront": pkg.SCHED_WAVEFRONT, "persistent": pkg.SCHED_PERSISTENT, "regen": pkg.SCHED_REGEN, "per-path": pkg.SCHED_PER_PATH}[args.schedule])
     ctx.set_option(pkg.OPT_TRAVERSAL, mode)
     ctx.set_option(pkg.OPT_BLOCK_THREADS, args.block)
+    if args.wave_slots:
+        ctx.set_option(pkg.OPT_WAVE_SLOTS, args.wave_slots)
 
     def upload_all():
         if inp["scene"] is not None:
@@ -233,7 +235,7 @@ def run_gpu(args):
     step_ms = [a.elapsed_time(b) for a, b in ev]
     kern_ms = [a.elapsed_time(b) for a, b in evk]
     cnt = ctx.counters()
-    gpu_launches = launches[0]
+    gpu_launches = cnt["kernel_launches"]  # every kernel this context launched in the timed region (clear, init, waves, resolve, tonemap)
 
     tot = torch.tensor([sum(step_ms), sum(kern_ms)], dtype=torch.float64, device="cuda")
     work = torch.tensor([cnt["segments"], cnt["shadow_rays"], cnt["paths"], gpu_launches], dtype=torch.float64, device="cuda")
@@ -346,9 +348,10 @@ def main():
     ap.add_argument("--workload", default="rubik", choices=sorted(WORKLOADS))
     ap.add_argument("--traversal", default="ordered", choices=["ordered", "reference"])
     ap.add_argument("--block", type=int, default=64)
-    ap.add_argument("--schedule", default="persistent", choices=["persistent", "regen", "per-path"])
+    ap.add_argument("--schedule", default="wavefront", choices=["wavefront", "persistent", "regen", "per-path"])
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the workload the CPU baseline renders")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--wave-slots", type=int, default=0, help="path slots of the wavefront schedule (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -43,7 +43,14 @@ typedef struct srt_counters {
 #define SRT_OPT_SCHEDULE 5       /* 0 = one path at a time per lane (the shader's schedule)
                                     1 = per-lane state machine with path regeneration + warp-synchronous traversal
                                     2 = persistent warps over 8x4 tiles, traversal state kept across refills of idle
-                                        lanes (default for models; same results, different lane schedule) */
+                                        lanes
+                                    3 = wavefront: one path slot per pixel, a persistent traversal kernel fed from ray
+                                        queues + full-warp shading kernels, queued wave by wave (default for models)
+                                    all four give the same bits; only the lane schedule differs */
+
+#define SRT_OPT_WAVE_SLOTS 6      /* wavefront schedule: path slots in flight (default 4 Mi) */
+#define SRT_OPT_SAMPLE_BUDGET_MB 7 /* wavefront schedule: size limit of the per-path sample buffer; longer launches are cut
+                                      into frame chunks (default 4096 MB) */
 
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */

@@ -58,7 +58,17 @@ struct srt_ctx {
   bool count_traversal = false;
   bool l2_persist = true;
   int block_threads = 64;
-  int schedule = SCHED_PERSISTENT;
+  int schedule = SCHED_WAVEFRONT;
+
+  // wavefront schedule: path slots + queues (sized for the pixels this context renders), polling state
+  PathPool pool;
+  uint32_t pool_slots = 0;
+  unsigned int* h_live = nullptr;  // pinned ring the device reports live_pixels into
+  cudaEvent_t wave_events[4] = {nullptr, nullptr, nullptr, nullptr};
+  uint64_t waves = 0;
+  uint32_t wave_slots = 4u << 20;              // path slots of the pool (SRT_OPT_WAVE_SLOTS)
+  size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
+  size_t sample_budget_bytes = (size_t)4 << 30;  // sample buffer budget per frame chunk (SRT_OPT_SAMPLE_BUDGET_MB)
 
   DeviceCounters* d_counters = nullptr;
   uint64_t kernel_launches = 0;
@@ -88,6 +98,15 @@ static void dfree(T*& p) {
   p = nullptr;
 }
 
+static void free_pool(srt_ctx* ctx) {
+  PathPool& p = ctx->pool;
+  dfree(p.r0); dfree(p.r1); dfree(p.hit); dfree(p.p0); dfree(p.p1); dfree(p.path); dfree(p.p3);
+  dfree(p.list[0]); dfree(p.list[1]); dfree(p.q); dfree(p.samples);
+  p.cap = 0;
+  ctx->pool_slots = 0;
+  ctx->sample_entries = 0;
+}
+
 extern "C" const char* srt_version(void) { return "srt_b200 0.1 sm_100a"; }
 
 extern "C" const char* srt_last_error(const srt_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
@@ -109,6 +128,7 @@ extern "C" int srt_create(srt_ctx** out, int device) {
   CU(nullptr, cudaSetDevice(device));
   srt_ctx* ctx = new srt_ctx();
   ctx->device = device;
+  memset(&ctx->pool, 0, sizeof ctx->pool);
   memset(&ctx->params, 0, sizeof ctx->params);
   memset(ctx->lights, 0, sizeof ctx->lights);
   if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -130,6 +150,10 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris); dfree(ctx->d_mats); dfree(ctx->d_bvhs);
   dfree(ctx->d_noise_xy); dfree(ctx->d_noise_x); dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
   dfree(ctx->d_counters);
+  free_pool(ctx);
+  if (ctx->h_live) cudaFreeHost(ctx->h_live);
+  for (cudaEvent_t& e : ctx->wave_events)
+    if (e) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -156,8 +180,18 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
       ctx->block_threads = value;
       return 0;
   }
+  if (key == SRT_OPT_WAVE_SLOTS) {
+    if (value < 1024) return fail(ctx, "SRT_OPT_WAVE_SLOTS: at least 1024");
+    ctx->wave_slots = (uint32_t)value;
+    return 0;
+  }
+  if (key == SRT_OPT_SAMPLE_BUDGET_MB) {
+    if (value < 1) return fail(ctx, "SRT_OPT_SAMPLE_BUDGET_MB: at least 1");
+    ctx->sample_budget_bytes = (size_t)value << 20;
+    return 0;
+  }
   if (key == SRT_OPT_SCHEDULE) {
-    if (value < SCHED_PER_PATH || value > SCHED_PERSISTENT) return fail(ctx, "SRT_OPT_SCHEDULE: 0, 1 or 2");
+    if (value < SCHED_PER_PATH || value > SCHED_WAVEFRONT) return fail(ctx, "SRT_OPT_SCHEDULE: 0, 1, 2 or 3");
     ctx->schedule = value;
     return 0;
   }
@@ -354,7 +388,7 @@ extern "C" int srt_set_params(srt_ctx* ctx, const srt_params* p) {
     return fail(ctx, "srt_set_params: Width/Height must be positive multiples of 8 (src/main.cpp:706), got %dx%d", p->width, p->height);
   if ((int64_t)p->width * p->height >= (1 << 30)) return fail(ctx, "srt_set_params: Width*Height must be < 2^30");
   if (p->accum_frames < 1 && !p->reset_accum) return fail(ctx, "srt_set_params: accumFrames must be >= 1");
-  if (p->max_depth < 0) return fail(ctx, "srt_set_params: max_depth < 0");
+  if (p->max_depth < 0 || p->max_depth > 255) return fail(ctx, "srt_set_params: max_depth must be 0..255");
   ctx->params = *p;
   ctx->have_params = true;
   return 0;
@@ -488,6 +522,94 @@ int check_ready(srt_ctx* ctx) {
 
 }  // namespace
 
+namespace {
+
+int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries) {
+  PathPool& p = ctx->pool;
+  if (!(ctx->pool_slots >= slots && p.q)) {
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    float4* keep = p.samples;
+    p.samples = nullptr;
+    free_pool(ctx);
+    p.samples = keep;
+    CU(ctx, cudaMalloc(&p.r0, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.r1, (size_t)slots * 16));
+    CU(ctx, cudaMalloc(&p.hit, (size_t)slots * 8)); CU(ctx, cudaMalloc(&p.p0, (size_t)slots * 16));
+    CU(ctx, cudaMalloc(&p.p1, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.path, (size_t)slots * 8));
+    CU(ctx, cudaMalloc(&p.p3, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.list[0], (size_t)slots * 4));
+    CU(ctx, cudaMalloc(&p.list[1], (size_t)slots * 4)); CU(ctx, cudaMalloc(&p.q, sizeof(WaveCounters)));
+    ctx->pool_slots = slots;
+  }
+  p.cap = slots;
+  if (ctx->sample_entries < sample_entries) {
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    dfree(p.samples);
+    CU(ctx, cudaMalloc(&p.samples, sample_entries * sizeof(float4)));
+    ctx->sample_entries = sample_entries;
+  }
+  if (!ctx->h_live) CU(ctx, cudaHostAlloc(&ctx->h_live, 4 * sizeof(unsigned int), cudaHostAllocDefault));
+  for (cudaEvent_t& e : ctx->wave_events)
+    if (!e) CU(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  return 0;
+}
+
+// Wavefront schedule.  The launch's frames are cut into chunks whose sample buffer (16 B per path) fits the budget;
+// per chunk: init, then trace+logic pairs queued in batches -- after each batch the device reports how many slots
+// still carry a path, and the host looks at the report of the batch BEFORE the one it has just queued, so the GPU
+// always has a batch in flight -- then the resolve kernel.  Returns with everything queued.
+int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
+  const int n_bands = (fp_all.y1 - fp_all.y0) / 8;
+  const int my_bands = (n_bands - fp_all.stripe_rank + fp_all.stripe_world - 1) / fp_all.stripe_world;
+  const uint32_t n_pixels = (uint32_t)(fp_all.width / 8) * (uint32_t)my_bands * 2u * 32u;
+  if (n_pixels == 0) return 0;
+  const size_t budget_entries = ctx->sample_budget_bytes / sizeof(float4);
+  int chunk_frames = (int)(budget_entries / n_pixels);
+  if (chunk_frames < 1) chunk_frames = 1;
+  if (chunk_frames > fp_all.n_frames) chunk_frames = fp_all.n_frames;
+  const DeviceScene sc = device_scene(ctx);
+  uint32_t* ids = ctx->ids_enabled ? ctx->d_ids : nullptr;
+  const int kBatch = 8;
+
+  for (int done = 0; done < fp_all.n_frames; done += chunk_frames) {
+    FrameParams fp = fp_all;
+    fp.accum_frames = fp_all.accum_frames + done;
+    fp.n_frames = fp_all.n_frames - done < chunk_frames ? fp_all.n_frames - done : chunk_frames;
+    const unsigned long long n_paths = (unsigned long long)n_pixels * (unsigned long long)fp.n_frames;
+    uint32_t slots = ctx->wave_slots;
+    if ((unsigned long long)slots > n_paths) slots = (uint32_t)n_paths;
+    slots = (slots + 31u) & ~31u;
+    if (ensure_pool(ctx, slots, (size_t)n_pixels * (size_t)chunk_frames)) return 1;
+    ctx->pool.n_pixels = n_pixels;
+    ctx->pool.n_paths = n_paths;
+    // primary ids are those of the launch's LAST frame
+    uint32_t* chunk_ids = (done + fp.n_frames == fp_all.n_frames) ? ids : nullptr;
+    CU(ctx, launch_wf_init(sc, fp, ctx->pool, ctx->d_counters, ctx->stream));
+    ctx->kernel_launches++;
+    int parity = 0;
+    for (int batch = 0;; ++batch) {
+      for (int w = 0; w < kBatch; ++w) {
+        CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, ctx->traversal, ctx->count_traversal, chunk_ids, ctx->d_counters,
+                               ctx->block_threads, ctx->stream));
+        parity ^= 1;
+      }
+      ctx->kernel_launches += 2 * kBatch;
+      ctx->waves += kBatch;
+      const int s = batch & 3;
+      CU(ctx, cudaMemcpyAsync(&ctx->h_live[s], &ctx->pool.q->live_slots, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+      CU(ctx, cudaEventRecord(ctx->wave_events[s], ctx->stream));
+      if (batch >= 1) {
+        const int prev = (batch - 1) & 3;
+        CU(ctx, cudaEventSynchronize(ctx->wave_events[prev]));
+        if (ctx->h_live[prev] == 0) break;
+      }
+    }
+    CU(ctx, launch_wf_resolve(fp, ctx->pool, ctx->d_accum, ctx->d_out, ctx->stream));
+    ctx->kernel_launches++;
+  }
+  return 0;
+}
+
+}  // namespace
+
 extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
   if (!ctx) return 1;
   if (n_frames < 0) return fail(ctx, "srt_render: n_frames < 0");
@@ -501,6 +623,11 @@ extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
   if (n_frames == 0 || ctx->row1 == ctx->row0) return 0;
   FrameParams fp;
   fill_frame_params(ctx, n_frames, fp);
+  if (ctx->params.show_model && ctx->schedule == SCHED_WAVEFRONT) {
+    if (render_wavefront(ctx, fp)) return 1;
+    ctx->params.accum_frames += n_frames;
+    return 0;
+  }
   CU(ctx, launch_pathtrace(device_scene(ctx), fp, ctx->params.show_model != 0, ctx->traversal, ctx->count_traversal, ctx->schedule,
                            ctx->d_accum, ctx->d_out, ctx->ids_enabled ? ctx->d_ids : nullptr, ctx->d_counters, &ctx->d_counters->next_tile,
                            ctx->block_threads, ctx->stream));

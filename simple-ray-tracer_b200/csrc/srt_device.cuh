@@ -58,7 +58,7 @@ struct BvhRecord {
 // SRT_OPT_TRAVERSAL values (srt_b200.h)
 enum { TRAV_REFERENCE = 0, TRAV_ORDERED = 1 };
 // SRT_OPT_SCHEDULE values (srt_b200.h)
-enum { SCHED_PER_PATH = 0, SCHED_REGEN = 1, SCHED_PERSISTENT = 2 };
+enum { SCHED_PER_PATH = 0, SCHED_REGEN = 1, SCHED_PERSISTENT = 2, SCHED_WAVEFRONT = 3 };
 
 #define SRT_MAX_BVHS 64
 
@@ -101,6 +101,34 @@ struct DeviceCounters {
   unsigned long long segments, shadow_rays, paths, capped_paths, nodes, tris;
   unsigned int next_tile;  // work counter of the persistent kernel (zeroed before each launch)
   unsigned int _pad;
+};
+
+// ---- wavefront schedule (srt_wavefront.cuh): queues, path slots, per-frame sample buffer ---------------------------
+struct WaveCounters {
+  unsigned int n_closest[2];  // entries at the front of list[parity]
+  unsigned int n_shadow[2];   // entries at the back of list[parity]
+  unsigned int cursor;        // fetch cursor of wf_trace_kernel
+  unsigned int live_slots;    // slots that still carry a path
+  unsigned long long next_path;  // next path (frame-major: frame * n_pixels + pixel slot) to hand to a free slot
+};
+
+// Per-slot records (SoA, 16 B each unless noted).  A slot carries ONE path at a time; when the path ends the slot
+// takes the next path of the launch from WaveCounters::next_path.
+struct PathPool {
+  float4* r0;    // ray origin.xyz, tmax (initial intersection_distance)
+  float4* r1;    // ray direction.xyz, bits: kind | light index << 8
+  uint2* hit;    // result: primitive (or SRT_NO_HIT), distance bits
+  float4* p0;    // throughput.xyz, light weight of the pending shadow ray
+  float4* p1;    // colour.xyz, bits: depth | rand_index << 8 | iter << 20
+  uint2* path;   // (pixel slot, frame of the launch) of the path in this slot  (8 B)
+  float4* p3;    // while a shadow ray is out: incoming direction.xyz, bits: primitive the path stands on
+  uint32_t* list[2];
+  uint32_t cap;  // slots (= entries per list)
+  WaveCounters* q;
+  // one fp32 sample per path of the launch, frame-major, summed per pixel in frame order by wf_resolve_kernel
+  float4* samples;
+  uint32_t n_pixels;           // pixel slots of this launch (8x4 tiles x 32)
+  unsigned long long n_paths;  // n_pixels * frames of this launch
 };
 
 }  // namespace srt

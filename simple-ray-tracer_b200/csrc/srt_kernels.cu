@@ -10,6 +10,7 @@
 #include "srt_path.cuh"
 #include "srt_regen.cuh"
 #include "srt_persistent.cuh"
+#include "srt_wavefront.cuh"
 
 namespace srt {
 
@@ -261,6 +262,81 @@ cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool 
   }
   return count ? launch_path_sched<true, TRAV_ORDERED, true>(sched, sc, fp, accum, out, ids, counters, block, stream)
                : launch_path_sched<true, TRAV_ORDERED, false>(sched, sc, fp, accum, out, ids, counters, block, stream);
+}
+
+cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool,
+                           DeviceCounters* counters, cudaStream_t stream) {
+  if (pool.cap == 0) return cudaSuccess;
+  wf_init_kernel<<<(pool.cap + 127u) / 128u, 128, 0, stream>>>(sc, fp, pool, counters);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_wf_resolve(const FrameParams& fp, const PathPool& pool, float4* accum, uchar4* out,
+                              cudaStream_t stream) {
+  if (pool.n_pixels == 0) return cudaSuccess;
+  wf_resolve_kernel<<<(pool.n_pixels + 127u) / 128u, 128, 0, stream>>>(fp, pool, accum, out);
+  return cudaGetLastError();
+}
+
+namespace {
+struct WfGrid {
+  int sms = 0;
+  int trace_blocks_per_sm[2][2] = {{0, 0}, {0, 0}};  // [mode][count], for the block size it was computed with
+  int block = 0;
+  size_t smem = 0;
+};
+WfGrid g_wf_grid;  // launch geometry is a property of the device + kernel, computed once per (block, smem)
+
+template <int MODE, bool COUNT>
+cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity,
+                            DeviceCounters* counters, int block, cudaStream_t stream) {
+  auto k = wf_trace_kernel<MODE, COUNT>;
+  const size_t smem = (size_t)fp.stack_cap * block * sizeof(uint2);
+  cudaError_t e;
+  if (g_wf_grid.block != block || g_wf_grid.smem != smem || g_wf_grid.sms == 0) {
+    int dev = 0;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&g_wf_grid.sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    g_wf_grid.block = block;
+    g_wf_grid.smem = smem;
+    for (int m = 0; m < 2; ++m) g_wf_grid.trace_blocks_per_sm[m][0] = g_wf_grid.trace_blocks_per_sm[m][1] = 0;
+  }
+  int& per_sm = g_wf_grid.trace_blocks_per_sm[MODE][COUNT ? 1 : 0];
+  if (per_sm == 0) {
+    if (smem > 48 * 1024 &&
+        (e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+      return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, block, smem)) != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+  }
+  // persistent warps: every resident slot of all SMs once, but never more warps than the pool has 32-ray chunks
+  long grid = (long)g_wf_grid.sms * per_sm;
+  long need = ((long)pool.cap / 32 + block / 32 - 1) / (block / 32);
+  if (grid > need) grid = need;
+  if (grid < 1) grid = 1;
+  k<<<(unsigned)grid, block, smem, stream>>>(sc, fp, pool, parity, counters);
+  return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
+                           bool count, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
+  cudaError_t e;
+  if (mode == TRAV_REFERENCE)
+    e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, counters, block, stream)
+              : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, counters, block, stream);
+  else
+    e = count ? wf_trace_launch<TRAV_ORDERED, true>(sc, fp, pool, parity, counters, block, stream)
+              : wf_trace_launch<TRAV_ORDERED, false>(sc, fp, pool, parity, counters, block, stream);
+  if (e != cudaSuccess) return e;
+  // logic: a fixed grid of warps strides over the wave's 32-entry chunks
+  long warps = (long)pool.cap / 32;
+  long blocks = (warps + 3) / 4;
+  long max_blocks = (long)(g_wf_grid.sms > 0 ? g_wf_grid.sms : 148) * 8;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks < 1) blocks = 1;
+  wf_logic_kernel<<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool, parity, ids, counters);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream) {

@@ -12,6 +12,13 @@ namespace srt {
 cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool model, int mode, bool count, int sched,
                              float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters,
                              unsigned int* next_tile, int block, cudaStream_t stream);
+// Wavefront schedule (srt_wavefront.cuh): one init launch, then trace+logic pairs queued by the caller.
+cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool,
+                           DeviceCounters* counters, cudaStream_t stream);
+cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
+                           bool count, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream);
+cudaError_t launch_wf_resolve(const FrameParams& fp, const PathPool& pool, float4* accum, uchar4* out,
+                              cudaStream_t stream);
 cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream);
 cudaError_t launch_tonemap(const float4* accum, uchar4* out, size_t n, float frames, cudaStream_t stream);
 cudaError_t launch_trace_rays(const DeviceScene& sc, int mode, int stack_cap, const srt_ray* rays, uint32_t n_rays,

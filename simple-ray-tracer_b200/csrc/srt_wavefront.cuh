@@ -1,0 +1,473 @@
+// srt_wavefront.cuh -- wavefront schedule of the path tracer: the per-pixel work of GetRayColor / main()
+// (shaders/raytrace_compute.glsl:208-294, 296-414) cut at its two CheckHit calls into kernels that each keep a
+// whole warp on ONE kind of work.
+//
+// Why: the persistent-warp megakernel (srt_persistent.cuh) runs 11 of 32 lanes per instruction on Rubik
+// (profiles/r01a_*): lanes that finished a ray wait for a divergent shading pass (3 lanes wide, 67 KB of code missing the
+// instruction cache) and lanes that still traverse wait for them.  Here
+//   * the launch's paths (pixels x frames, frame-major, pixels in 8x4 tile order so the primary rays of a warp stay
+//     coherent) are independent; a pool of PATH SLOTS carries the live ones between kernels in 128-bit SoA records
+//   * wf_trace_kernel : persistent warps; a lane whose ray ended FETCHES the next ray of the wave from a queue
+//     (32 B load + root-box test) instead of shading, so the warp keeps traversing with full lanes; results go back to
+//     the slot as (primitive, distance)
+//   * wf_logic_kernel : consumes the wave's results queue by queue -- all lanes of a warp are either "closest-hit
+//     came back" (hit point, light sampling, emit shadow ray) or "shadow ray came back" (direct light, lobe choice,
+//     roulette, bounce) -- and appends the next wave's rays to the closest / shadow queue; a finished path writes its
+//     sample to samples[frame][pixel] and its slot takes the next path of the launch (regeneration), so waves stay
+//     millions of rays wide until the launch runs out of paths
+//   * wf_resolve_kernel : per pixel, accum + sample[0] + sample[1] + ... in frame order -- the shader's own
+//     accumulation order (raytrace_compute.glsl:404-406) -- so results stay bit-identical to the shader's schedule.
+//     The sample buffer is what 180 GB of HBM buys: 16 B per path (2.1 GB for 64 frames at 1080p; longer launches
+//     are cut into frame chunks by the host)
+//   * the host queues trace+logic pairs until every pixel has run its frames (srt_api.cu)
+// One list holds both queues: closest-hit rays grow from the front, shadow rays from the back.
+#pragma once
+
+#include "srt_path.cuh"
+#include "srt_persistent.cuh"
+
+namespace srt {
+
+#define SRT_WF_REFILL_THRESHOLD 6
+#define SRT_WF_KIND_CLOSEST 0u
+#define SRT_WF_KIND_SHADOW 1u
+
+__device__ __forceinline__ uint32_t wf_pack(int depth, int rand_index, int iter) {
+  return (uint32_t)depth | ((uint32_t)rand_index << 8) | ((uint32_t)iter << 20);
+}
+
+// GetRay + SampleSquare (raytrace_compute.glsl:78-90, raytrace_utils.glsl:10-17) for frame f of the launch
+__device__ __forceinline__ V3 wf_primary_dir(const DeviceScene& sc, const FrameParams& fp, int x, int y, int pix, int f) {
+  int samp = (fp.accum_frames + f) % fp.n_texels;
+  int idx = (pix + samp) % fp.n_texels;
+  float2 jit = __ldg(sc.noise_unit_xy + idx);
+  float ox = jit.x - 0.5f, oy = jit.y - 0.5f;
+  V3 pixel_sample = fp.pixel00 + (((float)x + ox) * fp.delta_u) + (((float)y + oy) * fp.delta_v);
+  return pixel_sample - fp.center;
+}
+
+// ---- wave 0: the first pool.cap paths of the launch -----------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool,
+               DeviceCounters* __restrict__ counters) {
+  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long first = pool.n_paths < (unsigned long long)pool.cap ? pool.n_paths : (unsigned long long)pool.cap;
+  if (slot == 0) {
+    pool.q->n_closest[0] = (unsigned int)first;
+    pool.q->n_shadow[0] = 0;
+    pool.q->n_closest[1] = 0;
+    pool.q->n_shadow[1] = 0;
+    pool.q->cursor = 0;
+    pool.q->live_slots = (unsigned int)first;
+    pool.q->next_path = first;
+    atomicAdd(&counters->segments, first);
+    atomicAdd(&counters->paths, pool.n_paths);
+  }
+  if (slot >= first) return;
+  const uint32_t pixel = slot % pool.n_pixels, f = slot / pool.n_pixels;
+  int x, y;
+  tile_pixel(fp, pixel >> 5, pixel & 31, x, y);
+  const int pix = y * fp.height + x;  // Q4
+  V3 d = wf_primary_dir(sc, fp, x, y, pix, (int)f);
+  pool.r0[slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
+  pool.r1[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
+  pool.p0[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+  pool.p1[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0)));
+  pool.path[slot] = make_uint2(pixel, f);
+  pool.list[0][slot] = slot;
+}
+
+// ---- trace: Intersects / CheckHit of one wave (ray_intersects.glsl:99-133, raytrace_compute.glsl:143-162) ---------
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(SRT_MAX_BLOCK_THREADS)
+wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity,
+                DeviceCounters* __restrict__ counters) {
+  extern __shared__ uint2 s_stack_all[];
+  uint2* s_stack = s_stack_all + threadIdx.x;
+  const int stride = blockDim.x;
+  const unsigned FULL = 0xFFFFFFFFu;
+  const int lane = threadIdx.x & 31;
+  WaveCounters* q = pool.q;
+  const uint32_t n_front = q->n_closest[parity];
+  const uint32_t n_total = n_front + q->n_shadow[parity];
+  const uint32_t* __restrict__ list = parity ? pool.list[1] : pool.list[0];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // the logic kernel of this wave fills the other list from empty
+    q->n_closest[parity ^ 1] = 0;
+    q->n_shadow[parity ^ 1] = 0;
+  }
+
+  unsigned int n_nodes = 0, n_tris = 0;
+  bool trav = false, any_hit = false, exact_box = false;
+  uint32_t slot = 0;
+  V3 ray_o = v3(0.0f), ray_d = v3(0.0f), to = v3(0.0f), td = v3(0.0f), inv = v3(0.0f);
+  float best = 0.0f;
+  uint32_t hit = SRT_NO_HIT, best_rank = 0xFFFFFFFFu, cur = 0, bvh_i = 0, tri = 0, tri_end = 0;
+  int sp = 0;
+  bool exhausted = false;  // warp-uniform: the queue has no more rays
+
+  auto finish_ray = [&]() {  // the lane's ray is done: hand the result to the slot
+    pool.hit[slot] = make_uint2(hit, __float_as_uint(best));
+    trav = false;
+  };
+  auto enter = [&]() {
+    for (;;) {
+      if (bvh_i >= fp.bvh_count) {
+        finish_ray();
+        return;
+      }
+      const BvhRecord* bvh = sc.bvhs + bvh_i;
+      to = mat4_mul_(bvh->frame, ray_o, 1.0f);
+      td = mat4_mul_(bvh->frame, ray_d, 0.0f);
+      inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
+      exact_box = isinf_(inv.x) || isinf_(inv.y) || isinf_(inv.z) || isnan_(inv.x) || isnan_(inv.y) || isnan_(inv.z);
+      best_rank = 0xFFFFFFFFu;
+      bool in_root;
+      float d_root = box_distance(to, inv, bvh->root_min[0], bvh->root_min[1], bvh->root_min[2], bvh->root_max[0],
+                                  bvh->root_max[1], bvh->root_max[2], in_root);
+      if (COUNT) n_nodes++;
+      if ((d_root < best) && !isinf_(d_root)) {
+        cur = bvh->root_ref;
+        sp = 0;
+        tri = tri_end = 0;
+        return;
+      }
+      ++bvh_i;
+    }
+  };
+  auto pop = [&]() {
+    for (;;) {
+      if (sp == 0) {
+        ++bvh_i;
+        enter();
+        return;
+      }
+      --sp;
+      uint2 e = s_stack[sp * stride];
+      if (__uint_as_float(e.y) < best) {
+        cur = e.x;
+        return;
+      }
+    }
+  };
+
+  for (;;) {
+    // ---- refill idle lanes from the wave's queue ------------------------------------------------------------
+    while (!exhausted) {
+      const unsigned idle = __ballot_sync(FULL, !trav);
+      if (idle == 0) break;
+      uint32_t base = 0;
+      const int n_idle = __popc(idle);
+      if (lane == 0) base = atomicAdd(&q->cursor, (unsigned int)n_idle);
+      base = __shfl_sync(FULL, base, 0);
+      if (base + n_idle >= n_total) exhausted = true;
+      if (!trav) {
+        const uint32_t idx = base + __popc(idle & ((1u << lane) - 1u));
+        if (idx < n_total) {
+          slot = __ldg(list + (idx < n_front ? idx : pool.cap - 1u - (idx - n_front)));
+          const float4 a = pool.r0[slot], b = pool.r1[slot];
+          ray_o = v3(a.x, a.y, a.z);
+          ray_d = v3(b.x, b.y, b.z);
+          best = a.w;
+          any_hit = (__float_as_uint(b.w) & 0xFFu) == SRT_WF_KIND_SHADOW;
+          hit = SRT_NO_HIT;
+          bvh_i = 0;
+          trav = true;
+          enter();  // may end the ray at once (root box missed): the lane is idle again and refills next turn
+        }
+      }
+    }
+    if (!__any_sync(FULL, trav)) break;
+
+    // ---- traverse until enough lanes are idle again ----------------------------------------------------------
+    for (;;) {
+      while (__any_sync(FULL, trav && !(cur & SRT_LEAF_BIT))) {
+        const bool exact = __any_sync(FULL, trav && exact_box);
+        if (trav && !(cur & SRT_LEAF_BIT)) {
+          const float4* p = reinterpret_cast<const float4*>(sc.pairs + cur);
+          float4 na = __ldg(p), nb = __ldg(p + 1), nc = __ldg(p + 2);
+          uint4 nd = __ldg(reinterpret_cast<const uint4*>(p + 3));
+          bool in_l, in_r;
+          float dl, dr;
+          if (exact) {
+            dl = box_distance(to, inv, na.x, na.y, na.z, na.w, nb.x, nb.y, in_l);
+            dr = box_distance(to, inv, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, in_r);
+          } else {
+            dl = box_distance_fast(to, inv, na.x, na.y, na.z, na.w, nb.x, nb.y, in_l);
+            dr = box_distance_fast(to, inv, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, in_r);
+          }
+          if (COUNT) n_nodes += 2;
+          bool pl = (dl < best) && !isinf_(dl);
+          bool pr = (dr < best) && !isinf_(dr);
+          if (pl && pr) {
+            bool right_first = (MODE == TRAV_REFERENCE || in_l || in_r) ? true : !(dl < dr);
+            uint32_t second = right_first ? nd.x : nd.y;
+            float d_second = right_first ? dl : dr;
+            s_stack[sp * stride] = make_uint2(second, __float_as_uint(d_second));
+            ++sp;
+            cur = right_first ? nd.y : nd.x;
+          } else if (pl || pr) {
+            cur = pl ? nd.x : nd.y;
+          } else {
+            pop();
+          }
+        }
+      }
+      if (trav && tri >= tri_end) {
+        uint2 leaf = __ldg(sc.leaves + (cur & ~SRT_LEAF_BIT));
+        tri = leaf.x;
+        tri_end = leaf.x + leaf.y;
+      }
+      while (__any_sync(FULL, trav && tri < tri_end)) {
+        if (trav && tri < tri_end) {
+          if (COUNT) n_tris++;
+          if (triangle_test<MODE>(sc.tris, tri, to, td, best, best_rank)) {
+            hit = tri;
+            if (any_hit) finish_ray();  // shadow ray: the first accepted triangle decides
+          }
+          ++tri;
+        }
+      }
+      if (trav) pop();
+      const int n_idle = __popc(__ballot_sync(FULL, !trav));
+      if (n_idle == 32) break;
+      if (!exhausted && n_idle >= SRT_WF_REFILL_THRESHOLD) break;
+    }
+  }
+
+  if (COUNT) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      n_nodes += __shfl_down_sync(FULL, n_nodes, o);
+      n_tris += __shfl_down_sync(FULL, n_tris, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&counters->nodes, (unsigned long long)n_nodes);
+      atomicAdd(&counters->tris, (unsigned long long)n_tris);
+    }
+  }
+}
+
+// ---- logic: everything GetRayColor does between two CheckHit calls (raytrace_compute.glsl:225-292) -----------------
+__global__ void __launch_bounds__(128)
+wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity,
+                uint32_t* __restrict__ primary_ids, DeviceCounters* __restrict__ counters) {
+  const unsigned FULL = 0xFFFFFFFFu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+  WaveCounters* q = pool.q;
+  const uint32_t n_a = q->n_closest[parity], n_b = q->n_shadow[parity];
+  const uint32_t chunks_a = (n_a + 31u) >> 5, chunks_b = (n_b + 31u) >> 5;
+  const uint32_t* __restrict__ list_in = parity ? pool.list[1] : pool.list[0];
+  uint32_t* __restrict__ list_out = parity ? pool.list[0] : pool.list[1];
+  if (blockIdx.x == 0 && threadIdx.x == 0) q->cursor = 0;  // for the next wave's trace kernel
+  const V3 sky = v3(0.05f);
+  unsigned int n_seg = 0, n_shadow = 0, n_capped = 0, n_done = 0;
+
+  for (uint32_t g = warp; g < chunks_a + chunks_b; g += n_warps) {
+    const bool region_a = g < chunks_a;  // warp-uniform: which queue this chunk belongs to
+    const uint32_t idx = (region_a ? g : g - chunks_a) * 32u + lane;
+    const bool valid = idx < (region_a ? n_a : n_b);
+    const uint32_t slot = valid ? __ldg(list_in + (region_a ? idx : pool.cap - 1u - idx)) : 0u;
+    const uint2 path = valid ? pool.path[slot] : make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
+    int x = 0, y = 0;
+    tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
+    const int pix = y * fp.height + x;  // Q4
+
+    V3 origin = v3(0.0f), dir = v3(0.0f), throughput = v3(0.0f), color = v3(0.0f);
+    int depth = 0, rand_index = 0, iter = 0, li = 0;
+    uint32_t hit_prim = SRT_NO_HIT;
+    float light_weight = 0.0f, shadow_mult = 1.0f;
+    bool shade = false, have_light = false, finish = false, emit_closest = false, emit_shadow = false;
+
+    if (valid) {
+      const uint2 h = pool.hit[slot];
+      const float4 a = pool.r0[slot], b = pool.r1[slot], t0 = pool.p0[slot], c1 = pool.p1[slot];
+      origin = v3(a.x, a.y, a.z);
+      throughput = v3(t0.x, t0.y, t0.z);
+      color = v3(c1.x, c1.y, c1.z);
+      const uint32_t packed = __float_as_uint(c1.w);
+      depth = (int)(packed & 0xFFu);
+      rand_index = (int)((packed >> 8) & 0xFFFu);
+      iter = (int)(packed >> 20);
+      if (region_a) {
+        // ---- a closest-hit ray came back (raytrace_compute.glsl:225-236) ----
+        dir = v3(b.x, b.y, b.z);
+        if (primary_ids != nullptr && iter == 0 && path.y == (uint32_t)(fp.n_frames - 1))
+          primary_ids[(size_t)y * fp.width + x] = h.x;
+        if (h.x == SRT_NO_HIT) {
+          finish = true;  // :287-289
+        } else {
+          hit_prim = h.x;
+          origin = (__uint_as_float(h.y) * dir) + origin;  // rec.p (:155)
+          if (sample_lights(sc, fp, pix, origin, light_weight, li)) {
+            const DeviceLight& l = fp.lights[li];
+            const V3 lpos = v3(l.px, l.py, l.pz);
+            const V3 sd = normalize_(lpos - origin);  // :168
+            const float len = length_(lpos - origin);  // :169
+            pool.r0[slot] = make_float4(origin.x, origin.y, origin.z, len);
+            pool.r1[slot] = make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8)));
+            pool.p3[slot] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(hit_prim));
+            pool.p0[slot] = make_float4(throughput.x, throughput.y, throughput.z, light_weight);
+            emit_shadow = true;
+            n_shadow++;
+          } else {
+            shade = true;
+          }
+        }
+      } else {
+        // ---- a shadow ray came back (:235-246): the path still stands at the ray's origin ----
+        const float4 c3 = pool.p3[slot];
+        dir = v3(c3.x, c3.y, c3.z);
+        hit_prim = __float_as_uint(c3.w);
+        li = (int)(__float_as_uint(b.w) >> 8);
+        light_weight = t0.w;
+        shadow_mult = (h.x != SRT_NO_HIT) ? 0.0f : 1.0f;
+        have_light = true;
+        shade = true;
+      }
+    }
+
+    if (shade) {
+      // ---- direct light, lobe choice, roulette, bounce (:238-285) ----
+      const float4* tp = reinterpret_cast<const float4*>(sc.tris + hit_prim);
+      const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
+      const V3 N = normalize_(cross_(v3(r1.x, r1.y, r1.z), v3(r2.x, r2.y, r2.z)));  // ray_intersects.glsl:90
+      const float4* mp = reinterpret_cast<const float4*>(sc.mats + __float_as_uint(r0.w));
+      const float4 ma = __ldg(mp), mb = __ldg(mp + 1);
+      SurfMat mat;
+      mat.albedo = v3(ma.x, ma.y, ma.z);
+      mat.roughness = ma.w;
+      mat.specular = v3(mb.x, mb.y, mb.z);
+      mat.metalness = 0.1f;  // raytrace_utils.glsl:172-173
+      mat.use_spec = true;
+      const V3 p = origin;
+      const V3 V = -dir;
+      if (have_light) {
+        const DeviceLight& l = fp.lights[li];
+        color = color + throughput * sample_direct(p, N, mat, V, l, shadow_mult) * light_weight;  // useSpec
+      }
+      const float prob = brdf_probability(mat, V, N);  // metalness 0.1 != 1: the lobe is always drawn (:249-264)
+      const float fd = (float)depth;
+      const bool specular_lobe = rand_uniform(sc, fp, pix, p.x + fd, p.y + fd) < prob;
+      throughput = throughput / (specular_lobe ? prob : (1.0f - prob));
+      bool alive = true;
+      if (depth <= 0) {
+        const float survival = clamp_(luminance(throughput), 0.1f, 1.0f);
+        const float fr = (float)rand_index;
+        if (rand_uniform(sc, fp, pix, p.x + fr, p.y + fr) > survival) {
+          alive = false;
+        } else {
+          throughput = throughput / survival;
+          rand_index++;
+        }
+      } else {
+        depth--;
+      }
+      V3 new_dir, weight;
+      if (alive && sample_indirect(sc, fp, pix, p, N, V, mat, specular_lobe, new_dir, weight)) {
+        throughput = throughput * weight;
+        if (++iter >= SRT_MAX_PATH_ITERS) {  // decree Q9
+          n_capped++;
+          finish = true;
+        } else {
+          pool.r0[slot] = make_float4(p.x, p.y, p.z, inf_());
+          pool.r1[slot] = make_float4(new_dir.x, new_dir.y, new_dir.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
+          pool.p0[slot] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
+          pool.p1[slot] = make_float4(color.x, color.y, color.z, __uint_as_float(wf_pack(depth, rand_index, iter)));
+          emit_closest = true;
+          n_seg++;
+        }
+      } else {
+        finish = true;
+      }
+    }
+
+    // ---- the path ended: its sample goes to samples[frame][pixel] (:292); the slot takes the launch's next path ----
+    const unsigned m_f = __ballot_sync(FULL, finish);
+    if (m_f) {
+      unsigned long long base = 0;
+      const int leader = __ffs(m_f) - 1;
+      if (lane == leader) base = atomicAdd(&q->next_path, (unsigned long long)__popc(m_f));
+      base = __shfl_sync(FULL, base, leader);
+      if (finish) {
+        color = color + throughput * sky;  // Q19
+        const V3 pixel_color = v3(0.0f) + color;  // main(): pixelColor = vec3(0) + GetRayColor(...)
+        pool.samples[(size_t)path.y * pool.n_pixels + path.x] = make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f);
+        const unsigned long long next = base + (unsigned long long)__popc(m_f & lt_mask);
+        if (next < pool.n_paths) {
+          const uint32_t pixel = (uint32_t)(next % pool.n_pixels), f = (uint32_t)(next / pool.n_pixels);
+          int nx, ny;
+          tile_pixel(fp, pixel >> 5, pixel & 31, nx, ny);
+          const V3 d = wf_primary_dir(sc, fp, nx, ny, ny * fp.height + nx, (int)f);
+          pool.r0[slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
+          pool.r1[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
+          pool.p0[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+          pool.p1[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0)));
+          pool.path[slot] = make_uint2(pixel, f);
+          emit_closest = true;
+          n_seg++;
+        } else {
+          n_done++;
+        }
+      }
+    }
+
+    // ---- next wave's queues: closest-hit rays at the front, shadow rays at the back ----
+    const unsigned m_c = __ballot_sync(FULL, emit_closest);
+    if (m_c) {
+      uint32_t base = 0;
+      const int leader = __ffs(m_c) - 1;
+      if (lane == leader) base = atomicAdd(&q->n_closest[parity ^ 1], (unsigned int)__popc(m_c));
+      base = __shfl_sync(FULL, base, leader);
+      if (emit_closest) list_out[base + __popc(m_c & lt_mask)] = slot;
+    }
+    const unsigned m_s = __ballot_sync(FULL, emit_shadow);
+    if (m_s) {
+      uint32_t base = 0;
+      const int leader = __ffs(m_s) - 1;
+      if (lane == leader) base = atomicAdd(&q->n_shadow[parity ^ 1], (unsigned int)__popc(m_s));
+      base = __shfl_sync(FULL, base, leader);
+      if (emit_shadow) list_out[pool.cap - 1u - (base + __popc(m_s & lt_mask))] = slot;
+    }
+  }
+
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    n_seg += __shfl_down_sync(FULL, n_seg, o);
+    n_shadow += __shfl_down_sync(FULL, n_shadow, o);
+    n_capped += __shfl_down_sync(FULL, n_capped, o);
+    n_done += __shfl_down_sync(FULL, n_done, o);
+  }
+  if (lane == 0) {
+    if (n_seg) atomicAdd(&counters->segments, (unsigned long long)n_seg);
+    if (n_shadow) atomicAdd(&counters->shadow_rays, (unsigned long long)n_shadow);
+    if (n_capped) atomicAdd(&counters->capped_paths, (unsigned long long)n_capped);
+    if (n_done) atomicSub(&q->live_slots, n_done);
+  }
+}
+
+// ---- resolve: main()'s accumulate + tonemap (raytrace_compute.glsl:404-413) once every path of the launch is in --------
+__global__ void __launch_bounds__(128)
+wf_resolve_kernel(const __grid_constant__ FrameParams fp, PathPool pool, float4* __restrict__ accum,
+                  uchar4* __restrict__ out) {
+  const uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pixel >= pool.n_pixels) return;
+  int x, y;
+  tile_pixel(fp, pixel >> 5, pixel & 31, x, y);
+  const size_t texel = (size_t)y * fp.width + x;
+  const float4 prev = accum[texel];
+  V3 acc = v3(prev.x, prev.y, prev.z);
+  const float4* __restrict__ s = pool.samples + pixel;
+  for (int f = 0; f < fp.n_frames; ++f) {  // frame order = the shader's order of additions
+    const float4 c = __ldcs(s + (size_t)f * pool.n_pixels);
+    acc = acc + v3(c.x, c.y, c.z);
+  }
+  accum[texel] = make_float4(acc.x, acc.y, acc.z, 1.0f);
+  const V3 lin = acc / (float)(fp.accum_frames + fp.n_frames - 1);
+  out[texel] = make_uchar4(to_unorm8(linear_to_srgb(lin.x)), to_unorm8(linear_to_srgb(lin.y)),
+                           to_unorm8(linear_to_srgb(lin.z)), 255);
+}
+
+}  // namespace srt

@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 
 
 def gpu_render(pkg, ctx, W, H, show_model, n_frames, traversal, scene=None, lights=None, cam=None, first_frame=1,
-               max_depth=0, noise=None, rows=None, schedule=2):
+               max_depth=0, noise=None, rows=None, schedule=3):
     unit, uniform = noise if noise is not None else scenes.noise_tables(W, H)
     lights = lights if lights is not None else (scenes.model_lights() if show_model else scenes.sphere_lights())
     cam = cam or scenes.reset_camera(show_model)
@@ -101,7 +101,7 @@ def test_spheres_multi_frame_bit_exact(pkg, ctx, oracle, frames):
     assert np.array_equal(out, oout)
 
 
-@pytest.mark.parametrize("schedule", [0, 1, 2])
+@pytest.mark.parametrize("schedule", [0, 1, 2, 3])
 def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     """C2's scene at a size the oracle finishes in seconds; reference visiting order => bit-exact."""
     scene = scenes.rubik_scene()
@@ -114,7 +114,7 @@ def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     assert ocnt["capped_paths"] == 0 and cnt["capped_paths"] == 0
 
 
-@pytest.mark.parametrize("schedule", [0, 1, 2])
+@pytest.mark.parametrize("schedule", [0, 1, 2, 3])
 def test_rubik_ordered_traversal_matches_bar_ties(pkg, ctx, oracle, schedule):
     """Ordered traversal: same image except documented grazing ties (budget: 1e-4 of the pixels; ids identical
     on every pixel outside that budget, radiance bit-exact there too)."""
@@ -124,6 +124,21 @@ def test_rubik_ordered_traversal_matches_bar_ties(pkg, ctx, oracle, schedule):
     bad = (acc.view(np.uint32) != oacc.view(np.uint32)).any(axis=2)
     assert bad.mean() <= 1e-4, "ordered traversal differs on %d pixels" % bad.sum()
     assert (ids != oids).mean() <= 1e-4
+
+
+def test_wavefront_small_pool_and_frame_chunks_bit_exact(pkg, ctx, oracle):
+    """Wavefront schedule with a pool far smaller than the launch (slots regenerate many times) and a sample budget
+    that cuts the launch into several frame chunks: still the oracle's bits."""
+    scene = scenes.rubik_scene()
+    ctx.set_option(pkg.OPT_WAVE_SLOTS, 4096)
+    ctx.set_option(pkg.OPT_SAMPLE_BUDGET_MB, 1)  # 1 MB / 16 B = 65536 entries = 2 frames of 160x96... per chunk
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 256, 128, True, 5, pkg.TRAV_REFERENCE, scene=scene, schedule=3)
+    oacc, oout, oids, ocnt = cpu_render(oracle, 256, 128, True, 5, scene=scene)
+    assert np.array_equal(ids, oids)
+    assert_bit_exact(acc, oacc)
+    assert np.array_equal(out, oout)
+    assert cnt["segments"] == ocnt["segments"] and cnt["shadow_rays"] == ocnt["shadow_rays"]
+    assert cnt["paths"] == 256 * 128 * 5
 
 
 def test_rubik_inside_view_and_depth8(pkg, ctx, oracle):
