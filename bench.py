@@ -29,10 +29,19 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import scenes  # noqa: E402  (deterministic inputs; no reference access at run time)
 
 WORKLOADS = {
-    # name: (show_model, width, height, frames per step, description)
-    "rubik": (True, 1920, 1080, 64,
+    # name: (show_model, width, height, frames per step, maxDepth (0 = the shader's 5), description)
+    "rubik": (True, 1920, 1080, 64, 0,
               "objects/Rubik (1188 tris, reference-built BVH, 6 lights) 1920x1080, 64 spp per step, maxDepth 5"),
-    "spheres": (False, 1920, 1080, 64, "built-in 5-sphere scene, 2 lights, 1920x1080, 64 spp per step"),
+    "spheres": (False, 1920, 1080, 64, 0, "built-in 5-sphere scene, 2 lights, 1920x1080, 64 spp per step"),
+    # BASELINE.json configs[2]; the Airplane .obj is absent from the reference mount, so a documented procedural mesh
+    # with the Airplane .mtl materials stands in (tests/scenes.py:write_airplane_standin) -- never under the Airplane name
+    "airplane-standin": (True, 1920, 1080, 64, 0,
+                         "airplane-standin (procedural airliner mesh, ~110 k tris, the 6 materials of 11803_Airplane_v1_l1.mtl, "
+                         "BVH by the reference algorithm) 1920x1080, 64 spp per step, maxDepth 5"),
+    # BASELINE.json configs[4]
+    "soup": (True, 1920, 1080, 4, 8,
+             "synthetic random triangle soup (PCG32 0xC0FFEE, BVH by the reference algorithm) 1920x1080, 4 spp per step, "
+             "maxDepth 8, camera (0,0,120) looking -z"),
 }
 METRIC = "Mrays/s (path segments) at 1080p 64spp"
 UNIT = "Mrays/s"
@@ -89,13 +98,27 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def workload_inputs(name):
-    show_model, W, H, spp, desc = WORKLOADS[name]
+def workload_inputs(name, soup_tris=10_000_000):
+    import tempfile
+    show_model, W, H, spp, max_depth, desc = WORKLOADS[name]
     unit, uniform = scenes.noise_tables(W, H)
+    cam = scenes.reset_camera(show_model)
+    scene = None
+    if name == "rubik":
+        scene = scenes.rubik_scene()
+    elif name == "airplane-standin":
+        with tempfile.TemporaryDirectory() as d:
+            obj, n_tri = scenes.write_airplane_standin(d, detail=128)
+            scene = scenes.load_obj_scene(d, obj, d)
+        desc = desc.replace("~110 k tris", "%d tris, %d nodes" % (len(scene["triangles"]), len(scene["nodes"])))
+    elif name == "soup":
+        with tempfile.TemporaryDirectory() as d:
+            scene, info = scenes.soup_scene(soup_tris, d)
+        desc = desc.replace("soup (", "soup of %d triangles, %d nodes, depth %d (" % (info["triangles"], info["nodes"], info["depth"]))
+        cam = scenes.reset_camera(True, origin=(0.0, 0.0, 120.0))
     return {"show_model": show_model, "W": W, "H": H, "spp": spp, "desc": desc, "unit": unit, "uniform": uniform,
-            "scene": scenes.rubik_scene() if show_model else None,
-            "lights": scenes.model_lights() if show_model else scenes.sphere_lights(),
-            "cam": scenes.reset_camera(show_model)}
+            "scene": scene, "max_depth": max_depth,
+            "lights": scenes.model_lights() if show_model else scenes.sphere_lights(), "cam": cam}
 
 
 def oracle_run(inp, first_frame, n_frames, threads=0):
@@ -103,7 +126,7 @@ def oracle_run(inp, first_frame, n_frames, threads=0):
     import __graft_entry__ as g
     O = g.load_oracle()
     p = O.make_params(inp["W"], inp["H"], inp["cam"], inp["show_model"], first_frame, len(inp["lights"]),
-                      1 if inp["show_model"] else 0)
+                      1 if inp["show_model"] else 0, inp["max_depth"])
     t0 = time.perf_counter()
     _, _, _, cnt = O.render(p, n_frames, inp["scene"], inp["unit"], inp["uniform"], inp["lights"], want_out=False,
                             want_ids=False, n_threads=threads)
@@ -118,7 +141,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    inp = workload_inputs(args.workload)
+    inp = workload_inputs(args.workload, args.soup_tris)
     cores = os.cpu_count() or 1
     for w in range(args.warmup):
         oracle_run(inp, 1 + w, 1)
@@ -128,7 +151,7 @@ def run_reference(args):
         secs += dt
         segs += cnt["segments"]
     value = segs / secs / 1e6
-    sample = "1 frame (1 spp) of the 64-spp workload per step, whole 1920x1080 image"
+    sample = "1 frame (1 spp) of the %d-spp workload per step, whole 1920x1080 image" % inp["spp"]
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
@@ -158,7 +181,7 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = g.load_package()
-    inp = workload_inputs(args.workload)
+    inp = workload_inputs(args.workload, args.soup_tris)
     W, H, spp, show_model = inp["W"], inp["H"], inp["spp"], inp["show_model"]
     mode = pkg.TRAV_REFERENCE if args.traversal == "reference" else pkg.TRAV_ORDERED
 
@@ -171,6 +194,8 @@ def run_gpu(args):
     ctx.set_option(pkg.OPT_BLOCK_THREADS, args.block)
     if args.wave_slots:
         ctx.set_option(pkg.OPT_WAVE_SLOTS, args.wave_slots)
+    if args.refill:
+        ctx.set_option(pkg.OPT_REFILL, args.refill)
 
     def upload_all():
         if inp["scene"] is not None:
@@ -186,7 +211,8 @@ def run_gpu(args):
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def params(reset):
-        return pkg.make_params(W, H, inp["cam"], show_model, accum_frames=1, bvh_count=1 if show_model else 0, reset=reset)
+        return pkg.make_params(W, H, inp["cam"], show_model, accum_frames=1, bvh_count=1 if show_model else 0, reset=reset,
+                               max_depth=inp["max_depth"])
 
     launches = [0]
 
@@ -351,6 +377,8 @@ def main():
     ap.add_argument("--schedule", default="wavefront", choices=["wavefront", "persistent", "regen", "per-path"])
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the workload the CPU baseline renders")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
+    ap.add_argument("--refill", type=int, default=0, help="refill threshold of the wavefront trace kernel (0 = default)")
     ap.add_argument("--wave-slots", type=int, default=0, help="path slots of the wavefront schedule (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -48,9 +48,11 @@ typedef struct srt_counters {
                                         queues + full-warp shading kernels, queued wave by wave (default for models)
                                     all four give the same bits; only the lane schedule differs */
 
-#define SRT_OPT_WAVE_SLOTS 6      /* wavefront schedule: path slots in flight (default 4 Mi) */
+#define SRT_OPT_WAVE_SLOTS 6      /* wavefront schedule: path slots in flight, 104 B each (default 128 Mi, never more than the launch has paths) */
 #define SRT_OPT_SAMPLE_BUDGET_MB 7 /* wavefront schedule: size limit of the per-path sample buffer; longer launches are cut
                                       into frame chunks (default 4096 MB) */
+
+#define SRT_OPT_REFILL 8          /* wavefront schedule: idle lanes per warp that trigger a queue fetch (1..32, default 12) */
 
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */

@@ -66,7 +66,8 @@ struct srt_ctx {
   unsigned int* h_live = nullptr;  // pinned ring the device reports live_pixels into
   cudaEvent_t wave_events[4] = {nullptr, nullptr, nullptr, nullptr};
   uint64_t waves = 0;
-  uint32_t wave_slots = 4u << 20;              // path slots of the pool (SRT_OPT_WAVE_SLOTS)
+  int refill_threshold = 12;                   // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL)
+  uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
   size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
   size_t sample_budget_bytes = (size_t)4 << 30;  // sample buffer budget per frame chunk (SRT_OPT_SAMPLE_BUDGET_MB)
 
@@ -179,6 +180,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
       if (value < 32 || value > SRT_MAX_BLOCK_THREADS || value % 32) return fail(ctx, "SRT_OPT_BLOCK_THREADS: 32..%d, multiple of 32", SRT_MAX_BLOCK_THREADS);
       ctx->block_threads = value;
       return 0;
+  }
+  if (key == SRT_OPT_REFILL) {
+    if (value < 1 || value > 32) return fail(ctx, "SRT_OPT_REFILL: 1..32");
+    ctx->refill_threshold = value;
+    return 0;
   }
   if (key == SRT_OPT_WAVE_SLOTS) {
     if (value < 1024) return fail(ctx, "SRT_OPT_WAVE_SLOTS: at least 1024");
@@ -587,7 +593,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     int parity = 0;
     for (int batch = 0;; ++batch) {
       for (int w = 0; w < kBatch; ++w) {
-        CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, ctx->traversal, ctx->count_traversal, chunk_ids, ctx->d_counters,
+        CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, ctx->traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
                                ctx->block_threads, ctx->stream));
         parity ^= 1;
       }

@@ -288,7 +288,7 @@ struct WfGrid {
 WfGrid g_wf_grid;  // launch geometry is a property of the device + kernel, computed once per (block, smem)
 
 template <int MODE, bool COUNT>
-cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity,
+cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
                             DeviceCounters* counters, int block, cudaStream_t stream) {
   auto k = wf_trace_kernel<MODE, COUNT>;
   const size_t smem = (size_t)fp.stack_cap * block * sizeof(uint2);
@@ -314,20 +314,20 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
   long need = ((long)pool.cap / 32 + block / 32 - 1) / (block / 32);
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  k<<<(unsigned)grid, block, smem, stream>>>(sc, fp, pool, parity, counters);
+  k<<<(unsigned)grid, block, smem, stream>>>(sc, fp, pool, parity, refill, counters);
   return cudaGetLastError();
 }
 }  // namespace
 
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
-                           bool count, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
+                           bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
   cudaError_t e;
   if (mode == TRAV_REFERENCE)
-    e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, counters, block, stream)
-              : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, counters, block, stream);
+    e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, refill, counters, block, stream)
+              : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, refill, counters, block, stream);
   else
-    e = count ? wf_trace_launch<TRAV_ORDERED, true>(sc, fp, pool, parity, counters, block, stream)
-              : wf_trace_launch<TRAV_ORDERED, false>(sc, fp, pool, parity, counters, block, stream);
+    e = count ? wf_trace_launch<TRAV_ORDERED, true>(sc, fp, pool, parity, refill, counters, block, stream)
+              : wf_trace_launch<TRAV_ORDERED, false>(sc, fp, pool, parity, refill, counters, block, stream);
   if (e != cudaSuccess) return e;
   // logic: a fixed grid of warps strides over the wave's 32-entry chunks
   long warps = (long)pool.cap / 32;

@@ -28,7 +28,6 @@
 
 namespace srt {
 
-#define SRT_WF_REFILL_THRESHOLD 6
 #define SRT_WF_KIND_CLOSEST 0u
 #define SRT_WF_KIND_SHADOW 1u
 
@@ -81,7 +80,7 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
 template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(SRT_MAX_BLOCK_THREADS)
 wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity,
-                DeviceCounters* __restrict__ counters) {
+                int refill_threshold, DeviceCounters* __restrict__ counters) {
   extern __shared__ uint2 s_stack_all[];
   uint2* s_stack = s_stack_all + threadIdx.x;
   const int stride = blockDim.x;
@@ -212,6 +211,8 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           }
         }
       }
+      // leaves: one triangle per lane per iteration, in the leaf's order.  (Popping inside this loop so that a lane
+      // stays here across sibling leaves was tried: same bits, 20 % slower -- the pop/enter code bloats the loop.)
       if (trav && tri >= tri_end) {
         uint2 leaf = __ldg(sc.leaves + (cur & ~SRT_LEAF_BIT));
         tri = leaf.x;
@@ -230,7 +231,7 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       if (trav) pop();
       const int n_idle = __popc(__ballot_sync(FULL, !trav));
       if (n_idle == 32) break;
-      if (!exhausted && n_idle >= SRT_WF_REFILL_THRESHOLD) break;
+      if (!exhausted && n_idle >= refill_threshold) break;
     }
   }
 

@@ -141,6 +141,38 @@ def test_wavefront_small_pool_and_frame_chunks_bit_exact(pkg, ctx, oracle):
     assert cnt["paths"] == 256 * 128 * 5
 
 
+@pytest.mark.parametrize("schedule", [2, 3])
+def test_airplane_standin_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
+    """BASELINE.json configs[2]'s scene is absent from the reference mount; its documented stand-in (6 Airplane
+    materials, leaves of up to ~100 triangles from the reference's midpoint builder) through the host loader."""
+    name, n_tri = scenes.write_airplane_standin(str(tmp_path), detail=40)
+    scene = scenes.load_obj_scene(str(tmp_path), name, str(tmp_path))
+    assert len(scene["triangles"]) == n_tri and len(scene["materials"]) == 6
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 320, 184, True, 3, pkg.TRAV_REFERENCE, scene=scene, schedule=schedule)
+    oacc, oout, oids, ocnt = cpu_render(oracle, 320, 184, True, 3, scene=scene)
+    assert (oids != pkg.NO_HIT).mean() > 0.05
+    assert np.array_equal(ids, oids)
+    assert_bit_exact(acc, oacc)
+    assert np.array_equal(out, oout)
+    assert cnt["segments"] == ocnt["segments"] and cnt["shadow_rays"] == ocnt["shadow_rays"]
+    acc2, _, ids2, _ = gpu_render(pkg, ctx, 320, 184, True, 3, pkg.TRAV_ORDERED, scene=scene, schedule=schedule)
+    bad = (canon(acc2) != canon(oacc)).any(axis=2)
+    assert bad.mean() <= 1e-4 and (ids2 != oids).mean() <= 1e-4  # documented grazing ties only
+
+
+def test_soup_depth8_bit_exact(pkg, ctx, oracle, tmp_path):
+    """BASELINE.json configs[4] at a size the oracle finishes in seconds: random soup, maxDepth 8, camera (0,0,120)."""
+    scene, info = scenes.soup_scene(20000, str(tmp_path))
+    assert info["depth"] <= 63
+    cam = scenes.reset_camera(True, origin=(0.0, 0.0, 120.0))
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 256, 144, True, 2, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8)
+    oacc, oout, oids, ocnt = cpu_render(oracle, 256, 144, True, 2, scene=scene, cam=cam, max_depth=8)
+    assert np.array_equal(ids, oids)
+    assert_bit_exact(acc, oacc)
+    assert cnt["segments"] == ocnt["segments"] and cnt["shadow_rays"] == ocnt["shadow_rays"]
+    assert ocnt["capped_paths"] == 0
+
+
 def test_rubik_inside_view_and_depth8(pkg, ctx, oracle):
     """Camera inside the model's bounds looking around (many bounces), maxDepth 8 as C5 uses."""
     scene = scenes.rubik_scene()
