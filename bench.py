@@ -245,6 +245,10 @@ def run_gpu(args):
     # ---- timed region: K steps, device time by CUDA events on the launching stream, L2 flushed between steps
     ctx.reset_counters()
     launches[0] = 0
+    wavefront = show_model and args.schedule == "wavefront"
+    if wavefront:
+        ctx.set_option(pkg.OPT_TIME_KERNELS, 1)  # CUDA events around every trace / logic launch, on the launching stream
+        ctx.kernel_times()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     evk = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     sampler = ClockSampler(local) if rank == 0 else None
@@ -260,28 +264,37 @@ def run_gpu(args):
     clocks = sampler.stop() if sampler else None
     step_ms = [a.elapsed_time(b) for a, b in ev]
     kern_ms = [a.elapsed_time(b) for a, b in evk]
+    trace_ms = logic_ms = 0.0
+    n_waves = 0
+    if wavefront:
+        trace_ms, logic_ms, n_waves = ctx.kernel_times()
+        ctx.set_option(pkg.OPT_TIME_KERNELS, 0)
     cnt = ctx.counters()
     gpu_launches = cnt["kernel_launches"]  # every kernel this context launched in the timed region (clear, init, waves, resolve, tonemap)
 
-    tot = torch.tensor([sum(step_ms), sum(kern_ms)], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([sum(step_ms), sum(kern_ms), trace_ms, logic_ms, float(n_waves)], dtype=torch.float64, device="cuda")
     work = torch.tensor([cnt["segments"], cnt["shadow_rays"], cnt["paths"], gpu_launches], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tot, op=dist.ReduceOp.MAX)
         dist.all_reduce(work, op=dist.ReduceOp.SUM)
-    total_ms, kernel_ms = [float(v) for v in tot.tolist()]
+    total_ms, kernel_ms, trace_ms, logic_ms, n_waves = [float(v) for v in tot.tolist()]
     segments, shadow, paths, gpu_launches = [int(v) for v in work.tolist()]
     ms_per_step = total_ms / args.steps
     value = segments / (total_ms * 1e-3) / 1e6
 
-    # ---- traversal work per ray (untimed counting pass, 4 frames) for the roofline's algorithmic bytes
+    # ---- traversal work per ray for the roofline's algorithmic bytes: an untimed counting pass (4 frames) in the
+    # SHADER's visiting order (Nn, Nt "as executed by the reference traversal order"); shadow rays stop at
+    # the first accepted triangle here, the shader runs them to the end, so the figure is a lower bound of the shader's
     nodes_per_ray = tris_per_ray = 0.0
     if show_model:
+        ctx.set_option(pkg.OPT_TRAVERSAL, pkg.TRAV_REFERENCE)
         ctx.set_option(pkg.OPT_COUNT_TRAVERSAL, 1)
         ctx.reset_counters()
         ctx.set_params(params(1)); ctx.render(1)
         ctx.set_params(params(0)); ctx.render(4)
         c2 = ctx.counters()
         ctx.set_option(pkg.OPT_COUNT_TRAVERSAL, 0)
+        ctx.set_option(pkg.OPT_TRAVERSAL, mode)
         w2 = torch.tensor([c2["nodes"], c2["tris"], c2["segments"] + c2["shadow_rays"]], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(w2, op=dist.ReduceOp.SUM)
@@ -322,20 +335,33 @@ def run_gpu(args):
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (pathtrace_kernel): algorithmic gather bytes per ray
+    # ---- roofline of the dominant kernel: algorithmic gather bytes per ray over its CUDA-event time
     peaks, which = measured_peaks()
     rays = segments + shadow
     bytes_per_ray = 32.0 * nodes_per_ray + 52.0 * tris_per_ray
-    kernel_s = kernel_ms * 1e-3
-    achieved = rays * bytes_per_ray / kernel_s / 1e9 if kernel_s > 0 else 0.0
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)",
-                "kernel": "pathtrace_kernel", "kernel_ms_per_step": kernel_ms / args.steps,
+    if wavefront:
+        # wf_trace_kernel does ALL box and triangle tests; its launches of one step differ in size (one per wave), so
+        # bytes per launch and duration per launch are both averages over the timed region's launches
+        kname, k_ms, k_launches = "wf_trace_kernel", trace_ms, max(n_waves, 1.0)
+    else:
+        kname, k_ms, k_launches = "pathtrace_persistent_kernel" if args.schedule == "persistent" else "pathtrace_kernel", kernel_ms, float(args.steps * world)
+    achieved = rays * bytes_per_ray / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+    scene_mb = 0.0
+    if inp["scene"] is not None:
+        scene_mb = (32 * len(inp["scene"]["nodes"]) + 48 * len(inp["scene"]["triangles"])) / 1e6
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"] * world, "unit": "GB/s",
+                "frac": achieved / (peaks["hbm_gbs"] * world), "traffic": None,
+                "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs, burst copy figure, x n_gpus)",
+                "kernel": kname, "kernel_launches": k_launches, "kernel_ms_total": k_ms,
+                "bytes_per_launch": rays * bytes_per_ray / k_launches, "ms_per_launch": k_ms / k_launches,
+                "logic_kernel_ms_total": logic_ms,
                 "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
-                "rays_per_step": rays / args.steps,
-                "note": "algorithmic bytes = rays x (32 B x nodes box-tested + 52 B x triangles tested) as the reference "
-                        "traversal executes them; this scene (0.2 MB) and the noise tables (25 MB) stay in L1/L2, so the "
-                        "figure is on-chip gather bandwidth quoted against the HBM copy peak, not DRAM traffic"}
+                "rays_per_step": rays / args.steps, "scene_mb": scene_mb,
+                "note": "algorithmic bytes = rays x (32 B x nodes box-tested + 52 B x triangles tested), counted in the "
+                        "shader's visiting order; duration = sum of CUDA-event times around the kernel's launches on the "
+                        "launching stream (max over ranks; achieved and peak are whole-job). A scene smaller than the "
+                        "126 MB L2 is served from L1/L2, so the figure is then on-chip gather bandwidth quoted against the "
+                        "HBM copy peak (it may exceed 1), not DRAM traffic; see profiles/ for dram__bytes"}
 
     cpu_baseline = None
     if world == 1 and not args.no_cpu:

@@ -54,6 +54,9 @@ typedef struct srt_counters {
 
 #define SRT_OPT_REFILL 8          /* wavefront schedule: idle lanes per warp that trigger a queue fetch (1..32, default 12) */
 
+#define SRT_OPT_TIME_KERNELS 9    /* wavefront schedule: 1 = bracket every trace / logic launch with CUDA events on the launching
+                                     stream (read with srt_get_kernel_times) */
+
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */
 int srt_create(srt_ctx** out, int device);
@@ -132,6 +135,9 @@ int srt_trace_rays(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, uint32_t 
                    float* hit_t);
 
 int srt_get_counters(srt_ctx* ctx, srt_counters* out);
+/* Sums of the CUDA-event durations of the wavefront schedule's trace and logic launches since the last call
+ * (needs SRT_OPT_TIME_KERNELS = 1); waves = launches of each kind.  Synchronises the stream. */
+int srt_get_kernel_times(srt_ctx* ctx, double* trace_ms, double* logic_ms, uint64_t* waves);
 int srt_reset_counters(srt_ctx* ctx);
 
 /* Device-side evaluation of the numeric decree (srt_detmath.h), for bit-for-bit checks against the host:

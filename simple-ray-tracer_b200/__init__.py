@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsrt_b200.so")
 
 OPT_TRAVERSAL, OPT_COUNT_TRAVERSAL, OPT_L2_PERSIST, OPT_BLOCK_THREADS, OPT_SCHEDULE = 1, 2, 3, 4, 5
-OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL = 6, 7, 8
+OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS = 6, 7, 8, 9
 SCHED_PER_PATH, SCHED_REGEN, SCHED_PERSISTENT, SCHED_WAVEFRONT = 0, 1, 2, 3
 TRAV_REFERENCE, TRAV_ORDERED = 0, 1
 NO_HIT = 0xFFFFFFFF
@@ -33,7 +33,7 @@ EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
            "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays",
-           "srt_get_counters", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
+           "srt_get_counters", "srt_get_kernel_times", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
 
 
 class Params(C.Structure):  # srt_params, include/srt_types.h
@@ -203,6 +203,12 @@ class Context:
         c = Counters()
         self._ck(self._lib.srt_get_counters(self._h, C.byref(c)))
         return {k: int(getattr(c, k)) for k, _ in Counters._fields_}
+
+    def kernel_times(self):
+        """(trace_ms, logic_ms, waves) of the wavefront launches since the last call (OPT_TIME_KERNELS must be on)."""
+        t, l, w = C.c_double(), C.c_double(), C.c_uint64()
+        self._ck(self._lib.srt_get_kernel_times(self._h, C.byref(t), C.byref(l), C.byref(w)))
+        return t.value, l.value, w.value
 
     def reset_counters(self):
         self._ck(self._lib.srt_reset_counters(self._h))

@@ -66,6 +66,10 @@ struct srt_ctx {
   unsigned int* h_live = nullptr;  // pinned ring the device reports live_pixels into
   cudaEvent_t wave_events[4] = {nullptr, nullptr, nullptr, nullptr};
   uint64_t waves = 0;
+  // optional per-kernel timing of the wavefront schedule (SRT_OPT_TIME_KERNELS): three events per wave
+  bool time_kernels = false;
+  std::vector<cudaEvent_t> timing_events;
+  size_t timing_used = 0;
   int refill_threshold = 12;                   // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL)
   uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
   size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
@@ -152,6 +156,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   dfree(ctx->d_noise_xy); dfree(ctx->d_noise_x); dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
   dfree(ctx->d_counters);
   free_pool(ctx);
+  for (cudaEvent_t e : ctx->timing_events) cudaEventDestroy(e);
   if (ctx->h_live) cudaFreeHost(ctx->h_live);
   for (cudaEvent_t& e : ctx->wave_events)
     if (e) cudaEventDestroy(e);
@@ -180,6 +185,10 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
       if (value < 32 || value > SRT_MAX_BLOCK_THREADS || value % 32) return fail(ctx, "SRT_OPT_BLOCK_THREADS: 32..%d, multiple of 32", SRT_MAX_BLOCK_THREADS);
       ctx->block_threads = value;
       return 0;
+  }
+  if (key == SRT_OPT_TIME_KERNELS) {
+    ctx->time_kernels = value != 0;
+    return 0;
   }
   if (key == SRT_OPT_REFILL) {
     if (value < 1 || value > 32) return fail(ctx, "SRT_OPT_REFILL: 1..32");
@@ -593,8 +602,20 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     int parity = 0;
     for (int batch = 0;; ++batch) {
       for (int w = 0; w < kBatch; ++w) {
+        cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+        if (ctx->time_kernels) {
+          while (ctx->timing_events.size() < ctx->timing_used + 3) {
+            cudaEvent_t e;
+            CU(ctx, cudaEventCreate(&e));
+            ctx->timing_events.push_back(e);
+          }
+          for (int k = 0; k < 3; ++k) ev[k] = ctx->timing_events[ctx->timing_used + k];
+          ctx->timing_used += 3;
+          CU(ctx, cudaEventRecord(ev[0], ctx->stream));
+        }
         CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, ctx->traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
-                               ctx->block_threads, ctx->stream));
+                               ctx->block_threads, ctx->stream, ev[1]));
+        if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], ctx->stream));
         parity ^= 1;
       }
       ctx->kernel_launches += 2 * kBatch;
@@ -748,6 +769,25 @@ extern "C" int srt_get_counters(srt_ctx* ctx, srt_counters* out) {
   out->segments = h.segments; out->shadow_rays = h.shadow_rays; out->paths = h.paths;
   out->capped_paths = h.capped_paths; out->kernel_launches = ctx->kernel_launches;
   out->nodes = h.nodes; out->tris = h.tris;
+  return 0;
+}
+
+extern "C" int srt_get_kernel_times(srt_ctx* ctx, double* trace_ms, double* logic_ms, uint64_t* waves) {
+  if (!ctx) return 1;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  double t = 0.0, l = 0.0;
+  for (size_t i = 0; i + 2 < ctx->timing_used + 0 && i + 2 < ctx->timing_events.size() + 0; i += 3) {
+    float a = 0.0f, b = 0.0f;
+    CU(ctx, cudaEventElapsedTime(&a, ctx->timing_events[i], ctx->timing_events[i + 1]));
+    CU(ctx, cudaEventElapsedTime(&b, ctx->timing_events[i + 1], ctx->timing_events[i + 2]));
+    t += a;
+    l += b;
+  }
+  if (trace_ms) *trace_ms = t;
+  if (logic_ms) *logic_ms = l;
+  if (waves) *waves = ctx->timing_used / 3;
+  ctx->timing_used = 0;
   return 0;
 }
 

@@ -320,7 +320,8 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
 }  // namespace
 
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
-                           bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream) {
+                           bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
+                           cudaEvent_t after_trace) {
   cudaError_t e;
   if (mode == TRAV_REFERENCE)
     e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, refill, counters, block, stream)
@@ -329,6 +330,7 @@ cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const P
     e = count ? wf_trace_launch<TRAV_ORDERED, true>(sc, fp, pool, parity, refill, counters, block, stream)
               : wf_trace_launch<TRAV_ORDERED, false>(sc, fp, pool, parity, refill, counters, block, stream);
   if (e != cudaSuccess) return e;
+  if (after_trace != nullptr && (e = cudaEventRecord(after_trace, stream)) != cudaSuccess) return e;
   // logic: a fixed grid of warps strides over the wave's 32-entry chunks
   long warps = (long)pool.cap / 32;
   long blocks = (warps + 3) / 4;

@@ -16,7 +16,8 @@ cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool 
 cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool,
                            DeviceCounters* counters, cudaStream_t stream);
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
-                           bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream);
+                           bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
+                           cudaEvent_t after_trace = nullptr);
 cudaError_t launch_wf_resolve(const FrameParams& fp, const PathPool& pool, float4* accum, uchar4* out,
                               cudaStream_t stream);
 cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream);

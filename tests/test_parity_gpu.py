@@ -196,6 +196,33 @@ def test_row_bands_equal_whole_image(pkg, ctx, oracle):
     assert np.array_equal(both.view(np.uint32), whole.view(np.uint32))
 
 
+@pytest.mark.parametrize("world", [2, 3])
+def test_interleaved_stripes_sum_to_whole_image(pkg, ctx, oracle, world):
+    """The multi-GPU split on one device: every rank's context renders its interleaved 8-row bands (srt_set_stripe),
+    rows it does not own stay +0.0, and the SUM of the ranks' accumulation images (what the NCCL reduce computes)
+    has the bits of the whole-image render and of the oracle."""
+    scene = scenes.rubik_scene()
+    W, H, frames = 320, 200, 3
+    whole, _, _, cnt = gpu_render(pkg, ctx, W, H, True, frames, pkg.TRAV_REFERENCE, scene=scene)
+    total = np.zeros_like(whole)
+    segs = 0
+    for rank in range(world):
+        c = pkg.Context(0)
+        try:
+            c.set_stripe(rank, world)
+            part, _, _, pc = gpu_render(pkg, c, W, H, True, frames, pkg.TRAV_REFERENCE, scene=scene)
+        finally:
+            c.close()
+        own = np.array([(y // 8) % world == rank for y in range(H)])
+        assert not part[~own][..., :3].any()  # untouched rows are exactly zero
+        total = total + part
+        segs += pc["segments"]
+    assert np.array_equal(canon(total[..., :3]), canon(whole[..., :3]))
+    assert segs == cnt["segments"]
+    oacc, _, _, _ = cpu_render(oracle, W, H, True, frames, scene=scene)
+    assert np.array_equal(canon(total[..., :3]), canon(oacc[..., :3]))
+
+
 def test_trace_rays_reference_fixture_shape(pkg, ctx, oracle):
     """The reference's (disabled, stale) 64-ray test re-cast with oracle-derived expectations
     (include/compute/tests/BVH_intergration_tests.cpp:69-113)."""
