@@ -105,7 +105,7 @@ static void dfree(T*& p) {
 
 static void free_pool(srt_ctx* ctx) {
   PathPool& p = ctx->pool;
-  dfree(p.r0); dfree(p.r1); dfree(p.hit); dfree(p.p0); dfree(p.p1); dfree(p.path); dfree(p.p3);
+  dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.path); dfree(p.p3);
   dfree(p.list[0]); dfree(p.list[1]); dfree(p.q); dfree(p.samples);
   p.cap = 0;
   ctx->pool_slots = 0;
@@ -547,9 +547,8 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries) {
     p.samples = nullptr;
     free_pool(ctx);
     p.samples = keep;
-    CU(ctx, cudaMalloc(&p.r0, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.r1, (size_t)slots * 16));
-    CU(ctx, cudaMalloc(&p.hit, (size_t)slots * 8)); CU(ctx, cudaMalloc(&p.p0, (size_t)slots * 16));
-    CU(ctx, cudaMalloc(&p.p1, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.path, (size_t)slots * 8));
+    CU(ctx, cudaMalloc(&p.ray, (size_t)slots * 32)); CU(ctx, cudaMalloc(&p.hit, (size_t)slots * 8));
+    CU(ctx, cudaMalloc(&p.pst, (size_t)slots * 32)); CU(ctx, cudaMalloc(&p.path, (size_t)slots * 8));
     CU(ctx, cudaMalloc(&p.p3, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.list[0], (size_t)slots * 4));
     CU(ctx, cudaMalloc(&p.list[1], (size_t)slots * 4)); CU(ctx, cudaMalloc(&p.q, sizeof(WaveCounters)));
     ctx->pool_slots = slots;

@@ -115,11 +115,12 @@ struct WaveCounters {
 // Per-slot records (SoA, 16 B each unless noted).  A slot carries ONE path at a time; when the path ends the slot
 // takes the next path of the launch from WaveCounters::next_path.
 struct PathPool {
-  float4* r0;    // ray origin.xyz, tmax (initial intersection_distance)
-  float4* r1;    // ray direction.xyz, bits: kind | light index << 8
+  // records that are always read together share one 32 B sector (slots are gathered through the queues)
+  float4* ray;   // [2*slot]   ray origin.xyz, tmax (initial intersection_distance)
+                 // [2*slot+1] ray direction.xyz, bits: kind | light index << 8
   uint2* hit;    // result: primitive (or SRT_NO_HIT), distance bits
-  float4* p0;    // throughput.xyz, light weight of the pending shadow ray
-  float4* p1;    // colour.xyz, bits: depth | rand_index << 8 | iter << 20
+  float4* pst;   // [2*slot]   throughput.xyz, light weight of the pending shadow ray
+                 // [2*slot+1] colour.xyz, bits: depth | rand_index << 8 | iter << 20
   uint2* path;   // (pixel slot, frame of the launch) of the path in this slot  (8 B)
   float4* p3;    // while a shadow ray is out: incoming direction.xyz, bits: primitive the path stands on
   uint32_t* list[2];

@@ -332,12 +332,13 @@ cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const P
   if (e != cudaSuccess) return e;
   if (after_trace != nullptr && (e = cudaEventRecord(after_trace, stream)) != cudaSuccess) return e;
   // logic: a fixed grid of warps strides over the wave's 32-entry chunks
+  const long warps_per_block = SRT_WF_LOGIC_THREADS / 32;
   long warps = (long)pool.cap / 32;
-  long blocks = (warps + 3) / 4;
-  long max_blocks = (long)(g_wf_grid.sms > 0 ? g_wf_grid.sms : 148) * 8;
+  long blocks = (warps + warps_per_block - 1) / warps_per_block;
+  long max_blocks = (long)(g_wf_grid.sms > 0 ? g_wf_grid.sms : 148) * SRT_WF_LOGIC_BLOCKS_PER_SM * 2;
   if (blocks > max_blocks) blocks = max_blocks;
   if (blocks < 1) blocks = 1;
-  wf_logic_kernel<<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool, parity, ids, counters);
+  wf_logic_kernel<<<(unsigned)blocks, SRT_WF_LOGIC_THREADS, 0, stream>>>(sc, fp, pool, parity, ids, counters);
   return cudaGetLastError();
 }
 

@@ -28,6 +28,8 @@
 
 namespace srt {
 
+#define SRT_WF_LOGIC_THREADS 256
+#define SRT_WF_LOGIC_BLOCKS_PER_SM 4  // 64 registers per thread: the kernel waits on gathers, occupancy hides them
 #define SRT_WF_KIND_CLOSEST 0u
 #define SRT_WF_KIND_SHADOW 1u
 
@@ -68,10 +70,10 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   tile_pixel(fp, pixel >> 5, pixel & 31, x, y);
   const int pix = y * fp.height + x;  // Q4
   V3 d = wf_primary_dir(sc, fp, x, y, pix, (int)f);
-  pool.r0[slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
-  pool.r1[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
-  pool.p0[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-  pool.p1[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0)));
+  pool.ray[2 * (size_t)slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
+  pool.ray[2 * (size_t)slot + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
+  pool.pst[2 * (size_t)slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+  pool.pst[2 * (size_t)slot + 1] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0)));
   pool.path[slot] = make_uint2(pixel, f);
   pool.list[0][slot] = slot;
 }
@@ -103,6 +105,10 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   uint32_t hit = SRT_NO_HIT, best_rank = 0xFFFFFFFFu, cur = 0, bvh_i = 0, tri = 0, tri_end = 0;
   int sp = 0;
   bool exhausted = false;  // warp-uniform: the queue has no more rays
+  const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
+  int lane_cap = (int)((n_total + total_warps - 1) / total_warps);  // rays a warp holds at a time
+  lane_cap = lane_cap < 4 ? 4 : (lane_cap > 32 ? 32 : lane_cap);
+  const int refill_at = refill_threshold < (lane_cap + 1) / 2 ? refill_threshold : (lane_cap + 1) / 2;
 
   auto finish_ray = [&]() {  // the lane's ray is done: hand the result to the slot
     pool.hit[slot] = make_uint2(hit, __float_as_uint(best));
@@ -151,19 +157,22 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
 
   for (;;) {
     // ---- refill idle lanes from the wave's queue ------------------------------------------------------------
+    // (a small wave is spread over all warps: at most lane_cap rays per warp, so its duration is the lockstep time
+    // of a few rays instead of 32)
     while (!exhausted) {
       const unsigned idle = __ballot_sync(FULL, !trav);
-      if (idle == 0) break;
+      const int n_want = lane_cap - (32 - __popc(idle));
+      if (n_want <= 0) break;
       uint32_t base = 0;
-      const int n_idle = __popc(idle);
-      if (lane == 0) base = atomicAdd(&q->cursor, (unsigned int)n_idle);
+      if (lane == 0) base = atomicAdd(&q->cursor, (unsigned int)n_want);
       base = __shfl_sync(FULL, base, 0);
-      if (base + n_idle >= n_total) exhausted = true;
-      if (!trav) {
-        const uint32_t idx = base + __popc(idle & ((1u << lane) - 1u));
+      if (base + n_want >= n_total) exhausted = true;
+      const int my_rank = __popc(idle & ((1u << lane) - 1u));
+      if (!trav && my_rank < n_want) {
+        const uint32_t idx = base + my_rank;
         if (idx < n_total) {
           slot = __ldg(list + (idx < n_front ? idx : pool.cap - 1u - (idx - n_front)));
-          const float4 a = pool.r0[slot], b = pool.r1[slot];
+          const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1];
           ray_o = v3(a.x, a.y, a.z);
           ray_d = v3(b.x, b.y, b.z);
           best = a.w;
@@ -231,7 +240,7 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       if (trav) pop();
       const int n_idle = __popc(__ballot_sync(FULL, !trav));
       if (n_idle == 32) break;
-      if (!exhausted && n_idle >= refill_threshold) break;
+      if (!exhausted && n_idle - (32 - lane_cap) >= refill_at) break;
     }
   }
 
@@ -249,7 +258,7 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
 }
 
 // ---- logic: everything GetRayColor does between two CheckHit calls (raytrace_compute.glsl:225-292) -----------------
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(SRT_WF_LOGIC_THREADS, SRT_WF_LOGIC_BLOCKS_PER_SM)
 wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity,
                 uint32_t* __restrict__ primary_ids, DeviceCounters* __restrict__ counters) {
   const unsigned FULL = 0xFFFFFFFFu;
@@ -284,7 +293,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
 
     if (valid) {
       const uint2 h = pool.hit[slot];
-      const float4 a = pool.r0[slot], b = pool.r1[slot], t0 = pool.p0[slot], c1 = pool.p1[slot];
+      const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1], t0 = pool.pst[2 * (size_t)slot], c1 = pool.pst[2 * (size_t)slot + 1];
       origin = v3(a.x, a.y, a.z);
       throughput = v3(t0.x, t0.y, t0.z);
       color = v3(c1.x, c1.y, c1.z);
@@ -307,10 +316,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
             const V3 lpos = v3(l.px, l.py, l.pz);
             const V3 sd = normalize_(lpos - origin);  // :168
             const float len = length_(lpos - origin);  // :169
-            pool.r0[slot] = make_float4(origin.x, origin.y, origin.z, len);
-            pool.r1[slot] = make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8)));
+            pool.ray[2 * (size_t)slot] = make_float4(origin.x, origin.y, origin.z, len);
+            pool.ray[2 * (size_t)slot + 1] = make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8)));
             pool.p3[slot] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(hit_prim));
-            pool.p0[slot] = make_float4(throughput.x, throughput.y, throughput.z, light_weight);
+            pool.pst[2 * (size_t)slot] = make_float4(throughput.x, throughput.y, throughput.z, light_weight);
             emit_shadow = true;
             n_shadow++;
           } else {
@@ -373,10 +382,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           n_capped++;
           finish = true;
         } else {
-          pool.r0[slot] = make_float4(p.x, p.y, p.z, inf_());
-          pool.r1[slot] = make_float4(new_dir.x, new_dir.y, new_dir.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
-          pool.p0[slot] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
-          pool.p1[slot] = make_float4(color.x, color.y, color.z, __uint_as_float(wf_pack(depth, rand_index, iter)));
+          pool.ray[2 * (size_t)slot] = make_float4(p.x, p.y, p.z, inf_());
+          pool.ray[2 * (size_t)slot + 1] = make_float4(new_dir.x, new_dir.y, new_dir.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
+          pool.pst[2 * (size_t)slot] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
+          pool.pst[2 * (size_t)slot + 1] = make_float4(color.x, color.y, color.z, __uint_as_float(wf_pack(depth, rand_index, iter)));
           emit_closest = true;
           n_seg++;
         }
@@ -402,10 +411,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           int nx, ny;
           tile_pixel(fp, pixel >> 5, pixel & 31, nx, ny);
           const V3 d = wf_primary_dir(sc, fp, nx, ny, ny * fp.height + nx, (int)f);
-          pool.r0[slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
-          pool.r1[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
-          pool.p0[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-          pool.p1[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0)));
+          pool.ray[2 * (size_t)slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
+          pool.ray[2 * (size_t)slot + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
+          pool.pst[2 * (size_t)slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+          pool.pst[2 * (size_t)slot + 1] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0)));
           pool.path[slot] = make_uint2(pixel, f);
           emit_closest = true;
           n_seg++;
