@@ -194,6 +194,8 @@ def run_gpu(args):
     ctx.set_option(pkg.OPT_BLOCK_THREADS, args.block)
     if args.wave_slots:
         ctx.set_option(pkg.OPT_WAVE_SLOTS, args.wave_slots)
+    if args.l2_persist >= 0:
+        ctx.set_option(pkg.OPT_L2_PERSIST, args.l2_persist)
     if args.refill:
         ctx.set_option(pkg.OPT_REFILL, args.refill)
 
@@ -308,12 +310,18 @@ def run_gpu(args):
     ctx.reset_counters()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
+        ta = time.perf_counter()
         upload_all()
+        tb = time.perf_counter()
         step()
+        tc = time.perf_counter()
         if rank == 0:
             ctx.read_output(out_host)
         else:
             ctx.sync()
+        if os.environ.get("SRT_BENCH_DEBUG"):
+            print("e2e iteration: upload %.1f ms, queue %.1f ms, finish+read %.1f ms" % (
+                (tb - ta) * 1e3, (tc - tb) * 1e3, (time.perf_counter() - tc) * 1e3), file=sys.stderr)
     barrier()
     e2e_s = time.perf_counter() - t0
     ce = ctx.counters()
@@ -404,6 +412,7 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the workload the CPU baseline renders")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
+    ap.add_argument("--l2-persist", type=int, default=-1, help="1/0: pin the BVH top levels in L2 (default: library default, on)")
     ap.add_argument("--refill", type=int, default=0, help="refill threshold of the wavefront trace kernel (0 = default)")
     ap.add_argument("--wave-slots", type=int, default=0, help="path slots of the wavefront schedule (0 = library default)")
     args = ap.parse_args()

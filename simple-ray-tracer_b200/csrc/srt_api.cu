@@ -7,7 +7,9 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "srt_b200.h"
@@ -27,6 +29,9 @@ struct srt_ctx {
   uint32_t n_nodes = 0, n_tris = 0, n_mats = 0;
   int tree_depth = 0;
   bool have_scene = false;
+  size_t top_pair_bytes = 0;             // breadth-first prefix of d_pairs (top BVH levels)
+  cudaStream_t l2_window_stream = nullptr;  // stream the access-policy window is currently set on
+  bool l2_window_on = false;
 
   // device scene
   NodePair* d_pairs = nullptr;
@@ -37,6 +42,8 @@ struct srt_ctx {
   float2* d_noise_xy = nullptr;
   float* d_noise_x = nullptr;
   uint32_t noise_count = 0;
+  char* noise_stage = nullptr;  // pinned staging buffer of the packed noise tables
+  size_t noise_stage_bytes = 0;
 
   // images
   int width = 0, height = 0;
@@ -158,6 +165,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   free_pool(ctx);
   for (cudaEvent_t e : ctx->timing_events) cudaEventDestroy(e);
   if (ctx->h_live) cudaFreeHost(ctx->h_live);
+  if (ctx->noise_stage) cudaFreeHost(ctx->noise_stage);
   for (cudaEvent_t& e : ctx->wave_events)
     if (e) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -216,7 +224,12 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
 // ---- scene upload: reference layouts -> device layouts ----------------------------------------
 namespace {
 
+// Inner nodes of the first SRT_TOP_LEVELS levels are laid out breadth-first at the front of the NodePair array (every
+// ray walks them; that prefix is what the L2 access-policy window pins), deeper subtrees depth-first behind it.
+#define SRT_TOP_LEVELS 14
+
 struct Relayout {
+  size_t top_pairs = 0;  // NodePair records of the breadth-first prefix (all BVHs)
   std::vector<NodePair> pairs;
   std::vector<uint2> leaves;
   std::vector<BvhRecord> bvhs;
@@ -241,11 +254,11 @@ bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_
     memcpy(rec.root_min, nodes[root].min_bounds, 12);
     memcpy(rec.root_max, nodes[root].max_bounds, 12);
     // refs[] collects (slot -> ref); slot 0xFFFFFFFF = the root reference of this BVH
-    std::vector<Item> stack;
-    stack.push_back({root, 0xFFFFFFFFu, 0});
-    while (!stack.empty()) {
-      Item it = stack.back();
-      stack.pop_back();
+    std::vector<Item> fifo, stack;  // fifo: breadth-first over the top levels; stack: depth-first below them
+    fifo.push_back({root, 0xFFFFFFFFu, 0});
+    size_t fifo_head = 0;
+    std::vector<Item> deep_roots;
+    auto visit = [&](const Item& it, bool breadth_first) -> bool {
       if (seen[it.node] == b + 1) return fail(ctx, "bvh %u: node %u reached twice (not a tree)", b, it.node), false;
       seen[it.node] = b + 1;
       if (it.depth > out.depth) out.depth = it.depth;
@@ -268,13 +281,38 @@ bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_
         p.c = make_float4(r.min_bounds[2], r.max_bounds[0], r.max_bounds[1], r.max_bounds[2]);
         p.d = make_uint4(0, 0, 0, 0);
         out.pairs.push_back(p);
-        // left subtree first so that records of a subtree are contiguous
-        stack.push_back({c + 1, ref * 2 + 1, it.depth + 1});
-        stack.push_back({c, ref * 2 + 0, it.depth + 1});
+        const Item left = {c, ref * 2 + 0, it.depth + 1}, right = {c + 1, ref * 2 + 1, it.depth + 1};
+        if (breadth_first) {
+          if (it.depth + 1 < SRT_TOP_LEVELS) {
+            fifo.push_back(left);
+            fifo.push_back(right);
+          } else {
+            deep_roots.push_back(left);
+            deep_roots.push_back(right);
+          }
+        } else {
+          // left subtree first so that records of a subtree are contiguous
+          stack.push_back(right);
+          stack.push_back(left);
+        }
       }
       if (it.slot == 0xFFFFFFFFu) rec.root_ref = ref;
       else if (it.slot & 1) out.pairs[it.slot >> 1].d.y = ref;
       else out.pairs[it.slot >> 1].d.x = ref;
+      return true;
+    };
+    while (fifo_head < fifo.size()) {
+      const Item it = fifo[fifo_head++];
+      if (!visit(it, true)) return false;
+    }
+    if (b == 0) out.top_pairs = out.pairs.size();  // the window pins the first BVH's top levels
+    for (const Item& r0 : deep_roots) {
+      stack.push_back(r0);
+      while (!stack.empty()) {
+        const Item it = stack.back();
+        stack.pop_back();
+        if (!visit(it, false)) return false;
+      }
     }
     // rank = order in which the shader's traversal (right child popped first) meets the triangles
     std::vector<uint32_t> order;
@@ -353,6 +391,8 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   ctx->n_tris = n_triangles;
   ctx->n_mats = n_materials;
   ctx->tree_depth = rl.depth;
+  ctx->top_pair_bytes = rl.top_pairs * sizeof(NodePair);
+  ctx->l2_window_stream = nullptr;  // re-apply the access-policy window on the next launch
   ctx->have_scene = true;
   return 0;
 }
@@ -373,18 +413,49 @@ extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const floa
   if (!ctx) return 1;
   if (!unit_vec3 || !uniform_vec3 || count == 0) return fail(ctx, "srt_upload_noise: NULL table or count 0");
   CU(ctx, cudaSetDevice(ctx->device));
-  // the shader reads noiseTex.xy (raytrace_utils.glsl:15) and noiseUniformTex.x (:52) only: keep those, packed
-  std::vector<float2> xy(count);
-  std::vector<float> x(count);
-  for (uint32_t i = 0; i < count; ++i) {
-    xy[i] = make_float2(unit_vec3[3 * (size_t)i], unit_vec3[3 * (size_t)i + 1]);
-    x[i] = uniform_vec3[3 * (size_t)i];
+  // the shader reads noiseTex.xy (raytrace_utils.glsl:15) and noiseUniformTex.x (:52) only: keep those, packed.
+  // Packing goes straight into a pinned staging buffer (kept between calls) on a few host threads.
+  const size_t bytes = (size_t)count * 12;
+  if (ctx->noise_stage_bytes < bytes) {
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->noise_stage) cudaFreeHost(ctx->noise_stage);
+    ctx->noise_stage = nullptr;
+    ctx->noise_stage_bytes = 0;
+    CU(ctx, cudaHostAlloc(&ctx->noise_stage, bytes, cudaHostAllocDefault));
+    ctx->noise_stage_bytes = bytes;
   }
-  CU(ctx, cudaStreamSynchronize(ctx->stream));
-  if (upload_vec(ctx, ctx->d_noise_xy, xy) || upload_vec(ctx, ctx->d_noise_x, x)) return 1;
-  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  if (ctx->noise_count != count || !ctx->d_noise_xy) {
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    dfree(ctx->d_noise_xy);
+    dfree(ctx->d_noise_x);
+    CU(ctx, cudaMalloc(&ctx->d_noise_xy, (size_t)count * sizeof(float2)));
+    CU(ctx, cudaMalloc(&ctx->d_noise_x, (size_t)count * sizeof(float)));
+  }
+  CU(ctx, cudaStreamSynchronize(ctx->stream));  // the previous upload has left the staging buffer
+  float2* xy = reinterpret_cast<float2*>(ctx->noise_stage);
+  float* x = reinterpret_cast<float*>(ctx->noise_stage + (size_t)count * sizeof(float2));
+  auto pack = [=](uint32_t b, uint32_t e) {
+    for (uint32_t i = b; i < e; ++i) {
+      xy[i] = make_float2(unit_vec3[3 * (size_t)i], unit_vec3[3 * (size_t)i + 1]);
+      x[i] = uniform_vec3[3 * (size_t)i];
+    }
+  };
+  unsigned n_threads = count >= (1u << 18) ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+  if (n_threads <= 1) {
+    pack(0, count);
+  } else {
+    std::vector<std::thread> pool;
+    const uint32_t per = (count + n_threads - 1) / n_threads;
+    for (unsigned t = 0; t < n_threads; ++t) {
+      const uint32_t b = std::min(count, t * per), e = std::min(count, (t + 1) * per);
+      if (b < e) pool.emplace_back(pack, b, e);
+    }
+    for (auto& t : pool) t.join();
+  }
+  CU(ctx, cudaMemcpyAsync(ctx->d_noise_xy, xy, (size_t)count * sizeof(float2), cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(ctx->d_noise_x, x, (size_t)count * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
   ctx->noise_count = count;
-  return 0;
+  return 0;  // the copies are ordered before any later launch on the context's stream
 }
 
 extern "C" int srt_set_lights(srt_ctx* ctx, const srt_light* lights, int32_t count) {
@@ -566,6 +637,37 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries) {
   return 0;
 }
 
+// SRT_OPT_L2_PERSIST: the top levels of the BVH (every ray walks them) are pinned in L2 with an access-policy window on
+// the launching stream; the rest of the scene streams through the remaining L2.  Matters when the scene is far larger
+// than the 126 MB L2 (the 10 M-triangle soup); a scene that fits L2 entirely is resident anyway.
+int apply_l2_window(srt_ctx* ctx) {
+  const bool want = ctx->l2_persist && ctx->have_scene && ctx->top_pair_bytes > 0;
+  if (want == ctx->l2_window_on && (!want || ctx->l2_window_stream == ctx->stream)) return 0;
+  cudaDeviceProp prop;
+  CU(ctx, cudaGetDeviceProperties(&prop, ctx->device));
+  if (prop.accessPolicyMaxWindowSize <= 0 || prop.persistingL2CacheMaxSize <= 0) return 0;
+  cudaStreamAttrValue attr;
+  memset(&attr, 0, sizeof attr);
+  if (want) {
+    size_t bytes = std::min(ctx->top_pair_bytes, (size_t)prop.accessPolicyMaxWindowSize);
+    bytes = std::min(bytes, (size_t)prop.persistingL2CacheMaxSize);
+    CU(ctx, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes));
+    attr.accessPolicyWindow.base_ptr = ctx->d_pairs;
+    attr.accessPolicyWindow.num_bytes = bytes;
+    attr.accessPolicyWindow.hitRatio = 1.0f;
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  } else {
+    attr.accessPolicyWindow.num_bytes = 0;
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+  }
+  CU(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+  ctx->l2_window_on = want;
+  ctx->l2_window_stream = want ? ctx->stream : nullptr;
+  return 0;
+}
+
 // Wavefront schedule.  The launch's frames are cut into chunks whose sample buffer (16 B per path) fits the budget;
 // per chunk: init, then trace+logic pairs queued in batches -- after each batch the device reports how many slots
 // still carry a path, and the host looks at the report of the batch BEFORE the one it has just queued, so the GPU
@@ -647,6 +749,7 @@ extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
     return 0;
   }
   if (n_frames == 0 || ctx->row1 == ctx->row0) return 0;
+  if (ctx->params.show_model && apply_l2_window(ctx)) return 1;
   FrameParams fp;
   fill_frame_params(ctx, n_frames, fp);
   if (ctx->params.show_model && ctx->schedule == SCHED_WAVEFRONT) {
