@@ -30,7 +30,14 @@ struct SurfMat {  // Material, raytrace_types.glsl:4-10
 __device__ __forceinline__ float rand_uniform(const DeviceScene& sc, const FrameParams& fp, int pix, float sx, float sy) {
   float r = fract_(sin_(dot2_(sx, sy, 12.9898f, 78.233f)) * 43758.5453f);  // randFloat, raytrace_utils.glsl:28-30
   float scaled = r * fp.width_f * fp.height_f;
-  int idx = (pix + f2i_(scaled)) % fp.n_texels;
+  // (index + int(scaled)) % (Width*Height), raytrace_utils.glsl:46-50.  r is in [0,1] so int(scaled) is in
+  // [0, Width*Height]; with pix < Width*Height (any image at least as wide as high) two conditional subtractions ARE the
+  // modulo, and the general case falls through to it
+  const uint32_t n = (uint32_t)fp.n_texels;
+  uint32_t idx = (uint32_t)pix + (uint32_t)f2i_(scaled);
+  if (idx >= n) idx -= n;
+  if (idx >= n) idx -= n;
+  if (idx >= n) idx %= n;
   return __ldg(sc.noise_uniform_x + idx);
 }
 
