@@ -11,5 +11,7 @@ unit, uniform = scenes.noise_tables(W, H)
 ctx.upload_scene(scenes.rubik_scene()); ctx.upload_noise(unit, uniform); ctx.set_lights(scenes.model_lights()); ctx.resize(W, H)
 ctx.set_option(pkg.OPT_TRAVERSAL, mode); ctx.set_option(pkg.OPT_SCHEDULE, sched)
 ctx.set_params(pkg.make_params(W, H, scenes.reset_camera(True), True, accum_frames=1, bvh_count=1))
-ctx.render(2); ctx.render(spp)
+warm = int(sys.argv[4]) if len(sys.argv) > 4 else 2
+if warm: ctx.render(warm)
+ctx.render(spp)
 print(ctx.counters())

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -70,6 +71,7 @@ struct srt_ctx {
   // wavefront schedule: path slots + queues (sized for the pixels this context renders), polling state
   PathPool pool;
   uint32_t pool_slots = 0;
+  size_t pool_list_cap = 0;
   unsigned int* h_live = nullptr;  // pinned ring the device reports live_pixels into
   cudaEvent_t wave_events[4] = {nullptr, nullptr, nullptr, nullptr};
   uint64_t waves = 0;
@@ -199,7 +201,7 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
     return 0;
   }
   if (key == SRT_OPT_REFILL) {
-    if (value < 1 || value > 32) return fail(ctx, "SRT_OPT_REFILL: 1..32");
+    if ((value & 0xFF) < 1 || (value & 0xFF) > 32) return fail(ctx, "SRT_OPT_REFILL: low byte 1..32");
     ctx->refill_threshold = value;
     return 0;
   }
@@ -233,7 +235,8 @@ struct Relayout {
   std::vector<NodePair> pairs;
   std::vector<uint2> leaves;
   std::vector<BvhRecord> bvhs;
-  std::vector<uint32_t> rank;  // per triangle: position in the shader's visiting order
+  std::vector<uint32_t> rank;       // per triangle: position in the shader's visiting order
+  std::vector<uint32_t> remaining;  // per triangle: triangles that follow it in its leaf (0 = last of the leaf)
   int depth = 0;
 };
 
@@ -242,6 +245,7 @@ struct Relayout {
 bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* nodes, uint32_t n_nodes,
               uint32_t n_tris, Relayout& out) {
   out.rank.assign(n_tris, 0xFFFFFFFFu);
+  out.remaining.assign(n_tris, 0u);
   uint32_t next_rank = 0;
   std::vector<uint32_t> seen(n_nodes, 0);  // BVH (1-based) that reached the node
   struct Item { uint32_t node; uint32_t slot; int depth; };  // slot: where to write this node's reference
@@ -263,17 +267,21 @@ bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_
       seen[it.node] = b + 1;
       if (it.depth > out.depth) out.depth = it.depth;
       const srt_bvh_node& n = nodes[it.node];
-      uint32_t ref;
+      uint32_t ref, direct;  // direct: the same child for kernels that walk a leaf by its triangles' `remaining` marks
       if (n.prim_count > 0) {
         if ((uint64_t)n.first_child_or_prim_index + n.prim_count > n_tris)
           return fail(ctx, "node %u: triangles [%u,+%u) out of range", it.node, n.first_child_or_prim_index, n.prim_count), false;
         ref = SRT_LEAF_BIT | (uint32_t)out.leaves.size();
         out.leaves.push_back(make_uint2(n.first_child_or_prim_index, n.prim_count));
+        if (n.first_child_or_prim_index >= SRT_LEAF_BIT) return fail(ctx, "too many triangles"), false;
+        direct = SRT_LEAF_BIT | n.first_child_or_prim_index;
+        for (uint32_t k = 0; k < n.prim_count; ++k) out.remaining[n.first_child_or_prim_index + k] = n.prim_count - 1 - k;
       } else {
         uint32_t c = n.first_child_or_prim_index;
         if ((uint64_t)c + 1 >= n_nodes) return fail(ctx, "node %u: children %u,%u out of range", it.node, c, c + 1), false;
         ref = (uint32_t)out.pairs.size();
-        if (ref >= SRT_LEAF_BIT) return fail(ctx, "too many inner nodes"), false;
+        if (ref >= SRT_LEAF_BIT - 1u) return fail(ctx, "too many inner nodes"), false;
+        direct = ref;
         const srt_bvh_node &l = nodes[c], &r = nodes[c + 1];
         NodePair p;
         p.a = make_float4(l.min_bounds[0], l.min_bounds[1], l.min_bounds[2], l.max_bounds[0]);
@@ -296,9 +304,16 @@ bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_
           stack.push_back(left);
         }
       }
-      if (it.slot == 0xFFFFFFFFu) rec.root_ref = ref;
-      else if (it.slot & 1) out.pairs[it.slot >> 1].d.y = ref;
-      else out.pairs[it.slot >> 1].d.x = ref;
+      if (it.slot == 0xFFFFFFFFu) {
+        rec.root_ref = ref;
+        rec.root_direct = direct;
+      } else if (it.slot & 1) {
+        out.pairs[it.slot >> 1].d.y = ref;
+        out.pairs[it.slot >> 1].d.w = direct;
+      } else {
+        out.pairs[it.slot >> 1].d.x = ref;
+        out.pairs[it.slot >> 1].d.z = direct;
+      }
       return true;
     };
     while (fifo_head < fifo.size()) {
@@ -370,6 +385,7 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
     r.v0 = make_float4(v0[0], v0[1], v0[2], u2f(t.material_idx));
     r.e1 = make_float4(v1[0] - v0[0], v1[1] - v0[1], v1[2] - v0[2], u2f(rl.rank[i]));
     r.e2 = make_float4(v2[0] - v0[0], v2[1] - v0[1], v2[2] - v0[2], 0.0f);
+    memcpy(&r.e2.w, &rl.remaining[i], 4);
     tris[i] = r;
   }
   std::vector<MatRecord> mats(n_materials);
@@ -620,11 +636,15 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries) {
     p.samples = keep;
     CU(ctx, cudaMalloc(&p.ray, (size_t)slots * 32)); CU(ctx, cudaMalloc(&p.hit, (size_t)slots * 8));
     CU(ctx, cudaMalloc(&p.pst, (size_t)slots * 32)); CU(ctx, cudaMalloc(&p.path, (size_t)slots * 8));
-    CU(ctx, cudaMalloc(&p.p3, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.list[0], (size_t)slots * 4));
-    CU(ctx, cudaMalloc(&p.list[1], (size_t)slots * 4)); CU(ctx, cudaMalloc(&p.q, sizeof(WaveCounters)));
+    // every logic warp can leave one partly used reservation per queue: room for those holes beside the slots
+    ctx->pool_list_cap = (size_t)slots + 2u * (size_t)launch_wf_max_logic_warps() * 256u;
+    if (ctx->pool_list_cap >= 0xFFFFFFFFull) return fail(ctx, "wavefront pool too large");
+    CU(ctx, cudaMalloc(&p.p3, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.list[0], ctx->pool_list_cap * 4));
+    CU(ctx, cudaMalloc(&p.list[1], ctx->pool_list_cap * 4)); CU(ctx, cudaMalloc(&p.q, sizeof(WaveCounters)));
     ctx->pool_slots = slots;
   }
   p.cap = slots;
+  p.list_cap = (uint32_t)ctx->pool_list_cap;
   if (ctx->sample_entries < sample_entries) {
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     dfree(p.samples);
@@ -885,6 +905,7 @@ extern "C" int srt_get_kernel_times(srt_ctx* ctx, double* trace_ms, double* logi
     CU(ctx, cudaEventElapsedTime(&b, ctx->timing_events[i + 1], ctx->timing_events[i + 2]));
     t += a;
     l += b;
+    if (getenv("SRT_WAVE_LOG")) fprintf(stderr, "wave %zu: trace %.3f ms, logic %.3f ms\n", i / 3, a, b);
   }
   if (trace_ms) *trace_ms = t;
   if (logic_ms) *logic_ms = l;

@@ -18,11 +18,13 @@ namespace srt {
 // a time, ray_intersects.glsl:107).  Child references:
 //   bit 31 clear: index of the child's own NodePair record (child is an inner node)
 //   bit 31 set  : index into the leaf table (child is a leaf)
+// and, for kernels that walk a leaf triangle by triangle until TriRecord's `remaining` mark says 0, the same two
+// children as DIRECT references: bit 31 set = index of the leaf's first triangle (no leaf-table fetch on arrival).
 struct NodePair {
   float4 a;  // L.min.xyz, L.max.x
   float4 b;  // L.max.yz,  R.min.xy
   float4 c;  // R.min.z,   R.max.xyz
-  uint4 d;   // L.ref, R.ref, unused, unused
+  uint4 d;   // L.ref, R.ref, L.direct, R.direct
 };
 static_assert(sizeof(NodePair) == 64, "NodePair is one 64 B fetch");
 
@@ -35,7 +37,7 @@ static_assert(sizeof(NodePair) == 64, "NodePair is one 64 B fetch");
 struct TriRecord {
   float4 v0;  // v0.xyz, bits: material index
   float4 e1;  // edge_1.xyz, bits: rank in the reference's visiting order (tie-break key)
-  float4 e2;  // edge_2.xyz, unused
+  float4 e2;  // edge_2.xyz, bits: triangles that follow this one in its leaf (0 marks the leaf's last triangle)
 };
 static_assert(sizeof(TriRecord) == 48, "TriRecord is three 16 B fetches");
 
@@ -52,7 +54,7 @@ struct BvhRecord {
   float root_min[3];
   uint32_t root_ref;
   float root_max[3];
-  uint32_t _pad;
+  uint32_t root_direct;  // root as a direct reference (see NodePair::d)
 };
 
 // SRT_OPT_TRAVERSAL values (srt_b200.h)
@@ -123,8 +125,9 @@ struct PathPool {
                  // [2*slot+1] colour.xyz, bits: depth | rand_index << 8 | iter << 20
   uint2* path;   // (pixel slot, frame of the launch) of the path in this slot  (8 B)
   float4* p3;    // while a shadow ray is out: incoming direction.xyz, bits: primitive the path stands on
-  uint32_t* list[2];
-  uint32_t cap;  // slots (= entries per list)
+  uint32_t* list[2];   // list_cap entries each: closest-hit queue from the front, shadow queue from the back
+  uint32_t cap;        // slots
+  uint32_t list_cap;   // cap + room for the holes the logic warps' chunked reservations can leave
   WaveCounters* q;
   // one fp32 sample per path of the launch, frame-major, summed per pixel in frame order by wf_resolve_kernel
   float4* samples;

@@ -271,6 +271,13 @@ cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const P
   return cudaGetLastError();
 }
 
+uint32_t launch_wf_max_logic_warps() {
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+    sms = 148;
+  return (uint32_t)sms * SRT_WF_LOGIC_BLOCKS_PER_SM * 2u * (SRT_WF_LOGIC_THREADS / 32u);
+}
+
 cudaError_t launch_wf_resolve(const FrameParams& fp, const PathPool& pool, float4* accum, uchar4* out,
                               cudaStream_t stream) {
   if (pool.n_pixels == 0) return cudaSuccess;
@@ -335,7 +342,7 @@ cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const P
   const long warps_per_block = SRT_WF_LOGIC_THREADS / 32;
   long warps = (long)pool.cap / 32;
   long blocks = (warps + warps_per_block - 1) / warps_per_block;
-  long max_blocks = (long)(g_wf_grid.sms > 0 ? g_wf_grid.sms : 148) * SRT_WF_LOGIC_BLOCKS_PER_SM * 2;
+  long max_blocks = (long)launch_wf_max_logic_warps() / warps_per_block;
   if (blocks > max_blocks) blocks = max_blocks;
   if (blocks < 1) blocks = 1;
   wf_logic_kernel<<<(unsigned)blocks, SRT_WF_LOGIC_THREADS, 0, stream>>>(sc, fp, pool, parity, ids, counters);

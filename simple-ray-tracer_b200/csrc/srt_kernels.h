@@ -18,6 +18,8 @@ cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const P
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
                            cudaEvent_t after_trace = nullptr);
+// upper bound of the warps launch_wf_wave gives wf_logic_kernel (sizes the queues' room for holes)
+uint32_t launch_wf_max_logic_warps();
 cudaError_t launch_wf_resolve(const FrameParams& fp, const PathPool& pool, float4* accum, uchar4* out,
                               cudaStream_t stream);
 cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream);

@@ -50,9 +50,10 @@ __device__ __forceinline__ float box_distance(V3 o, V3 inv, float mnx, float mny
 // becomes the closest hit; the normal (ray_intersects.glsl:90) is computed once for the final winner instead.
 template <int MODE>
 __device__ __forceinline__ bool triangle_test(const TriRecord* __restrict__ tris, uint32_t idx, V3 o, V3 d, float& best,
-                                              uint32_t& best_rank) {
+                                              uint32_t& best_rank, uint32_t& remaining) {
   const float4* p = reinterpret_cast<const float4*>(tris + idx);
   float4 r0 = __ldg(p), r1 = __ldg(p + 1), r2 = __ldg(p + 2);
+  remaining = __float_as_uint(r2.w);
   V3 v0 = v3(r0.x, r0.y, r0.z), edge_1 = v3(r1.x, r1.y, r1.z), edge_2 = v3(r2.x, r2.y, r2.z);
   V3 h = cross_(d, edge_2);
   float a = dot_(edge_1, h);
@@ -79,6 +80,13 @@ __device__ __forceinline__ bool triangle_test(const TriRecord* __restrict__ tris
     }
   }
   return false;
+}
+
+template <int MODE>
+__device__ __forceinline__ bool triangle_test(const TriRecord* __restrict__ tris, uint32_t idx, V3 o, V3 d, float& best,
+                                              uint32_t& best_rank) {
+  uint32_t remaining;
+  return triangle_test<MODE>(tris, idx, o, d, best, best_rank, remaining);
 }
 
 // Intersects (ray_intersects.glsl:99-133).  `best` is the shader's inout intersection_distance.

@@ -30,6 +30,10 @@ namespace srt {
 
 #define SRT_WF_LOGIC_THREADS 256
 #define SRT_WF_LOGIC_BLOCKS_PER_SM 4  // 64 registers per thread: the kernel waits on gathers, occupancy hides them
+#define SRT_WF_APPEND_CHUNK 256u     // most queue entries a logic warp reserves per atomic (unused ones become holes)
+#define SRT_WF_HOLE 0xFFFFFFFFu      // list entry that carries no slot
+#define SRT_WF_FETCH_MAX 2048u       // most queue entries a trace warp reserves per atomic
+#define SRT_WF_NEED_POP 0x7FFFFFFFu  // a lane's `cur` between the end of its leaf and its pop (never a NodePair index)
 #define SRT_WF_KIND_CLOSEST 0u
 #define SRT_WF_KIND_SHADOW 1u
 
@@ -109,6 +113,8 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   int lane_cap = (int)((n_total + total_warps - 1) / total_warps);  // rays a warp holds at a time
   lane_cap = lane_cap < 4 ? 4 : (lane_cap > 32 ? 32 : lane_cap);
   const int refill_at = refill_threshold < (lane_cap + 1) / 2 ? refill_threshold : (lane_cap + 1) / 2;
+  uint32_t r_next = 0, r_end = 0;  // warp-private range of queue entries (warp-uniform)
+  uint32_t seen_cursor = 0;        // how far the shared cursor had moved when this warp last looked
 
   auto finish_ray = [&]() {  // the lane's ray is done: hand the result to the slot
     pool.hit[slot] = make_uint2(hit, __float_as_uint(best));
@@ -157,21 +163,36 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
 
   for (;;) {
     // ---- refill idle lanes from the wave's queue ------------------------------------------------------------
-    // (a small wave is spread over all warps: at most lane_cap rays per warp, so its duration is the lockstep time
-    // of a few rays instead of 32)
+    // A warp reserves a RANGE of queue entries with one atomic and hands them to its idle lanes without further
+    // atomics (one cursor shared by 4736 warps serialises in L2).  Ranges shrink as the queue drains (guided
+    // self-scheduling) so the last warps do not sit on long private ranges; a small wave is spread over all warps
+    // (lane_cap).
     while (!exhausted) {
       const unsigned idle = __ballot_sync(FULL, !trav);
       const int n_want = lane_cap - (32 - __popc(idle));
       if (n_want <= 0) break;
-      uint32_t base = 0;
-      if (lane == 0) base = atomicAdd(&q->cursor, (unsigned int)n_want);
-      base = __shfl_sync(FULL, base, 0);
-      if (base + n_want >= n_total) exhausted = true;
+      if (r_next == r_end) {
+        uint32_t chunk = (n_total - seen_cursor) / (total_warps * 4u);
+        chunk = chunk > SRT_WF_FETCH_MAX ? SRT_WF_FETCH_MAX : chunk;
+        chunk = chunk < (uint32_t)lane_cap ? (uint32_t)lane_cap : chunk;
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&q->cursor, chunk);
+        base = __shfl_sync(FULL, base, 0);
+        if (base >= n_total) {
+          exhausted = true;
+          break;
+        }
+        r_next = base;
+        r_end = base + chunk < n_total ? base + chunk : n_total;
+        seen_cursor = r_end;
+      }
+      const int n_take = (int)(r_end - r_next) < n_want ? (int)(r_end - r_next) : n_want;
       const int my_rank = __popc(idle & ((1u << lane) - 1u));
-      if (!trav && my_rank < n_want) {
-        const uint32_t idx = base + my_rank;
-        if (idx < n_total) {
-          slot = __ldg(list + (idx < n_front ? idx : pool.cap - 1u - (idx - n_front)));
+      if (!trav && my_rank < n_take) {
+        const uint32_t idx = r_next + my_rank;
+        const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
+        if (entry != SRT_WF_HOLE) {
+          slot = entry;
           const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1];
           ray_o = v3(a.x, a.y, a.z);
           ray_d = v3(b.x, b.y, b.z);
@@ -183,6 +204,7 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           enter();  // may end the ray at once (root box missed): the lane is idle again and refills next turn
         }
       }
+      r_next += n_take;
     }
     if (!__any_sync(FULL, trav)) break;
 
@@ -274,12 +296,21 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   if (blockIdx.x == 0 && threadIdx.x == 0) q->cursor = 0;  // for the next wave's trace kernel
   const V3 sky = v3(0.05f);
   unsigned int n_seg = 0, n_shadow = 0, n_capped = 0, n_done = 0;
+  bool paths_out = *(volatile unsigned long long*)&q->next_path >= pool.n_paths;  // warp-uniform
+  // warp-private ranges of the output queues, reserved append_chunk entries at a time (one atomic each); what is left
+  // of a range when the warp moves on is filled with holes, which the consumers skip
+  uint32_t c_next = 0, c_end = 0, s_next = 0, s_end = 0;
+  // a warp that handles few entries reserves as little: the tail waves keep the exact one-atomic-per-32 behaviour
+  uint32_t append_chunk = (chunks_a + chunks_b + n_warps - 1u) / n_warps * 32u;
+  append_chunk = append_chunk > SRT_WF_APPEND_CHUNK ? SRT_WF_APPEND_CHUNK : append_chunk;
 
   for (uint32_t g = warp; g < chunks_a + chunks_b; g += n_warps) {
     const bool region_a = g < chunks_a;  // warp-uniform: which queue this chunk belongs to
     const uint32_t idx = (region_a ? g : g - chunks_a) * 32u + lane;
-    const bool valid = idx < (region_a ? n_a : n_b);
-    const uint32_t slot = valid ? __ldg(list_in + (region_a ? idx : pool.cap - 1u - idx)) : 0u;
+    const bool in_range = idx < (region_a ? n_a : n_b);
+    const uint32_t entry = in_range ? __ldg(list_in + (region_a ? idx : pool.list_cap - 1u - idx)) : SRT_WF_HOLE;
+    const bool valid = entry != SRT_WF_HOLE;
+    const uint32_t slot = valid ? entry : 0u;
     const uint2 path = valid ? pool.path[slot] : make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
     int x = 0, y = 0;
     tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
@@ -397,10 +428,15 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     // ---- the path ended: its sample goes to samples[frame][pixel] (:292); the slot takes the launch's next path ----
     const unsigned m_f = __ballot_sync(FULL, finish);
     if (m_f) {
-      unsigned long long base = 0;
-      const int leader = __ffs(m_f) - 1;
-      if (lane == leader) base = atomicAdd(&q->next_path, (unsigned long long)__popc(m_f));
-      base = __shfl_sync(FULL, base, leader);
+      // next_path only grows: once it has passed the launch's last path no warp needs the atomic any more (with every
+      // path of the launch in flight from wave 0 that is always; 4 M same-address atomics cost 4 ms there)
+      unsigned long long base = pool.n_paths;
+      if (!paths_out) {
+        const int leader = __ffs(m_f) - 1;
+        if (lane == leader) base = atomicAdd(&q->next_path, (unsigned long long)__popc(m_f));
+        base = __shfl_sync(FULL, base, leader);
+        paths_out = base >= pool.n_paths;
+      }
       if (finish) {
         color = color + throughput * sky;  // Q19
         const V3 pixel_color = v3(0.0f) + color;  // main(): pixelColor = vec3(0) + GetRayColor(...)
@@ -427,21 +463,33 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     // ---- next wave's queues: closest-hit rays at the front, shadow rays at the back ----
     const unsigned m_c = __ballot_sync(FULL, emit_closest);
     if (m_c) {
-      uint32_t base = 0;
-      const int leader = __ffs(m_c) - 1;
-      if (lane == leader) base = atomicAdd(&q->n_closest[parity ^ 1], (unsigned int)__popc(m_c));
-      base = __shfl_sync(FULL, base, leader);
-      if (emit_closest) list_out[base + __popc(m_c & lt_mask)] = slot;
+      const uint32_t m = (uint32_t)__popc(m_c);
+      if (c_next + m > c_end) {
+        for (uint32_t i = c_next + lane; i < c_end; i += 32) list_out[i] = SRT_WF_HOLE;
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&q->n_closest[parity ^ 1], append_chunk);
+        c_next = __shfl_sync(FULL, base, 0);
+        c_end = c_next + append_chunk;
+      }
+      if (emit_closest) list_out[c_next + __popc(m_c & lt_mask)] = slot;
+      c_next += m;
     }
     const unsigned m_s = __ballot_sync(FULL, emit_shadow);
     if (m_s) {
-      uint32_t base = 0;
-      const int leader = __ffs(m_s) - 1;
-      if (lane == leader) base = atomicAdd(&q->n_shadow[parity ^ 1], (unsigned int)__popc(m_s));
-      base = __shfl_sync(FULL, base, leader);
-      if (emit_shadow) list_out[pool.cap - 1u - (base + __popc(m_s & lt_mask))] = slot;
+      const uint32_t m = (uint32_t)__popc(m_s);
+      if (s_next + m > s_end) {
+        for (uint32_t i = s_next + lane; i < s_end; i += 32) list_out[pool.list_cap - 1u - i] = SRT_WF_HOLE;
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&q->n_shadow[parity ^ 1], append_chunk);
+        s_next = __shfl_sync(FULL, base, 0);
+        s_end = s_next + append_chunk;
+      }
+      if (emit_shadow) list_out[pool.list_cap - 1u - (s_next + __popc(m_s & lt_mask))] = slot;
+      s_next += m;
     }
   }
+  for (uint32_t i = c_next + lane; i < c_end; i += 32) list_out[i] = SRT_WF_HOLE;
+  for (uint32_t i = s_next + lane; i < s_end; i += 32) list_out[pool.list_cap - 1u - i] = SRT_WF_HOLE;
 
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
