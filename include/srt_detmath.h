@@ -107,6 +107,14 @@ SRT_HD float div_(float a, float b) {
   return a / b;
 #endif
 }
+// 1/x, correctly rounded: the same bits as div_(1.0f, x) (IEEE division is correctly rounded too), fewer instructions
+SRT_HD float rcp_(float x) {
+#if defined(__CUDA_ARCH__)
+  return __frcp_rn(x);
+#else
+  return 1.0f / x;
+#endif
+}
 SRT_HD float length_(V3 a) { return sqrt_(dot_(a, a)); }
 SRT_HD V3 normalize_(V3 a) { float l = length_(a); return v3(div_(a.x, l), div_(a.y, l), div_(a.z, l)); }
 SRT_HD V3 reflect_(V3 I, V3 N) { float k = 2.0f * dot_(N, I); return I - k * N; }

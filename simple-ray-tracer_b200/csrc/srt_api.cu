@@ -201,7 +201,7 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
     return 0;
   }
   if (key == SRT_OPT_REFILL) {
-    if ((value & 0xFF) < 1 || (value & 0xFF) > 32) return fail(ctx, "SRT_OPT_REFILL: low byte 1..32");
+    if (value < 1 || value > 32) return fail(ctx, "SRT_OPT_REFILL: 1..32");
     ctx->refill_threshold = value;
     return 0;
   }

@@ -296,8 +296,9 @@ WfGrid g_wf_grid;  // launch geometry is a property of the device + kernel, comp
 
 template <int MODE, bool COUNT>
 cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
-                            DeviceCounters* counters, int block, cudaStream_t stream) {
+                            DeviceCounters* counters, int /*block*/, cudaStream_t stream) {
   auto k = wf_trace_kernel<MODE, COUNT>;
+  const int block = SRT_WF_TRACE_THREADS;  // fixed: the stack stride is a compile-time constant of the kernel
   const size_t smem = (size_t)fp.stack_cap * block * sizeof(uint2);
   cudaError_t e;
   if (g_wf_grid.block != block || g_wf_grid.smem != smem || g_wf_grid.sms == 0) {

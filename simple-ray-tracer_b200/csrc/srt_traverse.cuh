@@ -58,7 +58,7 @@ __device__ __forceinline__ bool triangle_test(const TriRecord* __restrict__ tris
   V3 h = cross_(d, edge_2);
   float a = dot_(edge_1, h);
   if (a > -0.0001f && a < 0.0001f) return false;
-  float f = div_(1.0f, a);
+  float f = rcp_(a);
   V3 s = o - v0;
   float u = f * dot_(s, h);
   if (u < 0.0f || u > 1.0f) return false;

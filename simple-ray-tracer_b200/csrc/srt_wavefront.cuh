@@ -28,6 +28,8 @@
 
 namespace srt {
 
+#define SRT_WF_TRACE_THREADS 64   // block of the trace kernel (two warps share an SM slot; 64 measured best of 32..256)
+#define SRT_WF_DESCENT_CUTOFF 5   // a_min of the trace kernel's descent phase (0, 3, 5, 7, 10 measured: 1801..1907..1862 Mseg/s)
 #define SRT_WF_LOGIC_THREADS 256
 #define SRT_WF_LOGIC_BLOCKS_PER_SM 4  // 64 registers per thread: the kernel waits on gathers, occupancy hides them
 #define SRT_WF_APPEND_CHUNK 256u     // most queue entries a logic warp reserves per atomic (unused ones become holes)
@@ -51,6 +53,14 @@ __device__ __forceinline__ V3 wf_primary_dir(const DeviceScene& sc, const FrameP
   return pixel_sample - fp.center;
 }
 
+// path number of the launch -> (pixel slot, frame): a warp's 32 consecutive paths are the 8x4 pixels of one tile in one
+// frame.  (32 frames of one pixel per warp instead -- near-identical origins for a warp's bounce rays -- measured the
+// same, 1911 vs 1907 Mseg/s: the divergence comes from the directions.)
+__device__ __forceinline__ void wf_path_id(const PathPool& pool, unsigned long long p, uint32_t& pixel, uint32_t& f) {
+  pixel = (uint32_t)(p % pool.n_pixels);
+  f = (uint32_t)(p / pool.n_pixels);
+}
+
 // ---- wave 0: the first pool.cap paths of the launch -----------------------------------------------------------------
 __global__ void __launch_bounds__(128)
 wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool,
@@ -69,7 +79,8 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
     atomicAdd(&counters->paths, pool.n_paths);
   }
   if (slot >= first) return;
-  const uint32_t pixel = slot % pool.n_pixels, f = slot / pool.n_pixels;
+  uint32_t pixel, f;
+  wf_path_id(pool, slot, pixel, f);
   int x, y;
   tile_pixel(fp, pixel >> 5, pixel & 31, x, y);
   const int pix = y * fp.height + x;  // Q4
@@ -82,14 +93,42 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   pool.list[0][slot] = slot;
 }
 
+// The traversal stack lives in shared memory, one column per thread; addressed by 32-bit shared addresses so that a
+// push or a pop is one instruction plus the pointer bump (generic addressing recomputes the window base every time).
+__device__ __forceinline__ void wf_sts(uint32_t addr, uint32_t x, uint32_t y) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ uint2 wf_lds(uint32_t addr) {
+  uint2 r;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(addr) : "memory");
+  return r;
+}
+
+// The two slab distances of IntersectsBox (ray_intersects.glsl:50-56).  wf_slab_fast uses the hardware min/max: the
+// same bits whenever no slab product is NaN, i.e. whenever 1/dir is finite in all three components.
+__device__ __forceinline__ void wf_slab(V3 o, V3 inv, float mnx, float mny, float mnz, float mxx, float mxy, float mxz,
+                                        float& t_near, float& t_far) {
+  float t0x = (mnx - o.x) * inv.x, t0y = (mny - o.y) * inv.y, t0z = (mnz - o.z) * inv.z;
+  float t1x = (mxx - o.x) * inv.x, t1y = (mxy - o.y) * inv.y, t1z = (mxz - o.z) * inv.z;
+  t_near = max_(max_(min_(t0x, t1x), min_(t0y, t1y)), min_(t0z, t1z));
+  t_far = min_(min_(max_(t0x, t1x), max_(t0y, t1y)), max_(t0z, t1z));
+}
+__device__ __forceinline__ void wf_slab_fast(V3 o, V3 inv, float mnx, float mny, float mnz, float mxx, float mxy,
+                                             float mxz, float& t_near, float& t_far) {
+  float t0x = (mnx - o.x) * inv.x, t0y = (mny - o.y) * inv.y, t0z = (mnz - o.z) * inv.z;
+  float t1x = (mxx - o.x) * inv.x, t1y = (mxy - o.y) * inv.y, t1z = (mxz - o.z) * inv.z;
+  t_near = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+  t_far = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+}
+
 // ---- trace: Intersects / CheckHit of one wave (ray_intersects.glsl:99-133, raytrace_compute.glsl:143-162) ---------
 template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(SRT_MAX_BLOCK_THREADS)
+__global__ void __launch_bounds__(SRT_WF_TRACE_THREADS)
 wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity,
                 int refill_threshold, DeviceCounters* __restrict__ counters) {
   extern __shared__ uint2 s_stack_all[];
-  uint2* s_stack = s_stack_all + threadIdx.x;
-  const int stride = blockDim.x;
+  const uint32_t sp_base = (uint32_t)__cvta_generic_to_shared(s_stack_all + threadIdx.x);
+  constexpr uint32_t sp_step = SRT_WF_TRACE_THREADS * (uint32_t)sizeof(uint2);
   const unsigned FULL = 0xFFFFFFFFu;
   const int lane = threadIdx.x & 31;
   WaveCounters* q = pool.q;
@@ -106,12 +145,13 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   uint32_t slot = 0;
   V3 ray_o = v3(0.0f), ray_d = v3(0.0f), to = v3(0.0f), td = v3(0.0f), inv = v3(0.0f);
   float best = 0.0f;
-  uint32_t hit = SRT_NO_HIT, best_rank = 0xFFFFFFFFu, cur = 0, bvh_i = 0, tri = 0, tri_end = 0;
-  int sp = 0;
+  uint32_t hit = SRT_NO_HIT, best_rank = 0xFFFFFFFFu, cur = 0, bvh_i = 0;
+  uint32_t sp = sp_base;  // shared address of the next free stack entry
   bool exhausted = false;  // warp-uniform: the queue has no more rays
   const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
   int lane_cap = (int)((n_total + total_warps - 1) / total_warps);  // rays a warp holds at a time
   lane_cap = lane_cap < 4 ? 4 : (lane_cap > 32 ? 32 : lane_cap);
+  constexpr int a_min = SRT_WF_DESCENT_CUTOFF;
   const int refill_at = refill_threshold < (lane_cap + 1) / 2 ? refill_threshold : (lane_cap + 1) / 2;
   uint32_t r_next = 0, r_end = 0;  // warp-private range of queue entries (warp-uniform)
   uint32_t seen_cursor = 0;        // how far the shared cursor had moved when this warp last looked
@@ -137,9 +177,8 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
                                   bvh->root_max[1], bvh->root_max[2], in_root);
       if (COUNT) n_nodes++;
       if ((d_root < best) && !isinf_(d_root)) {
-        cur = bvh->root_ref;
-        sp = 0;
-        tri = tri_end = 0;
+        cur = bvh->root_direct;
+        sp = sp_base;
         return;
       }
       ++bvh_i;
@@ -147,13 +186,13 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   };
   auto pop = [&]() {
     for (;;) {
-      if (sp == 0) {
+      if (sp == sp_base) {
         ++bvh_i;
         enter();
         return;
       }
-      --sp;
-      uint2 e = s_stack[sp * stride];
+      sp -= sp_step;
+      uint2 e = wf_lds(sp);
       if (__uint_as_float(e.y) < best) {
         cur = e.x;
         return;
@@ -209,57 +248,62 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     if (!__any_sync(FULL, trav)) break;
 
     // ---- traverse until enough lanes are idle again ----------------------------------------------------------
+    // Two phases in turn: lanes that stand on inner nodes descend, then lanes that stand in leaves test triangles.
+    // The descent does not wait for its last stragglers: it stops when no more than a_min lanes are still on inner
+    // nodes while others have a leaf to work on (the stragglers go on in the next descent).  A lane's own sequence of
+    // box and triangle tests does not change, so neither does the result.  Tried and dropped, same bits each time:
+    // one step per turn of whichever kind most lanes wait for ("majority vote", 13 % slower: long phases keep the
+    // lanes in step), cutting the leaf phase's tail the same way (no gain), popping inside the leaf loop (20 % slower).
     for (;;) {
-      while (__any_sync(FULL, trav && !(cur & SRT_LEAF_BIT))) {
-        const bool exact = __any_sync(FULL, trav && exact_box);
-        if (trav && !(cur & SRT_LEAF_BIT)) {
+      for (;;) {
+        const int a = __popc(__ballot_sync(FULL, trav && cur < SRT_WF_NEED_POP));
+        if (a <= a_min && (a == 0 || __any_sync(FULL, trav && (cur & SRT_LEAF_BIT)))) break;
+        if (trav && cur < SRT_WF_NEED_POP) {
           const float4* p = reinterpret_cast<const float4*>(sc.pairs + cur);
           float4 na = __ldg(p), nb = __ldg(p + 1), nc = __ldg(p + 2);
           uint4 nd = __ldg(reinterpret_cast<const uint4*>(p + 3));
-          bool in_l, in_r;
-          float dl, dr;
-          if (exact) {
-            dl = box_distance(to, inv, na.x, na.y, na.z, na.w, nb.x, nb.y, in_l);
-            dr = box_distance(to, inv, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, in_r);
+          float nl, fl, nr, fr;
+          if (exact_box) {  // an axis-parallel ray: rare, and only its own lanes take the slow min/max
+            wf_slab(to, inv, na.x, na.y, na.z, na.w, nb.x, nb.y, nl, fl);
+            wf_slab(to, inv, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, nr, fr);
           } else {
-            dl = box_distance_fast(to, inv, na.x, na.y, na.z, na.w, nb.x, nb.y, in_l);
-            dr = box_distance_fast(to, inv, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, in_r);
+            wf_slab_fast(to, inv, na.x, na.y, na.z, na.w, nb.x, nb.y, nl, fl);
+            wf_slab_fast(to, inv, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, nr, fr);
           }
           if (COUNT) n_nodes += 2;
-          bool pl = (dl < best) && !isinf_(dl);
-          bool pr = (dr < best) && !isinf_(dr);
+          // IntersectsBox returns near, or far when the origin is inside (near < 0), or inf on a miss; the caller takes
+          // the child when that is < best and not infinite (ray_intersects.glsl:56-58,108).  +inf is never < best.
+          const bool front_l = nl >= 0.0f, front_r = nr >= 0.0f;
+          const float dl = front_l ? nl : fl, dr = front_r ? nr : fr;
+          const bool pl = (nl <= fl) && (dl < best) && (dl != -inf_());
+          const bool pr = (nr <= fr) && (dr < best) && (dr != -inf_());
           if (pl && pr) {
-            bool right_first = (MODE == TRAV_REFERENCE || in_l || in_r) ? true : !(dl < dr);
-            uint32_t second = right_first ? nd.x : nd.y;
-            float d_second = right_first ? dl : dr;
-            s_stack[sp * stride] = make_uint2(second, __float_as_uint(d_second));
-            ++sp;
-            cur = right_first ? nd.y : nd.x;
+            const bool right_first = (MODE == TRAV_REFERENCE || !front_l || !front_r) ? true : !(dl < dr);
+            wf_sts(sp, right_first ? nd.z : nd.w, __float_as_uint(right_first ? dl : dr));
+            sp += sp_step;
+            cur = right_first ? nd.w : nd.z;
           } else if (pl || pr) {
-            cur = pl ? nd.x : nd.y;
+            cur = pl ? nd.z : nd.w;
           } else {
             pop();
           }
         }
       }
-      // leaves: one triangle per lane per iteration, in the leaf's order.  (Popping inside this loop so that a lane
-      // stays here across sibling leaves was tried: same bits, 20 % slower -- the pop/enter code bloats the loop.)
-      if (trav && tri >= tri_end) {
-        uint2 leaf = __ldg(sc.leaves + (cur & ~SRT_LEAF_BIT));
-        tri = leaf.x;
-        tri_end = leaf.x + leaf.y;
-      }
-      while (__any_sync(FULL, trav && tri < tri_end)) {
-        if (trav && tri < tri_end) {
+      // leaves: one triangle per lane per iteration, in the leaf's order; a direct reference IS the triangle's index
+      // and the record says whether more follow
+      while (__any_sync(FULL, trav && (cur & SRT_LEAF_BIT))) {
+        if (trav && (cur & SRT_LEAF_BIT)) {
+          const uint32_t tri = cur & ~SRT_LEAF_BIT;
+          uint32_t remaining;
           if (COUNT) n_tris++;
-          if (triangle_test<MODE>(sc.tris, tri, to, td, best, best_rank)) {
+          if (triangle_test<MODE>(sc.tris, tri, to, td, best, best_rank, remaining)) {
             hit = tri;
             if (any_hit) finish_ray();  // shadow ray: the first accepted triangle decides
           }
-          ++tri;
+          cur = remaining ? cur + 1u : SRT_WF_NEED_POP;
         }
       }
-      if (trav) pop();
+      if (trav && cur == SRT_WF_NEED_POP) pop();
       const int n_idle = __popc(__ballot_sync(FULL, !trav));
       if (n_idle == 32) break;
       if (!exhausted && n_idle - (32 - lane_cap) >= refill_at) break;
@@ -443,7 +487,8 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         pool.samples[(size_t)path.y * pool.n_pixels + path.x] = make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f);
         const unsigned long long next = base + (unsigned long long)__popc(m_f & lt_mask);
         if (next < pool.n_paths) {
-          const uint32_t pixel = (uint32_t)(next % pool.n_pixels), f = (uint32_t)(next / pool.n_pixels);
+          uint32_t pixel, f;
+          wf_path_id(pool, next, pixel, f);
           int nx, ny;
           tile_pixel(fp, pixel >> 5, pixel & 31, nx, ny);
           const V3 d = wf_primary_dir(sc, fp, nx, ny, ny * fp.height + nx, (int)f);
