@@ -134,6 +134,17 @@ int srt_read_primary_ids(srt_ctx* ctx, uint32_t* ids /* W*H */);
 int srt_trace_rays(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, uint32_t bvh_count, uint32_t* hit_tri,
                    float* hit_t);
 
+/* IntersectionUtils::BVH<Prim>::BVH(prims, center_fn, bounds_fn)  (include/intersection_utils/bvh.h:40-148), built on
+ * the device: the same midpoint splits, the same unstable partition, the same node numbering -- byte for byte the
+ * arrays GetBVH() / GetPrims() of the reference's host builder give.
+ * centre_xyz / min_xyz / max_xyz: what center_fn and bounds_fn return per primitive, n_prims xyz triples each (host).
+ * nodes_out: room for 2 * n_prims - 1 nodes; children and first primitives are relative to this tree (the flattening
+ * of several models rebases them, gpu_loader.cpp:120-130).  order_out[k] = input index of the primitive that ends
+ * up k-th (GetPrims()[k]).  depth_out / device_ms_out may be NULL. */
+int srt_build_bvh(srt_ctx* ctx, const float* centre_xyz, const float* min_xyz, const float* max_xyz, uint32_t n_prims,
+                  srt_bvh_node* nodes_out, uint32_t* n_nodes_out, uint32_t* order_out, uint32_t* depth_out,
+                  float* device_ms_out);
+
 int srt_get_counters(srt_ctx* ctx, srt_counters* out);
 /* Sums of the CUDA-event durations of the wavefront schedule's trace and logic launches since the last call
  * (needs SRT_OPT_TIME_KERNELS = 1); waves = launches of each kind.  Synchronises the stream. */

@@ -32,7 +32,7 @@ RAY_DT = np.dtype([("origin", "<f4", 3), ("_pad0", "<f4"), ("direction", "<f4", 
 EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt_set_option", "srt_upload_scene",
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
-           "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays",
+           "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_build_bvh",
            "srt_get_counters", "srt_get_kernel_times", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
 
 
@@ -198,6 +198,19 @@ class Context:
         t = np.empty(len(rays), np.float32)
         self._ck(self._lib.srt_trace_rays(self._h, _p(rays), C.c_uint32(len(rays)), C.c_uint32(bvh_count), _p(hit), _p(t)))
         return hit, t
+
+    def build_bvh(self, centre, lo, hi):
+        """Device build of the reference's BVH (bvh.h:40-148) from per-primitive centres and boxes.
+        Returns (nodes [NODE_DT, tree-relative indices], order [uint32], depth, device_ms)."""
+        centre, lo, hi = (np.ascontiguousarray(a, np.float32).reshape(-1, 3) for a in (centre, lo, hi))
+        n = len(centre)
+        assert len(lo) == n and len(hi) == n
+        nodes = np.zeros(max(2 * n - 1, 1), NODE_DT)
+        order = np.zeros(max(n, 1), np.uint32)
+        n_nodes, depth, ms = C.c_uint32(), C.c_uint32(), C.c_float()
+        self._ck(self._lib.srt_build_bvh(self._h, _p(centre), _p(lo), _p(hi), C.c_uint32(n), _p(nodes), C.byref(n_nodes),
+                                         _p(order), C.byref(depth), C.byref(ms)))
+        return nodes[:n_nodes.value].copy(), order[:n], depth.value, ms.value
 
     def counters(self):
         c = Counters()

@@ -15,6 +15,7 @@
 
 #include "srt_b200.h"
 #include "srt_kernels.h"
+#include "srt_bvh_build.h"
 
 using namespace srt;
 
@@ -880,6 +881,25 @@ extern "C" int srt_trace_rays(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays
   }
   cudaFree(d_rays); cudaFree(d_hit); cudaFree(d_t);
   return rc;
+}
+
+extern "C" int srt_build_bvh(srt_ctx* ctx, const float* centre_xyz, const float* min_xyz, const float* max_xyz,
+                             uint32_t n_prims, srt_bvh_node* nodes_out, uint32_t* n_nodes_out, uint32_t* order_out,
+                             uint32_t* depth_out, float* device_ms_out) {
+  if (!ctx) return 1;
+  if (!n_nodes_out || (n_prims && (!centre_xyz || !min_xyz || !max_xyz || !nodes_out || !order_out)))
+    return fail(ctx, "srt_build_bvh: null argument");
+  if (n_prims > 0x7FFFFFFFu) return fail(ctx, "srt_build_bvh: more than 2^31 - 1 primitives");
+  CU(ctx, cudaSetDevice(ctx->device));
+  BvhBuildResult r;
+  const char* what = "";
+  cudaError_t e = build_bvh_device(centre_xyz, min_xyz, max_xyz, n_prims, nodes_out, order_out, &r, ctx->stream, &what);
+  if (e != cudaSuccess) return fail(ctx, "srt_build_bvh: %s: %s", what, cudaGetErrorString(e));
+  ctx->kernel_launches += r.launches;
+  *n_nodes_out = r.n_nodes;
+  if (depth_out) *depth_out = r.depth;
+  if (device_ms_out) *device_ms_out = r.build_ms;
+  return 0;
 }
 
 extern "C" int srt_get_counters(srt_ctx* ctx, srt_counters* out) {

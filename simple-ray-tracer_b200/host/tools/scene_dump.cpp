@@ -1,10 +1,13 @@
-// scene_dump.cpp -- writes the five scene arrays the HOST loader would upload for one OBJ, in the container format
+// scene_dump.cpp -- writes the five scene arrays the HOST loader would upload for one OBJ -- or for several, names
+// separated by commas, flattened in that order the way UploadModelDataToGPU does -- in the container format
 // of the checker's reference dump (magic "SRTREF01", then five length-prefixed buffers: BVH ranges, nodes,
 // materials, triangles, vertices).  tests/ compare this byte for byte with the fixture made from the reference's own
 // loader.  CPU only.
 #include <cstdint>
 #include <cstdio>
+#include <algorithm>
 #include <exception>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -18,8 +21,15 @@ int main(int argc, char** argv) {
   }
   try {
     AssetUtils::SetObjectFolder(argv[1]);
-    auto model = AssetUtils::LoadObject(argv[2]);
-    std::vector<AssetUtils::Model*> models{model.get()};
+    std::vector<std::unique_ptr<AssetUtils::Model>> owned;
+    std::vector<AssetUtils::Model*> models;
+    const std::string names = argv[2];
+    for (std::size_t at = 0; at <= names.size();) {
+      const std::size_t comma = std::min(names.find(',', at), names.size());
+      owned.push_back(AssetUtils::LoadObject(names.substr(at, comma - at)));
+      models.push_back(owned.back().get());
+      at = comma + 1;
+    }
     const AssetUtils::FlatScene flat = AssetUtils::FlattenModels(models);
     std::FILE* f = std::fopen(argv[3], "wb");
     if (!f) {
@@ -37,8 +47,10 @@ int main(int argc, char** argv) {
     put(flat.triangles.data(), flat.triangles.size() * sizeof(srt_triangle));
     put(flat.vertices.data(), flat.vertices.size() * sizeof(srt_vertex));
     std::fclose(f);
-    std::fprintf(stderr, "%s: %zu nodes (depth %u), %zu triangles, %zu materials\n", argv[2], flat.nodes.size(),
-                 model->model_bvh.Depth(), flat.triangles.size(), flat.materials.size());
+    std::uint32_t depth = 0;
+    for (const AssetUtils::Model* m : models) depth = std::max(depth, m->model_bvh.Depth());
+    std::fprintf(stderr, "%s: %zu nodes (depth %u), %zu triangles, %zu materials\n", argv[2], flat.nodes.size(), depth,
+                 flat.triangles.size(), flat.materials.size());
   } catch (const std::exception& e) {
     std::fprintf(stderr, "scene_dump: %s\n", e.what());
     return 1;

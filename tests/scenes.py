@@ -101,6 +101,19 @@ def read_scene_dump(path):
     return dict(zip(("bvhs", "nodes", "materials", "triangles", "vertices"), out))
 
 
+def concat_scenes(a, b):
+    """Two flattened scenes as one upload, indices of the second rebased the way UploadModelDataToGPU does
+    (gpu_loader.cpp:120-130)."""
+    b = {k: v.copy() for k, v in b.items()}
+    b["triangles"]["v"] += len(a["vertices"])
+    b["triangles"]["material"] += len(a["materials"])
+    leaf = b["nodes"]["count"] > 0
+    b["nodes"]["index"][leaf] += len(a["triangles"])
+    b["nodes"]["index"][~leaf] += len(a["nodes"])
+    b["bvhs"]["first_index"] += len(a["nodes"])
+    return {k: np.ascontiguousarray(np.concatenate([a[k], b[k]])) for k in a}
+
+
 def _host_tool(name):
     import subprocess
     exe = os.path.join(HOST_DIR, name)

@@ -188,3 +188,29 @@ def test_missing_obj_reports_error_getting_geo(host_dump, tmp_path):
     (tmp_path / "objects" / "nothing").mkdir(parents=True)
     r = run_host(host_dump, tmp_path / "objects", "nothing", tmp_path, expect_ok=False)
     assert r.returncode == 1 and "error getting geo" in r.stderr  # model_loader.cpp:28-29
+
+
+def test_two_models_flatten_with_rebased_indices(host_dump, tmp_path):
+    """UploadModelDataToGPU over several models (gpu_loader.cpp:63-133): arrays appended in order, triangle corners
+    rebased by the vertices before, materials by the materials before, leaves by the triangles before, inner nodes by
+    the nodes before; one BVH range per model."""
+    import sys
+    sys.path.insert(0, scenes.GOLDEN)
+    import make_scene_golden as M
+    write_obj(tmp_path, "first", np.random.default_rng(11), 300, 60)
+    write_obj(tmp_path, "second", np.random.default_rng(12), 120, 10, cluster=True)
+    one = {n: run_host(host_dump, tmp_path / "objects", n, tmp_path) for n in ("first", "second")}
+    both = run_host(host_dump, tmp_path / "objects", "first,second", tmp_path)
+    dts = {"bvhs": M.BVH_DT, "nodes": M.NODE_DT, "materials": M.MAT_DT, "triangles": M.TRI_DT, "vertices": M.VERT_DT}
+    a = {k: np.frombuffer(one["first"][k], dts[k]) for k in NAMES}
+    b = {k: np.frombuffer(one["second"][k], dts[k]).copy() for k in NAMES}
+    got = {k: np.frombuffer(both[k], dts[k]) for k in NAMES}
+    b["triangles"]["v"] += len(a["vertices"])
+    b["triangles"]["material"] += len(a["materials"])
+    leaf = b["nodes"]["count"] > 0
+    b["nodes"]["index"][leaf] += len(a["triangles"])
+    b["nodes"]["index"][~leaf] += len(a["nodes"])
+    b["bvhs"]["first_index"] += len(a["nodes"])
+    for k in NAMES:
+        assert np.concatenate([a[k], b[k]]).tobytes() == got[k].tobytes(), k
+    assert len(got["bvhs"]) == 2 and got["bvhs"]["count"].tolist() == [len(a["nodes"]), len(b["nodes"])]

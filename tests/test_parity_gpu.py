@@ -160,6 +160,50 @@ def test_airplane_standin_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     assert bad.mean() <= 1e-4 and (ids2 != oids).mean() <= 1e-4  # documented grazing ties only
 
 
+def framed(scale, rot_y_deg, translate):
+    """World -> model matrix of a model placed with (scale, rotation about y, translation), column-major like
+    BVH.frame (raytrace_types.glsl:37): the inverse of T * R * S."""
+    c, s_ = np.cos(np.radians(rot_y_deg)), np.sin(np.radians(rot_y_deg))
+    R = np.array([[c, 0, s_, 0], [0, 1, 0, 0], [-s_, 0, c, 0], [0, 0, 0, 1]], np.float64)
+    S = np.diag([scale, scale, scale, 1.0])
+    T = np.eye(4)
+    T[:3, 3] = translate
+    return np.linalg.inv(T @ R @ S).astype(np.float32).T.reshape(16).copy()
+
+
+@pytest.mark.parametrize("schedule", [0, 2, 3])
+def test_two_models_with_frames_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
+    """SURVEY 8(f) N4: bvh_count = 2, each model behind its own world->model frame (raytrace_compute.glsl:144-161);
+    the closest hit is taken over both, t shared between model spaces as the shader does (Q14).  Then one frame is
+    replaced through UpdateModelMatrix (gpu_loader.cpp:185-196) and the picture must follow."""
+    name, _ = scenes.write_airplane_standin(str(tmp_path), detail=24)
+    scene = scenes.concat_scenes(scenes.rubik_scene(), scenes.load_obj_scene(str(tmp_path), name, str(tmp_path)))
+    assert len(scene["bvhs"]) == 2
+    scene["bvhs"]["frame"][0] = framed(0.6, 30.0, (-7.0, 2.0, 0.0))
+    scene["bvhs"]["frame"][1] = framed(1.3, -20.0, (6.0, 1.0, 5.0))
+    for mode in (pkg.TRAV_REFERENCE,):
+        acc, out, ids, cnt = gpu_render(pkg, ctx, 256, 128, True, 3, mode, scene=scene, schedule=schedule)
+        oacc, oout, oids, ocnt = cpu_render(oracle, 256, 128, True, 3, scene=scene)
+        first = int(scene["bvhs"]["count"][0])
+        tri_split = int(scene["nodes"]["index"][first:][scene["nodes"]["count"][first:] > 0].min())
+        seen = oids[oids != pkg.NO_HIT]
+        assert (seen < tri_split).any() and (seen >= tri_split).any()  # both models are in the picture
+        assert np.array_equal(ids, oids)
+        assert_bit_exact(acc, oacc)
+        assert np.array_equal(out, oout)
+        assert cnt["segments"] == ocnt["segments"] and cnt["shadow_rays"] == ocnt["shadow_rays"]
+    moved = framed(1.3, 75.0, (2.0, 4.0, -3.0))
+    ctx.update_frame(1, moved)
+    ctx.resize(256, 128)  # fresh (zeroed) accumulation image
+    ctx.enable_primary_ids(True)
+    ctx.set_params(pkg.make_params(256, 128, scenes.reset_camera(True), True, accum_frames=1, bvh_count=2))
+    ctx.render(2)
+    scene["bvhs"]["frame"][1] = moved
+    oacc2, _, oids2, _ = cpu_render(oracle, 256, 128, True, 2, scene=scene)
+    assert np.array_equal(ctx.read_primary_ids(), oids2) and not np.array_equal(oids2, oids)
+    assert_bit_exact(ctx.read_accum(), oacc2)
+
+
 def test_soup_depth8_bit_exact(pkg, ctx, oracle, tmp_path):
     """BASELINE.json configs[4] at a size the oracle finishes in seconds: random soup, maxDepth 8, camera (0,0,120)."""
     scene, info = scenes.soup_scene(20000, str(tmp_path))
