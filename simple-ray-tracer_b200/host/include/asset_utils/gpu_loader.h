@@ -28,6 +28,13 @@ void UpdateRays(std::uint32_t ray_count, const Common::Ray* ray_buffer);
 // test kernel (ray_intersects.glsl:135-161).  hit[i] = global triangle index or SRT_NO_HIT.
 void TraceRays(std::uint32_t bvh_count, std::vector<std::uint32_t>* hit, std::vector<float>* distance = nullptr);
 
+// Builds every BVH constructed from now on (LoadObject, BVH<Prim>(...)) on the device of the current context through
+// srt_build_bvh instead of on the host: same arrays, byte for byte (include/intersection_utils/bvh.h:40-148 is what both
+// restate).  min_prims: smaller inputs stay on the host (a level costs about ten launches).  on = false restores the
+// host builder.  last_ms, if given, receives the device time of the most recent build.
+void UseDeviceBVHBuilder(bool on, std::uint32_t min_prims = 4096);
+float LastDeviceBVHBuildMs();
+
 // The flattened arrays of the last upload, exactly as handed to the C-ABI (for tools and tests).
 struct FlatScene {
   std::vector<srt_bvh> bvhs;

@@ -37,6 +37,17 @@ struct BVHNode {
   bool IsLeaf() const { return prim_count > 0; }
 };
 
+// Optional builder behind the same constructor: given the per-primitive centres and boxes it fills the node array
+// (tree-relative indices), the primitive order (order[k] = input index of the primitive that ends up k-th) and the
+// depth, and returns true; false (or no builder installed) means "build here".  AssetUtils::UseDeviceBVHBuilder
+// installs srt_build_bvh, whose output is byte-identical to the loop below (tests/test_bvh_build_gpu.py).
+using ExternalBuildFn = bool (*)(const float* centre_xyz, const float* min_xyz, const float* max_xyz, std::uint32_t n,
+                                 std::vector<BVHNode>* nodes, std::vector<std::uint32_t>* order, std::uint32_t* depth);
+inline ExternalBuildFn& ExternalBuilder() {
+  static ExternalBuildFn fn = nullptr;
+  return fn;
+}
+
 template <class Prim>
 class BVH {
  public:
@@ -56,6 +67,12 @@ class BVH {
       hi[p] = box.second;
     }
     std::vector<std::uint32_t> order(n);
+    static_assert(sizeof(glm::vec3) == 3 * sizeof(float), "vec3 arrays are passed on as xyz triples");
+    if (ExternalBuilder() != nullptr &&
+        ExternalBuilder()(&centre[0].x, &lo[0].x, &hi[0].x, static_cast<std::uint32_t>(n), &bvh_, &order, &depth_)) {
+      Reorder(order);
+      return;
+    }
     for (std::size_t p = 0; p < n; ++p) order[p] = static_cast<std::uint32_t>(p);
 
     bvh_.resize(2 * n - 1);
@@ -112,10 +129,7 @@ class BVH {
     }
     bvh_.resize(used);
 
-    std::vector<Prim> in_leaf_order;
-    in_leaf_order.reserve(n);
-    for (std::uint32_t p : order) in_leaf_order.push_back(std::move(primatives_[p]));
-    primatives_ = std::move(in_leaf_order);
+    Reorder(order);
   }
 
   const std::vector<BVHNode>& GetBVH() const { return bvh_; }
@@ -124,6 +138,13 @@ class BVH {
   std::uint32_t Depth() const { return depth_; }
 
  private:
+  void Reorder(const std::vector<std::uint32_t>& order) {
+    std::vector<Prim> in_leaf_order;
+    in_leaf_order.reserve(order.size());
+    for (std::uint32_t p : order) in_leaf_order.push_back(std::move(primatives_[p]));
+    primatives_ = std::move(in_leaf_order);
+  }
+
   void Fit(const std::vector<std::uint32_t>& order, const std::vector<glm::vec3>& lo, const std::vector<glm::vec3>& hi,
            std::uint32_t node_idx) {
     BVHNode& node = bvh_[node_idx];

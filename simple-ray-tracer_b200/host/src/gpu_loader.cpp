@@ -53,4 +53,40 @@ void TraceRays(std::uint32_t bvh_count, std::vector<std::uint32_t>* hit, std::ve
 
 const FlatScene& LastUploadedScene() { return g_scene; }
 
+namespace {
+std::uint32_t g_device_bvh_min_prims = 4096;
+float g_device_bvh_ms = 0.0f;
+
+bool BuildOnDevice(const float* centre, const float* lo, const float* hi, std::uint32_t n,
+                   std::vector<IntersectionUtils::BVHNode>* nodes, std::vector<std::uint32_t>* order,
+                   std::uint32_t* depth) {
+  if (n < g_device_bvh_min_prims) return false;
+  srt_ctx* ctx = SrtHost::Current();
+  std::vector<srt_bvh_node> flat(2 * static_cast<std::size_t>(n) - 1);
+  std::uint32_t n_nodes = 0;
+  SrtHost::Check(srt_build_bvh(ctx, centre, lo, hi, n, flat.data(), &n_nodes, order->data(), depth, &g_device_bvh_ms), ctx,
+                 "BVH build on the device");
+  nodes->resize(n_nodes);
+  for (std::uint32_t i = 0; i < n_nodes; ++i) {
+    IntersectionUtils::BVHNode& out = (*nodes)[i];
+    const srt_bvh_node& in = flat[i];
+    out.min_bounds = glm::vec3(in.min_bounds[0], in.min_bounds[1], in.min_bounds[2]);
+    out.max_bounds = glm::vec3(in.max_bounds[0], in.max_bounds[1], in.max_bounds[2]);
+    out.prim_count = in.prim_count;
+    out.first_child = in.prim_count ? 0u : in.first_child_or_prim_index;
+    out.first_prim_index = in.prim_count ? in.first_child_or_prim_index : 0u;
+  }
+  // the host builder leaves an inner node's first_prim_index at the start of its span (= its left child's)
+  for (std::uint32_t i = n_nodes; i-- > 0;)
+    if (!(*nodes)[i].IsLeaf()) (*nodes)[i].first_prim_index = (*nodes)[(*nodes)[i].first_child].first_prim_index;
+  return true;
+}
+}  // namespace
+
+void UseDeviceBVHBuilder(bool on, std::uint32_t min_prims) {
+  g_device_bvh_min_prims = min_prims;
+  IntersectionUtils::ExternalBuilder() = on ? &BuildOnDevice : nullptr;
+}
+float LastDeviceBVHBuildMs() { return g_device_bvh_ms; }
+
 }  // namespace AssetUtils

@@ -9,6 +9,7 @@
 //                [--out FILE.ppm] [--device D] [--seed S] [--max-depth D] [--pose x y z yaw pitch]
 //                [--noise FILE]   raw fp32: W*H unit vectors (xyz) then W*H uniform triples, instead of std::rand()
 //                [--accum FILE]   also write the RGBA32F accumulation image as raw fp32
+//                [--device-bvh]   build the model's BVH on the device (same bytes as the host builder)
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -41,6 +42,7 @@ struct Options {
   std::string out = "out.ppm";
   std::string noise_file, accum_file;
   bool pose = false;
+  bool device_bvh = false;  // build the model's BVH with srt_build_bvh instead of on the host
   float px = 0, py = 0, pz = 0, yaw = -90, pitch = 0;
 };
 }  // namespace
@@ -69,6 +71,7 @@ int main(int argc, char** argv) {
     else if (a == "--out") { o.out = val(); ++i; }
     else if (a == "--noise") { o.noise_file = val(); ++i; }
     else if (a == "--accum") { o.accum_file = val(); ++i; }
+    else if (a == "--device-bvh") o.device_bvh = true;
     else if (a == "--pose") {
       o.pose = true;
       o.px = std::atof(val(1)); o.py = std::atof(val(2)); o.pz = std::atof(val(3));
@@ -123,6 +126,7 @@ int main(int argc, char** argv) {
     if (o.show_model) {
       const auto t0 = std::chrono::steady_clock::now();
       AssetUtils::SetObjectFolder(o.objects);
+      AssetUtils::UseDeviceBVHBuilder(o.device_bvh, 1);
       model = AssetUtils::LoadObject(o.model);
       std::vector<AssetUtils::Model*> models{model.get()};
       AssetUtils::UploadModelDataToGPU(models, 5);
@@ -177,10 +181,10 @@ int main(int argc, char** argv) {
     srt_counters c;
     srt_get_counters(compute.GetProgram(), &c);
     std::printf("{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"frames\": %d, \"ms_per_frame\": %.4f, "
-                "\"segments\": %llu, \"shadow_rays\": %llu, \"mseg_per_s\": %.2f, \"load_s\": %.3f, \"out\": \"%s\"}\n",
+                "\"segments\": %llu, \"shadow_rays\": %llu, \"mseg_per_s\": %.2f, \"load_s\": %.3f, \"bvh\": \"%s\", \"out\": \"%s\"}\n",
                 o.show_model ? o.model.c_str() : "spheres", o.width, o.height, o.frames, render_s * 1e3 / o.frames,
                 (unsigned long long)c.segments, (unsigned long long)c.shadow_rays, c.segments / render_s / 1e6, load_s,
-                o.out.c_str());
+                o.device_bvh ? "device" : "host", o.out.c_str());
   } catch (const std::exception& e) {
     std::fprintf(stderr, "srt_headless: %s\n", e.what());
     return 1;

@@ -1,0 +1,57 @@
+"""GPU test of the host front end: srt_headless -- the reference's frame loop on the
+reference-shaped C++ classes (Compute, Texture, Camera, LoadObject, UploadModelDataToGPU) -- must put the same bits
+into the accumulation image as the oracle does for the same OBJ, noise tables, lights and camera; and building the
+model's BVH on the device (--device-bvh) must not change a byte.
+"""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import scenes
+from test_parity_gpu import assert_bit_exact, cpu_render
+
+pytestmark = pytest.mark.gpu
+
+HOST = os.path.join(scenes.ROOT, "simple-ray-tracer_b200", "host")
+
+
+def run_headless(tmp_path, name, W, H, frames, tag, extra=()):
+    exe = os.path.join(HOST, "srt_headless")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-s", "-C", HOST, "srt_headless"], check=True)
+    accum, ppm = str(tmp_path / (tag + ".accum")), str(tmp_path / (tag + ".ppm"))
+    r = subprocess.run([exe, "--model", name, "--objects", str(tmp_path) + "/", "--width", str(W), "--height", str(H),
+                        "--frames", str(frames), "--batch", "2", "--noise", str(tmp_path / "noise.bin"), "--accum", accum,
+                        "--out", ppm, *extra], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    info = json.loads(r.stdout.strip().splitlines()[-1])
+    return np.fromfile(accum, np.float32).reshape(H, W, 4), open(ppm).read(), info
+
+
+def test_headless_front_end_matches_oracle_and_device_bvh_changes_nothing(oracle, tmp_path):
+    W, H, frames = 256, 128, 3
+    name, n_tri = scenes.write_airplane_standin(str(tmp_path), detail=32)
+    unit, uniform = scenes.noise_tables(W, H)
+    with open(tmp_path / "noise.bin", "wb") as f:
+        f.write(unit.tobytes())
+        f.write(uniform.tobytes())
+    acc_host, ppm_host, info_host = run_headless(tmp_path, name, W, H, frames, "host")
+    acc_dev, ppm_dev, info_dev = run_headless(tmp_path, name, W, H, frames, "dev", ["--device-bvh"])
+    assert info_host["bvh"] == "host" and info_dev["bvh"] == "device"
+    assert acc_host.tobytes() == acc_dev.tobytes() and ppm_host == ppm_dev
+    assert info_host["segments"] == info_dev["segments"]
+
+    scene = scenes.load_obj_scene(str(tmp_path), name, str(tmp_path))
+    assert len(scene["triangles"]) == n_tri
+    oacc, oout, _, ocnt = cpu_render(oracle, W, H, True, frames, scene=scene, noise=(unit, uniform))
+    assert_bit_exact(acc_host, oacc)
+    assert info_host["segments"] == ocnt["segments"] and info_host["shadow_rays"] == ocnt["shadow_rays"]
+    # the PPM (P3) holds the RGBA8 picture the oracle tonemaps, top row first (raytracer.cpp WritePPM)
+    tok = ppm_host.split()
+    assert tok[0] == "P3" and int(tok[1]) == W and int(tok[2]) == H and int(tok[3]) == 255
+    rgb = np.array(tok[4:], np.int64).reshape(H, W, 3)
+    want = oout[..., :3].astype(np.int64)
+    assert np.array_equal(rgb, want[::-1])
