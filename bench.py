@@ -137,21 +137,24 @@ def oracle_run(inp, first_frame, n_frames, threads=0):
 def run_reference(args):
     """--impl reference: the reference's own implementation of the path cannot run here (GLSL, no GL stack), so this
     arm times the committed CPU restatement of the shader (kind "port") on all host cores; each step is a bounded
-    sample of the workload: ONE frame (1 spp over the whole 1920x1080 image; per-frame cost is stationary)."""
+    sample of the workload: as many whole 1920x1080 frames (1 spp each; per-frame cost is stationary) as fit about five
+    seconds, sized from one calibration frame."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     inp = workload_inputs(args.workload, args.soup_tris)
     cores = os.cpu_count() or 1
-    for w in range(args.warmup):
-        oracle_run(inp, 1 + w, 1)
+    _, t1, _ = oracle_run(inp, 1, 1)  # calibration (also the first warm-up)
+    per_step = max(1, min(inp["spp"], int(5.0 / max(t1, 1e-3))))
+    for w in range(max(args.warmup - 1, 0)):
+        oracle_run(inp, 1 + w, per_step)
     secs, segs = 0.0, 0
     for k in range(args.steps):
-        _, dt, cnt = oracle_run(inp, 1 + args.warmup + k, 1)
+        _, dt, cnt = oracle_run(inp, 1 + (args.warmup + k) * per_step, per_step)
         secs += dt
         segs += cnt["segments"]
     value = segs / secs / 1e6
-    sample = "1 frame (1 spp) of the %d-spp workload per step, whole 1920x1080 image" % inp["spp"]
+    sample = "%d frame(s) (1 spp each) of the %d-spp workload per step, whole 1920x1080 image" % (per_step, inp["spp"])
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
@@ -357,8 +360,18 @@ def run_gpu(args):
     scene_mb = 0.0
     if inp["scene"] is not None:
         scene_mb = (32 * len(inp["scene"]["nodes"]) + 48 * len(inp["scene"]["triangles"])) / 1e6
+    # DRAM bytes per launch of the same kernel from the committed ncu pass over one step's launches (never measured in
+    # this run: numbers taken under a profiler are not bench values; the pass is per workload)
+    traffic, traffic_extra = None, {}
+    tf = os.path.join(ROOT, "profiles", "r01f_trace_dram_bytes.json")
+    if wavefront and world == 1 and args.workload == "rubik" and os.path.exists(tf):
+        t = json.load(open(tf))
+        traffic = t["dram_bytes_per_launch"]
+        traffic_extra = {"traffic_source": "profiles/r01f_trace_dram_bytes.json (dram__bytes_read.sum + dram__bytes_write.sum, "
+                                           "mean over the %d wf_trace_kernel launches of the pass)" % t["launches"],
+                         "l2_bytes_per_launch": t["l2_bytes_per_launch"], "l1_bytes_per_launch": t["l1_bytes_per_launch"]}
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"] * world, "unit": "GB/s",
-                "frac": achieved / (peaks["hbm_gbs"] * world), "traffic": None,
+                "frac": achieved / (peaks["hbm_gbs"] * world), "traffic": traffic,
                 "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs, burst copy figure, x n_gpus)",
                 "kernel": kname, "kernel_launches": k_launches, "kernel_ms_total": k_ms,
                 "bytes_per_launch": rays * bytes_per_ray / k_launches, "ms_per_launch": k_ms / k_launches,
@@ -370,13 +383,18 @@ def run_gpu(args):
                         "launching stream (max over ranks; achieved and peak are whole-job). A scene smaller than the "
                         "126 MB L2 is served from L1/L2, so the figure is then on-chip gather bandwidth quoted against the "
                         "HBM copy peak (it may exceed 1), not DRAM traffic; see profiles/ for dram__bytes"}
+    roofline.update(traffic_extra)
 
     cpu_baseline = None
     if world == 1 and not args.no_cpu:
-        v, dt, c = oracle_run(inp, 1, args.cpu_frames)
+        n_cpu = args.cpu_frames
+        if n_cpu <= 0:  # about 15 s of CPU work, sized from one calibration frame
+            _, t1, _ = oracle_run(inp, 1, 1)
+            n_cpu = max(1, min(inp["spp"], int(15.0 / max(t1, 1e-3))))
+        v, dt, c = oracle_run(inp, 1, n_cpu)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
-                        "sample": "%d frame(s) (1 spp each) of the workload, whole image, %.1f s" % (args.cpu_frames, dt),
-                        "ms_per_frame": dt / args.cpu_frames * 1e3}
+                        "sample": "%d of the workload's %d frames (1 spp each), whole image, %.1f s" % (n_cpu, inp["spp"], dt),
+                        "ms_per_frame": dt / n_cpu * 1e3}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -409,7 +427,8 @@ def main():
     ap.add_argument("--traversal", default="ordered", choices=["ordered", "reference"])
     ap.add_argument("--block", type=int, default=64)
     ap.add_argument("--schedule", default="wavefront", choices=["wavefront", "persistent", "regen", "per-path"])
-    ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the workload the CPU baseline renders")
+    ap.add_argument("--cpu-frames", type=int, default=0,
+                    help="frames of the workload the CPU baseline renders (0 = as many as fit about 15 s)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
     ap.add_argument("--l2-persist", type=int, default=-1, help="1/0: pin the BVH top levels in L2 (default: library default, on)")
