@@ -345,9 +345,9 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   // warp-private ranges of the output queues, reserved append_chunk entries at a time (one atomic each); what is left
   // of a range when the warp moves on is filled with holes, which the consumers skip
   uint32_t c_next = 0, c_end = 0, s_next = 0, s_end = 0;
-  // a warp that handles few entries reserves as little: the tail waves keep the exact one-atomic-per-32 behaviour
-  uint32_t append_chunk = (chunks_a + chunks_b + n_warps - 1u) / n_warps * 32u;
-  append_chunk = append_chunk > SRT_WF_APPEND_CHUNK ? SRT_WF_APPEND_CHUNK : append_chunk;
+  // a warp that makes no more than four turns reserves exactly what each turn emits (append_chunk = 0): no holes in
+  // the small waves, whose atomics do not contend anyway
+  const uint32_t append_chunk = (chunks_a + chunks_b) > 4u * n_warps ? SRT_WF_APPEND_CHUNK : 0u;
 
   for (uint32_t g = warp; g < chunks_a + chunks_b; g += n_warps) {
     const bool region_a = g < chunks_a;  // warp-uniform: which queue this chunk belongs to
@@ -513,9 +513,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       if (c_next + m > c_end) {
         for (uint32_t i = c_next + lane; i < c_end; i += 32) list_out[i] = SRT_WF_HOLE;
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(&q->n_closest[parity ^ 1], append_chunk);
+        const uint32_t want = append_chunk ? append_chunk : m;
+        if (lane == 0) base = atomicAdd(&q->n_closest[parity ^ 1], want);
         c_next = __shfl_sync(FULL, base, 0);
-        c_end = c_next + append_chunk;
+        c_end = c_next + want;
       }
       if (emit_closest) list_out[c_next + __popc(m_c & lt_mask)] = slot;
       c_next += m;
@@ -526,9 +527,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       if (s_next + m > s_end) {
         for (uint32_t i = s_next + lane; i < s_end; i += 32) list_out[pool.list_cap - 1u - i] = SRT_WF_HOLE;
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(&q->n_shadow[parity ^ 1], append_chunk);
+        const uint32_t want = append_chunk ? append_chunk : m;
+        if (lane == 0) base = atomicAdd(&q->n_shadow[parity ^ 1], want);
         s_next = __shfl_sync(FULL, base, 0);
-        s_end = s_next + append_chunk;
+        s_end = s_next + want;
       }
       if (emit_shadow) list_out[pool.list_cap - 1u - (s_next + __popc(m_s & lt_mask))] = slot;
       s_next += m;
