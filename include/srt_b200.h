@@ -57,6 +57,11 @@ typedef struct srt_counters {
 #define SRT_OPT_TIME_KERNELS 9    /* wavefront schedule: 1 = bracket every trace / logic launch with CUDA events on the launching
                                      stream (read with srt_get_kernel_times) */
 
+#define SRT_OPT_TEXTURES 10       /* 1 = materials with use_texture sample the image given by srt_set_texture at the interpolated
+                                     texture coordinate (raytrace_utils.glsl:145-167 with real handles and coordinates; arithmetic in
+                                     srt_texmath.h).  0 (default) = the decree for the reference as shipped: albedo = Kd (Q7).
+                                     Schedules 0 and 3 only. */
+
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */
 int srt_create(srt_ctx** out, int device);
@@ -74,6 +79,11 @@ int srt_set_option(srt_ctx* ctx, int key, int value);
 int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* nodes, uint32_t n_nodes,
                      const srt_material* materials, uint32_t n_materials, const srt_triangle* triangles,
                      uint32_t n_triangles, const srt_vertex* vertices, uint32_t n_vertices);
+
+/* AssetUtils::GPUTexture::GPUTexture(file, true) + GetHandle()  (include/asset_utils/gpu_texture.h:24-68,133-137) for the
+ * material `material_index` of the uploaded scene: the decoded image, RGBA8, row 0 first, REPEAT / LINEAR like the
+ * reference's sampler.  Takes effect with SRT_OPT_TEXTURES = 1; a new srt_upload_scene forgets every texture. */
+int srt_set_texture(srt_ctx* ctx, uint32_t material_index, const uint8_t* rgba8, uint32_t width, uint32_t height);
 
 /* AssetUtils::UpdateModelMatrix  (src/asset_utils/gpu_loader.cpp:185-196): glBufferSubData of bvhs[index].frame,
  * 16 floats column-major. */

@@ -102,6 +102,40 @@ def render(params, n_frames, scene, noise_unit, noise_uniform, lights, accum=Non
     return accum, out, ids, cnt.as_dict()
 
 
+_texture_keepalive = []
+
+
+def set_textures(textures):
+    """Textured-albedo option: [(material index, uint8 array [H,W,4], row 0 first), ...]; [] restores decree Q7."""
+    global _texture_keepalive
+    imgs = [np.ascontiguousarray(img, np.uint8) for _, img in textures]
+    n = len(imgs)
+    mat = (C.c_uint32 * max(n, 1))(*[m for m, _ in textures])
+    w = (C.c_uint32 * max(n, 1))(*[i.shape[1] for i in imgs])
+    h = (C.c_uint32 * max(n, 1))(*[i.shape[0] for i in imgs])
+    ptr = (C.c_void_p * max(n, 1))(*[i.ctypes.data for i in imgs])
+    _texture_keepalive = imgs
+    if lib().oracle_set_textures(mat, w, h, ptr, C.c_int(n)) != 0:
+        raise RuntimeError("oracle_set_textures failed")
+
+
+def tex_bilinear(image, s, t):
+    image = np.ascontiguousarray(image, np.uint8)
+    s = np.ascontiguousarray(s, np.float32)
+    t = np.ascontiguousarray(t, np.float32)
+    out = np.zeros((len(s), 3), np.float32)
+    lib().oracle_tex_bilinear(_p(image), C.c_uint32(image.shape[1]), C.c_uint32(image.shape[0]), _p(s), _p(t),
+                              C.c_uint32(len(s)), _p(out))
+    return out
+
+
+def tex_uv(v0, v1, v2, p, uv6):
+    a = [np.ascontiguousarray(x, np.float32) for x in (v0, v1, v2, p, uv6)]
+    out = np.zeros(2, np.float32)
+    lib().oracle_tex_uv(*[_p(x) for x in a], _p(out))
+    return out
+
+
 def trace_rays(scene, rays, bvh_count=1):
     rays = np.ascontiguousarray(rays)
     n = len(rays)

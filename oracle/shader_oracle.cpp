@@ -29,6 +29,7 @@
 #include <vector>
 
 #include "srt_detmath.h"
+#include "srt_texmath.h"
 #include "srt_types.h"
 
 using namespace srt;
@@ -172,12 +173,32 @@ float shadowedF90(V3 F0) {  // raytrace_utils.glsl:131-137
   return min_(1.0f, t * luminance(F0));
 }
 
-void TriangleToSupportedMat(const Inv& g, const srt_triangle& tri, V3 /*intersect_point*/, Material& out_mat) {
+// Textured-albedo OPTION (include/srt_texmath.h): images bound to materials by
+// oracle_set_textures.  Empty table = the default, decree Q7.
+struct OracleTexture {
+  uint32_t material, width, height;
+  const uint8_t* rgba8;
+};
+std::vector<OracleTexture> g_textures;
+
+void TriangleToSupportedMat(const Inv& g, const srt_triangle& tri, V3 intersect_point, Material& out_mat) {
   // raytrace_utils.glsl:140-175
   const srt_material& in_mat = g.materials[tri.material_idx];
   // DECREE Q7: the textured branch (:145-167) samples through a truncated bindless handle (undefined);
-  // albedo = Kd whether or not use_texture is set.
+  // albedo = Kd whether or not use_texture is set -- unless the option supplies a real image for the material.
   out_mat.albedo = ld3(in_mat.diffuse);
+  if (in_mat.use_texture != 0) {
+    for (const OracleTexture& tex : g_textures) {
+      if (tex.material != tri.material_idx) continue;
+      const srt_vertex &t0 = g.vertices[tri.v0_idx], &t1 = g.vertices[tri.v1_idx], &t2 = g.vertices[tri.v2_idx];
+      V3 v0v1 = ld3(t1.vertex) - ld3(t0.vertex);  // :150-151
+      V3 v0v2 = ld3(t2.vertex) - ld3(t0.vertex);
+      float s_, t_;
+      tex_barycentric_uv(ld3(t0.vertex), v0v1, v0v2, intersect_point, t0.texture[0], t0.texture[1], t1.texture[0],
+                         t1.texture[1], t2.texture[0], t2.texture[1], &s_, &t_);  // :152-164
+      out_mat.albedo = tex_bilinear(tex.rgba8, (int)tex.width, (int)tex.height, s_, t_);  // :165-166
+    }
+  }
   out_mat.specular = ld3(in_mat.specular);
   out_mat.roughness = 1 / (in_mat.specular_ex + 0.0000001f);
   out_mat.metalness = 0.1f;
@@ -788,6 +809,30 @@ typedef struct oracle_counters {
   uint64_t segments, shadow_rays, nodes, tris, accepted, noise_lookups, capped_paths, nan_pixels;
   uint64_t path_len_hist[16];
 } oracle_counters;
+
+// Textured-albedo option: binds n images (RGBA8, row 0 first) to materials; n = 0 restores the default (decree Q7).
+// The pixel pointers must stay valid while oracle_render runs.  Later entries for the same material win.
+int oracle_set_textures(const uint32_t* material, const uint32_t* width, const uint32_t* height,
+                        const uint8_t* const* rgba8, int n) {
+  g_textures.clear();
+  for (int i = 0; i < n; ++i) g_textures.push_back(OracleTexture{material[i], width[i], height[i], rgba8[i]});
+  return 0;
+}
+
+// Known-answer hooks for include/srt_texmath.h.
+void oracle_tex_bilinear(const uint8_t* rgba8, uint32_t width, uint32_t height, const float* s, const float* t, uint32_t n,
+                         float* rgb_out) {
+  for (uint32_t i = 0; i < n; ++i) {
+    V3 c = tex_bilinear(rgba8, (int)width, (int)height, s[i], t[i]);
+    rgb_out[3 * i] = c.x;
+    rgb_out[3 * i + 1] = c.y;
+    rgb_out[3 * i + 2] = c.z;
+  }
+}
+void oracle_tex_uv(const float* v0, const float* v1, const float* v2, const float* p, const float* uv6, float* st_out) {
+  tex_barycentric_uv(ld3(v0), ld3(v1) - ld3(v0), ld3(v2) - ld3(v0), ld3(p), uv6[0], uv6[1], uv6[2], uv6[3], uv6[4], uv6[5],
+                     &st_out[0], &st_out[1]);
+}
 
 // Renders frames accum_frames .. accum_frames+n_frames-1 (one dispatch each, like src/main.cpp:657-706)
 // over rows [y0, y1) into accum (W*H*4 fp32, read-modify-write) and out_rgba8 (W*H*4, may be NULL).

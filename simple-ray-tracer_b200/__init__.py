@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsrt_b200.so")
 
 OPT_TRAVERSAL, OPT_COUNT_TRAVERSAL, OPT_L2_PERSIST, OPT_BLOCK_THREADS, OPT_SCHEDULE = 1, 2, 3, 4, 5
-OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS = 6, 7, 8, 9
+OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS, OPT_TEXTURES = 6, 7, 8, 9, 10
 SCHED_PER_PATH, SCHED_REGEN, SCHED_PERSISTENT, SCHED_WAVEFRONT = 0, 1, 2, 3
 TRAV_REFERENCE, TRAV_ORDERED = 0, 1
 NO_HIT = 0xFFFFFFFF
@@ -32,7 +32,7 @@ RAY_DT = np.dtype([("origin", "<f4", 3), ("_pad0", "<f4"), ("direction", "<f4", 
 EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt_set_option", "srt_upload_scene",
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
-           "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_build_bvh",
+           "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_build_bvh", "srt_set_texture",
            "srt_get_counters", "srt_get_kernel_times", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
 
 
@@ -198,6 +198,13 @@ class Context:
         t = np.empty(len(rays), np.float32)
         self._ck(self._lib.srt_trace_rays(self._h, _p(rays), C.c_uint32(len(rays)), C.c_uint32(bvh_count), _p(hit), _p(t)))
         return hit, t
+
+    def set_texture(self, material_index, image):
+        """image: uint8 [H, W, 4], row 0 first (takes effect with OPT_TEXTURES = 1)."""
+        image = np.ascontiguousarray(image, np.uint8)
+        assert image.ndim == 3 and image.shape[2] == 4
+        self._ck(self._lib.srt_set_texture(self._h, C.c_uint32(material_index), _p(image), C.c_uint32(image.shape[1]),
+                                           C.c_uint32(image.shape[0])))
 
     def build_bvh(self, centre, lo, hi):
         """Device build of the reference's BVH (bvh.h:40-148) from per-primitive centres and boxes.

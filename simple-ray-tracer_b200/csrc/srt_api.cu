@@ -41,6 +41,16 @@ struct srt_ctx {
   TriRecord* d_tris = nullptr;
   MatRecord* d_mats = nullptr;
   BvhRecord* d_bvhs = nullptr;
+  // textured-albedo option (SRT_OPT_TEXTURES; include/srt_texmath.h)
+  bool textures_on = false;
+  TexTri* d_tex_tris = nullptr;            // built by srt_upload_scene when a material says use_texture
+  TexInfo* d_tex_info = nullptr;
+  unsigned char* d_texels = nullptr;
+  std::vector<unsigned char> h_texels;     // RGBA8 of every texture set so far
+  std::vector<TexInfo> h_tex_info;
+  std::vector<uint32_t> h_mat_tex;         // per material: 1 + texture index, 0 = none
+  std::vector<MatRecord> h_mats;
+  bool textures_dirty = false;
   float2* d_noise_xy = nullptr;
   float* d_noise_x = nullptr;
   uint32_t noise_count = 0;
@@ -116,7 +126,7 @@ static void dfree(T*& p) {
 static void free_pool(srt_ctx* ctx) {
   PathPool& p = ctx->pool;
   dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.path); dfree(p.p3);
-  dfree(p.list[0]); dfree(p.list[1]); dfree(p.q); dfree(p.samples);
+  dfree(p.list[0]); dfree(p.list[1]); dfree(p.q); dfree(p.samples); dfree(p.tex);
   p.cap = 0;
   ctx->pool_slots = 0;
   ctx->sample_entries = 0;
@@ -163,6 +173,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris); dfree(ctx->d_mats); dfree(ctx->d_bvhs);
+  dfree(ctx->d_tex_tris); dfree(ctx->d_tex_info); dfree(ctx->d_texels);
   dfree(ctx->d_noise_xy); dfree(ctx->d_noise_x); dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
   dfree(ctx->d_counters);
   free_pool(ctx);
@@ -196,6 +207,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
       if (value < 32 || value > SRT_MAX_BLOCK_THREADS || value % 32) return fail(ctx, "SRT_OPT_BLOCK_THREADS: 32..%d, multiple of 32", SRT_MAX_BLOCK_THREADS);
       ctx->block_threads = value;
       return 0;
+  }
+  if (key == SRT_OPT_TEXTURES) {
+    if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_TEXTURES: 0 or 1");
+    ctx->textures_on = value != 0;
+    return 0;
   }
   if (key == SRT_OPT_TIME_KERNELS) {
     ctx->time_kernels = value != 0;
@@ -238,6 +254,7 @@ struct Relayout {
   std::vector<BvhRecord> bvhs;
   std::vector<uint32_t> rank;       // per triangle: position in the shader's visiting order
   std::vector<uint32_t> remaining;  // per triangle: triangles that follow it in its leaf (0 = last of the leaf)
+  std::vector<uint32_t> tri_bvh;    // per triangle: the (last) BVH whose leaves hold it
   int depth = 0;
 };
 
@@ -247,6 +264,7 @@ bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_
               uint32_t n_tris, Relayout& out) {
   out.rank.assign(n_tris, 0xFFFFFFFFu);
   out.remaining.assign(n_tris, 0u);
+  out.tri_bvh.assign(n_tris, 0u);
   uint32_t next_rank = 0;
   std::vector<uint32_t> seen(n_nodes, 0);  // BVH (1-based) that reached the node
   struct Item { uint32_t node; uint32_t slot; int depth; };  // slot: where to write this node's reference
@@ -276,7 +294,10 @@ bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_
         out.leaves.push_back(make_uint2(n.first_child_or_prim_index, n.prim_count));
         if (n.first_child_or_prim_index >= SRT_LEAF_BIT) return fail(ctx, "too many triangles"), false;
         direct = SRT_LEAF_BIT | n.first_child_or_prim_index;
-        for (uint32_t k = 0; k < n.prim_count; ++k) out.remaining[n.first_child_or_prim_index + k] = n.prim_count - 1 - k;
+        for (uint32_t k = 0; k < n.prim_count; ++k) {
+          out.remaining[n.first_child_or_prim_index + k] = n.prim_count - 1 - k;
+          out.tri_bvh[n.first_child_or_prim_index + k] = b;
+        }
       } else {
         uint32_t c = n.first_child_or_prim_index;
         if ((uint64_t)c + 1 >= n_nodes) return fail(ctx, "node %u: children %u,%u out of range", it.node, c, c + 1), false;
@@ -397,6 +418,32 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
     mats[i].a = make_float4(m.diffuse[0], m.diffuse[1], m.diffuse[2], roughness);
     mats[i].b = make_float4(m.specular[0], m.specular[1], m.specular[2], 0.0f);
   }
+  // textured-albedo option: texture coordinates per triangle + the BVH whose frame gives the model-space hit point
+  bool any_textured = false;
+  for (uint32_t i = 0; i < n_materials; ++i) any_textured = any_textured || materials[i].use_texture != 0;
+  dfree(ctx->d_tex_tris);
+  if (any_textured) {
+    std::vector<TexTri> tt(n_triangles);
+    for (uint32_t i = 0; i < n_triangles; ++i) {
+      const srt_triangle& t = triangles[i];
+      const uint32_t v[3] = {t.v0_idx, t.v1_idx, t.v2_idx};
+      for (int c = 0; c < 3; ++c) {
+        tt[i].uv[2 * c] = vertices[v[c]].texture[0];
+        tt[i].uv[2 * c + 1] = vertices[v[c]].texture[1];
+      }
+      tt[i].bvh = rl.tri_bvh[i];
+      tt[i]._pad = 0;
+    }
+    if (upload_vec(ctx, ctx->d_tex_tris, tt)) return 1;
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  ctx->h_mats = mats;
+  ctx->h_mat_tex.assign(n_materials, 0u);
+  ctx->h_texels.clear();
+  ctx->h_tex_info.clear();
+  ctx->textures_dirty = false;
+  dfree(ctx->d_tex_info);
+  dfree(ctx->d_texels);
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   if (upload_vec(ctx, ctx->d_pairs, rl.pairs) || upload_vec(ctx, ctx->d_leaves, rl.leaves) ||
       upload_vec(ctx, ctx->d_tris, tris) || upload_vec(ctx, ctx->d_mats, mats) || upload_vec(ctx, ctx->d_bvhs, rl.bvhs))
@@ -550,6 +597,41 @@ extern "C" int srt_enable_primary_ids(srt_ctx* ctx, int enable) {
   return 0;
 }
 
+// ---- textured-albedo option ---------------------------------------------------------------------
+namespace {
+int flush_textures(srt_ctx* ctx) {
+  if (!ctx->textures_dirty) return 0;
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  if (upload_vec(ctx, ctx->d_texels, ctx->h_texels) || upload_vec(ctx, ctx->d_tex_info, ctx->h_tex_info)) return 1;
+  std::vector<MatRecord> mats = ctx->h_mats;
+  for (size_t i = 0; i < mats.size(); ++i) memcpy(&mats[i].b.w, &ctx->h_mat_tex[i], 4);
+  if (upload_vec(ctx, ctx->d_mats, mats)) return 1;
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->textures_dirty = false;
+  return 0;
+}
+}  // namespace
+
+extern "C" int srt_set_texture(srt_ctx* ctx, uint32_t material_index, const uint8_t* rgba8, uint32_t width, uint32_t height) {
+  if (!ctx) return 1;
+  if (!ctx->have_scene) return fail(ctx, "srt_set_texture: no scene uploaded");
+  if (material_index >= ctx->n_mats) return fail(ctx, "srt_set_texture: material %u out of range", material_index);
+  if (!rgba8 || width == 0 || height == 0 || width > 32768u || height > 32768u) return fail(ctx, "srt_set_texture: bad image");
+  if (!ctx->d_tex_tris) return fail(ctx, "srt_set_texture: no material of the uploaded scene has use_texture set");
+  TexInfo ti;
+  ti.offset = (uint32_t)(ctx->h_texels.size() / 4);
+  ti.width = width;
+  ti.height = height;
+  ti._pad = 0;
+  const size_t bytes = (size_t)width * height * 4;
+  if (ctx->h_texels.size() + bytes > ((size_t)1 << 34)) return fail(ctx, "srt_set_texture: more than 16 GB of texels");
+  ctx->h_texels.insert(ctx->h_texels.end(), rgba8, rgba8 + bytes);
+  ctx->h_tex_info.push_back(ti);
+  ctx->h_mat_tex[material_index] = (uint32_t)ctx->h_tex_info.size();
+  ctx->textures_dirty = true;
+  return 0;
+}
+
 // ---- dispatch -------------------------------------------------------------------------------
 namespace {
 
@@ -557,6 +639,10 @@ DeviceScene device_scene(const srt_ctx* ctx) {
   DeviceScene sc;
   sc.pairs = ctx->d_pairs; sc.leaves = ctx->d_leaves; sc.tris = ctx->d_tris; sc.mats = ctx->d_mats;
   sc.bvhs = ctx->d_bvhs; sc.noise_unit_xy = ctx->d_noise_xy; sc.noise_uniform_x = ctx->d_noise_x;
+  const bool tex = ctx->textures_on && ctx->d_tex_tris && ctx->d_texels;
+  sc.tex_tris = tex ? ctx->d_tex_tris : nullptr;
+  sc.tex_info = tex ? ctx->d_tex_info : nullptr;
+  sc.texels = tex ? ctx->d_texels : nullptr;
   return sc;
 }
 
@@ -644,6 +730,7 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries) {
     CU(ctx, cudaMalloc(&p.list[1], ctx->pool_list_cap * 4)); CU(ctx, cudaMalloc(&p.q, sizeof(WaveCounters)));
     ctx->pool_slots = slots;
   }
+  if (ctx->textures_on && !p.tex) CU(ctx, cudaMalloc(&p.tex, (size_t)ctx->pool_slots * 16));
   p.cap = slots;
   p.list_cap = (uint32_t)ctx->pool_list_cap;
   if (ctx->sample_entries < sample_entries) {
@@ -771,6 +858,9 @@ extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
   }
   if (n_frames == 0 || ctx->row1 == ctx->row0) return 0;
   if (ctx->params.show_model && apply_l2_window(ctx)) return 1;
+  if (ctx->textures_on && flush_textures(ctx)) return 1;
+  if (ctx->textures_on && ctx->d_texels && ctx->params.show_model && ctx->schedule != SCHED_WAVEFRONT && ctx->schedule != SCHED_PER_PATH)
+    return fail(ctx, "SRT_OPT_TEXTURES: schedules 0 (per path) and 3 (wavefront) sample textures; 1 and 2 do not");
   FrameParams fp;
   fill_frame_params(ctx, n_frames, fp);
   if (ctx->params.show_model && ctx->schedule == SCHED_WAVEFRONT) {

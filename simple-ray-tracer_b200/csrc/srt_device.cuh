@@ -44,7 +44,7 @@ static_assert(sizeof(TriRecord) == 48, "TriRecord is three 16 B fetches");
 // MaterialFromOBJ (raytrace_types.glsl:19-27) after TriangleToSupportedMat (raytrace_utils.glsl:140-175).
 struct MatRecord {
   float4 a;  // albedo (= Kd, decree Q7), roughness = 1/(Ns+1e-7)
-  float4 b;  // specular (= Ks), unused
+  float4 b;  // specular (= Ks), bits: 1 + index of the material's texture (0 = none; textured-albedo option)
 };
 
 // BVH (raytrace_types.glsl:32-38) plus the root's own box (the reference box-tests the root when it pops
@@ -64,7 +64,23 @@ enum { SCHED_PER_PATH = 0, SCHED_REGEN = 1, SCHED_PERSISTENT = 2, SCHED_WAVEFRON
 
 #define SRT_MAX_BVHS 64
 
+// Textured-albedo option (SRT_OPT_TEXTURES, include/srt_texmath.h): per triangle the three texture coordinates and
+// the BVH the triangle belongs to (its frame gives the model-space hit point the shader interpolates at,
+// raytrace_compute.glsl:156-159); per texture where its RGBA8 texels start.
+struct TexTri {
+  float uv[6];
+  uint32_t bvh;
+  uint32_t _pad;
+};
+struct TexInfo {
+  uint32_t offset;  // first texel in DeviceScene::texels
+  uint32_t width, height, _pad;
+};
+
 struct DeviceScene {
+  const TexTri* tex_tris;        // null unless the option is on AND some material has a texture
+  const TexInfo* tex_info;
+  const unsigned char* texels;   // RGBA8
   const NodePair* pairs;
   const uint2* leaves;     // (first triangle, count) per leaf
   const TriRecord* tris;
@@ -124,6 +140,7 @@ struct PathPool {
   float4* pst;   // [2*slot]   throughput.xyz, light weight of the pending shadow ray
                  // [2*slot+1] colour.xyz, bits: depth | rand_index << 8 | iter << 20
   uint2* path;   // (pixel slot, frame of the launch) of the path in this slot  (8 B)
+  float4* tex;   // textured-albedo option only: albedo.xyz of the surface the path stands on, w != 0 when it is textured
   float4* p3;    // while a shadow ray is out: incoming direction.xyz, bits: primitive the path stands on
   uint32_t* list[2];   // list_cap entries each: closest-hit queue from the front, shadow queue from the back
   uint32_t cap;        // slots

@@ -4,6 +4,7 @@
 #pragma once
 
 #include "srt_shade.cuh"
+#include "srt_texture.cuh"
 #include "srt_traverse.cuh"
 
 namespace srt {
@@ -41,6 +42,7 @@ __device__ __forceinline__ bool closest_hit_model(const DeviceScene& sc, const F
   const float4* mp = reinterpret_cast<const float4*>(sc.mats + __float_as_uint(r0.w));
   float4 ma = __ldg(mp), mb = __ldg(mp + 1);
   rec.mat.albedo = v3(ma.x, ma.y, ma.z);
+  textured_albedo(sc, hit, r0, r1, r2, mb, o, d, best, rec.mat.albedo);  // option; decree Q7 (Kd) otherwise
   rec.mat.roughness = ma.w;
   rec.mat.specular = v3(mb.x, mb.y, mb.z);
   rec.mat.metalness = 0.1f;   // raytrace_utils.glsl:172

@@ -364,6 +364,8 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     V3 origin = v3(0.0f), dir = v3(0.0f), throughput = v3(0.0f), color = v3(0.0f);
     int depth = 0, rand_index = 0, iter = 0, li = 0;
     uint32_t hit_prim = SRT_NO_HIT;
+    V3 tex_albedo = v3(0.0f);
+    bool has_tex = false;
     float light_weight = 0.0f, shadow_mult = 1.0f;
     bool shade = false, have_light = false, finish = false, emit_closest = false, emit_shadow = false;
 
@@ -386,6 +388,12 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           finish = true;  // :287-289
         } else {
           hit_prim = h.x;
+          if (sc.tex_tris != nullptr) {  // textured-albedo option: needs the ray as it was traced, so it happens here
+            const float4* tp = reinterpret_cast<const float4*>(sc.tris + hit_prim);
+            const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
+            const float4 mb = __ldg(reinterpret_cast<const float4*>(sc.mats + __float_as_uint(r0.w)) + 1);
+            has_tex = textured_albedo(sc, hit_prim, r0, r1, r2, mb, origin, dir, __uint_as_float(h.y), tex_albedo);
+          }
           origin = (__uint_as_float(h.y) * dir) + origin;  // rec.p (:155)
           if (sample_lights(sc, fp, pix, origin, light_weight, li)) {
             const DeviceLight& l = fp.lights[li];
@@ -396,6 +404,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
             pool.ray[2 * (size_t)slot + 1] = make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8)));
             pool.p3[slot] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(hit_prim));
             pool.pst[2 * (size_t)slot] = make_float4(throughput.x, throughput.y, throughput.z, light_weight);
+            if (sc.tex_tris != nullptr) pool.tex[slot] = make_float4(tex_albedo.x, tex_albedo.y, tex_albedo.z, has_tex ? 1.0f : 0.0f);
             emit_shadow = true;
             n_shadow++;
           } else {
@@ -410,6 +419,11 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         li = (int)(__float_as_uint(b.w) >> 8);
         light_weight = t0.w;
         shadow_mult = (h.x != SRT_NO_HIT) ? 0.0f : 1.0f;
+        if (sc.tex_tris != nullptr) {
+          const float4 ta = pool.tex[slot];
+          tex_albedo = v3(ta.x, ta.y, ta.z);
+          has_tex = ta.w != 0.0f;
+        }
         have_light = true;
         shade = true;
       }
@@ -423,7 +437,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       const float4* mp = reinterpret_cast<const float4*>(sc.mats + __float_as_uint(r0.w));
       const float4 ma = __ldg(mp), mb = __ldg(mp + 1);
       SurfMat mat;
-      mat.albedo = v3(ma.x, ma.y, ma.z);
+      mat.albedo = has_tex ? tex_albedo : v3(ma.x, ma.y, ma.z);
       mat.roughness = ma.w;
       mat.specular = v3(mb.x, mb.y, mb.z);
       mat.metalness = 0.1f;  // raytrace_utils.glsl:172-173

@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 
 
 def gpu_render(pkg, ctx, W, H, show_model, n_frames, traversal, scene=None, lights=None, cam=None, first_frame=1,
-               max_depth=0, noise=None, rows=None, schedule=3):
+               max_depth=0, noise=None, rows=None, schedule=3, textures=None):
     unit, uniform = noise if noise is not None else scenes.noise_tables(W, H)
     lights = lights if lights is not None else (scenes.model_lights() if show_model else scenes.sphere_lights())
     cam = cam or scenes.reset_camera(show_model)
@@ -22,6 +22,8 @@ def gpu_render(pkg, ctx, W, H, show_model, n_frames, traversal, scene=None, ligh
     ctx.set_option(pkg.OPT_SCHEDULE, schedule)
     if scene is not None:
         ctx.upload_scene(scene)
+        for material, image in textures or []:
+            ctx.set_texture(material, image)
     ctx.upload_noise(unit, uniform)
     ctx.set_lights(lights)
     ctx.resize(W, H)
