@@ -1,7 +1,7 @@
 // srt_texture.cuh -- the textured branch of TriangleToSupportedMat (raytrace_utils.glsl:145-167) as an OPTION
 // (SRT_OPT_TEXTURES = 1).  Default behaviour stays decree Q7 (albedo = Kd): the reference's own
 // branch is undefined (truncated handle, all texture coordinates zero).  Arithmetic: include/srt_texmath.h, shared with
-// the oracle.
+// the CPU checker.
 #pragma once
 
 #include "srt_device.cuh"
