@@ -26,6 +26,21 @@ void UploadModelDataToGPU(const std::vector<Model*>& models, std::uint32_t /*bin
                                   g_scene.triangles.data(), static_cast<std::uint32_t>(g_scene.triangles.size()),
                                   g_scene.vertices.data(), static_cast<std::uint32_t>(g_scene.vertices.size())),
                  ctx, "UploadModelDataToGPU");
+  // texture option (asset_utils/gpu_texture.h): the decoded images go to the materials that name them, in the
+  // flattened numbering (materials of earlier models first, gpu_loader.cpp:93-99)
+  SrtHost::Check(srt_set_option(ctx, SRT_OPT_TEXTURES, TexturesEnabled() ? 1 : 0), ctx, "UploadModelDataToGPU");
+  if (TexturesEnabled()) {
+    std::uint32_t material = 0;
+    for (const Model* model : models) {
+      for (const Material& m : model->model_materials) {
+        const GPUTexture::Image* image = m.use_texture ? m.texture.Pixels() : nullptr;
+        if (image != nullptr)
+          SrtHost::Check(srt_set_texture(ctx, material, image->rgba8.data(), image->width, image->height), ctx,
+                         "UploadModelDataToGPU (texture)");
+        ++material;
+      }
+    }
+  }
 }
 
 void UpdateModelMatrix(std::uint32_t index, const glm::mat4& matrix) {

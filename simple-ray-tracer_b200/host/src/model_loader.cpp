@@ -131,8 +131,11 @@ std::unique_ptr<CpuGeometry> ParseOBJ(const std::string& file_path, std::vector<
                   << std::endl;
     } else if (key == "vt") {
       glm::vec2 uv;
-      if (words.Next(&uv.x) && words.Next(&uv.y))
+      if (words.Next(&uv.x) && words.Next(&uv.y)) {
         geo->textures.push_back(uv);
+        // the reference never raises has_texcoords (Q6: every uploaded uv is zero); the texture option does
+        if (TexturesEnabled()) geo->has_texcoords = true;
+      }
       else
         std::cerr << "Failed to read 2 floats for texcoord." << std::endl;
     } else if (key == "f") {

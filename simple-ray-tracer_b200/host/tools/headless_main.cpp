@@ -10,6 +10,7 @@
 //                [--noise FILE]   raw fp32: W*H unit vectors (xyz) then W*H uniform triples, instead of std::rand()
 //                [--accum FILE]   also write the RGBA32F accumulation image as raw fp32
 //                [--device-bvh]   build the model's BVH on the device (same bytes as the host builder)
+//                [--textures]     sample the map_Kd PNGs at the OBJ's vt coordinates (default: albedo = Kd, decree Q7)
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -42,6 +43,7 @@ struct Options {
   std::string out = "out.ppm";
   std::string noise_file, accum_file;
   bool pose = false;
+  bool textures = false;    // decode map_Kd images, honour vt lines, sample them (default: decree Q7, albedo = Kd)
   bool device_bvh = false;  // build the model's BVH with srt_build_bvh instead of on the host
   float px = 0, py = 0, pz = 0, yaw = -90, pitch = 0;
 };
@@ -72,6 +74,7 @@ int main(int argc, char** argv) {
     else if (a == "--noise") { o.noise_file = val(); ++i; }
     else if (a == "--accum") { o.accum_file = val(); ++i; }
     else if (a == "--device-bvh") o.device_bvh = true;
+    else if (a == "--textures") o.textures = true;
     else if (a == "--pose") {
       o.pose = true;
       o.px = std::atof(val(1)); o.py = std::atof(val(2)); o.pz = std::atof(val(3));
@@ -127,6 +130,7 @@ int main(int argc, char** argv) {
       const auto t0 = std::chrono::steady_clock::now();
       AssetUtils::SetObjectFolder(o.objects);
       AssetUtils::UseDeviceBVHBuilder(o.device_bvh, 1);
+      AssetUtils::EnableTextures(o.textures);
       model = AssetUtils::LoadObject(o.model);
       std::vector<AssetUtils::Model*> models{model.get()};
       AssetUtils::UploadModelDataToGPU(models, 5);

@@ -16,10 +16,12 @@
 
 int main(int argc, char** argv) {
   if (argc < 4) {
-    std::fprintf(stderr, "usage: %s <objects folder> <object name> <out.bin>\n", argv[0]);
+    std::fprintf(stderr, "usage: %s <objects folder> <object name[,name...]> <out.bin> [textures]\n", argv[0]);
     return 2;
   }
   try {
+    // a fifth argument "textures" switches the texture option on: vt lines are honoured, map_Kd PNGs are decoded
+    AssetUtils::EnableTextures(argc > 4 && std::string(argv[4]) == "textures");
     AssetUtils::SetObjectFolder(argv[1]);
     std::vector<std::unique_ptr<AssetUtils::Model>> owned;
     std::vector<AssetUtils::Model*> models;

@@ -122,12 +122,59 @@ def _host_tool(name):
     return exe
 
 
-def load_obj_scene(objects_dir, name, workdir):
-    """OBJ -> flattened scene through the product's own loader + BVH builder."""
+def load_obj_scene(objects_dir, name, workdir, textures=False):
+    """OBJ -> flattened scene through the product's own loader + BVH builder.  textures=True switches the loader's
+    texture option on (vt lines honoured, map_Kd PNGs decoded)."""
     import subprocess
-    out = os.path.join(workdir, name + ".scene.bin")
-    subprocess.run([_host_tool("srt_scene_dump"), objects_dir, name, out], check=True, capture_output=True)
+    out = os.path.join(workdir, name.replace(",", "+") + ".scene.bin")
+    subprocess.run([_host_tool("srt_scene_dump"), objects_dir, name, out] + (["textures"] if textures else []), check=True,
+                   capture_output=True)
     return read_scene_dump(out)
+
+
+def write_png(path, img, colour_type=None, filters=None, palette=None):
+    """Minimal PNG writer for tests: img uint8 [H,W] (grey or palette indices), [H,W,2], [H,W,3] or [H,W,4]; every
+    scanline uses the filter type filters[y % len(filters)] (0-4, PNG specification section 9)."""
+    import struct
+    import zlib
+    img = np.ascontiguousarray(img, np.uint8)
+    if img.ndim == 2:
+        img = img[:, :, None]
+    H, W, ch = img.shape
+    if colour_type is None:
+        colour_type = {1: 0, 2: 4, 3: 2, 4: 6}[ch]
+    filters = filters or [0]
+
+    def paeth(a, b, c):
+        p = a + b - c
+        pa, pb, pc = abs(p - a), abs(p - b), abs(p - c)
+        return a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+
+    raw = bytearray()
+    prev = [0] * (W * ch)
+    for y in range(H):
+        cur = img[y].reshape(-1).tolist()
+        ft = filters[y % len(filters)]
+        raw.append(ft)
+        for i, v in enumerate(cur):
+            a = cur[i - ch] if i >= ch else 0
+            b = prev[i]
+            c = prev[i - ch] if i >= ch else 0
+            pred = [0, a, b, (a + b) // 2, paeth(a, b, c)][ft]
+            raw.append((v - pred) & 255)
+        prev = cur
+
+    def chunk(kind, data):
+        return struct.pack(">I", len(data)) + kind + data + struct.pack(">I", zlib.crc32(kind + data) & 0xFFFFFFFF)
+
+    z = zlib.compress(bytes(raw), 6)
+    half = len(z) // 2  # two IDAT chunks: the decoder must join them
+    body = chunk(b"IHDR", struct.pack(">IIBBBBB", W, H, 8, colour_type, 0, 0, 0))
+    if palette is not None:
+        body += chunk(b"PLTE", np.ascontiguousarray(palette, np.uint8).tobytes())
+    body += chunk(b"IDAT", z[:half]) + chunk(b"IDAT", z[half:]) + chunk(b"IEND", b"")
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + body)
 
 
 def soup_scene(n_triangles, workdir, seed=0xC0FFEE):

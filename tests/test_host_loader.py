@@ -214,3 +214,52 @@ def test_two_models_flatten_with_rebased_indices(host_dump, tmp_path):
     for k in NAMES:
         assert np.concatenate([a[k], b[k]]).tobytes() == got[k].tobytes(), k
     assert len(got["bvhs"]) == 2 and got["bvhs"]["count"].tolist() == [len(a["nodes"]), len(b["nodes"])]
+
+
+def decode_png_with_host(path, tmp_path):
+    exe = os.path.join(HOST, "srt_png_dump")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-s", "-C", HOST, "srt_png_dump"], check=True)
+    out = str(tmp_path / "png.raw")
+    r = subprocess.run([exe, str(path), out], capture_output=True, text=True)
+    if r.returncode != 0:
+        return None, r.stderr
+    b = open(out, "rb").read()
+    w, h = struct.unpack_from("<II", b, 0)
+    return np.frombuffer(b, np.uint8, w * h * 4, 8).reshape(h, w, 4), ""
+
+
+@pytest.mark.parametrize("channels", [1, 2, 3, 4, "palette"])
+def test_png_decoder_every_colour_type_and_filter(tmp_path, channels):
+    """The texture option's decoder (asset_utils/png_decode.h) against files written from known pixels with every
+    scanline filter, two IDAT chunks."""
+    rng = np.random.default_rng(3)
+    H, W = 11, 7
+    path = tmp_path / "t.png"
+    if channels == "palette":
+        pal = rng.integers(0, 256, (5, 3), dtype=np.uint8)
+        idx = rng.integers(0, 5, (H, W), dtype=np.uint8)
+        scenes.write_png(path, idx, colour_type=3, filters=[0, 1, 2, 3, 4], palette=pal)
+        want = np.concatenate([pal[idx], np.full((H, W, 1), 255, np.uint8)], axis=2)
+    else:
+        img = rng.integers(0, 256, (H, W, channels), dtype=np.uint8)
+        scenes.write_png(path, img, filters=[4, 3, 2, 1, 0])
+        if channels == 1:
+            want = np.concatenate([np.repeat(img, 3, 2), np.full((H, W, 1), 255, np.uint8)], 2)
+        elif channels == 2:
+            want = np.concatenate([np.repeat(img[:, :, :1], 3, 2), img[:, :, 1:]], 2)
+        elif channels == 3:
+            want = np.concatenate([img, np.full((H, W, 1), 255, np.uint8)], 2)
+        else:
+            want = img
+    got, err = decode_png_with_host(path, tmp_path)
+    assert got is not None, err
+    assert np.array_equal(got, want)
+
+
+def test_png_decoder_refuses_what_it_cannot_read(tmp_path):
+    (tmp_path / "no.png").write_bytes(b"not a png at all, not even close........")
+    got, err = decode_png_with_host(tmp_path / "no.png", tmp_path)
+    assert got is None and "not a PNG" in err
+    got, err = decode_png_with_host(tmp_path / "missing.png", tmp_path)
+    assert got is None and "cannot open" in err
