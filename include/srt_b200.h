@@ -62,6 +62,11 @@ typedef struct srt_counters {
                                      srt_texmath.h).  0 (default) = the decree for the reference as shipped: albedo = Kd (Q7).
                                      Schedules 0 and 3 only. */
 
+#define SRT_OPT_TAIL_PATHS 11     /* wavefront schedule: once no more than this many paths are alive (and none is left to start),
+                                     ONE kernel runs them all to their last bounce instead of ~50 ever smaller waves; the same
+                                     per-path arithmetic, the same bits (default 1 Mi; 0 = waves to the end).  Not used with
+                                     SRT_OPT_TEXTURES or SRT_OPT_COUNT_TRAVERSAL. */
+
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */
 int srt_create(srt_ctx** out, int device);

@@ -83,15 +83,17 @@ struct srt_ctx {
   PathPool pool;
   uint32_t pool_slots = 0;
   size_t pool_list_cap = 0;
-  unsigned int* h_live = nullptr;  // pinned ring the device reports live_pixels into
+  WaveCounters* h_live = nullptr;  // pinned ring the device reports its wave counters into (live slots, paths handed out)
   cudaEvent_t wave_events[4] = {nullptr, nullptr, nullptr, nullptr};
   uint64_t waves = 0;
+  uint64_t tail_launches = 0;
   // optional per-kernel timing of the wavefront schedule (SRT_OPT_TIME_KERNELS): three events per wave
   bool time_kernels = false;
   std::vector<cudaEvent_t> timing_events;
   size_t timing_used = 0;
   int refill_threshold = 12;                   // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL)
   uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
+  uint32_t tail_paths = 1u << 20;               // live paths at which the tail kernel takes over (SRT_OPT_TAIL_PATHS, 0 = never)
   size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
   size_t sample_budget_bytes = (size_t)4 << 30;  // sample buffer budget per frame chunk (SRT_OPT_SAMPLE_BUDGET_MB)
 
@@ -220,6 +222,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_REFILL) {
     if (value < 1 || value > 32) return fail(ctx, "SRT_OPT_REFILL: 1..32");
     ctx->refill_threshold = value;
+    return 0;
+  }
+  if (key == SRT_OPT_TAIL_PATHS) {
+    if (value < 0) return fail(ctx, "SRT_OPT_TAIL_PATHS: 0 (off) or a number of paths");
+    ctx->tail_paths = (uint32_t)value;
     return 0;
   }
   if (key == SRT_OPT_WAVE_SLOTS) {
@@ -739,7 +746,7 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries) {
     CU(ctx, cudaMalloc(&p.samples, sample_entries * sizeof(float4)));
     ctx->sample_entries = sample_entries;
   }
-  if (!ctx->h_live) CU(ctx, cudaHostAlloc(&ctx->h_live, 4 * sizeof(unsigned int), cudaHostAllocDefault));
+  if (!ctx->h_live) CU(ctx, cudaHostAlloc(&ctx->h_live, 4 * sizeof(WaveCounters), cudaHostAllocDefault));
   for (cudaEvent_t& e : ctx->wave_events)
     if (!e) CU(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   return 0;
@@ -792,6 +799,8 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
   const DeviceScene sc = device_scene(ctx);
   uint32_t* ids = ctx->ids_enabled ? ctx->d_ids : nullptr;
   const int kBatch = 8;
+  // the tail kernel carries neither the texture records nor the traversal counters
+  const bool tail_ok = ctx->tail_paths > 0 && !ctx->count_traversal && !(ctx->textures_on && ctx->d_texels);
 
   for (int done = 0; done < fp_all.n_frames; done += chunk_frames) {
     FrameParams fp = fp_all;
@@ -809,17 +818,45 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     CU(ctx, launch_wf_init(sc, fp, ctx->pool, ctx->d_counters, ctx->stream));
     ctx->kernel_launches++;
     int parity = 0;
+    // What the host knows about the launch: paths still alive and whether every path has been handed to a slot.  Both
+    // are exact before wave 0 and afterwards lag one batch behind the device.
+    unsigned long long live = n_paths < (unsigned long long)slots ? n_paths : (unsigned long long)slots;
+    bool all_out = n_paths <= (unsigned long long)slots;
+    auto timing_events = [&](cudaEvent_t* ev) -> int {
+      while (ctx->timing_events.size() < ctx->timing_used + 3) {
+        cudaEvent_t e;
+        CU(ctx, cudaEventCreate(&e));
+        ctx->timing_events.push_back(e);
+      }
+      for (int k = 0; k < 3; ++k) ev[k] = ctx->timing_events[ctx->timing_used + k];
+      ctx->timing_used += 3;
+      return 0;
+    };
     for (int batch = 0;; ++batch) {
-      for (int w = 0; w < kBatch; ++w) {
+      if (tail_ok && all_out && live <= (unsigned long long)ctx->tail_paths) {
+        // the rest of the launch in one kernel (srt_wf_tail.cuh); with SRT_OPT_TIME_KERNELS it is reported as one more
+        // trace launch (its shading included: the trace figure can only get worse by it)
         cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
         if (ctx->time_kernels) {
-          while (ctx->timing_events.size() < ctx->timing_used + 3) {
-            cudaEvent_t e;
-            CU(ctx, cudaEventCreate(&e));
-            ctx->timing_events.push_back(e);
-          }
-          for (int k = 0; k < 3; ++k) ev[k] = ctx->timing_events[ctx->timing_used + k];
-          ctx->timing_used += 3;
+          if (timing_events(ev)) return 1;
+          CU(ctx, cudaEventRecord(ev[0], ctx->stream));
+        }
+        CU(ctx, launch_wf_tail(sc, fp, ctx->pool, parity, ctx->traversal, chunk_ids, ctx->d_counters, ctx->stream));
+        if (ctx->time_kernels) {
+          CU(ctx, cudaEventRecord(ev[1], ctx->stream));
+          CU(ctx, cudaEventRecord(ev[2], ctx->stream));
+        }
+        ctx->kernel_launches++;
+        ctx->tail_launches++;
+        break;
+      }
+      // long waves are queued one at a time (the report of the wave before is back long before the wave ends); short
+      // ones in batches of kBatch so that the device never waits for the host
+      const int n_waves = live > (1ull << 20) ? 1 : kBatch;
+      for (int w = 0; w < n_waves; ++w) {
+        cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+        if (ctx->time_kernels) {
+          if (timing_events(ev)) return 1;
           CU(ctx, cudaEventRecord(ev[0], ctx->stream));
         }
         CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, ctx->traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
@@ -827,15 +864,17 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
         if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], ctx->stream));
         parity ^= 1;
       }
-      ctx->kernel_launches += 2 * kBatch;
-      ctx->waves += kBatch;
+      ctx->kernel_launches += 2 * n_waves;
+      ctx->waves += n_waves;
       const int s = batch & 3;
-      CU(ctx, cudaMemcpyAsync(&ctx->h_live[s], &ctx->pool.q->live_slots, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+      CU(ctx, cudaMemcpyAsync(&ctx->h_live[s], ctx->pool.q, sizeof(WaveCounters), cudaMemcpyDeviceToHost, ctx->stream));
       CU(ctx, cudaEventRecord(ctx->wave_events[s], ctx->stream));
       if (batch >= 1) {
         const int prev = (batch - 1) & 3;
         CU(ctx, cudaEventSynchronize(ctx->wave_events[prev]));
-        if (ctx->h_live[prev] == 0) break;
+        live = ctx->h_live[prev].live_slots;
+        all_out = ctx->h_live[prev].next_path >= n_paths;
+        if (live == 0) break;
       }
     }
     CU(ctx, launch_wf_resolve(fp, ctx->pool, ctx->d_accum, ctx->d_out, ctx->stream));

@@ -11,6 +11,7 @@
 #include "srt_regen.cuh"
 #include "srt_persistent.cuh"
 #include "srt_wavefront.cuh"
+#include "srt_wf_tail.cuh"
 
 namespace srt {
 
@@ -348,6 +349,39 @@ cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const P
   if (blocks < 1) blocks = 1;
   wf_logic_kernel<<<(unsigned)blocks, SRT_WF_LOGIC_THREADS, 0, stream>>>(sc, fp, pool, parity, ids, counters);
   return cudaGetLastError();
+}
+
+namespace {
+template <int MODE>
+cudaError_t wf_tail_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, uint32_t* ids,
+                           DeviceCounters* counters, cudaStream_t stream) {
+  static int per_sm = 0, sms = 0;
+  static size_t smem_set = 0;
+  auto k = wf_tail_kernel<MODE>;
+  const int block = SRT_WF_TRACE_THREADS;
+  const size_t smem = (size_t)fp.stack_cap * block * sizeof(uint2);
+  cudaError_t e;
+  if (per_sm == 0 || smem_set != smem) {
+    int dev = 0;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    if (smem > 48 * 1024 &&
+        (e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+      return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, block, smem)) != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    smem_set = smem;
+  }
+  // persistent warps: every resident slot of all SMs once; a small tail is spread over them one path per warp
+  k<<<(unsigned)(sms * per_sm), block, smem, stream>>>(sc, fp, pool, parity, ids, counters);
+  return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t launch_wf_tail(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
+                           uint32_t* ids, DeviceCounters* counters, cudaStream_t stream) {
+  return mode == TRAV_REFERENCE ? wf_tail_launch<TRAV_REFERENCE>(sc, fp, pool, parity, ids, counters, stream)
+                                : wf_tail_launch<TRAV_ORDERED>(sc, fp, pool, parity, ids, counters, stream);
 }
 
 cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream) {

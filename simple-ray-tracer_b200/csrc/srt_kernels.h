@@ -18,6 +18,9 @@ cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const P
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
                            cudaEvent_t after_trace = nullptr);
+// The end of a launch (srt_wf_tail.cuh): every path still in the queues of `parity` is run to its last bounce.
+cudaError_t launch_wf_tail(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
+                           uint32_t* ids, DeviceCounters* counters, cudaStream_t stream);
 // upper bound of the warps launch_wf_wave gives wf_logic_kernel (sizes the queues' room for holes)
 uint32_t launch_wf_max_logic_warps();
 cudaError_t launch_wf_resolve(const FrameParams& fp, const PathPool& pool, float4* accum, uchar4* out,

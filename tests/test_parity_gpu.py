@@ -14,7 +14,13 @@ pytestmark = pytest.mark.gpu
 
 
 def gpu_render(pkg, ctx, W, H, show_model, n_frames, traversal, scene=None, lights=None, cam=None, first_frame=1,
-               max_depth=0, noise=None, rows=None, schedule=3, textures=None):
+               max_depth=0, noise=None, rows=None, schedule=3, textures=None, tail=None):
+    """schedule 30 = the wavefront schedule (3) with waves to the very end (SRT_OPT_TAIL_PATHS = 0); plain 3 uses the
+    library's default, under which launches of these sizes run in the tail kernel right after wf_init_kernel."""
+    if schedule == 30:
+        schedule, tail = 3, 0
+    if tail is not None:
+        ctx.set_option(pkg.OPT_TAIL_PATHS, tail)
     unit, uniform = noise if noise is not None else scenes.noise_tables(W, H)
     lights = lights if lights is not None else (scenes.model_lights() if show_model else scenes.sphere_lights())
     cam = cam or scenes.reset_camera(show_model)
@@ -103,7 +109,7 @@ def test_spheres_multi_frame_bit_exact(pkg, ctx, oracle, frames):
     assert np.array_equal(out, oout)
 
 
-@pytest.mark.parametrize("schedule", [0, 1, 2, 3])
+@pytest.mark.parametrize("schedule", [0, 1, 2, 3, 30])
 def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     """C2's scene at a size the oracle finishes in seconds; reference visiting order => bit-exact."""
     scene = scenes.rubik_scene()
@@ -116,7 +122,7 @@ def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     assert ocnt["capped_paths"] == 0 and cnt["capped_paths"] == 0
 
 
-@pytest.mark.parametrize("schedule", [0, 1, 2, 3])
+@pytest.mark.parametrize("schedule", [0, 1, 2, 3, 30])
 def test_rubik_ordered_traversal_matches_bar_ties(pkg, ctx, oracle, schedule):
     """Ordered traversal: same image except documented grazing ties (budget: 1e-4 of the pixels; ids identical
     on every pixel outside that budget, radiance bit-exact there too)."""
@@ -143,7 +149,7 @@ def test_wavefront_small_pool_and_frame_chunks_bit_exact(pkg, ctx, oracle):
     assert cnt["paths"] == 256 * 128 * 5
 
 
-@pytest.mark.parametrize("schedule", [2, 3])
+@pytest.mark.parametrize("schedule", [2, 3, 30])
 def test_airplane_standin_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     """BASELINE.json configs[2]'s scene is absent from the reference mount; its documented stand-in (6 Airplane
     materials, leaves of up to ~100 triangles from the reference's midpoint builder) through the host loader."""
@@ -173,7 +179,7 @@ def framed(scale, rot_y_deg, translate):
     return np.linalg.inv(T @ R @ S).astype(np.float32).T.reshape(16).copy()
 
 
-@pytest.mark.parametrize("schedule", [0, 2, 3])
+@pytest.mark.parametrize("schedule", [0, 2, 3, 30])
 def test_two_models_with_frames_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     """SURVEY 8(f) N4: bvh_count = 2, each model behind its own world->model frame (raytrace_compute.glsl:144-161);
     the closest hit is taken over both, t shared between model spaces as the shader does (Q14).  Then one frame is
@@ -206,12 +212,14 @@ def test_two_models_with_frames_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     assert_bit_exact(ctx.read_accum(), oacc2)
 
 
-def test_soup_depth8_bit_exact(pkg, ctx, oracle, tmp_path):
+@pytest.mark.parametrize("schedule", [3, 30])
+def test_soup_depth8_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     """BASELINE.json configs[4] at a size the oracle finishes in seconds: random soup, maxDepth 8, camera (0,0,120)."""
     scene, info = scenes.soup_scene(20000, str(tmp_path))
     assert info["depth"] <= 63
     cam = scenes.reset_camera(True, origin=(0.0, 0.0, 120.0))
-    acc, out, ids, cnt = gpu_render(pkg, ctx, 256, 144, True, 2, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8)
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 256, 144, True, 2, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8,
+                                    schedule=schedule)
     oacc, oout, oids, ocnt = cpu_render(oracle, 256, 144, True, 2, scene=scene, cam=cam, max_depth=8)
     assert np.array_equal(ids, oids)
     assert_bit_exact(acc, oacc)
@@ -219,11 +227,13 @@ def test_soup_depth8_bit_exact(pkg, ctx, oracle, tmp_path):
     assert ocnt["capped_paths"] == 0
 
 
-def test_rubik_inside_view_and_depth8(pkg, ctx, oracle):
+@pytest.mark.parametrize("schedule", [3, 30])
+def test_rubik_inside_view_and_depth8(pkg, ctx, oracle, schedule):
     """Camera inside the model's bounds looking around (many bounces), maxDepth 8 as C5 uses."""
     scene = scenes.rubik_scene()
     cam = scenes.look_camera((0.3, 9.1, 12.0), -70.0, -12.0)
-    acc, out, ids, _ = gpu_render(pkg, ctx, 256, 256, True, 3, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8)
+    acc, out, ids, _ = gpu_render(pkg, ctx, 256, 256, True, 3, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8,
+                                  schedule=schedule)
     oacc, oout, oids, _ = cpu_render(oracle, 256, 256, True, 3, scene=scene, cam=cam, max_depth=8)
     assert np.array_equal(ids, oids)
     assert_bit_exact(acc, oacc)
