@@ -203,6 +203,8 @@ def run_gpu(args):
         ctx.set_option(pkg.OPT_REFILL, args.refill)
     if args.tail_paths >= 0:
         ctx.set_option(pkg.OPT_TAIL_PATHS, args.tail_paths)
+    if args.finder >= 0:
+        ctx.set_option(pkg.OPT_FINDER, args.finder)
 
     def upload_all():
         if inp["scene"] is not None:
@@ -407,6 +409,7 @@ def run_gpu(args):
                             if world > 1 else "single GPU",
                    "l2": "512 MB device buffer rewritten between timed steps (L2 flush)",
                    "tail_paths": "library default" if args.tail_paths < 0 else args.tail_paths,
+                   "hit_finder": dict(zip(("active", "cost_reference", "cost_finder"), ctx.finder_info())) if show_model else None,
                    "ms_per_frame": ms_per_step / spp},
         "segments_per_step": segments / args.steps, "shadow_rays_per_step": shadow / args.steps,
         "mrays_incl_shadow": rays / (total_ms * 1e-3) / 1e6,
@@ -436,6 +439,8 @@ def main():
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
     ap.add_argument("--l2-persist", type=int, default=-1, help="1/0: pin the BVH top levels in L2 (default: library default, on)")
     ap.add_argument("--refill", type=int, default=0, help="refill threshold of the wavefront trace kernel (0 = default)")
+    ap.add_argument("--finder", type=int, default=-1,
+                    help="hit finder of the wavefront schedule: 0 off, 1 on, 2 auto (-1 = library default, auto)")
     ap.add_argument("--tail-paths", type=int, default=-1,
                     help="live paths at which the wavefront schedule's tail kernel takes over (-1 = library default, 0 = never)")
     ap.add_argument("--wave-slots", type=int, default=0, help="path slots of the wavefront schedule (0 = library default)")

@@ -67,6 +67,16 @@ typedef struct srt_counters {
                                      per-path arithmetic, the same bits (default 1 Mi; 0 = waves to the end).  Not used with
                                      SRT_OPT_TEXTURES or SRT_OPT_COUNT_TRAVERSAL. */
 
+#define SRT_OPT_FINDER 12         /* wavefront schedule: how Intersects (ray_intersects.glsl:99-133) is evaluated.
+                                     0 = walk the reference BVH as the shader does
+                                     1 = hit finder: collect the triangles the ray passes the shader's triangle test against
+                                         through a private SAH tree, then replay the shader's box culls above those few
+                                         triangles in its visiting order -- the same hit and distance bit for bit (that of
+                                         SRT_OPT_TRAVERSAL = 0), a fraction of the tests
+                                     2 = (default) 1 when sample rays at srt_upload_scene say it is less work (Rubik, the
+                                         airplane), 0 otherwise (the random soup: every ray meets dozens of triangles)
+                                     Set before srt_upload_scene.  Scenes above 2 Mi triangles never use it. */
+
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */
 int srt_create(srt_ctx** out, int device);
@@ -165,6 +175,10 @@ int srt_get_counters(srt_ctx* ctx, srt_counters* out);
  * (needs SRT_OPT_TIME_KERNELS = 1); waves = launches of each kind.  Synchronises the stream. */
 int srt_get_kernel_times(srt_ctx* ctx, double* trace_ms, double* logic_ms, uint64_t* waves);
 int srt_reset_counters(srt_ctx* ctx);
+/* Hit finder (SRT_OPT_FINDER): whether the next srt_render of the uploaded scene goes through it, and the two figures
+ * srt_upload_scene measured on its sample rays (box tests + 1.5 x triangle tests per ray, walking the reference BVH
+ * vs finder + replay).  No reference call site (the shader has one way to intersect).  Any pointer may be NULL. */
+int srt_get_finder_info(srt_ctx* ctx, int32_t* active, double* cost_reference, double* cost_finder);
 
 /* Device-side evaluation of the numeric decree (srt_detmath.h), for bit-for-bit checks against the host:
  * which: 0 = sin, 1 = cos, 2 = pow(x, 1/2.4), 3 = randFloat(x, y[i]) (y required), 4 = linearToSrgb. */

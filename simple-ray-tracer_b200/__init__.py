@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsrt_b200.so")
 
 OPT_TRAVERSAL, OPT_COUNT_TRAVERSAL, OPT_L2_PERSIST, OPT_BLOCK_THREADS, OPT_SCHEDULE = 1, 2, 3, 4, 5
-OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS, OPT_TEXTURES, OPT_TAIL_PATHS = 6, 7, 8, 9, 10, 11
+OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS, OPT_TEXTURES, OPT_TAIL_PATHS, OPT_FINDER = 6, 7, 8, 9, 10, 11, 12
 SCHED_PER_PATH, SCHED_REGEN, SCHED_PERSISTENT, SCHED_WAVEFRONT = 0, 1, 2, 3
 TRAV_REFERENCE, TRAV_ORDERED = 0, 1
 NO_HIT = 0xFFFFFFFF
@@ -33,7 +33,7 @@ EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
            "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_build_bvh", "srt_set_texture",
-           "srt_get_counters", "srt_get_kernel_times", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
+           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
 
 
 class Params(C.Structure):  # srt_params, include/srt_types.h
@@ -229,6 +229,12 @@ class Context:
         t, l, w = C.c_double(), C.c_double(), C.c_uint64()
         self._ck(self._lib.srt_get_kernel_times(self._h, C.byref(t), C.byref(l), C.byref(w)))
         return t.value, l.value, w.value
+
+    def finder_info(self):
+        """(active, cost_reference, cost_finder): see srt_get_finder_info."""
+        a, r, f = C.c_int32(), C.c_double(), C.c_double()
+        self._ck(self._lib.srt_get_finder_info(self._h, C.byref(a), C.byref(r), C.byref(f)))
+        return bool(a.value), r.value, f.value
 
     def reset_counters(self):
         self._ck(self._lib.srt_reset_counters(self._h))

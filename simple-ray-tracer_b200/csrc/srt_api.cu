@@ -16,6 +16,7 @@
 #include "srt_b200.h"
 #include "srt_kernels.h"
 #include "srt_bvh_build.h"
+#include "srt_finder.h"
 
 using namespace srt;
 
@@ -41,6 +42,16 @@ struct srt_ctx {
   TriRecord* d_tris = nullptr;
   MatRecord* d_mats = nullptr;
   BvhRecord* d_bvhs = nullptr;
+  // hit finder (srt_finder.h): built at upload unless SRT_OPT_FINDER is 0
+  NodePair* d_fpairs = nullptr;
+  TriRecord* d_ftris = nullptr;
+  RefNode* d_rnodes = nullptr;
+  uint32_t* d_tri_leaf = nullptr;
+  int finder_mode = 2;           // SRT_OPT_FINDER: 0 off, 1 on, 2 where the sample rays say it pays
+  bool finder_ready = false;     // the arrays above describe the uploaded scene
+  bool finder_worthwhile = false;
+  int finder_depth = 0;
+  double finder_cost = 0.0, reference_cost = 0.0;
   // textured-albedo option (SRT_OPT_TEXTURES; include/srt_texmath.h)
   bool textures_on = false;
   TexTri* d_tex_tris = nullptr;            // built by srt_upload_scene when a material says use_texture
@@ -129,6 +140,7 @@ static void free_pool(srt_ctx* ctx) {
   PathPool& p = ctx->pool;
   dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.path); dfree(p.p3);
   dfree(p.list[0]); dfree(p.list[1]); dfree(p.q); dfree(p.samples); dfree(p.tex);
+  dfree(p.cand); dfree(p.rlist); dfree(p.olist); dfree(p.fq);
   p.cap = 0;
   ctx->pool_slots = 0;
   ctx->sample_entries = 0;
@@ -175,6 +187,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris); dfree(ctx->d_mats); dfree(ctx->d_bvhs);
+  dfree(ctx->d_fpairs); dfree(ctx->d_ftris); dfree(ctx->d_rnodes); dfree(ctx->d_tri_leaf);
   dfree(ctx->d_tex_tris); dfree(ctx->d_tex_info); dfree(ctx->d_texels);
   dfree(ctx->d_noise_xy); dfree(ctx->d_noise_x); dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
   dfree(ctx->d_counters);
@@ -222,6 +235,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_REFILL) {
     if (value < 1 || value > 32) return fail(ctx, "SRT_OPT_REFILL: 1..32");
     ctx->refill_threshold = value;
+    return 0;
+  }
+  if (key == SRT_OPT_FINDER) {
+    if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_FINDER: 0 (off), 1 (on) or 2 (auto)");
+    ctx->finder_mode = value;
     return 0;
   }
   if (key == SRT_OPT_TAIL_PATHS) {
@@ -416,6 +434,30 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
     r.e2 = make_float4(v2[0] - v0[0], v2[1] - v0[1], v2[2] - v0[2], 0.0f);
     memcpy(&r.e2.w, &rl.remaining[i], 4);
     tris[i] = r;
+  }
+  // hit finder: a private tree over the same triangles + what a replay of the shader's culls needs (srt_finder.h)
+  ctx->finder_ready = false;
+  ctx->finder_worthwhile = false;
+  dfree(ctx->d_fpairs); dfree(ctx->d_ftris); dfree(ctx->d_rnodes); dfree(ctx->d_tri_leaf);
+  for (BvhRecord& r : rl.bvhs) r.finder_root = r.root_node = 0u;
+  if (ctx->finder_mode != 0) {
+    FinderOut fo;
+    if (build_finder(bvhs, n_bvhs, nodes, n_nodes, triangles, vertices, tris, fo)) {
+      for (uint32_t b = 0; b < n_bvhs; ++b) {
+        rl.bvhs[b].finder_root = fo.root[b];
+        rl.bvhs[b].root_node = bvhs[b].first_index;
+        rl.bvhs[b].finder_pad = fo.pad[b];
+      }
+      if (upload_vec(ctx, ctx->d_fpairs, fo.pairs) || upload_vec(ctx, ctx->d_ftris, fo.tris) ||
+          upload_vec(ctx, ctx->d_rnodes, fo.rnodes) || upload_vec(ctx, ctx->d_tri_leaf, fo.tri_leaf))
+        return 1;
+      CU(ctx, cudaStreamSynchronize(ctx->stream));
+      ctx->finder_ready = true;
+      ctx->finder_worthwhile = fo.worthwhile;
+      ctx->finder_depth = fo.depth;
+      ctx->finder_cost = fo.cost_finder;
+      ctx->reference_cost = fo.cost_reference;
+    }
   }
   std::vector<MatRecord> mats(n_materials);
   for (uint32_t i = 0; i < n_materials; ++i) {
@@ -646,6 +688,7 @@ DeviceScene device_scene(const srt_ctx* ctx) {
   DeviceScene sc;
   sc.pairs = ctx->d_pairs; sc.leaves = ctx->d_leaves; sc.tris = ctx->d_tris; sc.mats = ctx->d_mats;
   sc.bvhs = ctx->d_bvhs; sc.noise_unit_xy = ctx->d_noise_xy; sc.noise_uniform_x = ctx->d_noise_x;
+  sc.fpairs = ctx->d_fpairs; sc.ftris = ctx->d_ftris; sc.rnodes = ctx->d_rnodes; sc.tri_leaf = ctx->d_tri_leaf;
   const bool tex = ctx->textures_on && ctx->d_tex_tris && ctx->d_texels;
   sc.tex_tris = tex ? ctx->d_tex_tris : nullptr;
   sc.tex_info = tex ? ctx->d_tex_info : nullptr;
@@ -676,6 +719,7 @@ void fill_frame_params(const srt_ctx* ctx, int n_frames, FrameParams& fp) {
   fp.bvh_count = p.bvh_count;
   fp.max_depth = p.max_depth > 0 ? p.max_depth : 5;  // raytrace_compute.glsl:370
   int cap = ctx->tree_depth + 1;
+  if (ctx->finder_ready && ctx->finder_depth + 1 > cap) cap = ctx->finder_depth + 1;
   fp.stack_cap = cap < 2 ? 2 : cap;
 
   const float focus_dist = 1.0f;                                  // :384
@@ -720,7 +764,11 @@ int check_ready(srt_ctx* ctx) {
 
 namespace {
 
-int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries) {
+bool finder_active(const srt_ctx* ctx) {
+  return ctx->finder_ready && !ctx->count_traversal && (ctx->finder_mode == 1 || (ctx->finder_mode == 2 && ctx->finder_worthwhile));
+}
+
+int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_finder) {
   PathPool& p = ctx->pool;
   if (!(ctx->pool_slots >= slots && p.q)) {
     CU(ctx, cudaStreamSynchronize(ctx->stream));
@@ -738,6 +786,13 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries) {
     ctx->pool_slots = slots;
   }
   if (ctx->textures_on && !p.tex) CU(ctx, cudaMalloc(&p.tex, (size_t)ctx->pool_slots * 16));
+  if (want_finder && !p.fq) {
+    CU(ctx, cudaMalloc(&p.cand, (size_t)ctx->pool_slots * SRT_CAND_MAX * sizeof(uint2)));
+    CU(ctx, cudaMalloc(&p.rlist, (size_t)ctx->pool_slots * 4));
+    CU(ctx, cudaMalloc(&p.olist, ctx->pool_list_cap * 4));
+    CU(ctx, cudaMalloc(&p.fq, sizeof(FinderQueues)));
+    CU(ctx, cudaMemsetAsync(p.fq, 0, sizeof(FinderQueues), ctx->stream));
+  }
   p.cap = slots;
   p.list_cap = (uint32_t)ctx->pool_list_cap;
   if (ctx->sample_entries < sample_entries) {
@@ -801,6 +856,9 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
   const int kBatch = 8;
   // the tail kernel carries neither the texture records nor the traversal counters
   const bool tail_ok = ctx->tail_paths > 0 && !ctx->count_traversal && !(ctx->textures_on && ctx->d_texels);
+  // the hit finder gives the reference visiting order's result (bit for bit); so does every kernel beside it then
+  const bool finder = finder_active(ctx);
+  const int traversal = finder ? (int)TRAV_REFERENCE : ctx->traversal;
 
   for (int done = 0; done < fp_all.n_frames; done += chunk_frames) {
     FrameParams fp = fp_all;
@@ -810,7 +868,8 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     uint32_t slots = ctx->wave_slots;
     if ((unsigned long long)slots > n_paths) slots = (uint32_t)n_paths;
     slots = (slots + 31u) & ~31u;
-    if (ensure_pool(ctx, slots, (size_t)n_pixels * (size_t)chunk_frames)) return 1;
+    if (finder && slots >= (1u << 28)) return fail(ctx, "SRT_OPT_FINDER: at most 2^28 - 1 path slots (SRT_OPT_WAVE_SLOTS)");
+    if (ensure_pool(ctx, slots, (size_t)n_pixels * (size_t)chunk_frames, finder)) return 1;
     ctx->pool.n_pixels = n_pixels;
     ctx->pool.n_paths = n_paths;
     // primary ids are those of the launch's LAST frame
@@ -841,7 +900,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
           if (timing_events(ev)) return 1;
           CU(ctx, cudaEventRecord(ev[0], ctx->stream));
         }
-        CU(ctx, launch_wf_tail(sc, fp, ctx->pool, parity, ctx->traversal, chunk_ids, ctx->d_counters, ctx->stream));
+        CU(ctx, launch_wf_tail(sc, fp, ctx->pool, parity, traversal, chunk_ids, ctx->d_counters, ctx->stream));
         if (ctx->time_kernels) {
           CU(ctx, cudaEventRecord(ev[1], ctx->stream));
           CU(ctx, cudaEventRecord(ev[2], ctx->stream));
@@ -859,12 +918,12 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
           if (timing_events(ev)) return 1;
           CU(ctx, cudaEventRecord(ev[0], ctx->stream));
         }
-        CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, ctx->traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
-                               ctx->block_threads, ctx->stream, ev[1]));
+        CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
+                               ctx->block_threads, ctx->stream, ev[1], finder));
         if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], ctx->stream));
         parity ^= 1;
       }
-      ctx->kernel_launches += 2 * n_waves;
+      ctx->kernel_launches += (finder ? 4 : 2) * n_waves;
       ctx->waves += n_waves;
       const int s = batch & 3;
       CU(ctx, cudaMemcpyAsync(&ctx->h_live[s], ctx->pool.q, sizeof(WaveCounters), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1060,6 +1119,14 @@ extern "C" int srt_get_kernel_times(srt_ctx* ctx, double* trace_ms, double* logi
   if (logic_ms) *logic_ms = l;
   if (waves) *waves = ctx->timing_used / 3;
   ctx->timing_used = 0;
+  return 0;
+}
+
+extern "C" int srt_get_finder_info(srt_ctx* ctx, int32_t* active, double* cost_reference, double* cost_finder) {
+  if (!ctx) return 1;
+  if (active) *active = finder_active(ctx) ? 1 : 0;
+  if (cost_reference) *cost_reference = ctx->reference_cost;
+  if (cost_finder) *cost_finder = ctx->finder_cost;
   return 0;
 }
 

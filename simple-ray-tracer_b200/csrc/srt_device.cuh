@@ -55,7 +55,25 @@ struct BvhRecord {
   uint32_t root_ref;
   float root_max[3];
   uint32_t root_direct;  // root as a direct reference (see NodePair::d)
+  // hit finder (srt_finder.h): the root of this BVH's private tree as a direct reference into DeviceScene::fpairs /
+  // ftris, the reference node the BVH starts at (where a replay stops), the finder's box padding
+  uint32_t finder_root;
+  uint32_t root_node;
+  float finder_pad;
+  uint32_t _pad;
 };
+static_assert(sizeof(BvhRecord) == 112, "BvhRecord: frame first (srt_update_frame rewrites its 64 bytes)");
+
+// Hit finder (srt_finder.h, srt_wf_find.cuh).  One record per node of the reference BVH in the reference's own
+// numbering: the box the shader tests when it pops the node (ray_intersects.glsl:107-110), the node above it and the
+// visiting rank of the first triangle below it -- what a replay of the shader's culls needs.
+struct RefNode {
+  float4 a;  // min.xyz, bits: parent node (0xFFFFFFFF above a root)
+  float4 b;  // max.xyz, bits: rank of the first triangle the shader's traversal meets in this subtree
+};
+#define SRT_CAND_MAX 8          // candidates kept per ray; a ray with more is traced by wf_trace_kernel instead
+#define SRT_CAND_BVH_SHIFT 26   // candidate word: triangle | bvh << 26
+#define SRT_FINDER_MAX_TRIS (1u << 21)
 
 // SRT_OPT_TRAVERSAL values (srt_b200.h)
 enum { TRAV_REFERENCE = 0, TRAV_ORDERED = 1 };
@@ -86,6 +104,13 @@ struct DeviceScene {
   const TriRecord* tris;
   const MatRecord* mats;
   const BvhRecord* bvhs;
+  // hit finder, null when the scene has none: a private BVH2 over the same triangles (padded boxes, leaves of <= 4,
+  // its own copy of the triangle records in ITS leaf order: v0.w = the triangle's index in `tris`), the reference
+  // nodes for the replay, and the reference leaf (node index) of every triangle
+  const NodePair* fpairs;
+  const TriRecord* ftris;
+  const RefNode* rnodes;
+  const uint32_t* tri_leaf;
   const float2* noise_unit_xy;  // noiseTex.xy   (raytrace_utils.glsl:15)
   const float* noise_uniform_x; // noiseUniformTex.x (raytrace_utils.glsl:52)
 };
@@ -130,6 +155,15 @@ struct WaveCounters {
   unsigned long long next_path;  // next path (frame-major: frame * n_pixels + pixel slot) to hand to a free slot
 };
 
+// Queues between wf_find_kernel and its two consumers (srt_wf_find.cuh); zeroed by wf_init_kernel / wf_logic_kernel.
+struct FinderQueues {
+  WaveCounters over;      // rays with more than SRT_CAND_MAX candidates: n_closest[0] entries of PathPool::olist, traced
+                          // by wf_trace_kernel (given a PathPool whose q / list[0] point here)
+  unsigned int n_replay;  // entries of PathPool::rlist
+  unsigned int cursor;    // fetch cursor of wf_find_kernel
+  unsigned int _pad[2];
+};
+
 // Per-slot records (SoA, 16 B each unless noted).  A slot carries ONE path at a time; when the path ends the slot
 // takes the next path of the launch from WaveCounters::next_path.
 struct PathPool {
@@ -146,6 +180,12 @@ struct PathPool {
   uint32_t cap;        // slots
   uint32_t list_cap;   // cap + room for the holes the logic warps' chunked reservations can leave
   WaveCounters* q;
+  // hit finder only (null otherwise): per slot SRT_CAND_MAX candidates (triangle | bvh << 26, distance bits), the
+  // list of rays to replay (slot | candidates << 28), the list of rays to trace the long way, their counters
+  uint2* cand;
+  uint32_t* rlist;
+  uint32_t* olist;
+  FinderQueues* fq;
   // one fp32 sample per path of the launch, frame-major, summed per pixel in frame order by wf_resolve_kernel
   float4* samples;
   uint32_t n_pixels;           // pixel slots of this launch (8x4 tiles x 32)

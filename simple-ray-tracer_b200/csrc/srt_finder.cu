@@ -1,0 +1,337 @@
+// srt_finder.cu -- builds the hit finder on the host at srt_upload_scene time (see srt_finder.h for what it is).
+// Host code only; compiled by nvcc because the records are the device's.
+#include "srt_finder.h"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+namespace srt {
+namespace {
+
+struct Box {
+  float mn[3], mx[3];
+  void clear() {
+    for (int a = 0; a < 3; ++a) { mn[a] = INFINITY; mx[a] = -INFINITY; }
+  }
+  void grow(const Box& o) {
+    for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], o.mn[a]); mx[a] = std::max(mx[a], o.mx[a]); }
+  }
+  float area() const {
+    float dx = mx[0] - mn[0], dy = mx[1] - mn[1], dz = mx[2] - mn[2];
+    return 2.0f * (dx * dy + dy * dz + dz * dx);
+  }
+};
+
+inline float u2f_(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+inline uint32_t f2u_(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+
+constexpr int kBins = 16;
+constexpr uint32_t kLeafMax = 4;
+
+struct Builder {
+  const std::vector<TriRecord>& ref;  // reference order
+  const std::vector<Box>& tb;         // per triangle (reference order)
+  std::vector<uint32_t> idx;          // triangles of the BVH being built, permuted in place
+  FinderOut& out;
+  float pad = 0.0f;
+
+  // builds the subtree over idx[lo, hi); returns its direct reference and its (unpadded) box
+  uint32_t build(uint32_t lo, uint32_t hi, int depth, Box& box) {
+    box.clear();
+    Box cb;  // of the centres
+    cb.clear();
+    for (uint32_t i = lo; i < hi; ++i) {
+      const Box& b = tb[idx[i]];
+      box.grow(b);
+      for (int a = 0; a < 3; ++a) {
+        float c = 0.5f * (b.mn[a] + b.mx[a]);
+        cb.mn[a] = std::min(cb.mn[a], c);
+        cb.mx[a] = std::max(cb.mx[a], c);
+      }
+    }
+    if (depth > out.depth) out.depth = depth;
+    if (hi - lo <= kLeafMax) {
+      const uint32_t first = (uint32_t)out.tris.size();
+      for (uint32_t i = lo; i < hi; ++i) {
+        TriRecord r = ref[idx[i]];
+        r.v0.w = u2f_(idx[i]);             // where the triangle is in the reference order (its material is looked up there)
+        r.e2.w = u2f_(hi - 1 - i);         // triangles that follow in this leaf
+        out.tris.push_back(r);
+      }
+      return SRT_LEAF_BIT | first;
+    }
+    // binned SAH over the three axes
+    float best_cost = INFINITY;
+    int best_axis = -1, best_bin = -1;
+    for (int a = 0; a < 3; ++a) {
+      if (!(cb.mx[a] > cb.mn[a])) continue;
+      Box bb[kBins];
+      uint32_t bc[kBins];
+      for (int b = 0; b < kBins; ++b) { bb[b].clear(); bc[b] = 0; }
+      const float scale = (float)kBins / (cb.mx[a] - cb.mn[a]);
+      for (uint32_t i = lo; i < hi; ++i) {
+        const Box& t = tb[idx[i]];
+        int b = (int)((0.5f * (t.mn[a] + t.mx[a]) - cb.mn[a]) * scale);
+        b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
+        bb[b].grow(t);
+        bc[b]++;
+      }
+      float la[kBins], ra[kBins];
+      uint32_t lc[kBins], rc[kBins];
+      Box acc;
+      acc.clear();
+      uint32_t c = 0;
+      for (int b = 0; b < kBins; ++b) {
+        if (bc[b]) acc.grow(bb[b]);
+        c += bc[b];
+        la[b] = c ? acc.area() : 0.0f;
+        lc[b] = c;
+      }
+      acc.clear();
+      c = 0;
+      for (int b = kBins - 1; b >= 0; --b) {
+        if (bc[b]) acc.grow(bb[b]);
+        c += bc[b];
+        ra[b] = c ? acc.area() : 0.0f;
+        rc[b] = c;
+      }
+      for (int b = 0; b + 1 < kBins; ++b) {
+        if (lc[b] == 0 || rc[b + 1] == 0) continue;
+        float cost = la[b] * (float)lc[b] + ra[b + 1] * (float)rc[b + 1];
+        if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = b; }
+      }
+    }
+    uint32_t mid = (lo + hi) / 2;  // all centres equal (or nothing to gain): split by count
+    if (best_axis >= 0) {
+      const int a = best_axis;
+      const float scale = (float)kBins / (cb.mx[a] - cb.mn[a]), base = cb.mn[a];
+      auto it = std::partition(idx.begin() + lo, idx.begin() + hi, [&](uint32_t t) {
+        int b = (int)((0.5f * (tb[t].mn[a] + tb[t].mx[a]) - base) * scale);
+        b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
+        return b <= best_bin;
+      });
+      uint32_t m = (uint32_t)(it - idx.begin());
+      if (m > lo && m < hi) mid = m;
+    }
+    const uint32_t me = (uint32_t)out.pairs.size();
+    out.pairs.push_back(NodePair());
+    Box lb, rb;
+    const uint32_t l = build(lo, mid, depth + 1, lb);
+    const uint32_t r = build(mid, hi, depth + 1, rb);
+    NodePair p;
+    p.a = make_float4(lb.mn[0] - pad, lb.mn[1] - pad, lb.mn[2] - pad, lb.mx[0] + pad);
+    p.b = make_float4(lb.mx[1] + pad, lb.mx[2] + pad, rb.mn[0] - pad, rb.mn[1] - pad);
+    p.c = make_float4(rb.mn[2] - pad, rb.mx[0] + pad, rb.mx[1] + pad, rb.mx[2] + pad);
+    p.d = make_uint4(l, r, l, r);
+    out.pairs[me] = p;
+    return me;
+  }
+};
+
+// ---- sample-ray cost of both ways (plain float arithmetic: an estimate, not a result) ---------------------------------
+struct Rng {
+  uint64_t s;
+  uint32_t next() { s = s * 6364136223846793005ull + 1442695040888963407ull; return (uint32_t)(s >> 33); }
+  float uni() { return (float)(next() & 0xFFFFFF) / 16777216.0f; }
+};
+
+inline bool slab(const float* o, const float* inv, const float* mn, const float* mx, float& tn, float& tf) {
+  tn = -INFINITY; tf = INFINITY;
+  for (int a = 0; a < 3; ++a) {
+    float t0 = (mn[a] - o[a]) * inv[a], t1 = (mx[a] - o[a]) * inv[a];
+    if (t0 != t0 || t1 != t1) continue;
+    tn = std::max(tn, std::min(t0, t1));
+    tf = std::min(tf, std::max(t0, t1));
+  }
+  return tn <= tf;
+}
+
+inline bool tri_hit(const TriRecord& r, const float* o, const float* d, float limit, float& t) {
+  const float e1[3] = {r.e1.x, r.e1.y, r.e1.z}, e2[3] = {r.e2.x, r.e2.y, r.e2.z}, v0[3] = {r.v0.x, r.v0.y, r.v0.z};
+  float h[3] = {d[1] * e2[2] - d[2] * e2[1], d[2] * e2[0] - d[0] * e2[2], d[0] * e2[1] - d[1] * e2[0]};
+  float a = e1[0] * h[0] + e1[1] * h[1] + e1[2] * h[2];
+  if (a > -0.0001f && a < 0.0001f) return false;
+  float f = 1.0f / a, s[3] = {o[0] - v0[0], o[1] - v0[1], o[2] - v0[2]};
+  float u = f * (s[0] * h[0] + s[1] * h[1] + s[2] * h[2]);
+  if (u < 0.0f || u > 1.0f) return false;
+  float q[3] = {s[1] * e1[2] - s[2] * e1[1], s[2] * e1[0] - s[0] * e1[2], s[0] * e1[1] - s[1] * e1[0]};
+  float v = f * (d[0] * q[0] + d[1] * q[1] + d[2] * q[2]);
+  if (v < 0.0f || u + v > 1.0f) return false;
+  t = f * (e2[0] * q[0] + e2[1] * q[1] + e2[2] * q[2]);
+  return t > 0.00001f && t < limit;
+}
+
+}  // namespace
+
+bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* nodes, uint32_t n_nodes,
+                  const srt_triangle* triangles, const srt_vertex* vertices, const std::vector<TriRecord>& tris_ref,
+                  FinderOut& out) {
+  const uint32_t n_tris = (uint32_t)tris_ref.size();
+  out = FinderOut();
+  if (n_tris == 0 || n_tris > SRT_FINDER_MAX_TRIS) return false;
+  std::vector<Box> tb(n_tris);
+  for (uint32_t i = 0; i < n_tris; ++i) {
+    const float* v[3] = {vertices[triangles[i].v0_idx].vertex, vertices[triangles[i].v1_idx].vertex,
+                         vertices[triangles[i].v2_idx].vertex};
+    // the device tests v0, v0 + edge_1, v0 + edge_2 in effect; the box takes the vertices AND those sums
+    const TriRecord& r = tris_ref[i];
+    const float w1[3] = {r.v0.x + r.e1.x, r.v0.y + r.e1.y, r.v0.z + r.e1.z}, w2[3] = {r.v0.x + r.e2.x, r.v0.y + r.e2.y, r.v0.z + r.e2.z};
+    for (int a = 0; a < 3; ++a) {
+      tb[i].mn[a] = std::min(std::min(v[0][a], std::min(v[1][a], v[2][a])), std::min(w1[a], w2[a]));
+      tb[i].mx[a] = std::max(std::max(v[0][a], std::max(v[1][a], v[2][a])), std::max(w1[a], w2[a]));
+    }
+  }
+  out.rnodes.assign(n_nodes, RefNode{make_float4(0, 0, 0, u2f_(0xFFFFFFFFu)), make_float4(0, 0, 0, u2f_(0u))});
+  out.tri_leaf.assign(n_tris, 0xFFFFFFFFu);
+  out.root.assign(n_bvhs, 0u);
+  out.pad.assign(n_bvhs, 0.0f);
+  std::vector<uint32_t> owner(n_nodes, 0xFFFFFFFFu);  // root that reached the node
+  std::vector<int> leaf_depth(n_nodes, 0);
+  for (uint32_t b = 0; b < n_bvhs; ++b) {
+    const uint32_t root = bvhs[b].first_index;
+    bool again = false;
+    for (uint32_t p = 0; p < b; ++p)
+      if (bvhs[p].first_index == root) { out.root[b] = out.root[p]; out.pad[b] = out.pad[p]; again = true; break; }
+    if (again) continue;  // the same tree under another frame
+    // walk the reference tree: parents, leaves, and (in reverse pre-order) the first visiting rank of every subtree
+    std::vector<uint32_t> pre, stack{root};
+    std::vector<uint32_t> mine;
+    out.rnodes[root].a.w = u2f_(0xFFFFFFFFu);
+    if (owner[root] != 0xFFFFFFFFu) return false;  // a root inside another BVH's tree: no single parent chain
+    std::vector<int> depth_of(1, 0);
+    std::vector<uint32_t> dstack{0};
+    while (!stack.empty()) {
+      const uint32_t n = stack.back();
+      stack.pop_back();
+      const int dep = (int)dstack.back();
+      dstack.pop_back();
+      if (owner[n] != 0xFFFFFFFFu) return false;
+      owner[n] = root;
+      pre.push_back(n);
+      const srt_bvh_node& node = nodes[n];
+      out.rnodes[n].a.x = node.min_bounds[0]; out.rnodes[n].a.y = node.min_bounds[1]; out.rnodes[n].a.z = node.min_bounds[2];
+      out.rnodes[n].b.x = node.max_bounds[0]; out.rnodes[n].b.y = node.max_bounds[1]; out.rnodes[n].b.z = node.max_bounds[2];
+      leaf_depth[n] = dep;
+      if (node.prim_count > 0) {
+        for (uint32_t k = 0; k < node.prim_count; ++k) {
+          const uint32_t t = node.first_child_or_prim_index + k;
+          if (out.tri_leaf[t] != 0xFFFFFFFFu) return false;  // a triangle in two leaves
+          out.tri_leaf[t] = n;
+          mine.push_back(t);
+        }
+      } else {
+        const uint32_t c = node.first_child_or_prim_index;
+        out.rnodes[c].a.w = u2f_(n);
+        out.rnodes[c + 1].a.w = u2f_(n);
+        stack.push_back(c); dstack.push_back((uint32_t)dep + 1);
+        stack.push_back(c + 1); dstack.push_back((uint32_t)dep + 1);
+      }
+    }
+    for (size_t i = pre.size(); i-- > 0;) {
+      const uint32_t n = pre[i];
+      const srt_bvh_node& node = nodes[n];
+      uint32_t fr = 0xFFFFFFFFu;
+      if (node.prim_count > 0) {
+        for (uint32_t k = 0; k < node.prim_count; ++k)
+          fr = std::min(fr, f2u_(tris_ref[node.first_child_or_prim_index + k].e1.w));
+      } else {
+        fr = std::min(f2u_(out.rnodes[node.first_child_or_prim_index].b.w), f2u_(out.rnodes[node.first_child_or_prim_index + 1].b.w));
+      }
+      out.rnodes[n].b.w = u2f_(fr);
+    }
+    if (mine.empty()) return false;
+    float ext = 0.0f;
+    for (int a = 0; a < 3; ++a) ext = std::max(ext, nodes[root].max_bounds[a] - nodes[root].min_bounds[a]);
+    if (!(ext > 0.0f) || !std::isfinite(ext)) return false;
+    Builder B{tris_ref, tb, std::move(mine), out};
+    B.pad = ext * (1.0f / 4096.0f);
+    Box whole;
+    out.root[b] = B.build(0, (uint32_t)B.idx.size(), 0, whole);
+    out.pad[b] = B.pad;
+  }
+  if (out.pairs.size() >= SRT_LEAF_BIT - 1u || out.depth > SRT_STACK_SIZE - 1) return false;
+
+  // ---- is it worth it?  Sample rays from the surfaces (where bounce and shadow rays start) and from outside (where
+  // camera rays start); count the tests of the shader's traversal and of finder + replay.
+  Rng rng{0x5EEDF1DDull};
+  double cost_ref = 0.0, cost_find = 0.0;
+  const int n_samples = 2048;
+  std::vector<uint32_t> st;
+  for (int s = 0; s < n_samples; ++s) {
+    const uint32_t b = rng.next() % n_bvhs;
+    const uint32_t root = bvhs[b].first_index;
+    const uint32_t t = rng.next() % n_tris;
+    if (owner[out.tri_leaf[t]] != root) { continue; }
+    const TriRecord& r = tris_ref[t];
+    float dir[3];
+    do {
+      for (int a = 0; a < 3; ++a) dir[a] = 2.0f * rng.uni() - 1.0f;
+    } while (dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2] > 1.0f || dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2] < 1e-4f);
+    float on[3] = {r.v0.x + 0.3f * r.e1.x + 0.3f * r.e2.x, r.v0.y + 0.3f * r.e1.y + 0.3f * r.e2.y, r.v0.z + 0.3f * r.e1.z + 0.3f * r.e2.z};
+    float o[3] = {on[0], on[1], on[2]};
+    if (s & 1) {  // from outside, aimed at the surface point
+      float ext = 0.0f;
+      for (int a = 0; a < 3; ++a) ext = std::max(ext, nodes[root].max_bounds[a] - nodes[root].min_bounds[a]);
+      for (int a = 0; a < 3; ++a) { o[a] = on[a] - 2.0f * ext * dir[a]; }
+    }
+    const float inv[3] = {1.0f / dir[0], 1.0f / dir[1], 1.0f / dir[2]};
+    // the shader's traversal
+    {
+      float best = INFINITY;
+      st.assign(1, root);
+      while (!st.empty()) {
+        const uint32_t n = st.back();
+        st.pop_back();
+        const srt_bvh_node& node = nodes[n];
+        float tn, tf;
+        cost_ref += 1.0;
+        if (!slab(o, inv, node.min_bounds, node.max_bounds, tn, tf)) continue;
+        const float d = tn >= 0.0f ? tn : tf;
+        if (!(d < best)) continue;
+        if (node.prim_count > 0) {
+          for (uint32_t k = 0; k < node.prim_count; ++k) {
+            float tt;
+            cost_ref += 1.5;
+            if (tri_hit(tris_ref[node.first_child_or_prim_index + k], o, dir, best, tt)) best = tt;
+          }
+        } else {
+          st.push_back(node.first_child_or_prim_index);
+          st.push_back(node.first_child_or_prim_index + 1);
+        }
+      }
+    }
+    // finder + replay
+    {
+      st.assign(1, out.root[b]);
+      while (!st.empty()) {
+        const uint32_t n = st.back();
+        st.pop_back();
+        if (n & SRT_LEAF_BIT) {
+          uint32_t i = n & ~SRT_LEAF_BIT;
+          for (;;) {
+            float tt;
+            cost_find += 1.5;
+            if (tri_hit(out.tris[i], o, dir, INFINITY, tt)) cost_find += 1.0 + leaf_depth[out.tri_leaf[f2u_(out.tris[i].v0.w)]];
+            if (f2u_(out.tris[i].e2.w) == 0u) break;
+            ++i;
+          }
+          continue;
+        }
+        const NodePair& p = out.pairs[n];
+        const float lmn[3] = {p.a.x, p.a.y, p.a.z}, lmx[3] = {p.a.w, p.b.x, p.b.y}, rmn[3] = {p.b.z, p.b.w, p.c.x}, rmx[3] = {p.c.y, p.c.z, p.c.w};
+        float tn, tf;
+        cost_find += 2.0;
+        if (slab(o, inv, lmn, lmx, tn, tf) && tf >= 0.0f) st.push_back(p.d.z);
+        if (slab(o, inv, rmn, rmx, tn, tf) && tf >= 0.0f) st.push_back(p.d.w);
+      }
+    }
+  }
+  out.cost_reference = cost_ref / n_samples;
+  out.cost_finder = cost_find / n_samples;
+  out.worthwhile = out.cost_finder < 0.75 * out.cost_reference;
+  return true;
+}
+
+}  // namespace srt

@@ -12,6 +12,7 @@
 #include "srt_persistent.cuh"
 #include "srt_wavefront.cuh"
 #include "srt_wf_tail.cuh"
+#include "srt_wf_find.cuh"
 
 namespace srt {
 
@@ -328,11 +329,51 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
 }
 }  // namespace
 
+namespace {
+// the trace step through the hit finder (srt_wf_find.cuh): candidates, then the rays with too many of them the long way,
+// then the replay of the shader's culls
+cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
+                           DeviceCounters* counters, int block, cudaStream_t stream) {
+  static int per_sm = 0, sms = 0;
+  static size_t smem_set = 0;
+  const size_t smem = (size_t)fp.stack_cap * SRT_WF_FIND_THREADS * 4u + (size_t)SRT_CAND_MAX * SRT_WF_FIND_THREADS * 8u;
+  cudaError_t e;
+  if (per_sm == 0 || smem_set != smem) {
+    int dev = 0;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    if (smem > 48 * 1024 &&
+        (e = cudaFuncSetAttribute(wf_find_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+      return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_find_kernel, SRT_WF_FIND_THREADS, smem)) != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    smem_set = smem;
+  }
+  long grid = (long)sms * per_sm;
+  long need = ((long)pool.cap / 32 + 1) / 2;
+  if (grid > need) grid = need;
+  if (grid < 1) grid = 1;
+  wf_find_kernel<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  PathPool over = pool;  // the overflow list, seen through the trace kernel's own interface
+  over.q = &pool.fq->over;
+  over.list[0] = pool.olist;
+  over.list[1] = pool.olist;
+  if ((e = wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, over, 0, refill, counters, block, stream)) != cudaSuccess) return e;
+  long blocks = ((long)pool.cap + 127) / 128;
+  if (blocks > (long)sms * 16) blocks = (long)sms * 16;
+  wf_replay_kernel<<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool);
+  return cudaGetLastError();
+}
+}  // namespace
+
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
-                           cudaEvent_t after_trace) {
+                           cudaEvent_t after_trace, bool finder) {
   cudaError_t e;
-  if (mode == TRAV_REFERENCE)
+  if (finder)
+    e = wf_find_launch(sc, fp, pool, parity, refill, counters, block, stream);
+  else if (mode == TRAV_REFERENCE)
     e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, refill, counters, block, stream)
               : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, refill, counters, block, stream);
   else

@@ -17,7 +17,7 @@ cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const P
                            DeviceCounters* counters, cudaStream_t stream);
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
-                           cudaEvent_t after_trace = nullptr);
+                           cudaEvent_t after_trace = nullptr, bool finder = false);
 // The end of a launch (srt_wf_tail.cuh): every path still in the queues of `parity` is run to its last bounce.
 cudaError_t launch_wf_tail(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            uint32_t* ids, DeviceCounters* counters, cudaStream_t stream);

@@ -75,6 +75,7 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
     pool.q->cursor = 0;
     pool.q->live_slots = (unsigned int)first;
     pool.q->next_path = first;
+    if (pool.fq != nullptr) memset(pool.fq, 0, sizeof(FinderQueues));
     atomicAdd(&counters->segments, first);
     atomicAdd(&counters->paths, pool.n_paths);
   }
@@ -338,7 +339,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   const uint32_t chunks_a = (n_a + 31u) >> 5, chunks_b = (n_b + 31u) >> 5;
   const uint32_t* __restrict__ list_in = parity ? pool.list[1] : pool.list[0];
   uint32_t* __restrict__ list_out = parity ? pool.list[0] : pool.list[1];
-  if (blockIdx.x == 0 && threadIdx.x == 0) q->cursor = 0;  // for the next wave's trace kernel
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // for the next wave's trace kernels
+    q->cursor = 0;
+    if (pool.fq != nullptr) memset(pool.fq, 0, sizeof(FinderQueues));
+  }
   const V3 sky = v3(0.05f);
   unsigned int n_seg = 0, n_shadow = 0, n_capped = 0, n_done = 0;
   bool paths_out = *(volatile unsigned long long*)&q->next_path >= pool.n_paths;  // warp-uniform

@@ -1,0 +1,331 @@
+// srt_wf_find.cuh -- the wavefront schedule's trace step through the HIT FINDER (srt_finder.h): same hit and distance
+// as Intersects / CheckHit (ray_intersects.glsl:99-133, raytrace_compute.glsl:143-162), from two kernels:
+//   * wf_find_kernel   : persistent warps fed from the wave's queues exactly like wf_trace_kernel, but walking the
+//     finder's SAH tree WITHOUT distance culling and collecting every triangle that passes the shader's triangle
+//     test against the ray's initial intersection_distance (the candidates).  No candidate: the ray missed, written
+//     at once (3 of 4 rays on Rubik).  Up to SRT_CAND_MAX candidates: stored per slot, the slot goes on the replay
+//     list.  More: the slot goes on the overflow list, which wf_trace_kernel walks the long way.
+//   * wf_replay_kernel : one thread per listed ray.  Candidates in the shader's visiting order; for each, the shader's
+//     own IntersectsBox on every reference node above it, against the distance of the last candidate accepted before
+//     that node's subtree begins -- the test the shader makes when it pops the node (:108-110).  A candidate that
+//     passes them all and is nearer than the running closest hit is what the shader would have accepted.
+// Why the replay is exact: the shader tests a node when it pops it, after every triangle of lower visiting rank and
+// before every triangle of its own subtree; its running distance at that moment is the distance of the last accepted
+// triangle of lower rank (or the initial distance); rejected triangle tests change nothing.  Padded boxes and a
+// NaN-ignoring slab test keep the finder conservative; tests compare whole frames with the oracle bit for bit.
+#pragma once
+
+#include "srt_wavefront.cuh"
+
+namespace srt {
+
+#define SRT_WF_FIND_THREADS 64
+
+__device__ __forceinline__ void wf_sts1(uint32_t addr, uint32_t x) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(x) : "memory");
+}
+__device__ __forceinline__ uint32_t wf_lds1(uint32_t addr) {
+  uint32_t r;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(addr) : "memory");
+  return r;
+}
+
+// conservative ray/box: hardware min/max drop NaN slabs (0 * inf), the boxes are padded
+__device__ __forceinline__ bool wf_find_box(V3 o, V3 inv, float tmax, float mnx, float mny, float mnz, float mxx, float mxy,
+                                            float mxz) {
+  float tn, tf;
+  wf_slab_fast(o, inv, mnx, mny, mnz, mxx, mxy, mxz, tn, tf);
+  return (tn <= tf) && (tf >= 0.0f) && (tn <= tmax);
+}
+
+__global__ void __launch_bounds__(SRT_WF_FIND_THREADS)
+wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity, int refill_threshold) {
+  extern __shared__ uint32_t s_find[];  // [stack_cap][64] node references, then [SRT_CAND_MAX][64] candidates (8 B)
+  const uint32_t sp_base = (uint32_t)__cvta_generic_to_shared(s_find + threadIdx.x);
+  constexpr uint32_t sp_step = SRT_WF_FIND_THREADS * 4u;
+  const uint32_t cand_base = (uint32_t)__cvta_generic_to_shared(s_find + fp.stack_cap * SRT_WF_FIND_THREADS) + threadIdx.x * 8u;
+  constexpr uint32_t cand_step = SRT_WF_FIND_THREADS * 8u;
+  const unsigned FULL = 0xFFFFFFFFu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  WaveCounters* q = pool.q;
+  FinderQueues* fq = pool.fq;
+  const uint32_t n_front = q->n_closest[parity];
+  const uint32_t n_total = n_front + q->n_shadow[parity];
+  const uint32_t* __restrict__ list = parity ? pool.list[1] : pool.list[0];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // the logic kernel of this wave fills the other list from empty
+    q->n_closest[parity ^ 1] = 0;
+    q->n_shadow[parity ^ 1] = 0;
+  }
+
+  bool trav = false, pending = false, overflow = false;
+  uint32_t slot = 0, cur = 0, bvh_i = 0, n_cand = 0;
+  V3 to = v3(0.0f), td = v3(0.0f), inv = v3(0.0f);
+  float tmax = 0.0f;
+  uint32_t sp = sp_base;
+  bool exhausted = false;
+  const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
+  int lane_cap = (int)((n_total + total_warps - 1) / total_warps);
+  lane_cap = lane_cap < 4 ? 4 : (lane_cap > 32 ? 32 : lane_cap);
+  const int refill_at = refill_threshold < (lane_cap + 1) / 2 ? refill_threshold : (lane_cap + 1) / 2;
+  uint32_t r_next = 0, r_end = 0, seen_cursor = 0;
+
+  auto enter = [&]() {  // next BVH whose (padded) root box the ray meets, or the end of the ray
+    for (;;) {
+      if (bvh_i >= fp.bvh_count) {
+        trav = false;
+        pending = true;
+        return;
+      }
+      const BvhRecord* bvh = sc.bvhs + bvh_i;
+      const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1];
+      to = mat4_mul_(bvh->frame, v3(a.x, a.y, a.z), 1.0f);
+      td = mat4_mul_(bvh->frame, v3(b.x, b.y, b.z), 0.0f);
+      inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
+      const float pad = bvh->finder_pad;
+      if (wf_find_box(to, inv, tmax, bvh->root_min[0] - pad, bvh->root_min[1] - pad, bvh->root_min[2] - pad,
+                      bvh->root_max[0] + pad, bvh->root_max[1] + pad, bvh->root_max[2] + pad)) {
+        cur = bvh->finder_root;
+        sp = sp_base;
+        return;
+      }
+      ++bvh_i;
+    }
+  };
+  auto pop = [&]() {
+    if (sp == sp_base) {
+      ++bvh_i;
+      enter();
+      return;
+    }
+    sp -= sp_step;
+    cur = wf_lds1(sp);
+  };
+
+  for (;;) {
+    // ---- rays that ended since the last visit: miss / replay list / overflow list ---------------------------------
+    {
+      const bool to_replay = pending && !overflow && n_cand > 0;
+      const bool to_over = pending && overflow;
+      if (pending && !overflow && n_cand == 0) pool.hit[slot] = make_uint2(SRT_NO_HIT, __float_as_uint(tmax));
+      const unsigned m_r = __ballot_sync(FULL, to_replay);
+      if (m_r) {
+        uint32_t base = 0;
+        const int leader = __ffs(m_r) - 1;
+        if (lane == leader) base = atomicAdd(&fq->n_replay, (unsigned int)__popc(m_r));
+        base = __shfl_sync(FULL, base, leader);
+        if (to_replay) {
+          uint2* dst = pool.cand + (size_t)slot * SRT_CAND_MAX;
+          for (uint32_t k = 0; k < n_cand; ++k) dst[k] = wf_lds(cand_base + k * cand_step);
+          pool.rlist[base + __popc(m_r & lt_mask)] = slot | (n_cand << 28);
+        }
+      }
+      const unsigned m_o = __ballot_sync(FULL, to_over);
+      if (m_o) {
+        uint32_t base = 0;
+        const int leader = __ffs(m_o) - 1;
+        if (lane == leader) base = atomicAdd(&fq->over.n_closest[0], (unsigned int)__popc(m_o));
+        base = __shfl_sync(FULL, base, leader);
+        if (to_over) pool.olist[base + __popc(m_o & lt_mask)] = slot;
+      }
+      pending = false;
+    }
+    // ---- refill idle lanes from the wave's queue (as wf_trace_kernel; the cursor is the finder's own) -------------------
+    while (!exhausted) {
+      const unsigned idle = __ballot_sync(FULL, !trav && !pending);  // a pending lane keeps its slot until the flush
+      const int n_want = lane_cap - (32 - __popc(idle));
+      if (n_want <= 0) break;
+      if (r_next == r_end) {
+        uint32_t chunk = (n_total - seen_cursor) / (total_warps * 4u);
+        chunk = chunk > SRT_WF_FETCH_MAX ? SRT_WF_FETCH_MAX : chunk;
+        chunk = chunk < (uint32_t)lane_cap ? (uint32_t)lane_cap : chunk;
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&fq->cursor, chunk);
+        base = __shfl_sync(FULL, base, 0);
+        if (base >= n_total) {
+          exhausted = true;
+          break;
+        }
+        r_next = base;
+        r_end = base + chunk < n_total ? base + chunk : n_total;
+        seen_cursor = r_end;
+      }
+      const int n_take = (int)(r_end - r_next) < n_want ? (int)(r_end - r_next) : n_want;
+      const int my_rank = __popc(idle & lt_mask);
+      if (!trav && !pending && my_rank < n_take) {
+        const uint32_t idx = r_next + my_rank;
+        const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
+        if (entry != SRT_WF_HOLE) {
+          slot = entry;
+          tmax = pool.ray[2 * (size_t)slot].w;
+          n_cand = 0;
+          overflow = false;
+          bvh_i = 0;
+          trav = true;
+          enter();  // may end the ray at once (no root box met): flushed as a miss on the next visit
+        }
+      }
+      r_next += n_take;
+      if (__any_sync(FULL, pending)) break;  // flush before those lanes are handed another ray
+    }
+    if (!__any_sync(FULL, trav)) {
+      if (__any_sync(FULL, pending)) continue;
+      break;
+    }
+
+    // ---- traverse until enough lanes are idle again: descent phase / leaf phase, as wf_trace_kernel ------------------
+    for (;;) {
+      for (;;) {
+        const int a = __popc(__ballot_sync(FULL, trav && cur < SRT_WF_NEED_POP));
+        if (a <= SRT_WF_DESCENT_CUTOFF && (a == 0 || __any_sync(FULL, trav && (cur & SRT_LEAF_BIT)))) break;
+        if (trav && cur < SRT_WF_NEED_POP) {
+          const float4* p = reinterpret_cast<const float4*>(sc.fpairs + cur);
+          const float4 na = __ldg(p), nb = __ldg(p + 1), nc = __ldg(p + 2);
+          const uint4 nd = __ldg(reinterpret_cast<const uint4*>(p + 3));
+          const bool pl = wf_find_box(to, inv, tmax, na.x, na.y, na.z, na.w, nb.x, nb.y);
+          const bool pr = wf_find_box(to, inv, tmax, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w);
+          if (pl && pr) {
+            wf_sts1(sp, nd.w);
+            sp += sp_step;
+            cur = nd.z;
+          } else if (pl || pr) {
+            cur = pl ? nd.z : nd.w;
+          } else {
+            pop();
+          }
+        }
+      }
+      while (__any_sync(FULL, trav && (cur & SRT_LEAF_BIT))) {
+        if (trav && (cur & SRT_LEAF_BIT)) {
+          // IntersectsTriangle (ray_intersects.glsl:61-96) against the ray's INITIAL intersection_distance
+          const float4* p = reinterpret_cast<const float4*>(sc.ftris + (cur & ~SRT_LEAF_BIT));
+          const float4 r0 = __ldg(p), r1 = __ldg(p + 1), r2 = __ldg(p + 2);
+          const V3 edge_1 = v3(r1.x, r1.y, r1.z), edge_2 = v3(r2.x, r2.y, r2.z);
+          const V3 h = cross_(td, edge_2);
+          const float a = dot_(edge_1, h);
+          if (!(a > -0.0001f && a < 0.0001f)) {
+            const float f = rcp_(a);
+            const V3 s = to - v3(r0.x, r0.y, r0.z);
+            const float u = f * dot_(s, h);
+            if (!(u < 0.0f || u > 1.0f)) {
+              const V3 qv = cross_(s, edge_1);
+              const float v = f * dot_(td, qv);
+              if (!(v < 0.0f || u + v > 1.0f)) {
+                const float t = f * dot_(edge_2, qv);
+                if (t > 0.00001f && t < tmax) {
+                  if (n_cand == SRT_CAND_MAX) {
+                    overflow = true;
+                    trav = false;
+                    pending = true;
+                  } else {
+                    wf_sts(cand_base + n_cand * cand_step, __float_as_uint(r0.w) | (bvh_i << SRT_CAND_BVH_SHIFT), __float_as_uint(t));
+                    n_cand++;
+                  }
+                }
+              }
+            }
+          }
+          cur = __float_as_uint(r2.w) ? cur + 1u : SRT_WF_NEED_POP;
+        }
+      }
+      if (trav && cur == SRT_WF_NEED_POP) pop();
+      const int n_idle = __popc(__ballot_sync(FULL, !trav));
+      if (n_idle == 32) break;
+      if (!exhausted && n_idle - (32 - lane_cap) >= refill_at) break;
+    }
+  }
+}
+
+// ---- replay: the shader's culls above each candidate, candidates in the shader's visiting order ------------------------
+__global__ void __launch_bounds__(128)
+wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool) {
+  const uint32_t n = pool.fq->n_replay;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t entry = pool.rlist[i];
+    const uint32_t slot = entry & 0x0FFFFFFFu, n_cand = entry >> 28;
+    const float4 ra = pool.ray[2 * (size_t)slot], rb = pool.ray[2 * (size_t)slot + 1];
+    const V3 ray_o = v3(ra.x, ra.y, ra.z), ray_d = v3(rb.x, rb.y, rb.z);
+    const bool any_hit = (__float_as_uint(rb.w) & 0xFFu) == SRT_WF_KIND_SHADOW;
+    // candidates: (triangle | bvh << 26, distance); keys = bvh << 26 | visiting rank (ranks stay below 2^26 with the finder)
+    uint32_t c_tri[SRT_CAND_MAX], c_key[SRT_CAND_MAX];
+    float c_t[SRT_CAND_MAX];
+    const uint2* src = pool.cand + (size_t)slot * SRT_CAND_MAX;
+#pragma unroll
+    for (int k = 0; k < SRT_CAND_MAX; ++k) {
+      if (k < (int)n_cand) {
+        const uint2 c = src[k];
+        const uint32_t tri = c.x & ((1u << SRT_CAND_BVH_SHIFT) - 1u);
+        c_tri[k] = tri;
+        c_t[k] = __uint_as_float(c.y);
+        c_key[k] = (c.x & ~((1u << SRT_CAND_BVH_SHIFT) - 1u)) | __float_as_uint(__ldg(&sc.tris[tri].e1.w));
+      } else {
+        c_tri[k] = 0;
+        c_t[k] = 0.0f;
+        c_key[k] = 0xFFFFFFFFu;
+      }
+    }
+    float best = ra.w;       // the shader's inout intersection_distance
+    uint32_t hit = SRT_NO_HIT;
+    uint32_t cur_bvh = 0xFFFFFFFFu;
+    V3 to = v3(0.0f), inv = v3(0.0f);
+    float best_in = best;    // the distance this BVH's traversal started with
+    uint32_t root_node = 0;
+    // accepted candidates of the current BVH, in visiting order (their distances decrease)
+    uint32_t a_rank[SRT_CAND_MAX];
+    float a_t[SRT_CAND_MAX];
+    int n_acc = 0;
+    for (uint32_t round = 0; round < n_cand; ++round) {
+      // next candidate in visiting order
+      int k = 0;
+      uint32_t key = 0xFFFFFFFFu;
+#pragma unroll
+      for (int j = 0; j < SRT_CAND_MAX; ++j)
+        if (c_key[j] < key) { key = c_key[j]; k = j; }
+      uint32_t tri = 0;
+      float t = 0.0f;
+#pragma unroll
+      for (int j = 0; j < SRT_CAND_MAX; ++j)
+        if (j == k) { tri = c_tri[j]; t = c_t[j]; c_key[j] = 0xFFFFFFFFu; }
+      const uint32_t bvh_i = key >> SRT_CAND_BVH_SHIFT, rank = key & ((1u << SRT_CAND_BVH_SHIFT) - 1u);
+      if (bvh_i != cur_bvh) {
+        const BvhRecord* bvh = sc.bvhs + bvh_i;
+        to = mat4_mul_(bvh->frame, ray_o, 1.0f);
+        const V3 td = mat4_mul_(bvh->frame, ray_d, 0.0f);
+        inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
+        root_node = bvh->root_node;
+        cur_bvh = bvh_i;
+        best_in = best;
+        n_acc = 0;
+      }
+      if (!(t < best)) continue;  // the shader's `t < intersection_distance` fails whatever the boxes say
+      bool seen = true;
+      for (uint32_t node = __ldg(sc.tri_leaf + tri);;) {
+        const float4 na = __ldg(&sc.rnodes[node].a), nb = __ldg(&sc.rnodes[node].b);
+        const uint32_t first_rank = __float_as_uint(nb.w);
+        float at_pop = best_in;
+#pragma unroll
+        for (int j = 0; j < SRT_CAND_MAX; ++j)
+          if (j < n_acc && a_rank[j] < first_rank) at_pop = a_t[j];
+        bool inside;
+        const float d = box_distance(to, inv, na.x, na.y, na.z, nb.x, nb.y, nb.z, inside);
+        if (!((d < at_pop) && !isinf_(d))) {  // ray_intersects.glsl:108
+          seen = false;
+          break;
+        }
+        node = (node == root_node) ? 0xFFFFFFFFu : __float_as_uint(na.w);
+        if (node == 0xFFFFFFFFu) break;
+      }
+      if (!seen) continue;
+      best = t;
+      hit = tri;
+      if (any_hit) break;  // CheckLightOccluded only reads rec.hit
+#pragma unroll
+      for (int j = 0; j < SRT_CAND_MAX; ++j)
+        if (j == n_acc) { a_rank[j] = rank; a_t[j] = t; }
+      n_acc++;
+    }
+    pool.hit[slot] = make_uint2(hit, __float_as_uint(best));
+  }
+}
+
+}  // namespace srt

@@ -14,13 +14,21 @@ pytestmark = pytest.mark.gpu
 
 
 def gpu_render(pkg, ctx, W, H, show_model, n_frames, traversal, scene=None, lights=None, cam=None, first_frame=1,
-               max_depth=0, noise=None, rows=None, schedule=3, textures=None, tail=None):
-    """schedule 30 = the wavefront schedule (3) with waves to the very end (SRT_OPT_TAIL_PATHS = 0); plain 3 uses the
-    library's default, under which launches of these sizes run in the tail kernel right after wf_init_kernel."""
+               max_depth=0, noise=None, rows=None, schedule=3, textures=None, tail=None, finder=None):
+    """Variants of the wavefront schedule (3): plain 3 = the library's defaults (hit finder where srt_upload_scene finds
+    it worthwhile -- Rubik yes, soup no --, and launches of these sizes run in the tail kernel right after
+    wf_init_kernel); 30 = waves to the very end (SRT_OPT_TAIL_PATHS = 0) walking the reference BVH (SRT_OPT_FINDER = 0);
+    31 = waves to the very end through the hit finder (SRT_OPT_FINDER = 1); 32 = default tail, finder off."""
     if schedule == 30:
-        schedule, tail = 3, 0
+        schedule, tail, finder = 3, 0, 0
+    elif schedule == 31:
+        schedule, tail, finder = 3, 0, 1
+    elif schedule == 32:
+        schedule, finder = 3, 0
     if tail is not None:
         ctx.set_option(pkg.OPT_TAIL_PATHS, tail)
+    if finder is not None:
+        ctx.set_option(pkg.OPT_FINDER, finder)
     unit, uniform = noise if noise is not None else scenes.noise_tables(W, H)
     lights = lights if lights is not None else (scenes.model_lights() if show_model else scenes.sphere_lights())
     cam = cam or scenes.reset_camera(show_model)
@@ -109,7 +117,7 @@ def test_spheres_multi_frame_bit_exact(pkg, ctx, oracle, frames):
     assert np.array_equal(out, oout)
 
 
-@pytest.mark.parametrize("schedule", [0, 1, 2, 3, 30])
+@pytest.mark.parametrize("schedule", [0, 1, 2, 3, 30, 31, 32])
 def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     """C2's scene at a size the oracle finishes in seconds; reference visiting order => bit-exact."""
     scene = scenes.rubik_scene()
@@ -122,7 +130,7 @@ def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     assert ocnt["capped_paths"] == 0 and cnt["capped_paths"] == 0
 
 
-@pytest.mark.parametrize("schedule", [0, 1, 2, 3, 30])
+@pytest.mark.parametrize("schedule", [0, 1, 2, 3, 30, 31, 32])
 def test_rubik_ordered_traversal_matches_bar_ties(pkg, ctx, oracle, schedule):
     """Ordered traversal: same image except documented grazing ties (budget: 1e-4 of the pixels; ids identical
     on every pixel outside that budget, radiance bit-exact there too)."""
@@ -149,7 +157,7 @@ def test_wavefront_small_pool_and_frame_chunks_bit_exact(pkg, ctx, oracle):
     assert cnt["paths"] == 256 * 128 * 5
 
 
-@pytest.mark.parametrize("schedule", [2, 3, 30])
+@pytest.mark.parametrize("schedule", [2, 3, 30, 31])
 def test_airplane_standin_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     """BASELINE.json configs[2]'s scene is absent from the reference mount; its documented stand-in (6 Airplane
     materials, leaves of up to ~100 triangles from the reference's midpoint builder) through the host loader."""
@@ -179,7 +187,7 @@ def framed(scale, rot_y_deg, translate):
     return np.linalg.inv(T @ R @ S).astype(np.float32).T.reshape(16).copy()
 
 
-@pytest.mark.parametrize("schedule", [0, 2, 3, 30])
+@pytest.mark.parametrize("schedule", [0, 2, 3, 30, 31])
 def test_two_models_with_frames_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     """SURVEY 8(f) N4: bvh_count = 2, each model behind its own world->model frame (raytrace_compute.glsl:144-161);
     the closest hit is taken over both, t shared between model spaces as the shader does (Q14).  Then one frame is
@@ -212,7 +220,7 @@ def test_two_models_with_frames_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     assert_bit_exact(ctx.read_accum(), oacc2)
 
 
-@pytest.mark.parametrize("schedule", [3, 30])
+@pytest.mark.parametrize("schedule", [3, 30, 31])
 def test_soup_depth8_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     """BASELINE.json configs[4] at a size the oracle finishes in seconds: random soup, maxDepth 8, camera (0,0,120)."""
     scene, info = scenes.soup_scene(20000, str(tmp_path))
@@ -227,7 +235,7 @@ def test_soup_depth8_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     assert ocnt["capped_paths"] == 0
 
 
-@pytest.mark.parametrize("schedule", [3, 30])
+@pytest.mark.parametrize("schedule", [3, 30, 31])
 def test_rubik_inside_view_and_depth8(pkg, ctx, oracle, schedule):
     """Camera inside the model's bounds looking around (many bounces), maxDepth 8 as C5 uses."""
     scene = scenes.rubik_scene()
