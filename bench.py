@@ -205,6 +205,8 @@ def run_gpu(args):
         ctx.set_option(pkg.OPT_TAIL_PATHS, args.tail_paths)
     if args.finder >= 0:
         ctx.set_option(pkg.OPT_FINDER, args.finder)
+    if args.primary_cull >= 0:
+        ctx.set_option(pkg.OPT_PRIMARY_CULL, args.primary_cull)
 
     def upload_all():
         if inp["scene"] is not None:
@@ -357,7 +359,12 @@ def run_gpu(args):
     if wavefront:
         # wf_trace_kernel does ALL box and triangle tests; its launches of one step differ in size (one per wave), so
         # bytes per launch and duration per launch are both averages over the timed region's launches
-        kname, k_ms, k_launches = "wf_trace_kernel", trace_ms, max(n_waves, 1.0)
+        # (with the hit finder the same tests are answered by wf_find_kernel + wf_replay_kernel, overflow rays by
+        # wf_trace_kernel; with the primary cull the root-box tests of culled primary rays by wf_init_kernel; the last
+        # paths by wf_tail_kernel: trace_ms brackets them all, shading of the tail included)
+        finder_on = bool(ctx.finder_info()[0])
+        kname = "wf_find_kernel+wf_replay_kernel (+wf_trace_kernel overflow, wf_init_kernel cull, wf_tail_kernel)" if finder_on else "wf_trace_kernel"
+        k_ms, k_launches = trace_ms, max(n_waves, 1.0)
     else:
         kname, k_ms, k_launches = "pathtrace_persistent_kernel" if args.schedule == "persistent" else "pathtrace_kernel", kernel_ms, float(args.steps * world)
     achieved = rays * bytes_per_ray / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
@@ -409,6 +416,7 @@ def run_gpu(args):
                             if world > 1 else "single GPU",
                    "l2": "512 MB device buffer rewritten between timed steps (L2 flush)",
                    "tail_paths": "library default" if args.tail_paths < 0 else args.tail_paths,
+                   "primary_cull": "library default (on)" if args.primary_cull < 0 else args.primary_cull,
                    "hit_finder": dict(zip(("active", "cost_reference", "cost_finder"), ctx.finder_info())) if show_model else None,
                    "ms_per_frame": ms_per_step / spp},
         "segments_per_step": segments / args.steps, "shadow_rays_per_step": shadow / args.steps,
@@ -439,6 +447,8 @@ def main():
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
     ap.add_argument("--l2-persist", type=int, default=-1, help="1/0: pin the BVH top levels in L2 (default: library default, on)")
     ap.add_argument("--refill", type=int, default=0, help="refill threshold of the wavefront trace kernel (0 = default)")
+    ap.add_argument("--primary-cull", type=int, default=-1,
+                    help="1/0: primary rays that miss every root box end in the init kernel (-1 = library default, on)")
     ap.add_argument("--finder", type=int, default=-1,
                     help="hit finder of the wavefront schedule: 0 off, 1 on, 2 auto (-1 = library default, auto)")
     ap.add_argument("--tail-paths", type=int, default=-1,

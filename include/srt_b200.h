@@ -77,6 +77,13 @@ typedef struct srt_counters {
                                          airplane), 0 otherwise (the random soup: every ray meets dozens of triangles)
                                      Set before srt_upload_scene.  Scenes above 2 Mi triangles never use it. */
 
+#define SRT_OPT_PRIMARY_CULL 13   /* wavefront schedule: 1 (default) = a primary ray that misses the root box of every BVH -- the
+                                     first test of the shader's own traversal (ray_intersects.glsl:106-110) -- ends where it is
+                                     generated: its path's sample is the sky term (raytrace_compute.glsl:287-292), it takes no
+                                     path slot and no queue entry.  Applies when every path of a frame chunk starts in wave 0
+                                     (chunks are sized for that when the pool holds at least one frame).  0 = every primary ray
+                                     goes through the queues.  Same bits either way. */
+
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */
 int srt_create(srt_ctx** out, int device);

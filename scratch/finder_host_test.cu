@@ -46,7 +46,7 @@ int main(int argc,char**argv){
   std::vector<int> seen(nt,0); for(auto&r:fo.tris)seen[F2U(r.v0.w)]++; for(uint32_t i=0;i<nt;++i)if(seen[i]!=1){printf("triangle %u appears %d times\n",i,seen[i]);return 1;}
   // rays: from surface points and from outside
   uint64_t s=12345; auto rnd=[&](){s=s*6364136223846793005ull+1442695040888963407ull;return (float)((s>>33)&0xFFFFFF)/16777216.0f;};
-  long mism=0,over=0,nray=200000; double cands=0;
+  long mism=0,over=0,nray=200000; double cands=0; long n_out=0,o_mism=0,o_unc=0,o_over=0,o_cands=0,o_boxes=0,o_tris=0,o_rboxes=0;
   for(long it=0;it<nray;++it){
     uint32_t t0=(uint32_t)(rnd()*nt)%nt; float d[3]={2*rnd()-1,2*rnd()-1,2*rnd()-1};
     float a=rnd()*0.8f,b=rnd()*(0.9f-a); float o[3]={tr[t0].v0.x+a*tr[t0].e1.x+b*tr[t0].e2.x,tr[t0].v0.y+a*tr[t0].e1.y+b*tr[t0].e2.y,tr[t0].v0.z+a*tr[t0].e1.z+b*tr[t0].e2.z};
@@ -69,7 +69,30 @@ int main(int argc,char**argv){
     for(auto&c:cs){if(!(c.t<b2))continue;bool sn=true;for(uint32_t n=fo.tri_leaf[c.tri];;){auto&R=fo.rnodes[n];float at=tmax;for(auto&a2:acc)if(a2.rank<F2U(R.b.w))at=a2.t;const float mn[3]={R.a.x,R.a.y,R.a.z},mx[3]={R.b.x,R.b.y,R.b.z};float bd=ibox(o,inv,mn,mx);if(!(bd<at&&!std::isinf(bd))){sn=false;break;}if(n==bvhs[0].first_index)break;n=F2U(R.a.w);if(n==0xFFFFFFFFu)break;}
       if(!sn)continue;b2=c.t;h2=c.tri;acc.push_back(c);}
     if(h2!=hit||(hit!=0xFFFFFFFFu&&b2!=best)){if(mism<5)printf("mismatch ray %ld: ref %u %g finder %u %g (cands %zu)\n",it,hit,best,h2,b2,cs.size());mism++;}
+    // ---- OUTSIDE mode: origin outside the root box on some axis: nearest-first finder walk with distance culling
+    {auto&rn=nodes[bvhs[0].first_index]; bool outside=false; for(int k=0;k<3;++k) if(o[k]<rn.min_bounds[k]||o[k]>rn.max_bounds[k]) outside=true;
+     if(outside){ n_out++;
+      const float pad=fo.pad[0]; const float tpad=4.0f*pad/sqrtf(d[0]*d[0]+d[1]*d[1]+d[2]*d[2]);
+      float tcull=tmax; std::vector<C> k2;
+      auto fb=[&](float mnx,float mny,float mnz,float mxx,float mxy,float mxz,float&tn){float t0x=(mnx-o[0])*inv[0],t0y=(mny-o[1])*inv[1],t0z=(mnz-o[2])*inv[2],t1x=(mxx-o[0])*inv[0],t1y=(mxy-o[1])*inv[1],t1z=(mxz-o[2])*inv[2];tn=fmaxf(fmaxf(fminf(t0x,t1x),fminf(t0y,t1y)),fminf(t0z,t1z));float tf=fminf(fminf(fmaxf(t0x,t1x),fmaxf(t0y,t1y)),fmaxf(t0z,t1z));return tn<=tf&&tf>=0&&tn<=tcull;};
+      float tn0;
+      if(fb(rn.min_bounds[0]-pad,rn.min_bounds[1]-pad,rn.min_bounds[2]-pad,rn.max_bounds[0]+pad,rn.max_bounds[1]+pad,rn.max_bounds[2]+pad,tn0)){
+        std::vector<uint32_t> st{fo.root[0]};while(!st.empty()){uint32_t c=st.back();st.pop_back();
+          if(c&SRT_LEAF_BIT){uint32_t i=c&~SRT_LEAF_BIT;for(;;){float t;o_tris++;if(tri(fo.tris[i],o,d,tmax,t)){if(t<=tcull){k2.push_back({F2U(fo.tris[i].v0.w),F2U(fo.tris[i].e1.w),t});float nt=t+t*(1.0f/1024.0f)+tpad;if(nt<tcull)tcull=nt;}}if(!F2U(fo.tris[i].e2.w))break;++i;}}
+          else{auto&p=fo.pairs[c];float tl,trr;o_boxes+=2;bool pl=fb(p.a.x,p.a.y,p.a.z,p.a.w,p.b.x,p.b.y,tl),pr=fb(p.b.z,p.b.w,p.c.x,p.c.y,p.c.z,p.c.w,trr);
+            if(pl&&pr){if(tl<=trr){st.push_back(p.d.w);st.push_back(p.d.z);}else{st.push_back(p.d.z);st.push_back(p.d.w);}}else if(pl)st.push_back(p.d.z);else if(pr)st.push_back(p.d.w);}}}
+      std::vector<C> kept; for(auto&c:k2) if(c.t<=tcull) kept.push_back(c);
+      o_cands+=kept.size(); if(kept.size()>8){o_over++;}
+      else{
+      std::sort(kept.begin(),kept.end(),[](const C&x,const C&y){return x.rank<y.rank;});
+      float b3=tmax;uint32_t h3=0xFFFFFFFFu;std::vector<C> acc3; bool uncertain=false;
+      for(auto&c:kept){if(!(c.t<b3))continue;bool sn=true;for(uint32_t n=fo.tri_leaf[c.tri];;){auto&R=fo.rnodes[n];float at=tmax;for(auto&a2:acc3)if(a2.rank<F2U(R.b.w))at=a2.t;const float mn[3]={R.a.x,R.a.y,R.a.z},mx[3]={R.b.x,R.b.y,R.b.z};float bd=ibox(o,inv,mn,mx);o_rboxes++;if(!(bd<at&&!std::isinf(bd))){sn=false;break;}if(bd>=tcull)uncertain=true;if(n==bvhs[0].first_index)break;n=F2U(R.a.w);if(n==0xFFFFFFFFu)break;}
+        if(!sn)continue;b3=c.t;h3=c.tri;acc3.push_back(c);}
+      if(uncertain)o_unc++;
+      else if(h3!=hit||(hit!=0xFFFFFFFFu&&b3!=best)){if(o_mism<5)printf("OUTSIDE mismatch ray %ld: ref %u %g finder %u %g (kept %zu)\n",it,hit,best,h3,b3,kept.size());o_mism++;}
+      }}}
   }
+  printf("outside rays %ld: mismatches %ld uncertain %ld overflow %ld kept/ray %.2f boxes/ray %.1f tris/ray %.1f replay boxes/ray %.1f\n",n_out,o_mism,o_unc,o_over,o_cands/(double)std::max(1L,n_out),o_boxes/(double)std::max(1L,n_out),o_tris/(double)std::max(1L,n_out),o_rboxes/(double)std::max(1L,n_out));
   printf("rays %ld mismatches %ld overflow(>8) %ld cands/ray %.2f\n",nray,mism,over,cands/nray);
-  return mism!=0;
+  return mism!=0||o_mism!=0;
 }

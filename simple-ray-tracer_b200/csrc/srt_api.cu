@@ -104,6 +104,7 @@ struct srt_ctx {
   size_t timing_used = 0;
   int refill_threshold = 12;                   // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL)
   uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
+  bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
   uint32_t tail_paths = 1u << 20;               // live paths at which the tail kernel takes over (SRT_OPT_TAIL_PATHS, 0 = never)
   size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
   size_t sample_budget_bytes = (size_t)4 << 30;  // sample buffer budget per frame chunk (SRT_OPT_SAMPLE_BUDGET_MB)
@@ -240,6 +241,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_FINDER) {
     if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_FINDER: 0 (off), 1 (on) or 2 (auto)");
     ctx->finder_mode = value;
+    return 0;
+  }
+  if (key == SRT_OPT_PRIMARY_CULL) {
+    if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_PRIMARY_CULL: 0 or 1");
+    ctx->primary_cull = value != 0;
     return 0;
   }
   if (key == SRT_OPT_TAIL_PATHS) {
@@ -850,6 +856,9 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
   const size_t budget_entries = ctx->sample_budget_bytes / sizeof(float4);
   int chunk_frames = (int)(budget_entries / n_pixels);
   if (chunk_frames < 1) chunk_frames = 1;
+  // a chunk whose paths all fit the pool starts them all in wave 0, where the primary cull applies
+  if (ctx->primary_cull && ctx->wave_slots / n_pixels >= 1u && (uint32_t)chunk_frames > ctx->wave_slots / n_pixels)
+    chunk_frames = (int)(ctx->wave_slots / n_pixels);
   if (chunk_frames > fp_all.n_frames) chunk_frames = fp_all.n_frames;
   const DeviceScene sc = device_scene(ctx);
   uint32_t* ids = ctx->ids_enabled ? ctx->d_ids : nullptr;
@@ -874,8 +883,8 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     ctx->pool.n_paths = n_paths;
     // primary ids are those of the launch's LAST frame
     uint32_t* chunk_ids = (done + fp.n_frames == fp_all.n_frames) ? ids : nullptr;
-    CU(ctx, launch_wf_init(sc, fp, ctx->pool, ctx->d_counters, ctx->stream));
-    ctx->kernel_launches++;
+    // every path of the chunk starts in wave 0: primary rays that miss every root box end in the init kernel
+    const bool cull = ctx->primary_cull && n_paths <= (unsigned long long)slots;
     int parity = 0;
     // What the host knows about the launch: paths still alive and whether every path has been handed to a slot.  Both
     // are exact before wave 0 and afterwards lag one batch behind the device.
@@ -891,6 +900,22 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
       ctx->timing_used += 3;
       return 0;
     };
+    {
+      // with the cull the init kernel answers rays (root-box tests): SRT_OPT_TIME_KERNELS reports it as one more trace
+      // launch, like the tail kernel
+      cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+      const bool timed = ctx->time_kernels && cull;
+      if (timed) {
+        if (timing_events(ev)) return 1;
+        CU(ctx, cudaEventRecord(ev[0], ctx->stream));
+      }
+      CU(ctx, launch_wf_init(sc, fp, ctx->pool, cull, chunk_ids, ctx->count_traversal, ctx->d_counters, ctx->stream));
+      if (timed) {
+        CU(ctx, cudaEventRecord(ev[1], ctx->stream));
+        CU(ctx, cudaEventRecord(ev[2], ctx->stream));
+      }
+      ctx->kernel_launches++;
+    }
     for (int batch = 0;; ++batch) {
       if (tail_ok && all_out && live <= (unsigned long long)ctx->tail_paths) {
         // the rest of the launch in one kernel (srt_wf_tail.cuh); with SRT_OPT_TIME_KERNELS it is reported as one more

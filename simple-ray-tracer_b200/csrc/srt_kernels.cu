@@ -266,10 +266,18 @@ cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool 
                : launch_path_sched<true, TRAV_ORDERED, false>(sched, sc, fp, accum, out, ids, counters, block, stream);
 }
 
-cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool,
-                           DeviceCounters* counters, cudaStream_t stream) {
+cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, bool cull,
+                           uint32_t* primary_ids, bool count_nodes, DeviceCounters* counters, cudaStream_t stream) {
   if (pool.cap == 0) return cudaSuccess;
-  wf_init_kernel<<<(pool.cap + 127u) / 128u, 128, 0, stream>>>(sc, fp, pool, counters);
+  const uint32_t blocks = (pool.cap + SRT_WF_INIT_THREADS - 1u) / SRT_WF_INIT_THREADS;
+  if (cull) {
+    // the blocks add the paths they keep to these two; the kernel's first thread writes the other fields
+    cudaError_t e = cudaMemsetAsync(pool.q, 0, sizeof(WaveCounters), stream);
+    if (e != cudaSuccess) return e;
+    wf_init_kernel<true><<<blocks, SRT_WF_INIT_THREADS, 0, stream>>>(sc, fp, pool, primary_ids, count_nodes ? 1 : 0, counters);
+  } else {
+    wf_init_kernel<false><<<blocks, SRT_WF_INIT_THREADS, 0, stream>>>(sc, fp, pool, primary_ids, 0, counters);
+  }
   return cudaGetLastError();
 }
 
@@ -330,8 +338,8 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
 }  // namespace
 
 namespace {
-// the trace step through the hit finder (srt_wf_find.cuh): candidates, then the rays with too many of them the long way,
-// then the replay of the shader's culls
+// the trace step through the hit finder (srt_wf_find.cuh): candidates, then the replay of the shader's culls, then the
+// rays with too many candidates (or a replay that could not be sure) the long way
 cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
                            DeviceCounters* counters, int block, cudaStream_t stream) {
   static int per_sm = 0, sms = 0;
@@ -355,14 +363,15 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
   if (grid < 1) grid = 1;
   wf_find_kernel<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  PathPool over = pool;  // the overflow list, seen through the trace kernel's own interface
+  long blocks = ((long)pool.cap + 127) / 128;
+  if (blocks > (long)sms * 16) blocks = (long)sms * 16;
+  wf_replay_kernel<<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  PathPool over = pool;  // the overflow list (the replay may have added to it), seen through the trace kernel's own interface
   over.q = &pool.fq->over;
   over.list[0] = pool.olist;
   over.list[1] = pool.olist;
   if ((e = wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, over, 0, refill, counters, block, stream)) != cudaSuccess) return e;
-  long blocks = ((long)pool.cap + 127) / 128;
-  if (blocks > (long)sms * 16) blocks = (long)sms * 16;
-  wf_replay_kernel<<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool);
   return cudaGetLastError();
 }
 }  // namespace

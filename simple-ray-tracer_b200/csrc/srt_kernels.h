@@ -13,8 +13,8 @@ cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool 
                              float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters,
                              unsigned int* next_tile, int block, cudaStream_t stream);
 // Wavefront schedule (srt_wavefront.cuh): one init launch, then trace+logic pairs queued by the caller.
-cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool,
-                           DeviceCounters* counters, cudaStream_t stream);
+cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, bool cull,
+                           uint32_t* primary_ids, bool count_nodes, DeviceCounters* counters, cudaStream_t stream);
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
                            cudaEvent_t after_trace = nullptr, bool finder = false);

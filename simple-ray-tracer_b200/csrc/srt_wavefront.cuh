@@ -62,30 +62,100 @@ __device__ __forceinline__ void wf_path_id(const PathPool& pool, unsigned long l
 }
 
 // ---- wave 0: the first pool.cap paths of the launch -----------------------------------------------------------------
-__global__ void __launch_bounds__(128)
+// CULL (SRT_OPT_PRIMARY_CULL, only when every path of the launch starts here): a primary ray whose CheckHit would end
+// at the root of every BVH -- the very test the trace kernel's enter() makes, IntersectsBox on the root against an
+// infinite intersection_distance (ray_intersects.glsl:106-110) -- never becomes a queue entry: its path's sample is
+// the sky term of GetRayColor's miss branch (raytrace_compute.glsl:287-292) and is written here.  The paths that are
+// left take consecutive slots (one pair of atomics per block), so wave 0 is as wide as the model on the screen and not
+// as the screen.
+#define SRT_WF_INIT_THREADS 256
+template <bool CULL>
+__global__ void __launch_bounds__(SRT_WF_INIT_THREADS)
 wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool,
-               DeviceCounters* __restrict__ counters) {
-  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+               uint32_t* __restrict__ primary_ids, int count_nodes, DeviceCounters* __restrict__ counters) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;  // path of the launch
   const unsigned long long first = pool.n_paths < (unsigned long long)pool.cap ? pool.n_paths : (unsigned long long)pool.cap;
-  if (slot == 0) {
-    pool.q->n_closest[0] = (unsigned int)first;
+  if (p == 0) {
+    if (!CULL) {  // with CULL the host zeroed both and the blocks add what they keep
+      pool.q->n_closest[0] = (unsigned int)first;
+      pool.q->live_slots = (unsigned int)first;
+    }
     pool.q->n_shadow[0] = 0;
     pool.q->n_closest[1] = 0;
     pool.q->n_shadow[1] = 0;
     pool.q->cursor = 0;
-    pool.q->live_slots = (unsigned int)first;
     pool.q->next_path = first;
     if (pool.fq != nullptr) memset(pool.fq, 0, sizeof(FinderQueues));
     atomicAdd(&counters->segments, first);
     atomicAdd(&counters->paths, pool.n_paths);
   }
-  if (slot >= first) return;
-  uint32_t pixel, f;
-  wf_path_id(pool, slot, pixel, f);
-  int x, y;
-  tile_pixel(fp, pixel >> 5, pixel & 31, x, y);
-  const int pix = y * fp.height + x;  // Q4
-  V3 d = wf_primary_dir(sc, fp, x, y, pix, (int)f);
+  const bool in_range = p < first;
+  if (!CULL && !in_range) return;
+  uint32_t pixel = 0, f = 0;
+  int x = 0, y = 0;
+  V3 d = v3(0.0f);
+  bool keep = false;
+  if (in_range) {
+    wf_path_id(pool, p, pixel, f);
+    tile_pixel(fp, pixel >> 5, pixel & 31, x, y);
+    const int pix = y * fp.height + x;  // Q4
+    d = wf_primary_dir(sc, fp, x, y, pix, (int)f);
+    keep = true;
+    if (CULL) {
+      keep = false;
+      for (uint32_t b = 0; b < fp.bvh_count; ++b) {  // CheckHit's loop (raytrace_compute.glsl:144-161), root tests only
+        const BvhRecord* bvh = sc.bvhs + b;
+        const V3 to = mat4_mul_(bvh->frame, fp.center, 1.0f);
+        const V3 td = mat4_mul_(bvh->frame, d, 0.0f);
+        const V3 inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
+        bool in_root;
+        const float d_root = box_distance(to, inv, bvh->root_min[0], bvh->root_min[1], bvh->root_min[2], bvh->root_max[0],
+                                          bvh->root_max[1], bvh->root_max[2], in_root);
+        if ((d_root < inf_()) && !isinf_(d_root)) {
+          keep = true;
+          break;
+        }
+      }
+    }
+  }
+  uint32_t slot = p;
+  if (CULL) {
+    __shared__ uint32_t s_count[SRT_WF_INIT_THREADS / 32];
+    __shared__ uint32_t s_base;
+    const unsigned FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const unsigned m_keep = __ballot_sync(FULL, keep);
+    if (lane == 0) s_count[w] = (uint32_t)__popc(m_keep);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t total = 0;
+      for (int i = 0; i < SRT_WF_INIT_THREADS / 32; ++i) {
+        const uint32_t c = s_count[i];
+        s_count[i] = total;
+        total += c;
+      }
+      uint32_t base = 0;
+      if (total) {
+        base = atomicAdd(&pool.q->n_closest[0], total);
+        atomicAdd(&pool.q->live_slots, total);
+      }
+      s_base = base;
+      if (count_nodes) {  // the root tests the trace kernel would have counted for the paths that end here
+        const unsigned long long start = (unsigned long long)blockIdx.x * blockDim.x;
+        const uint32_t here = start >= first ? 0u : (first - start < blockDim.x ? (uint32_t)(first - start) : blockDim.x);
+        atomicAdd(&counters->nodes, (unsigned long long)(here - total) * fp.bvh_count);
+      }
+    }
+    __syncthreads();
+    slot = s_base + s_count[w] + (uint32_t)__popc(m_keep & ((1u << lane) - 1u));
+    if (in_range && !keep) {
+      const V3 color = v3(0.0f) + v3(1.0f) * v3(0.05f);  // :288, Q19
+      const V3 pixel_color = v3(0.0f) + color;          // main(): pixelColor = vec3(0) + GetRayColor(...)
+      pool.samples[(size_t)f * pool.n_pixels + pixel] = make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f);
+      if (primary_ids != nullptr && f == (uint32_t)(fp.n_frames - 1)) primary_ids[(size_t)y * fp.width + x] = SRT_NO_HIT;
+    }
+    if (!keep) return;
+  }
   pool.ray[2 * (size_t)slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
   pool.ray[2 * (size_t)slot + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
   pool.pst[2 * (size_t)slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);

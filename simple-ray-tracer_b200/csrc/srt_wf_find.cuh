@@ -13,6 +13,17 @@
 // before every triangle of its own subtree; its running distance at that moment is the distance of the last accepted
 // triangle of lower rank (or the initial distance); rejected triangle tests change nothing.  Padded boxes and a
 // NaN-ignoring slab test keep the finder conservative; tests compare whole frames with the oracle bit for bit.
+//
+// OUTSIDE rays (one BVH, ray origin outside its root box on some axis: camera rays).  Such a ray is outside every
+// reference node too (a node's box lies inside its parent's), so IntersectsBox gives it entry distances only and the
+// shader's culls are ordinary closest-hit culls: what it returns is the nearest candidate, up to how rounding orders
+// distances that nearly tie.  A camera ray through the whole model has a dozen candidates (every wall it crosses), and
+// without distance culling it overflowed and walked the reference BVH.  For these rays the finder walk is nearest
+// child first and culls with  theta = t_min + t_min / 1024 + 4 pad / |d|  (t_min = nearest candidate so far): candidates
+// beyond theta are dropped.  The replay runs on what is left and is exact as long as no dropped candidate could have
+// changed a decision: a dropped candidate's distance exceeds theta, so it passes every `t < best` that a kept one
+// faces and can only matter through a box test whose entry distance is >= theta -- the replay checks exactly that on
+// every box it tests and hands such a ray (none in the test scenes) to the long way.
 #pragma once
 
 #include "srt_wavefront.cuh"
@@ -34,6 +45,13 @@ __device__ __forceinline__ uint32_t wf_lds1(uint32_t addr) {
 __device__ __forceinline__ bool wf_find_box(V3 o, V3 inv, float tmax, float mnx, float mny, float mnz, float mxx, float mxy,
                                             float mxz) {
   float tn, tf;
+  wf_slab_fast(o, inv, mnx, mny, mnz, mxx, mxy, mxz, tn, tf);
+  return (tn <= tf) && (tf >= 0.0f) && (tn <= tmax);
+}
+
+__device__ __forceinline__ bool wf_find_box_t(V3 o, V3 inv, float tmax, float mnx, float mny, float mnz, float mxx, float mxy,
+                                              float mxz, float& tn) {
+  float tf;
   wf_slab_fast(o, inv, mnx, mny, mnz, mxx, mxy, mxz, tn, tf);
   return (tn <= tf) && (tf >= 0.0f) && (tn <= tmax);
 }
@@ -62,6 +80,9 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   uint32_t slot = 0, cur = 0, bvh_i = 0, n_cand = 0;
   V3 to = v3(0.0f), td = v3(0.0f), inv = v3(0.0f);
   float tmax = 0.0f;
+  // OUTSIDE rays: tcull = theta (file header), tpad = 4 pad / |d|; every other ray keeps tcull = tmax
+  bool outside = false;
+  float tcull = 0.0f, tpad = 0.0f;
   uint32_t sp = sp_base;
   bool exhausted = false;
   const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
@@ -83,6 +104,10 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       td = mat4_mul_(bvh->frame, v3(b.x, b.y, b.z), 0.0f);
       inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
       const float pad = bvh->finder_pad;
+      tcull = tmax;
+      outside = fp.bvh_count == 1u && (to.x < bvh->root_min[0] || to.x > bvh->root_max[0] || to.y < bvh->root_min[1] ||
+                                       to.y > bvh->root_max[1] || to.z < bvh->root_min[2] || to.z > bvh->root_max[2]);
+      if (outside) tpad = 4.0f * pad * rsqrtf(td.x * td.x + td.y * td.y + td.z * td.z);
       if (wf_find_box(to, inv, tmax, bvh->root_min[0] - pad, bvh->root_min[1] - pad, bvh->root_min[2] - pad,
                       bvh->root_max[0] + pad, bvh->root_max[1] + pad, bvh->root_max[2] + pad)) {
         cur = bvh->finder_root;
@@ -116,8 +141,13 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
         base = __shfl_sync(FULL, base, leader);
         if (to_replay) {
           uint2* dst = pool.cand + (size_t)slot * SRT_CAND_MAX;
-          for (uint32_t k = 0; k < n_cand; ++k) dst[k] = wf_lds(cand_base + k * cand_step);
-          pool.rlist[base + __popc(m_r & lt_mask)] = slot | (n_cand << 28);
+          uint32_t w = 0;
+          for (uint32_t k = 0; k < n_cand; ++k) {  // an OUTSIDE ray keeps the candidates within its final theta
+            const uint2 c = wf_lds(cand_base + k * cand_step);
+            if (!outside || __uint_as_float(c.y) <= tcull) dst[w++] = c;
+          }
+          pool.hit[slot] = make_uint2(0u, __float_as_uint(outside ? tcull : inf_()));  // theta, for the replay
+          pool.rlist[base + __popc(m_r & lt_mask)] = slot | (w << 28);
         }
       }
       const unsigned m_o = __ballot_sync(FULL, to_over);
@@ -182,12 +212,14 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           const float4* p = reinterpret_cast<const float4*>(sc.fpairs + cur);
           const float4 na = __ldg(p), nb = __ldg(p + 1), nc = __ldg(p + 2);
           const uint4 nd = __ldg(reinterpret_cast<const uint4*>(p + 3));
-          const bool pl = wf_find_box(to, inv, tmax, na.x, na.y, na.z, na.w, nb.x, nb.y);
-          const bool pr = wf_find_box(to, inv, tmax, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w);
+          float tl, tr;
+          const bool pl = wf_find_box_t(to, inv, tcull, na.x, na.y, na.z, na.w, nb.x, nb.y, tl);
+          const bool pr = wf_find_box_t(to, inv, tcull, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, tr);
           if (pl && pr) {
-            wf_sts1(sp, nd.w);
+            const bool left_first = tl <= tr;  // nearer child first: an OUTSIDE ray's theta drops early
+            wf_sts1(sp, left_first ? nd.w : nd.z);
             sp += sp_step;
-            cur = nd.z;
+            cur = left_first ? nd.z : nd.w;
           } else if (pl || pr) {
             cur = pl ? nd.z : nd.w;
           } else {
@@ -212,7 +244,22 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
               const float v = f * dot_(td, qv);
               if (!(v < 0.0f || u + v > 1.0f)) {
                 const float t = f * dot_(edge_2, qv);
-                if (t > 0.00001f && t < tmax) {
+                if (t > 0.00001f && t < tmax && t <= tcull) {
+                  if (outside) {
+                    const float theta = t + t * (1.0f / 1024.0f) + tpad;
+                    if (theta < tcull) tcull = theta;
+                    if (n_cand == SRT_CAND_MAX) {  // make room: drop what the lower theta leaves behind
+                      uint32_t w = 0;
+                      for (uint32_t k = 0; k < SRT_CAND_MAX; ++k) {
+                        const uint2 c = wf_lds(cand_base + k * cand_step);
+                        if (__uint_as_float(c.y) <= tcull) {
+                          wf_sts(cand_base + w * cand_step, c.x, c.y);
+                          ++w;
+                        }
+                      }
+                      n_cand = w;
+                    }
+                  }
                   if (n_cand == SRT_CAND_MAX) {
                     overflow = true;
                     trav = false;
@@ -264,6 +311,8 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
         c_key[k] = 0xFFFFFFFFu;
       }
     }
+    const float theta = __uint_as_float(pool.hit[slot].y);  // +inf unless wf_find_kernel dropped candidates beyond it
+    bool uncertain = false;
     float best = ra.w;       // the shader's inout intersection_distance
     uint32_t hit = SRT_NO_HIT;
     uint32_t cur_bvh = 0xFFFFFFFFu;
@@ -312,6 +361,7 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
           seen = false;
           break;
         }
+        if (d >= theta) uncertain = true;  // a dropped candidate (all beyond theta) could have culled this node
         node = (node == root_node) ? 0xFFFFFFFFu : __float_as_uint(na.w);
         if (node == 0xFFFFFFFFu) break;
       }
@@ -324,7 +374,11 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
         if (j == n_acc) { a_rank[j] = rank; a_t[j] = t; }
       n_acc++;
     }
-    pool.hit[slot] = make_uint2(hit, __float_as_uint(best));
+    if (uncertain) {  // the long way (wf_trace_kernel over the overflow list, launched after this kernel)
+      pool.olist[atomicAdd(&pool.fq->over.n_closest[0], 1u)] = slot;
+    } else {
+      pool.hit[slot] = make_uint2(hit, __float_as_uint(best));
+    }
   }
 }
 

@@ -18,13 +18,18 @@ def gpu_render(pkg, ctx, W, H, show_model, n_frames, traversal, scene=None, ligh
     """Variants of the wavefront schedule (3): plain 3 = the library's defaults (hit finder where srt_upload_scene finds
     it worthwhile -- Rubik yes, soup no --, and launches of these sizes run in the tail kernel right after
     wf_init_kernel); 30 = waves to the very end (SRT_OPT_TAIL_PATHS = 0) walking the reference BVH (SRT_OPT_FINDER = 0);
-    31 = waves to the very end through the hit finder (SRT_OPT_FINDER = 1); 32 = default tail, finder off."""
+    31 = waves to the very end through the hit finder (SRT_OPT_FINDER = 1); 32 = default tail, finder off; 33 = the
+    defaults with SRT_OPT_PRIMARY_CULL = 0 (every primary ray through the queues; the others end root-box misses in
+    wf_init_kernel)."""
     if schedule == 30:
         schedule, tail, finder = 3, 0, 0
     elif schedule == 31:
         schedule, tail, finder = 3, 0, 1
     elif schedule == 32:
         schedule, finder = 3, 0
+    elif schedule == 33:
+        schedule = 3
+        ctx.set_option(pkg.OPT_PRIMARY_CULL, 0)
     if tail is not None:
         ctx.set_option(pkg.OPT_TAIL_PATHS, tail)
     if finder is not None:
@@ -117,7 +122,7 @@ def test_spheres_multi_frame_bit_exact(pkg, ctx, oracle, frames):
     assert np.array_equal(out, oout)
 
 
-@pytest.mark.parametrize("schedule", [0, 1, 2, 3, 30, 31, 32])
+@pytest.mark.parametrize("schedule", [0, 1, 2, 3, 30, 31, 32, 33])
 def test_rubik_reference_order_bit_exact(pkg, ctx, oracle, schedule):
     """C2's scene at a size the oracle finishes in seconds; reference visiting order => bit-exact."""
     scene = scenes.rubik_scene()
@@ -187,7 +192,7 @@ def framed(scale, rot_y_deg, translate):
     return np.linalg.inv(T @ R @ S).astype(np.float32).T.reshape(16).copy()
 
 
-@pytest.mark.parametrize("schedule", [0, 2, 3, 30, 31])
+@pytest.mark.parametrize("schedule", [0, 2, 3, 30, 31, 33])
 def test_two_models_with_frames_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     """SURVEY 8(f) N4: bvh_count = 2, each model behind its own world->model frame (raytrace_compute.glsl:144-161);
     the closest hit is taken over both, t shared between model spaces as the shader does (Q14).  Then one frame is
@@ -245,6 +250,38 @@ def test_rubik_inside_view_and_depth8(pkg, ctx, oracle, schedule):
     oacc, oout, oids, _ = cpu_render(oracle, 256, 256, True, 3, scene=scene, cam=cam, max_depth=8)
     assert np.array_equal(ids, oids)
     assert_bit_exact(acc, oacc)
+
+
+def test_primary_cull_same_bits_same_counts(pkg, ctx, oracle):
+    """SRT_OPT_PRIMARY_CULL: primary rays that miss every root box end in wf_init_kernel.  Same picture, same segment
+    and shadow-ray counts, and the counting pass (nodes box-tested, triangles tested in the shader's visiting order)
+    reports the same totals as with every primary ray walked by the trace kernel; a view that sees no model at all
+    (every path culled, wave 0 empty) is the sky colour everywhere."""
+    scene = scenes.rubik_scene()
+    res = {}
+    for cull in (1, 0):
+        ctx.set_option(pkg.OPT_PRIMARY_CULL, cull)
+        ctx.set_option(pkg.OPT_COUNT_TRAVERSAL, 1)
+        res[cull] = gpu_render(pkg, ctx, 320, 184, True, 3, pkg.TRAV_REFERENCE, scene=scene, schedule=30)
+    ctx.set_option(pkg.OPT_COUNT_TRAVERSAL, 0)
+    oacc, oout, oids, ocnt = cpu_render(oracle, 320, 184, True, 3, scene=scene)
+    for cull in (1, 0):
+        acc, out, ids, cnt = res[cull]
+        assert np.array_equal(ids, oids)
+        assert_bit_exact(acc, oacc)
+        assert np.array_equal(out, oout)
+        assert cnt["segments"] == ocnt["segments"] and cnt["shadow_rays"] == ocnt["shadow_rays"]
+    assert res[1][3]["nodes"] == res[0][3]["nodes"] and res[1][3]["tris"] == res[0][3]["tris"]
+    assert res[1][3]["nodes"] > 320 * 184 * 3
+    # looking away from the model: nothing survives the cull
+    ctx.set_option(pkg.OPT_PRIMARY_CULL, 1)
+    cam = scenes.look_camera((0.0, 9.0, 40.0), 90.0, 0.0)
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 320, 184, True, 2, pkg.TRAV_REFERENCE, scene=scene, cam=cam, schedule=3)
+    oacc, oout, oids, ocnt = cpu_render(oracle, 320, 184, True, 2, scene=scene, cam=cam)
+    assert (oids == pkg.NO_HIT).all() and np.array_equal(ids, oids)
+    assert_bit_exact(acc, oacc)
+    assert np.array_equal(out, oout)
+    assert cnt["segments"] == ocnt["segments"] == 320 * 184 * 2 and cnt["shadow_rays"] == 0
 
 
 def test_row_bands_equal_whole_image(pkg, ctx, oracle):
