@@ -9,8 +9,10 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <string>
 #include <thread>
+#include <map>
 #include <vector>
 
 #include "srt_b200.h"
@@ -67,6 +69,9 @@ struct srt_ctx {
   uint32_t noise_count = 0;
   char* noise_stage = nullptr;  // pinned staging buffer of the packed noise tables
   size_t noise_stage_bytes = 0;
+  std::map<void**, size_t> dev_capacity;  // bytes allocated behind the scene's device pointers (upload_vec)
+  float* d_noise_raw = nullptr; // device copy of the two tables as given (pinned callers: packed on the device)
+  size_t noise_raw_bytes = 0;
 
   // images
   int width = 0, height = 0;
@@ -196,6 +201,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   for (cudaEvent_t e : ctx->timing_events) cudaEventDestroy(e);
   if (ctx->h_live) cudaFreeHost(ctx->h_live);
   if (ctx->noise_stage) cudaFreeHost(ctx->noise_stage);
+  dfree(ctx->d_noise_raw);
   for (cudaEvent_t& e : ctx->wave_events)
     if (e) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -401,11 +407,18 @@ bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_
   return true;
 }
 
+// Device arrays of the scene keep their allocation between uploads when the new contents fit (a frame loop that
+// re-uploads the same scene pays no cudaFree / cudaMalloc); capacities live beside the pointers in the context.
 template <class T>
 int upload_vec(srt_ctx* ctx, T*& dst, const std::vector<T>& src) {
-  dfree(dst);
   size_t bytes = (src.size() ? src.size() : 1) * sizeof(T);
-  CU(ctx, cudaMalloc(&dst, bytes));
+  size_t& cap = ctx->dev_capacity[(void**)&dst];
+  if (!dst || cap < bytes || cap > 2 * bytes + 4096) {
+    dfree(dst);
+    cap = 0;
+    CU(ctx, cudaMalloc(&dst, bytes));
+    cap = bytes;
+  }
   if (!src.empty()) CU(ctx, cudaMemcpyAsync(dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
   return 0;
 }
@@ -420,6 +433,12 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   if (!bvhs || !nodes || !materials || !triangles || !vertices) return fail(ctx, "srt_upload_scene: NULL array");
   if (n_bvhs == 0 || n_bvhs > SRT_MAX_BVHS) return fail(ctx, "srt_upload_scene: n_bvhs must be 1..%d", SRT_MAX_BVHS);
   CU(ctx, cudaSetDevice(ctx->device));
+  const bool log = getenv("SRT_UPLOAD_LOG") != nullptr;
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+    return std::chrono::duration<double, std::milli>(b - a).count();
+  };
+  const auto t_start = now();
   Relayout rl;
   if (!relayout(ctx, bvhs, n_bvhs, nodes, n_nodes, n_triangles, rl)) return 1;
   if (rl.depth > SRT_STACK_SIZE - 1)
@@ -441,10 +460,10 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
     memcpy(&r.e2.w, &rl.remaining[i], 4);
     tris[i] = r;
   }
+  const auto t_relayout = now();
   // hit finder: a private tree over the same triangles + what a replay of the shader's culls needs (srt_finder.h)
   ctx->finder_ready = false;
   ctx->finder_worthwhile = false;
-  dfree(ctx->d_fpairs); dfree(ctx->d_ftris); dfree(ctx->d_rnodes); dfree(ctx->d_tri_leaf);
   for (BvhRecord& r : rl.bvhs) r.finder_root = r.root_node = 0u;
   if (ctx->finder_mode != 0) {
     FinderOut fo;
@@ -465,6 +484,8 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
       ctx->reference_cost = fo.cost_reference;
     }
   }
+  const auto t_finder = now();
+  if (!ctx->finder_ready) { dfree(ctx->d_fpairs); dfree(ctx->d_ftris); dfree(ctx->d_rnodes); dfree(ctx->d_tri_leaf); }
   std::vector<MatRecord> mats(n_materials);
   for (uint32_t i = 0; i < n_materials; ++i) {
     const srt_material& m = materials[i];
@@ -513,6 +534,9 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   ctx->top_pair_bytes = rl.top_pairs * sizeof(NodePair);
   ctx->l2_window_stream = nullptr;  // re-apply the access-policy window on the next launch
   ctx->have_scene = true;
+  if (log)
+    fprintf(stderr, "srt_upload_scene: relayout + records %.2f ms, finder build + upload %.2f ms, rest %.2f ms\n",
+            ms(t_start, t_relayout), ms(t_relayout, t_finder), ms(t_finder, now()));
   return 0;
 }
 
@@ -533,8 +557,46 @@ extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const floa
   if (!unit_vec3 || !uniform_vec3 || count == 0) return fail(ctx, "srt_upload_noise: NULL table or count 0");
   CU(ctx, cudaSetDevice(ctx->device));
   // the shader reads noiseTex.xy (raytrace_utils.glsl:15) and noiseUniformTex.x (:52) only: keep those, packed.
-  // Packing goes straight into a pinned staging buffer (kept between calls) on a few host threads.
   const size_t bytes = (size_t)count * 12;
+  const auto t0 = std::chrono::steady_clock::now();
+  if (ctx->noise_count != count || !ctx->d_noise_xy) {
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    dfree(ctx->d_noise_xy);
+    dfree(ctx->d_noise_x);
+    ctx->noise_count = 0;
+    CU(ctx, cudaMalloc(&ctx->d_noise_xy, (size_t)count * sizeof(float2)));
+    CU(ctx, cudaMalloc(&ctx->d_noise_x, (size_t)count * sizeof(float)));
+  }
+  // Tables in page-locked host memory (cudaHostAlloc / cudaHostRegister): both go to the device as they are, by DMA,
+  // and a kernel packs them there; the call returns with the copies queued, so the tables must stay as they are until
+  // the context next synchronises (srt_sync, srt_render, srt_read_*).
+  {
+    cudaPointerAttributes a0, a1;
+    const bool p0 = cudaPointerGetAttributes(&a0, unit_vec3) == cudaSuccess && a0.type == cudaMemoryTypeHost;
+    const bool p1 = cudaPointerGetAttributes(&a1, uniform_vec3) == cudaSuccess && a1.type == cudaMemoryTypeHost;
+    cudaGetLastError();  // an unregistered pointer is not an error here
+    if (p0 && p1) {
+      if (ctx->noise_raw_bytes < 2 * bytes) {
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        dfree(ctx->d_noise_raw);
+        ctx->noise_raw_bytes = 0;
+        CU(ctx, cudaMalloc(&ctx->d_noise_raw, 2 * bytes));
+        ctx->noise_raw_bytes = 2 * bytes;
+      }
+      float* raw_unit = ctx->d_noise_raw;
+      float* raw_uniform = ctx->d_noise_raw + (size_t)count * 3;
+      CU(ctx, cudaMemcpyAsync(raw_unit, unit_vec3, bytes, cudaMemcpyHostToDevice, ctx->stream));
+      CU(ctx, cudaMemcpyAsync(raw_uniform, uniform_vec3, bytes, cudaMemcpyHostToDevice, ctx->stream));
+      CU(ctx, launch_pack_noise(raw_unit, raw_uniform, ctx->d_noise_xy, ctx->d_noise_x, count, ctx->stream));
+      ctx->kernel_launches++;
+      ctx->noise_count = count;
+      if (getenv("SRT_UPLOAD_LOG"))
+        fprintf(stderr, "srt_upload_noise: pinned tables, queued in %.2f ms\n",
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+      return 0;
+    }
+  }
+  // Pageable tables: packed straight into a pinned staging buffer (kept between calls) on a few host threads.
   if (ctx->noise_stage_bytes < bytes) {
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     if (ctx->noise_stage) cudaFreeHost(ctx->noise_stage);
@@ -542,13 +604,6 @@ extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const floa
     ctx->noise_stage_bytes = 0;
     CU(ctx, cudaHostAlloc(&ctx->noise_stage, bytes, cudaHostAllocDefault));
     ctx->noise_stage_bytes = bytes;
-  }
-  if (ctx->noise_count != count || !ctx->d_noise_xy) {
-    CU(ctx, cudaStreamSynchronize(ctx->stream));
-    dfree(ctx->d_noise_xy);
-    dfree(ctx->d_noise_x);
-    CU(ctx, cudaMalloc(&ctx->d_noise_xy, (size_t)count * sizeof(float2)));
-    CU(ctx, cudaMalloc(&ctx->d_noise_x, (size_t)count * sizeof(float)));
   }
   CU(ctx, cudaStreamSynchronize(ctx->stream));  // the previous upload has left the staging buffer
   float2* xy = reinterpret_cast<float2*>(ctx->noise_stage);
@@ -574,6 +629,9 @@ extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const floa
   CU(ctx, cudaMemcpyAsync(ctx->d_noise_xy, xy, (size_t)count * sizeof(float2), cudaMemcpyHostToDevice, ctx->stream));
   CU(ctx, cudaMemcpyAsync(ctx->d_noise_x, x, (size_t)count * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
   ctx->noise_count = count;
+  if (getenv("SRT_UPLOAD_LOG"))
+    fprintf(stderr, "srt_upload_noise: pageable tables, packed + queued in %.2f ms\n",
+            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
   return 0;  // the copies are ordered before any later launch on the context's stream
 }
 
@@ -943,8 +1001,10 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
           if (timing_events(ev)) return 1;
           CU(ctx, cudaEventRecord(ev[0], ctx->stream));
         }
+        // camera rays are in the chunk's first wave and, while slots still take new paths, in any later one
+        const int finder_kind = !finder ? 0 : ((batch == 0 && w == 0) || !all_out) ? 2 : 1;
         CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
-                               ctx->block_threads, ctx->stream, ev[1], finder));
+                               ctx->block_threads, ctx->stream, ev[1], finder_kind));
         if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], ctx->stream));
         parity ^= 1;
       }

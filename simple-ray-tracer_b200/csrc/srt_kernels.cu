@@ -340,10 +340,12 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
 namespace {
 // the trace step through the hit finder (srt_wf_find.cuh): candidates, then the replay of the shader's culls, then the
 // rays with too many candidates (or a replay that could not be sure) the long way
+template <bool OUTSIDE>
 cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
                            DeviceCounters* counters, int block, cudaStream_t stream) {
   static int per_sm = 0, sms = 0;
   static size_t smem_set = 0;
+  auto k = wf_find_kernel<OUTSIDE>;
   const size_t smem = (size_t)fp.stack_cap * SRT_WF_FIND_THREADS * 4u + (size_t)SRT_CAND_MAX * SRT_WF_FIND_THREADS * 8u;
   cudaError_t e;
   if (per_sm == 0 || smem_set != smem) {
@@ -351,9 +353,9 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
     if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
     if (smem > 48 * 1024 &&
-        (e = cudaFuncSetAttribute(wf_find_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+        (e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
       return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_find_kernel, SRT_WF_FIND_THREADS, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, SRT_WF_FIND_THREADS, smem)) != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
     smem_set = smem;
   }
@@ -361,7 +363,7 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
   long need = ((long)pool.cap / 32 + 1) / 2;
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  wf_find_kernel<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill);
+  k<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   long blocks = ((long)pool.cap + 127) / 128;
   if (blocks > (long)sms * 16) blocks = (long)sms * 16;
@@ -378,10 +380,12 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
 
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
-                           cudaEvent_t after_trace, bool finder) {
+                           cudaEvent_t after_trace, int finder) {
   cudaError_t e;
-  if (finder)
-    e = wf_find_launch(sc, fp, pool, parity, refill, counters, block, stream);
+  if (finder == 2)  // a wave that may hold camera rays
+    e = wf_find_launch<true>(sc, fp, pool, parity, refill, counters, block, stream);
+  else if (finder)
+    e = wf_find_launch<false>(sc, fp, pool, parity, refill, counters, block, stream);
   else if (mode == TRAV_REFERENCE)
     e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, refill, counters, block, stream)
               : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, refill, counters, block, stream);
@@ -432,6 +436,22 @@ cudaError_t launch_wf_tail(const DeviceScene& sc, const FrameParams& fp, const P
                            uint32_t* ids, DeviceCounters* counters, cudaStream_t stream) {
   return mode == TRAV_REFERENCE ? wf_tail_launch<TRAV_REFERENCE>(sc, fp, pool, parity, ids, counters, stream)
                                 : wf_tail_launch<TRAV_ORDERED>(sc, fp, pool, parity, ids, counters, stream);
+}
+
+// noiseTex.xy / noiseUniformTex.x (raytrace_utils.glsl:15,52) out of the two RGB32F tables as the host holds them
+__global__ void pack_noise_kernel(const float* __restrict__ unit3, const float* __restrict__ uniform3,
+                                  float2* __restrict__ xy, float* __restrict__ x, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  xy[i] = make_float2(unit3[3 * (size_t)i], unit3[3 * (size_t)i + 1]);
+  x[i] = uniform3[3 * (size_t)i];
+}
+
+cudaError_t launch_pack_noise(const float* unit3, const float* uniform3, float2* xy, float* x, uint32_t n,
+                              cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  pack_noise_kernel<<<(n + 255u) / 256u, 256, 0, stream>>>(unit3, uniform3, xy, x, n);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t stream) {

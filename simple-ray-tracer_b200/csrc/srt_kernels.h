@@ -13,11 +13,13 @@ cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool 
                              float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters,
                              unsigned int* next_tile, int block, cudaStream_t stream);
 // Wavefront schedule (srt_wavefront.cuh): one init launch, then trace+logic pairs queued by the caller.
+cudaError_t launch_pack_noise(const float* unit3, const float* uniform3, float2* xy, float* x, uint32_t n,
+                              cudaStream_t stream);
 cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, bool cull,
                            uint32_t* primary_ids, bool count_nodes, DeviceCounters* counters, cudaStream_t stream);
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
-                           cudaEvent_t after_trace = nullptr, bool finder = false);
+                           cudaEvent_t after_trace = nullptr, int finder = 0);  // finder: 0 = walk the reference BVH, 1 = hit finder, 2 = hit finder with its outside-ray walk (waves that may hold camera rays)
 // The end of a launch (srt_wf_tail.cuh): every path still in the queues of `parity` is run to its last bounce.
 cudaError_t launch_wf_tail(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            uint32_t* ids, DeviceCounters* counters, cudaStream_t stream);

@@ -31,6 +31,9 @@
 namespace srt {
 
 #define SRT_WF_FIND_THREADS 64
+#ifndef SRT_WF_FIND_MIN_BLOCKS
+#define SRT_WF_FIND_MIN_BLOCKS 16  // 64 registers
+#endif
 
 __device__ __forceinline__ void wf_sts1(uint32_t addr, uint32_t x) {
   asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(x) : "memory");
@@ -56,7 +59,10 @@ __device__ __forceinline__ bool wf_find_box_t(V3 o, V3 inv, float tmax, float mn
   return (tn <= tf) && (tf >= 0.0f) && (tn <= tmax);
 }
 
-__global__ void __launch_bounds__(SRT_WF_FIND_THREADS)
+// OUTSIDE = false: the kernel without the outside-ray handling (every ray walks the finder tree without distance
+// culling, as an inside ray does either way); the host uses it for the waves that cannot hold camera rays.
+template <bool OUTSIDE>
+__global__ void __launch_bounds__(SRT_WF_FIND_THREADS, SRT_WF_FIND_MIN_BLOCKS)
 wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity, int refill_threshold) {
   extern __shared__ uint32_t s_find[];  // [stack_cap][64] node references, then [SRT_CAND_MAX][64] candidates (8 B)
   const uint32_t sp_base = (uint32_t)__cvta_generic_to_shared(s_find + threadIdx.x);
@@ -105,7 +111,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
       const float pad = bvh->finder_pad;
       tcull = tmax;
-      outside = fp.bvh_count == 1u && (to.x < bvh->root_min[0] || to.x > bvh->root_max[0] || to.y < bvh->root_min[1] ||
+      outside = OUTSIDE && fp.bvh_count == 1u && (to.x < bvh->root_min[0] || to.x > bvh->root_max[0] || to.y < bvh->root_min[1] ||
                                        to.y > bvh->root_max[1] || to.z < bvh->root_min[2] || to.z > bvh->root_max[2]);
       if (outside) tpad = 4.0f * pad * rsqrtf(td.x * td.x + td.y * td.y + td.z * td.z);
       if (wf_find_box(to, inv, tmax, bvh->root_min[0] - pad, bvh->root_min[1] - pad, bvh->root_min[2] - pad,
@@ -144,9 +150,9 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           uint32_t w = 0;
           for (uint32_t k = 0; k < n_cand; ++k) {  // an OUTSIDE ray keeps the candidates within its final theta
             const uint2 c = wf_lds(cand_base + k * cand_step);
-            if (!outside || __uint_as_float(c.y) <= tcull) dst[w++] = c;
+            if (!OUTSIDE || !outside || __uint_as_float(c.y) <= tcull) dst[w++] = c;
           }
-          pool.hit[slot] = make_uint2(0u, __float_as_uint(outside ? tcull : inf_()));  // theta, for the replay
+          pool.hit[slot] = make_uint2(0u, __float_as_uint((OUTSIDE && outside) ? tcull : inf_()));  // theta, for the replay
           pool.rlist[base + __popc(m_r & lt_mask)] = slot | (w << 28);
         }
       }
@@ -213,10 +219,10 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           const float4 na = __ldg(p), nb = __ldg(p + 1), nc = __ldg(p + 2);
           const uint4 nd = __ldg(reinterpret_cast<const uint4*>(p + 3));
           float tl, tr;
-          const bool pl = wf_find_box_t(to, inv, tcull, na.x, na.y, na.z, na.w, nb.x, nb.y, tl);
-          const bool pr = wf_find_box_t(to, inv, tcull, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, tr);
+          const bool pl = wf_find_box_t(to, inv, OUTSIDE ? tcull : tmax, na.x, na.y, na.z, na.w, nb.x, nb.y, tl);
+          const bool pr = wf_find_box_t(to, inv, OUTSIDE ? tcull : tmax, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, tr);
           if (pl && pr) {
-            const bool left_first = tl <= tr;  // nearer child first: an OUTSIDE ray's theta drops early
+            const bool left_first = !OUTSIDE || tl <= tr;  // nearer child first: an OUTSIDE ray's theta drops early
             wf_sts1(sp, left_first ? nd.w : nd.z);
             sp += sp_step;
             cur = left_first ? nd.z : nd.w;
@@ -244,8 +250,8 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
               const float v = f * dot_(td, qv);
               if (!(v < 0.0f || u + v > 1.0f)) {
                 const float t = f * dot_(edge_2, qv);
-                if (t > 0.00001f && t < tmax && t <= tcull) {
-                  if (outside) {
+                if (t > 0.00001f && t < tmax && (!OUTSIDE || t <= tcull)) {
+                  if (OUTSIDE && outside) {
                     const float theta = t + t * (1.0f / 1024.0f) + tpad;
                     if (theta < tcull) tcull = theta;
                     if (n_cand == SRT_CAND_MAX) {  // make room: drop what the lower theta leaves behind

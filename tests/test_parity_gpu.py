@@ -284,6 +284,24 @@ def test_primary_cull_same_bits_same_counts(pkg, ctx, oracle):
     assert cnt["segments"] == ocnt["segments"] == 320 * 184 * 2 and cnt["shadow_rays"] == 0
 
 
+def test_pinned_noise_tables_same_picture(pkg, ctx, oracle):
+    """srt_upload_noise takes page-locked tables by DMA and packs them on the device (pageable ones are packed by host
+    threads): the same picture either way, and a scene re-upload into the kept device allocations changes nothing."""
+    import torch
+    scene = scenes.rubik_scene()
+    W, H = 320, 184
+    unit, uniform = scenes.noise_tables(W, H)
+    keep = [torch.from_numpy(np.ascontiguousarray(a, np.float32)).pin_memory() for a in (unit, uniform)]
+    acc, out, ids, _ = gpu_render(pkg, ctx, W, H, True, 2, pkg.TRAV_REFERENCE, scene=scene, noise=(keep[0].numpy(), keep[1].numpy()))
+    oacc, oout, oids, _ = cpu_render(oracle, W, H, True, 2, scene=scene)
+    assert np.array_equal(ids, oids)
+    assert_bit_exact(acc, oacc)
+    ctx.upload_scene(scene)  # second upload of the same scene: device arrays reused
+    acc2, _, ids2, _ = gpu_render(pkg, ctx, W, H, True, 2, pkg.TRAV_REFERENCE, scene=None, noise=(unit, uniform))
+    assert np.array_equal(ids2, oids)
+    assert_bit_exact(acc2, oacc)
+
+
 def test_row_bands_equal_whole_image(pkg, ctx, oracle):
     """The image-tile half of the multi-GPU split: rendering two row bands gives the bits of one full render."""
     scene = scenes.rubik_scene()
