@@ -296,8 +296,8 @@ def test_pinned_noise_tables_same_picture(pkg, ctx, oracle):
     oacc, oout, oids, _ = cpu_render(oracle, W, H, True, 2, scene=scene)
     assert np.array_equal(ids, oids)
     assert_bit_exact(acc, oacc)
-    ctx.upload_scene(scene)  # second upload of the same scene: device arrays reused
-    acc2, _, ids2, _ = gpu_render(pkg, ctx, W, H, True, 2, pkg.TRAV_REFERENCE, scene=None, noise=(unit, uniform))
+    # second upload of the same scene (device arrays reused), pageable tables this time
+    acc2, _, ids2, _ = gpu_render(pkg, ctx, W, H, True, 2, pkg.TRAV_REFERENCE, scene=scene, noise=(unit, uniform))
     assert np.array_equal(ids2, oids)
     assert_bit_exact(acc2, oacc)
 
