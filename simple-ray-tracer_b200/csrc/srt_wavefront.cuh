@@ -423,11 +423,32 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   // the small waves, whose atomics do not contend anyway
   const uint32_t append_chunk = (chunks_a + chunks_b) > 4u * n_warps ? SRT_WF_APPEND_CHUNK : 0u;
 
-  for (uint32_t g = warp; g < chunks_a + chunks_b; g += n_warps) {
-    const bool region_a = g < chunks_a;  // warp-uniform: which queue this chunk belongs to
-    const uint32_t idx = (region_a ? g : g - chunks_a) * 32u + lane;
-    const bool in_range = idx < (region_a ? n_a : n_b);
-    const uint32_t entry = in_range ? __ldg(list_in + (region_a ? idx : pool.list_cap - 1u - idx)) : SRT_WF_HOLE;
+  // Paths whose closest hit came back and for which SampleLights selects no light (1 in 12 on Rubik) go straight on to
+  // the lobe choice and the bounce (raytrace_compute.glsl:232-234 skipped): alone among 32 lanes that wait for their
+  // shadow rays' results, that code ran 2.8 lanes wide and was 45 % of the first wave's instructions
+  // (profiles/r01i_*).  Their slots are put aside per warp instead and shaded 32 at a time.
+  __shared__ uint32_t s_stash[SRT_WF_LOGIC_THREADS / 32][64];
+  uint32_t* stash = s_stash[threadIdx.x >> 5];
+  uint32_t stash_n = 0;  // warp-uniform
+  const uint32_t total_chunks = chunks_a + chunks_b;
+
+  for (uint32_t g = warp;;) {
+    const bool stashed = stash_n >= 32u || (g >= total_chunks && stash_n > 0u);  // this turn shades put-aside paths
+    if (!stashed && g >= total_chunks) break;
+    bool region_a = true;  // warp-uniform: which queue this chunk belongs to
+    uint32_t entry = SRT_WF_HOLE;
+    if (stashed) {
+      const uint32_t take = stash_n < 32u ? stash_n : 32u;
+      if ((uint32_t)lane < take) entry = stash[stash_n - take + lane];
+      stash_n -= take;
+      __syncwarp();
+    } else {
+      region_a = g < chunks_a;
+      const uint32_t idx = (region_a ? g : g - chunks_a) * 32u + lane;
+      const bool in_range = idx < (region_a ? n_a : n_b);
+      if (in_range) entry = __ldg(list_in + (region_a ? idx : pool.list_cap - 1u - idx));
+      g += n_warps;
+    }
     const bool valid = entry != SRT_WF_HOLE;
     const uint32_t slot = valid ? entry : 0u;
     const uint2 path = valid ? pool.path[slot] : make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
@@ -441,7 +462,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     V3 tex_albedo = v3(0.0f);
     bool has_tex = false;
     float light_weight = 0.0f, shadow_mult = 1.0f;
-    bool shade = false, have_light = false, finish = false, emit_closest = false, emit_shadow = false;
+    bool shade = false, have_light = false, finish = false, emit_closest = false, emit_shadow = false, put_aside = false;
 
     if (valid) {
       const uint2 h = pool.hit[slot];
@@ -469,7 +490,9 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
             has_tex = textured_albedo(sc, hit_prim, r0, r1, r2, mb, origin, dir, __uint_as_float(h.y), tex_albedo);
           }
           origin = (__uint_as_float(h.y) * dir) + origin;  // rec.p (:155)
-          if (sample_lights(sc, fp, pix, origin, light_weight, li)) {
+          if (stashed) {
+            shade = true;  // put aside in an earlier turn: no light was selected; the slot still holds the traced ray
+          } else if (sample_lights(sc, fp, pix, origin, light_weight, li)) {
             const DeviceLight& l = fp.lights[li];
             const V3 lpos = v3(l.px, l.py, l.pz);
             const V3 sd = normalize_(lpos - origin);  // :168
@@ -482,7 +505,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
             emit_shadow = true;
             n_shadow++;
           } else {
-            shade = true;
+            put_aside = true;
           }
         }
       } else {
@@ -500,6 +523,15 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         }
         have_light = true;
         shade = true;
+      }
+    }
+
+    {
+      const unsigned m_p = __ballot_sync(FULL, put_aside);
+      if (m_p) {  // at most 31 entries are waiting here, so 64 hold them all
+        if (put_aside) stash[stash_n + __popc(m_p & lt_mask)] = slot;
+        stash_n += (uint32_t)__popc(m_p);
+        __syncwarp();
       }
     }
 

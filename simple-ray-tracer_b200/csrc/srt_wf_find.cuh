@@ -323,6 +323,7 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
     uint32_t hit = SRT_NO_HIT;
     uint32_t cur_bvh = 0xFFFFFFFFu;
     V3 to = v3(0.0f), inv = v3(0.0f);
+    bool exact_box = false;
     float best_in = best;    // the distance this BVH's traversal started with
     uint32_t root_node = 0;
     // accepted candidates of the current BVH, in visiting order (their distances decrease)
@@ -347,6 +348,7 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
         to = mat4_mul_(bvh->frame, ray_o, 1.0f);
         const V3 td = mat4_mul_(bvh->frame, ray_d, 0.0f);
         inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
+        exact_box = isinf_(inv.x) || isinf_(inv.y) || isinf_(inv.z) || isnan_(inv.x) || isnan_(inv.y) || isnan_(inv.z);
         root_node = bvh->root_node;
         cur_bvh = bvh_i;
         best_in = best;
@@ -361,8 +363,15 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
 #pragma unroll
         for (int j = 0; j < SRT_CAND_MAX; ++j)
           if (j < n_acc && a_rank[j] < first_rank) at_pop = a_t[j];
-        bool inside;
-        const float d = box_distance(to, inv, na.x, na.y, na.z, nb.x, nb.y, nb.z, inside);
+        float d;
+        if (exact_box) {  // an axis-parallel ray: GLSL min/max on NaN slabs (Q17)
+          bool inside;
+          d = box_distance(to, inv, na.x, na.y, na.z, nb.x, nb.y, nb.z, inside);
+        } else {          // the same bits from the hardware min/max (as wf_trace_kernel)
+          float tn, tf;
+          wf_slab_fast(to, inv, na.x, na.y, na.z, nb.x, nb.y, nb.z, tn, tf);
+          d = tn <= tf ? ((tn >= 0.0f) ? tn : tf) : inf_();
+        }
         if (!((d < at_pop) && !isinf_(d))) {  // ray_intersects.glsl:108
           seen = false;
           break;
