@@ -78,45 +78,55 @@ struct Builder {
       tasks->push_back(Task{lo, hi, depth});
       return kTaskRef | (uint32_t)(tasks->size() - 1);
     }
-    // binned SAH over the three axes
+    // binned SAH over the three axes: one pass over the triangles fills the bins of all three
     float best_cost = INFINITY;
     int best_axis = -1, best_bin = -1;
-    for (int a = 0; a < 3; ++a) {
-      if (!(cb.mx[a] > cb.mn[a])) continue;
-      Box bb[kBins];
-      uint32_t bc[kBins];
-      for (int b = 0; b < kBins; ++b) { bb[b].clear(); bc[b] = 0; }
-      const float scale = (float)kBins / (cb.mx[a] - cb.mn[a]);
+    {
+      Box bb[3][kBins];
+      uint32_t bc[3][kBins];
+      float scale[3];
+      bool live[3];
+      for (int a = 0; a < 3; ++a) {
+        live[a] = cb.mx[a] > cb.mn[a];
+        scale[a] = live[a] ? (float)kBins / (cb.mx[a] - cb.mn[a]) : 0.0f;
+        for (int b = 0; b < kBins; ++b) { bb[a][b].clear(); bc[a][b] = 0; }
+      }
       for (uint32_t i = lo; i < hi; ++i) {
         const Box& t = tb[idx[i]];
-        int b = (int)((0.5f * (t.mn[a] + t.mx[a]) - cb.mn[a]) * scale);
-        b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
-        bb[b].grow(t);
-        bc[b]++;
+        for (int a = 0; a < 3; ++a) {
+          if (!live[a]) continue;
+          int b = (int)((0.5f * (t.mn[a] + t.mx[a]) - cb.mn[a]) * scale[a]);
+          b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
+          bb[a][b].grow(t);
+          bc[a][b]++;
+        }
       }
-      float la[kBins], ra[kBins];
-      uint32_t lc[kBins], rc[kBins];
-      Box acc;
-      acc.clear();
-      uint32_t c = 0;
-      for (int b = 0; b < kBins; ++b) {
-        if (bc[b]) acc.grow(bb[b]);
-        c += bc[b];
-        la[b] = c ? acc.area() : 0.0f;
-        lc[b] = c;
-      }
-      acc.clear();
-      c = 0;
-      for (int b = kBins - 1; b >= 0; --b) {
-        if (bc[b]) acc.grow(bb[b]);
-        c += bc[b];
-        ra[b] = c ? acc.area() : 0.0f;
-        rc[b] = c;
-      }
-      for (int b = 0; b + 1 < kBins; ++b) {
-        if (lc[b] == 0 || rc[b + 1] == 0) continue;
-        float cost = la[b] * (float)lc[b] + ra[b + 1] * (float)rc[b + 1];
-        if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = b; }
+      for (int a = 0; a < 3; ++a) {
+        if (!live[a]) continue;
+        float la[kBins], ra[kBins];
+        uint32_t lc[kBins], rc[kBins];
+        Box acc;
+        acc.clear();
+        uint32_t c = 0;
+        for (int b = 0; b < kBins; ++b) {
+          if (bc[a][b]) acc.grow(bb[a][b]);
+          c += bc[a][b];
+          la[b] = c ? acc.area() : 0.0f;
+          lc[b] = c;
+        }
+        acc.clear();
+        c = 0;
+        for (int b = kBins - 1; b >= 0; --b) {
+          if (bc[a][b]) acc.grow(bb[a][b]);
+          c += bc[a][b];
+          ra[b] = c ? acc.area() : 0.0f;
+          rc[b] = c;
+        }
+        for (int b = 0; b + 1 < kBins; ++b) {
+          if (lc[b] == 0 || rc[b + 1] == 0) continue;
+          float cost = la[b] * (float)lc[b] + ra[b + 1] * (float)rc[b + 1];
+          if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = b; }
+        }
       }
     }
     uint32_t mid = (lo + hi) / 2;  // all centres equal (or nothing to gain): split by count
