@@ -290,7 +290,10 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
 }
 
 // ---- replay: the shader's culls above each candidate, candidates in the shader's visiting order ------------------------
-__global__ void __launch_bounds__(128)
+#ifndef SRT_WF_REPLAY_MIN_BLOCKS
+#define SRT_WF_REPLAY_MIN_BLOCKS 1
+#endif
+__global__ void __launch_bounds__(128, SRT_WF_REPLAY_MIN_BLOCKS)
 wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool) {
   const uint32_t n = pool.fq->n_replay;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
