@@ -361,13 +361,13 @@ def run_gpu(args):
     peaks, which = measured_peaks()
     rays = segments + shadow
     bytes_per_ray = 32.0 * nodes_per_ray + 52.0 * tris_per_ray
+    finder_on = bool(show_model and wavefront and ctx.finder_info()[0])
     if wavefront:
         # wf_trace_kernel does ALL box and triangle tests; its launches of one step differ in size (one per wave), so
         # bytes per launch and duration per launch are both averages over the timed region's launches
         # (with the hit finder the same tests are answered by wf_find_kernel + wf_replay_kernel, overflow rays by
         # wf_trace_kernel; with the primary cull the root-box tests of culled primary rays by wf_init_kernel; the last
         # paths by wf_tail_kernel: trace_ms brackets them all, shading of the tail included)
-        finder_on = bool(ctx.finder_info()[0])
         kname = "wf_find_kernel+wf_replay_kernel (+wf_trace_kernel overflow, wf_init_kernel cull, wf_tail_kernel)" if finder_on else "wf_trace_kernel"
         k_ms, k_launches = trace_ms, max(n_waves, 1.0)
     else:
@@ -379,12 +379,13 @@ def run_gpu(args):
     # DRAM bytes per launch of the same kernel from the committed ncu pass over one step's launches (never measured in
     # this run: numbers taken under a profiler are not bench values; the pass is per workload)
     traffic, traffic_extra = None, {}
-    tf = os.path.join(ROOT, "profiles", "r01f_trace_dram_bytes.json")
+    tf = os.path.join(ROOT, "profiles", "r01i_trace_dram_bytes.json" if finder_on else "r01f_trace_dram_bytes.json")
     if wavefront and world == 1 and args.workload == "rubik" and os.path.exists(tf):
         t = json.load(open(tf))
         traffic = t["dram_bytes_per_launch"]
-        traffic_extra = {"traffic_source": "profiles/r01f_trace_dram_bytes.json (dram__bytes_read.sum + dram__bytes_write.sum, "
-                                           "mean over the %d wf_trace_kernel launches of the pass)" % t["launches"],
+        traffic_extra = {"traffic_source": "profiles/%s (dram__bytes_read.sum + dram__bytes_write.sum of the kernels that "
+                                           "answer rays, per trace launch as SRT_OPT_TIME_KERNELS counts them, from an ncu "
+                                           "pass of this command)" % os.path.basename(tf),
                          "l2_bytes_per_launch": t["l2_bytes_per_launch"], "l1_bytes_per_launch": t["l1_bytes_per_launch"]}
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"] * world, "unit": "GB/s",
                 "frac": achieved / (peaks["hbm_gbs"] * world), "traffic": traffic,
@@ -398,7 +399,10 @@ def run_gpu(args):
                         "shader's visiting order; duration = sum of CUDA-event times around the kernel's launches on the "
                         "launching stream (max over ranks; achieved and peak are whole-job). A scene smaller than the "
                         "126 MB L2 is served from L1/L2, so the figure is then on-chip gather bandwidth quoted against the "
-                        "HBM copy peak (it may exceed 1), not DRAM traffic; see profiles/ for dram__bytes"}
+                        "HBM copy peak (it may exceed 1), not DRAM traffic; see profiles/ for dram__bytes. With the hit "
+                        "finder the same rays are answered with a fraction of those tests, so the figure is a rate of "
+                        "reference work answered; what binds the kernels is instruction issue (ncu: 68-80 % of issue slots "
+                        "busy at 25-27 of 32 lanes, profiles/r01i_ncu_full_summary.txt)"}
     roofline.update(traffic_extra)
 
     cpu_baseline = None

@@ -291,7 +291,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
 
 // ---- replay: the shader's culls above each candidate, candidates in the shader's visiting order ------------------------
 #ifndef SRT_WF_REPLAY_MIN_BLOCKS
-#define SRT_WF_REPLAY_MIN_BLOCKS 1
+#define SRT_WF_REPLAY_MIN_BLOCKS 8  // 64 registers (88 B of spills): 1 / 6 / 8 measured 36.56 / 36.38 / 36.25 ms per Rubik step
 #endif
 __global__ void __launch_bounds__(128, SRT_WF_REPLAY_MIN_BLOCKS)
 wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool) {
