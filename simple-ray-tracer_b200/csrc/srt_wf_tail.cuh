@@ -22,8 +22,11 @@ namespace srt {
 
 #define SRT_WF_TAIL_SHADE_AT 8  // lanes waiting for shading / a new path that end a traversal round
 
+#ifndef SRT_WF_TAIL_MIN_BLOCKS
+#define SRT_WF_TAIL_MIN_BLOCKS 1
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(SRT_WF_TRACE_THREADS)
+__global__ void __launch_bounds__(SRT_WF_TRACE_THREADS, SRT_WF_TAIL_MIN_BLOCKS)
 wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity,
                uint32_t* __restrict__ primary_ids, DeviceCounters* __restrict__ counters) {
   extern __shared__ uint2 s_stack_all[];
