@@ -1,5 +1,9 @@
-// SCRATCH: host-only check of build_finder(): emulates wf_find_kernel + wf_replay_kernel on the built arrays in plain
-// float and compares with an emulation of the shader's traversal in the same arithmetic.
+// TEST INFRASTRUCTURE (tests/test_finder_emulation.py): host-only check of build_finder() and of the algorithm behind
+// wf_find_kernel + wf_replay_kernel (srt_wf_find.cuh): both are emulated on the built arrays in plain float and compared
+// with an emulation of the shader's traversal (ray_intersects.glsl:99-133) in the same arithmetic -- rays from surface
+// points, from outside, from a camera position, axis-parallel, with finite and infinite intersection_distance; and the
+// OUTSIDE walk (distance bound theta, replay that reports rays it cannot be sure of).  The kernels themselves are checked
+// bit for bit against the oracle by the GPU suite; this pins the argument they rest on where no GPU is needed.
 #include <stdio.h>
 #include <stdlib.h>
 #include <math.h>
@@ -51,6 +55,12 @@ int main(int argc,char**argv){
     uint32_t t0=(uint32_t)(rnd()*nt)%nt; float d[3]={2*rnd()-1,2*rnd()-1,2*rnd()-1};
     float a=rnd()*0.8f,b=rnd()*(0.9f-a); float o[3]={tr[t0].v0.x+a*tr[t0].e1.x+b*tr[t0].e2.x,tr[t0].v0.y+a*tr[t0].e1.y+b*tr[t0].e2.y,tr[t0].v0.z+a*tr[t0].e1.z+b*tr[t0].e2.z};
     if(it%3==1){for(int k=0;k<3;++k)o[k]-=40.0f*d[k];}
+    if(it%4==2){  // from one camera position towards a point near the model (a frame's camera rays)
+      auto&rb=nodes[bvhs[0].first_index]; float c[3],e[3]; for(int k=0;k<3;++k){c[k]=0.5f*(rb.min_bounds[k]+rb.max_bounds[k]);e[k]=rb.max_bounds[k]-rb.min_bounds[k];}
+      float cam[3]={c[0],c[1],c[2]+2.2f*std::max(e[0],std::max(e[1],e[2]))};
+      float tgt[3]={c[0]+(rnd()-0.5f)*1.3f*e[0],c[1]+(rnd()-0.5f)*1.3f*e[1],c[2]+(rnd()-0.5f)*e[2]};
+      for(int k=0;k<3;++k){o[k]=cam[k];d[k]=tgt[k]-cam[k];}
+      float nl=1.0f/sqrtf(d[0]*d[0]+d[1]*d[1]+d[2]*d[2]); for(int k=0;k<3;++k)d[k]*=nl*(0.5f+rnd()); }
     if(it%7==3)d[it%3]=0.0f;  // axis-parallel
     float tmax=(it%5==2)?rnd()*30.0f:INFINITY;
     float inv[3]={1.0f/d[0],1.0f/d[1],1.0f/d[2]};
