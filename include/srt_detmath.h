@@ -143,13 +143,7 @@ SRT_HD V3 mat4_mul_(const float* m, V3 v, float w) {
 }
 
 /* ---- sin / cos ---------------------------------------------------------------------------- */
-/* SRT_SINCOS_OUT_OF_LINE (a build-time experiment): one copy per kernel instead of one per call site (a dozen in the
-   wavefront logic kernel, whose 77 KB of code miss the instruction cache); the same operations either way. */
-#if defined(__CUDACC__) && defined(SRT_SINCOS_OUT_OF_LINE)
-static __host__ __device__ __noinline__ float sincos_core_(float x, int want_cos) {
-#else
 SRT_HD float sincos_core_(float x, int want_cos) {
-#endif
   if (!(abs_(x) <= 1.0e8f)) {
     if (isnan_(x) || isinf_(x)) return u2f(0x7fc00000u);
     x = fmodf(x, 6.2831854820251465f); /* fmod is exact in IEEE arithmetic on both sides */

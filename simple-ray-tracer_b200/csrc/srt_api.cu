@@ -37,6 +37,10 @@ struct srt_ctx {
   size_t top_pair_bytes = 0;             // breadth-first prefix of d_pairs (top BVH levels)
   cudaStream_t l2_window_stream = nullptr;  // stream the access-policy window is currently set on
   bool l2_window_on = false;
+  const void* l2_window_ptr = nullptr;      // what the window covers
+  size_t l2_window_bytes = 0;
+  size_t l2_limit_set = (size_t)-1;         // last cudaLimitPersistingL2CacheSize this context asked for
+  int l2_max_window = -1, l2_max_persist = -1;  // device limits (-1: not asked yet)
 
   // device scene
   NodePair* d_pairs = nullptr;
@@ -532,7 +536,6 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   ctx->n_mats = n_materials;
   ctx->tree_depth = rl.depth;
   ctx->top_pair_bytes = rl.top_pairs * sizeof(NodePair);
-  ctx->l2_window_stream = nullptr;  // re-apply the access-policy window on the next launch
   ctx->have_scene = true;
   if (log)
     fprintf(stderr, "srt_upload_scene: relayout + records %.2f ms, finder build + upload %.2f ms, rest %.2f ms\n",
@@ -876,16 +879,31 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
 // than the 126 MB L2 (the 10 M-triangle soup); a scene that fits L2 entirely is resident anyway.
 int apply_l2_window(srt_ctx* ctx) {
   const bool want = ctx->l2_persist && ctx->have_scene && ctx->top_pair_bytes > 0;
-  if (want == ctx->l2_window_on && (!want || ctx->l2_window_stream == ctx->stream)) return 0;
-  cudaDeviceProp prop;
-  CU(ctx, cudaGetDeviceProperties(&prop, ctx->device));
-  if (prop.accessPolicyMaxWindowSize <= 0 || prop.persistingL2CacheMaxSize <= 0) return 0;
+  if (ctx->l2_max_window < 0) {  // device limits, asked once (cudaGetDeviceProperties is slow)
+    int w = 0, p = 0;
+    CU(ctx, cudaDeviceGetAttribute(&w, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device));
+    CU(ctx, cudaDeviceGetAttribute(&p, cudaDevAttrMaxPersistingL2CacheSize, ctx->device));
+    ctx->l2_max_window = w;
+    ctx->l2_max_persist = p;
+  }
+  if (ctx->l2_max_window <= 0 || ctx->l2_max_persist <= 0) return 0;
+  size_t bytes = 0;
+  if (want) {
+    bytes = std::min(ctx->top_pair_bytes, (size_t)ctx->l2_max_window);
+    bytes = std::min(bytes, (size_t)ctx->l2_max_persist);
+  }
+  // nothing to do when the window that is set already covers the same bytes of the same array on the same stream (a
+  // frame loop that re-uploads its scene lands in the kept allocation: cudaDeviceSetLimit alone costs milliseconds)
+  if (want == ctx->l2_window_on && (!want || (ctx->l2_window_stream == ctx->stream && ctx->l2_window_ptr == (const void*)ctx->d_pairs &&
+                                              ctx->l2_window_bytes == bytes)))
+    return 0;
   cudaStreamAttrValue attr;
   memset(&attr, 0, sizeof attr);
   if (want) {
-    size_t bytes = std::min(ctx->top_pair_bytes, (size_t)prop.accessPolicyMaxWindowSize);
-    bytes = std::min(bytes, (size_t)prop.persistingL2CacheMaxSize);
-    CU(ctx, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes));
+    if (ctx->l2_limit_set != bytes) {
+      CU(ctx, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes));
+      ctx->l2_limit_set = bytes;
+    }
     attr.accessPolicyWindow.base_ptr = ctx->d_pairs;
     attr.accessPolicyWindow.num_bytes = bytes;
     attr.accessPolicyWindow.hitRatio = 1.0f;
@@ -899,6 +917,8 @@ int apply_l2_window(srt_ctx* ctx) {
   CU(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
   ctx->l2_window_on = want;
   ctx->l2_window_stream = want ? ctx->stream : nullptr;
+  ctx->l2_window_ptr = want ? (const void*)ctx->d_pairs : nullptr;
+  ctx->l2_window_bytes = bytes;
   return 0;
 }
 

@@ -23,7 +23,7 @@ namespace srt {
 #define SRT_WF_TAIL_SHADE_AT 8  // lanes waiting for shading / a new path that end a traversal round
 
 #ifndef SRT_WF_TAIL_MIN_BLOCKS
-#define SRT_WF_TAIL_MIN_BLOCKS 1
+#define SRT_WF_TAIL_MIN_BLOCKS 13  // 72 registers (48 B of spills): 1 / 13 / 16 measured 36.32 / 35.98 / 35.93 ms per Rubik step, 49.70 / 49.75 / 50.32 on the airplane stand-in
 #endif
 template <int MODE>
 __global__ void __launch_bounds__(SRT_WF_TRACE_THREADS, SRT_WF_TAIL_MIN_BLOCKS)
