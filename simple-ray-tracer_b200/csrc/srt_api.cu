@@ -114,6 +114,8 @@ struct srt_ctx {
   int refill_threshold = 12;                   // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL)
   uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
   bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
+  int prefetch_mode = 2;                        // SRT_OPT_PREFETCH: 0 off, 1 on, 2 = when the scene is larger than L2
+  uint32_t* d_culled = nullptr;                 // bit map of the paths the cull ended (one bit per sample entry)
   uint32_t tail_paths = 1u << 20;               // live paths at which the tail kernel takes over (SRT_OPT_TAIL_PATHS, 0 = never)
   size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
   size_t sample_budget_bytes = (size_t)4 << 30;  // sample buffer budget per frame chunk (SRT_OPT_SAMPLE_BUDGET_MB)
@@ -151,6 +153,8 @@ static void free_pool(srt_ctx* ctx) {
   dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.path); dfree(p.p3);
   dfree(p.list[0]); dfree(p.list[1]); dfree(p.q); dfree(p.samples); dfree(p.tex);
   dfree(p.cand); dfree(p.rlist); dfree(p.olist); dfree(p.fq);
+  dfree(ctx->d_culled);
+  p.culled = nullptr;
   p.cap = 0;
   ctx->pool_slots = 0;
   ctx->sample_entries = 0;
@@ -251,6 +255,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_FINDER) {
     if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_FINDER: 0 (off), 1 (on) or 2 (auto)");
     ctx->finder_mode = value;
+    return 0;
+  }
+  if (key == SRT_OPT_PREFETCH) {
+    if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_PREFETCH: 0 (off), 1 (on) or 2 (auto)");
+    ctx->prefetch_mode = value;
     return 0;
   }
   if (key == SRT_OPT_PRIMARY_CULL) {
@@ -788,6 +797,10 @@ void fill_frame_params(const srt_ctx* ctx, int n_frames, FrameParams& fp) {
   int cap = ctx->tree_depth + 1;
   if (ctx->finder_ready && ctx->finder_depth + 1 > cap) cap = ctx->finder_depth + 1;
   fp.stack_cap = cap < 2 ? 2 : cap;
+  {
+    const size_t scene_bytes = (size_t)ctx->n_nodes * 32u + (size_t)ctx->n_tris * sizeof(TriRecord);
+    fp.prefetch_l2 = ctx->prefetch_mode == 1 || (ctx->prefetch_mode == 2 && scene_bytes > ((size_t)96 << 20)) ? 1 : 0;
+  }
 
   const float focus_dist = 1.0f;                                  // :384
   float aspect = (float)p.width / (float)p.height;                // :368
@@ -865,7 +878,9 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
   if (ctx->sample_entries < sample_entries) {
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     dfree(p.samples);
+    dfree(ctx->d_culled);
     CU(ctx, cudaMalloc(&p.samples, sample_entries * sizeof(float4)));
+    CU(ctx, cudaMalloc(&ctx->d_culled, (sample_entries / 32 + 1) * sizeof(uint32_t)));
     ctx->sample_entries = sample_entries;
   }
   if (!ctx->h_live) CU(ctx, cudaHostAlloc(&ctx->h_live, 4 * sizeof(WaveCounters), cudaHostAllocDefault));
@@ -963,6 +978,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     uint32_t* chunk_ids = (done + fp.n_frames == fp_all.n_frames) ? ids : nullptr;
     // every path of the chunk starts in wave 0: primary rays that miss every root box end in the init kernel
     const bool cull = ctx->primary_cull && n_paths <= (unsigned long long)slots;
+    ctx->pool.culled = cull ? ctx->d_culled : nullptr;
     int parity = 0;
     // What the host knows about the launch: paths still alive and whether every path has been handed to a slot.  Both
     // are exact before wave 0 and afterwards lag one batch behind the device.

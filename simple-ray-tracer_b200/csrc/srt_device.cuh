@@ -136,6 +136,7 @@ struct FrameParams {
   uint32_t bvh_count;
   int max_depth;
   int stack_cap;         // entries per thread in the shared-memory traversal stack
+  int prefetch_l2;       // 1 = wf_trace_kernel prefetches stacked children into L2 (scenes larger than L2)
   V3 center, pixel00, delta_u, delta_v;
   DeviceLight lights[SRT_MAX_LIGHTS];
 };
@@ -188,6 +189,9 @@ struct PathPool {
   FinderQueues* fq;
   // one fp32 sample per path of the launch, frame-major, summed per pixel in frame order by wf_resolve_kernel
   float4* samples;
+  // primary cull only (null otherwise): one bit per path of the launch, frame-major like `samples`; a set bit says the
+  // path ended in wf_init_kernel with the sky sample, which is then NOT stored (wf_resolve_kernel adds the constant)
+  uint32_t* culled;
   uint32_t n_pixels;           // pixel slots of this launch (8x4 tiles x 32)
   unsigned long long n_paths;  // n_pixels * frames of this launch
 };

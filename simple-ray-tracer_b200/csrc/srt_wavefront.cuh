@@ -148,12 +148,12 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
     }
     __syncthreads();
     slot = s_base + s_count[w] + (uint32_t)__popc(m_keep & ((1u << lane) - 1u));
-    if (in_range && !keep) {
-      const V3 color = v3(0.0f) + v3(1.0f) * v3(0.05f);  // :288, Q19
-      const V3 pixel_color = v3(0.0f) + color;          // main(): pixelColor = vec3(0) + GetRayColor(...)
-      pool.samples[(size_t)f * pool.n_pixels + pixel] = make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f);
-      if (primary_ids != nullptr && f == (uint32_t)(fp.n_frames - 1)) primary_ids[(size_t)y * fp.width + x] = SRT_NO_HIT;
-    }
+    // the sky sample of a culled path is a constant: one bit says so instead of 16 stored bytes (a warp's 32 paths are
+    // 32 consecutive entries of the frame-major sample order, so its ballot IS their word of the bit map)
+    const unsigned m_culled = __ballot_sync(FULL, in_range && !keep);
+    if (lane == 0 && p < first) pool.culled[p >> 5] = m_culled;
+    if (in_range && !keep && primary_ids != nullptr && f == (uint32_t)(fp.n_frames - 1))
+      primary_ids[(size_t)y * fp.width + x] = SRT_NO_HIT;
     if (!keep) return;
   }
   pool.ray[2 * (size_t)slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
@@ -350,9 +350,17 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           const bool pr = (nr <= fr) && (dr < best) && (dr != -inf_());
           if (pl && pr) {
             const bool right_first = (MODE == TRAV_REFERENCE || !front_l || !front_r) ? true : !(dl < dr);
-            wf_sts(sp, right_first ? nd.z : nd.w, __float_as_uint(right_first ? dl : dr));
+            const uint32_t later = right_first ? nd.z : nd.w;
+            wf_sts(sp, later, __float_as_uint(right_first ? dl : dr));
             sp += sp_step;
             cur = right_first ? nd.w : nd.z;
+            // a scene far larger than L2 (the 10 M-triangle soup): the child that waits on the stack is asked into L2
+            // now, so that its pop finds it there instead of in DRAM (the walk is latency-bound: 16 warps per issue
+            // wait on long-scoreboard, one 64 B request per lane in flight; profiles/r01j_soup_*)
+            if (fp.prefetch_l2) {
+              const void* ptr = (later & SRT_LEAF_BIT) ? (const void*)(sc.tris + (later & ~SRT_LEAF_BIT)) : (const void*)(sc.pairs + later);
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
+            }
           } else if (pl || pr) {
             cur = pl ? nd.z : nd.w;
           } else {
@@ -686,9 +694,19 @@ wf_resolve_kernel(const __grid_constant__ FrameParams fp, PathPool pool, float4*
   const float4 prev = accum[texel];
   V3 acc = v3(prev.x, prev.y, prev.z);
   const float4* __restrict__ s = pool.samples + pixel;
+  // a path that ended in wf_init_kernel (primary cull): GetRayColor's miss branch on the first segment
+  // (raytrace_compute.glsl:287-292, Q19) and main()'s pixelColor = vec3(0) + GetRayColor(...)
+  const V3 sky_color = v3(0.0f) + v3(1.0f) * v3(0.05f);
+  const V3 sky_sample = v3(0.0f) + sky_color;
   for (int f = 0; f < fp.n_frames; ++f) {  // frame order = the shader's order of additions
-    const float4 c = __ldcs(s + (size_t)f * pool.n_pixels);
-    acc = acc + v3(c.x, c.y, c.z);
+    const size_t e = (size_t)f * pool.n_pixels + pixel;
+    const bool culled = pool.culled != nullptr && ((__ldg(pool.culled + (e >> 5)) >> (pixel & 31u)) & 1u);  // word: warp-uniform
+    if (culled) {
+      acc = acc + sky_sample;
+    } else {
+      const float4 c = __ldcs(s + (size_t)f * pool.n_pixels);
+      acc = acc + v3(c.x, c.y, c.z);
+    }
   }
   accum[texel] = make_float4(acc.x, acc.y, acc.z, 1.0f);
   const V3 lin = acc / (float)(fp.accum_frames + fp.n_frames - 1);
