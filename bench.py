@@ -207,8 +207,6 @@ def run_gpu(args):
         ctx.set_option(pkg.OPT_FINDER, args.finder)
     if args.primary_cull >= 0:
         ctx.set_option(pkg.OPT_PRIMARY_CULL, args.primary_cull)
-    if args.prefetch >= 0:
-        ctx.set_option(pkg.OPT_PREFETCH, args.prefetch)
 
     # the step's host inputs: the two noise tables live in pinned host memory (the library then DMAs them as they are
     # and packs on the device; pageable tables are packed by host threads first), the scene arrays are pageable
@@ -458,7 +456,6 @@ def main():
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
     ap.add_argument("--l2-persist", type=int, default=-1, help="1/0: pin the BVH top levels in L2 (default: library default, on)")
     ap.add_argument("--refill", type=int, default=0, help="refill threshold of the wavefront trace kernel (0 = default)")
-    ap.add_argument("--prefetch", type=int, default=-1, help="0/1/2: L2 prefetch of stacked BVH children (-1 = library default, auto)")
     ap.add_argument("--primary-cull", type=int, default=-1,
                     help="1/0: primary rays that miss every root box end in the init kernel (-1 = library default, on)")
     ap.add_argument("--finder", type=int, default=-1,

@@ -84,10 +84,6 @@ typedef struct srt_counters {
                                      (chunks are sized for that when the pool holds at least one frame).  0 = every primary ray
                                      goes through the queues.  Same bits either way. */
 
-#define SRT_OPT_PREFETCH 14       /* wavefront schedule, walk of the reference BVH: 1 = a child that is put on the traversal stack is
-                                     prefetched into L2 (prefetch.global.L2); 0 = not; 2 (default) = when nodes + triangle records
-                                     exceed 96 MB (the 10 M-triangle soup; a scene that fits L2 gains nothing).  Same bits. */
-
 /* Graphics::Compute::Compute(path) + Init()  (src/graphics/Shader.cpp:14-26,125-157): create the "program".
  * Kernels are AOT-compiled for sm_100a, so there is no source path.  device = CUDA ordinal. */
 int srt_create(srt_ctx** out, int device);

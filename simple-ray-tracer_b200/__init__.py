@@ -16,7 +16,6 @@ LIB_PATH = os.path.join(HERE, "libsrt_b200.so")
 OPT_TRAVERSAL, OPT_COUNT_TRAVERSAL, OPT_L2_PERSIST, OPT_BLOCK_THREADS, OPT_SCHEDULE = 1, 2, 3, 4, 5
 OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS, OPT_TEXTURES, OPT_TAIL_PATHS, OPT_FINDER = 6, 7, 8, 9, 10, 11, 12
 OPT_PRIMARY_CULL = 13
-OPT_PREFETCH = 14
 SCHED_PER_PATH, SCHED_REGEN, SCHED_PERSISTENT, SCHED_WAVEFRONT = 0, 1, 2, 3
 TRAV_REFERENCE, TRAV_ORDERED = 0, 1
 NO_HIT = 0xFFFFFFFF

@@ -114,7 +114,6 @@ struct srt_ctx {
   int refill_threshold = 12;                   // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL)
   uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
   bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
-  int prefetch_mode = 2;                        // SRT_OPT_PREFETCH: 0 off, 1 on, 2 = when the scene is larger than L2
   uint32_t* d_culled = nullptr;                 // bit map of the paths the cull ended (one bit per sample entry)
   uint32_t tail_paths = 1u << 20;               // live paths at which the tail kernel takes over (SRT_OPT_TAIL_PATHS, 0 = never)
   size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
@@ -255,11 +254,6 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_FINDER) {
     if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_FINDER: 0 (off), 1 (on) or 2 (auto)");
     ctx->finder_mode = value;
-    return 0;
-  }
-  if (key == SRT_OPT_PREFETCH) {
-    if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_PREFETCH: 0 (off), 1 (on) or 2 (auto)");
-    ctx->prefetch_mode = value;
     return 0;
   }
   if (key == SRT_OPT_PRIMARY_CULL) {
@@ -797,10 +791,6 @@ void fill_frame_params(const srt_ctx* ctx, int n_frames, FrameParams& fp) {
   int cap = ctx->tree_depth + 1;
   if (ctx->finder_ready && ctx->finder_depth + 1 > cap) cap = ctx->finder_depth + 1;
   fp.stack_cap = cap < 2 ? 2 : cap;
-  {
-    const size_t scene_bytes = (size_t)ctx->n_nodes * 32u + (size_t)ctx->n_tris * sizeof(TriRecord);
-    fp.prefetch_l2 = ctx->prefetch_mode == 1 || (ctx->prefetch_mode == 2 && scene_bytes > ((size_t)96 << 20)) ? 1 : 0;
-  }
 
   const float focus_dist = 1.0f;                                  // :384
   float aspect = (float)p.width / (float)p.height;                // :368

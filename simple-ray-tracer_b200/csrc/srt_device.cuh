@@ -136,7 +136,6 @@ struct FrameParams {
   uint32_t bvh_count;
   int max_depth;
   int stack_cap;         // entries per thread in the shared-memory traversal stack
-  int prefetch_l2;       // 1 = wf_trace_kernel prefetches stacked children into L2 (scenes larger than L2)
   V3 center, pixel00, delta_u, delta_v;
   DeviceLight lights[SRT_MAX_LIGHTS];
 };

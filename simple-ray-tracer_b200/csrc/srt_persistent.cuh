@@ -37,10 +37,11 @@ __device__ __forceinline__ float box_distance_fast(V3 o, V3 inv, float mnx, floa
 
 // maps lane `in_tile` of the i-th 8x4 tile of this launch's share of the image to pixel coordinates
 __device__ __forceinline__ void tile_pixel(const FrameParams& fp, uint32_t tile, int in_tile, int& x, int& y) {
-  const int tiles_x = fp.width >> 3;
-  int tile_row = tile / tiles_x;  // two 4-row tiles per 8-row band
+  const uint32_t tiles_x = (uint32_t)fp.width >> 3;
+  const uint32_t row_u = tile / tiles_x;  // two 4-row tiles per 8-row band (unsigned: half the instructions of int /)
+  const int tile_row = (int)row_u;
   int band = (tile_row >> 1) * fp.stripe_world + fp.stripe_rank;
-  x = ((tile % tiles_x) << 3) + (in_tile & 7);
+  x = (int)((tile - row_u * tiles_x) << 3) + (in_tile & 7);
   y = fp.y0 + (band << 3) + ((tile_row & 1) << 2) + (in_tile >> 3);
 }
 

@@ -46,7 +46,12 @@ __device__ __forceinline__ uint32_t wf_pack(int depth, int rand_index, int iter)
 // GetRay + SampleSquare (raytrace_compute.glsl:78-90, raytrace_utils.glsl:10-17) for frame f of the launch
 __device__ __forceinline__ V3 wf_primary_dir(const DeviceScene& sc, const FrameParams& fp, int x, int y, int pix, int f) {
   int samp = (fp.accum_frames + f) % fp.n_texels;
-  int idx = (pix + samp) % fp.n_texels;
+  int idx = pix + samp;  // (pix + samp) % n_texels: one conditional subtraction when both terms are below n_texels
+  if (pix < fp.n_texels && idx >= 0) {
+    if (idx >= fp.n_texels) idx -= fp.n_texels;
+  } else {
+    idx = (pix + samp) % fp.n_texels;
+  }
   float2 jit = __ldg(sc.noise_unit_xy + idx);
   float ox = jit.x - 0.5f, oy = jit.y - 0.5f;
   V3 pixel_sample = fp.pixel00 + (((float)x + ox) * fp.delta_u) + (((float)y + oy) * fp.delta_v);
@@ -57,8 +62,14 @@ __device__ __forceinline__ V3 wf_primary_dir(const DeviceScene& sc, const FrameP
 // frame.  (32 frames of one pixel per warp instead -- near-identical origins for a warp's bounce rays -- measured the
 // same, 1911 vs 1907 Mseg/s: the divergence comes from the directions.)
 __device__ __forceinline__ void wf_path_id(const PathPool& pool, unsigned long long p, uint32_t& pixel, uint32_t& f) {
-  pixel = (uint32_t)(p % pool.n_pixels);
-  f = (uint32_t)(p / pool.n_pixels);
+  if ((p >> 32) == 0ull) {  // a 64-bit division is ~150 instructions, and 132.7 M camera paths each do one
+    const uint32_t p32 = (uint32_t)p;
+    f = p32 / pool.n_pixels;
+    pixel = p32 - f * pool.n_pixels;
+  } else {
+    pixel = (uint32_t)(p % pool.n_pixels);
+    f = (uint32_t)(p / pool.n_pixels);
+  }
 }
 
 // ---- wave 0: the first pool.cap paths of the launch -----------------------------------------------------------------
@@ -350,17 +361,9 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           const bool pr = (nr <= fr) && (dr < best) && (dr != -inf_());
           if (pl && pr) {
             const bool right_first = (MODE == TRAV_REFERENCE || !front_l || !front_r) ? true : !(dl < dr);
-            const uint32_t later = right_first ? nd.z : nd.w;
-            wf_sts(sp, later, __float_as_uint(right_first ? dl : dr));
+            wf_sts(sp, right_first ? nd.z : nd.w, __float_as_uint(right_first ? dl : dr));
             sp += sp_step;
             cur = right_first ? nd.w : nd.z;
-            // a scene far larger than L2 (the 10 M-triangle soup): the child that waits on the stack is asked into L2
-            // now, so that its pop finds it there instead of in DRAM (the walk is latency-bound: 16 warps per issue
-            // wait on long-scoreboard, one 64 B request per lane in flight; profiles/r01j_soup_*)
-            if (fp.prefetch_l2) {
-              const void* ptr = (later & SRT_LEAF_BIT) ? (const void*)(sc.tris + (later & ~SRT_LEAF_BIT)) : (const void*)(sc.pairs + later);
-              asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
-            }
           } else if (pl || pr) {
             cur = pl ? nd.z : nd.w;
           } else {
