@@ -38,6 +38,10 @@ WORKLOADS = {
     "airplane-standin": (True, 1920, 1080, 64, 0,
                          "airplane-standin (procedural airliner mesh, ~110 k tris, the 6 materials of 11803_Airplane_v1_l1.mtl, "
                          "BVH by the reference algorithm) 1920x1080, 64 spp per step, maxDepth 5"),
+    # BASELINE.json configs[3]: the same stand-in at 3840x2160, 1024 spp, meant for 2/4/8 GPUs (image bands + NCCL reduce)
+    "airplane-standin-4k": (True, 3840, 2160, 1024, 0,
+                            "airplane-standin (procedural airliner mesh, ~110 k tris, the 6 materials of 11803_Airplane_v1_l1.mtl, "
+                            "BVH by the reference algorithm) 3840x2160, 1024 spp per step, maxDepth 5"),
     # BASELINE.json configs[4]
     "soup": (True, 1920, 1080, 4, 8,
              "synthetic random triangle soup (PCG32 0xC0FFEE, BVH by the reference algorithm) 1920x1080, 4 spp per step, "
@@ -106,7 +110,7 @@ def workload_inputs(name, soup_tris=10_000_000):
     scene = None
     if name == "rubik":
         scene = scenes.rubik_scene()
-    elif name == "airplane-standin":
+    elif name in ("airplane-standin", "airplane-standin-4k"):
         with tempfile.TemporaryDirectory() as d:
             obj, n_tri = scenes.write_airplane_standin(d, detail=128)
             scene = scenes.load_obj_scene(d, obj, d)
