@@ -302,6 +302,32 @@ def test_pinned_noise_tables_same_picture(pkg, ctx, oracle):
     assert_bit_exact(acc2, oacc)
 
 
+@pytest.mark.parametrize("which", ["rubik", "airplane-standin"])
+def test_full_size_defaults_equal_the_plain_walk(pkg, ctx, tmp_path, which):
+    """At the bench's full size (1920x1080, 64 spp in one launch: 132.7 M paths, too many for the oracle) the library's
+    defaults -- hit finder with its distance-bounded walk for camera rays, primary cull, tail kernel, no-light paths put
+    aside -- must give the very bits of the plain schedule that the tests above pin to the oracle at smaller sizes: every
+    ray through wf_trace_kernel in the shader's visiting order, waves to the end, every camera ray through the queues."""
+    if which == "rubik":
+        scene = scenes.rubik_scene()
+    else:
+        name, _ = scenes.write_airplane_standin(str(tmp_path), detail=128)
+        scene = scenes.load_obj_scene(str(tmp_path), name, str(tmp_path))
+    W, H, spp = 1920, 1080, 64
+    noise = scenes.noise_tables(W, H)
+    ctx.set_option(pkg.OPT_FINDER, 1)
+    acc, out, ids, cnt = gpu_render(pkg, ctx, W, H, True, spp, pkg.TRAV_REFERENCE, scene=scene, noise=noise, schedule=3)
+    assert ctx.finder_info()[0]
+    ctx.set_option(pkg.OPT_PRIMARY_CULL, 0)
+    acc0, out0, ids0, cnt0 = gpu_render(pkg, ctx, W, H, True, spp, pkg.TRAV_REFERENCE, scene=scene, noise=noise, schedule=30)
+    assert not ctx.finder_info()[0]
+    assert cnt["paths"] == W * H * spp == cnt0["paths"]
+    assert cnt["segments"] == cnt0["segments"] and cnt["shadow_rays"] == cnt0["shadow_rays"]
+    assert np.array_equal(ids, ids0)
+    assert np.array_equal(acc.view(np.uint32), acc0.view(np.uint32))
+    assert np.array_equal(out, out0)
+
+
 def test_row_bands_equal_whole_image(pkg, ctx, oracle):
     """The image-tile half of the multi-GPU split: rendering two row bands gives the bits of one full render."""
     scene = scenes.rubik_scene()
