@@ -5,7 +5,11 @@
 #include <math.h>
 #include <string.h>
 
+#include <stdio.h>
+#include <stdlib.h>
+
 #include <algorithm>
+#include <chrono>
 #include <atomic>
 #include <thread>
 
@@ -31,6 +35,7 @@ inline uint32_t f2u_(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 
 constexpr int kBins = 16;
 constexpr uint32_t kLeafMax = 4;
+constexpr uint32_t kSampleAbove = 8192;
 
 // Subtrees of no more than `grain` triangles are put aside as tasks while the top of the tree is built; the tasks then
 // run on host threads, each into its own arrays, and are appended with their references shifted.  (A 110 k-triangle
@@ -51,10 +56,14 @@ struct Builder {
 
   // builds the subtree over idx[lo, hi); returns its direct reference and its (unpadded) box
   uint32_t build(uint32_t lo, uint32_t hi, int depth, Box& box) {
+    // A node of more than kSampleAbove triangles looks at every 8th one for the bounds of the centres and for the
+    // bins (the split plane of a big node is a statistic; its box is the union of its children's, exact); the partition
+    // still touches every triangle.  The top levels are the serial part of the build: 3 passes over all triangles each.
+    const uint32_t stride = (hi - lo) > kSampleAbove ? 8u : 1u;
     box.clear();
     Box cb;  // of the centres
     cb.clear();
-    for (uint32_t i = lo; i < hi; ++i) {
+    for (uint32_t i = lo; i < hi; i += stride) {
       const Box& b = tb[idx[i]];
       box.grow(b);
       for (int a = 0; a < 3; ++a) {
@@ -91,7 +100,7 @@ struct Builder {
         scale[a] = live[a] ? (float)kBins / (cb.mx[a] - cb.mn[a]) : 0.0f;
         for (int b = 0; b < kBins; ++b) { bb[a][b].clear(); bc[a][b] = 0; }
       }
-      for (uint32_t i = lo; i < hi; ++i) {
+      for (uint32_t i = lo; i < hi; i += stride) {
         const Box& t = tb[idx[i]];
         for (int a = 0; a < 3; ++a) {
           if (!live[a]) continue;
@@ -146,6 +155,10 @@ struct Builder {
     Box lb, rb;
     const uint32_t l = build(lo, mid, depth + 1, lb);
     const uint32_t r = build(mid, hi, depth + 1, rb);
+    if (stride > 1u) {  // the sampled pass saw part of the node: its box is its children's
+      box = lb;
+      box.grow(rb);
+    }
     NodePair p;
     p.a = make_float4(lb.mn[0] - pad, lb.mn[1] - pad, lb.mn[2] - pad, lb.mx[0] + pad);
     p.b = make_float4(lb.mx[1] + pad, lb.mx[2] + pad, rb.mn[0] - pad, rb.mn[1] - pad);
@@ -169,6 +182,7 @@ uint32_t build_tree(const std::vector<TriRecord>& ref, const std::vector<Box>& t
   const size_t pair0 = out.pairs.size();
   Box whole;
   uint32_t root = top.build(0, n, 0, whole);
+  if (getenv("SRT_UPLOAD_LOG")) fprintf(stderr, "build_tree: %u triangles, %zu tasks of <= %u, %u threads\n", n, tasks.size(), top.grain, n_threads);
   if (tasks.empty()) return root;
   struct Part { std::vector<NodePair> pairs; std::vector<TriRecord> tris; int depth = 0; uint32_t root = 0; };
   std::vector<Part> parts(tasks.size());
@@ -247,6 +261,13 @@ bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* node
                   FinderOut& out) {
   const uint32_t n_tris = (uint32_t)tris_ref.size();
   out = FinderOut();
+  const bool log = getenv("SRT_UPLOAD_LOG") != nullptr;
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+    return std::chrono::duration<double, std::milli>(b - a).count();
+  };
+  const auto t0 = now();
+  double ms_tree = 0.0;
   if (n_tris == 0 || n_tris > SRT_FINDER_MAX_TRIS) return false;
   std::vector<Box> tb(n_tris);
   for (uint32_t i = 0; i < n_tris; ++i) {
@@ -323,11 +344,14 @@ bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* node
     for (int a = 0; a < 3; ++a) ext = std::max(ext, nodes[root].max_bounds[a] - nodes[root].min_bounds[a]);
     if (!(ext > 0.0f) || !std::isfinite(ext)) return false;
     const float pad = ext * (1.0f / 4096.0f);
+    const auto tt = now();
     out.root[b] = build_tree(tris_ref, tb, mine, pad, out);
+    ms_tree += ms(tt, now());
     out.pad[b] = pad;
   }
   if (out.pairs.size() >= SRT_LEAF_BIT - 1u || out.depth > SRT_STACK_SIZE - 1) return false;
 
+  const auto t1 = now();
   // ---- is it worth it?  Sample rays from the surfaces (where bounce and shadow rays start) and from outside (where
   // camera rays start); count the tests of the shader's traversal and of finder + replay.
   Rng rng{0x5EEDF1DDull};
@@ -408,6 +432,9 @@ bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* node
   // measured (profiles/r01h_*): Rubik 111.5 vs 166.8 -> 2.0x faster through the finder, airplane stand-in 188.0 vs 237.8 ->
   // 2.3x (the test count flatters the reference walk, whose lock-step warps wait for its 100-triangle leaves)
   out.worthwhile = out.cost_finder < 0.9 * out.cost_reference;
+  if (log)
+    fprintf(stderr, "build_finder: boxes + reference-tree walk %.2f ms, SAH tree %.2f ms, sample rays %.2f ms\n",
+            ms(t0, t1) - ms_tree, ms_tree, ms(t1, now()));
   return true;
 }
 

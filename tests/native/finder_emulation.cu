@@ -8,6 +8,7 @@
 #include <stdlib.h>
 #include <math.h>
 #include <string.h>
+#include <time.h>
 #include <algorithm>
 #include <vector>
 #include "srt_finder.h"
@@ -44,7 +45,8 @@ int main(int argc,char**argv){
   std::vector<TriRecord> tr(nt);
   for(uint32_t i=0;i<nt;++i){const float*v0=verts[tris[i].v0_idx].vertex,*v1=verts[tris[i].v1_idx].vertex,*v2=verts[tris[i].v2_idx].vertex;
     tr[i].v0=make_float4(v0[0],v0[1],v0[2],U2F(tris[i].material_idx));tr[i].e1=make_float4(v1[0]-v0[0],v1[1]-v0[1],v1[2]-v0[2],U2F(rank[i]));tr[i].e2=make_float4(v2[0]-v0[0],v2[1]-v0[1],v2[2]-v0[2],0);}
-  FinderOut fo; bool ok=build_finder(bvhs.data(),bvhs.size(),nodes.data(),nodes.size(),tris.data(),verts.data(),tr,fo);
+  FinderOut fo; const double t_b0=(double)clock()/CLOCKS_PER_SEC; struct timespec ts0,ts1; clock_gettime(CLOCK_MONOTONIC,&ts0); bool ok=build_finder(bvhs.data(),bvhs.size(),nodes.data(),nodes.size(),tris.data(),verts.data(),tr,fo);
+  clock_gettime(CLOCK_MONOTONIC,&ts1); printf("build_finder: %.2f ms wall, %.2f ms cpu\n",(ts1.tv_sec-ts0.tv_sec)*1e3+(ts1.tv_nsec-ts0.tv_nsec)*1e-6,((double)clock()/CLOCKS_PER_SEC-t_b0)*1e3);
   printf("build ok=%d pairs=%zu ftris=%zu depth=%d cost ref %.1f finder %.1f worthwhile=%d\n",ok,fo.pairs.size(),fo.tris.size(),fo.depth,fo.cost_reference,fo.cost_finder,fo.worthwhile);
   if(!ok)return 0;
   std::vector<int> seen(nt,0); for(auto&r:fo.tris)seen[F2U(r.v0.w)]++; for(uint32_t i=0;i<nt;++i)if(seen[i]!=1){printf("triangle %u appears %d times\n",i,seen[i]);return 1;}
