@@ -20,7 +20,9 @@
 
 namespace srt {
 
-#define SRT_WF_TAIL_SHADE_AT 8  // lanes waiting for shading / a new path that end a traversal round
+#ifndef SRT_WF_TAIL_SHADE_AT
+#define SRT_WF_TAIL_SHADE_AT 16  // lanes waiting for shading / a new path that end a traversal round (4 / 8 / 12 / 16 / 24 measured: 37.14 / 35.98 / 35.51 / 35.22 / 35.26 ms per Rubik step)
+#endif
 
 #ifndef SRT_WF_TAIL_MIN_BLOCKS
 #define SRT_WF_TAIL_MIN_BLOCKS 13  // 72 registers (48 B of spills): 1 / 13 / 16 measured 36.32 / 35.98 / 35.93 ms per Rubik step, 49.70 / 49.75 / 50.32 on the airplane stand-in
