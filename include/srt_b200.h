@@ -52,7 +52,8 @@ typedef struct srt_counters {
 #define SRT_OPT_SAMPLE_BUDGET_MB 7 /* wavefront schedule: size limit of the per-path sample buffer; longer launches are cut
                                       into frame chunks (default 4096 MB) */
 
-#define SRT_OPT_REFILL 8          /* wavefront schedule: idle lanes per warp that trigger a queue fetch (1..32, default 12) */
+#define SRT_OPT_REFILL 8          /* wavefront schedule: idle lanes per warp that trigger a queue fetch (1..32; default: 12 in the
+                                     trace kernel, 16 in the find kernel) */
 
 #define SRT_OPT_TIME_KERNELS 9    /* wavefront schedule: 1 = bracket every trace / logic launch with CUDA events on the launching
                                      stream (read with srt_get_kernel_times) */

@@ -111,7 +111,7 @@ struct srt_ctx {
   bool time_kernels = false;
   std::vector<cudaEvent_t> timing_events;
   size_t timing_used = 0;
-  int refill_threshold = 12;                   // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL)
+  int refill_threshold = 0;                    // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL; 0 = each kernel's own default)
   uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
   bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
   uint32_t* d_culled = nullptr;                 // bit map of the paths the cull ended (one bit per sample entry)

@@ -332,7 +332,7 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
   long need = ((long)pool.cap / 32 + block / 32 - 1) / (block / 32);
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  k<<<(unsigned)grid, block, smem, stream>>>(sc, fp, pool, parity, refill, counters);
+  k<<<(unsigned)grid, block, smem, stream>>>(sc, fp, pool, parity, refill > 0 ? refill : SRT_WF_TRACE_REFILL, counters);
   return cudaGetLastError();
 }
 }  // namespace
@@ -363,7 +363,7 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
   long need = ((long)pool.cap / 32 + 1) / 2;
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  k<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill);
+  k<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill > 0 ? refill : SRT_WF_FIND_REFILL);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   long blocks = ((long)pool.cap + 127) / 128;
   if (blocks > (long)sms * 16) blocks = (long)sms * 16;

@@ -29,6 +29,7 @@
 namespace srt {
 
 #define SRT_WF_TRACE_THREADS 64   // block of the trace kernel (two warps share an SM slot; 64 measured best of 32..256)
+#define SRT_WF_TRACE_REFILL 12    // idle lanes that send a trace warp back to the queue (8 / 12 / 16 measured: 1872 / 1907 / 1887 Mseg/s walking the reference BVH)
 #define SRT_WF_DESCENT_CUTOFF 5   // a_min of the trace kernel's descent phase (0, 3, 5, 7, 10 measured: 1801..1907..1862 Mseg/s)
 #define SRT_WF_LOGIC_THREADS 256
 #define SRT_WF_LOGIC_BLOCKS_PER_SM 4  // 64 registers per thread: the kernel waits on gathers, occupancy hides them
