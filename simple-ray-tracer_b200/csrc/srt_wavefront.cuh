@@ -31,8 +31,12 @@ namespace srt {
 #define SRT_WF_TRACE_THREADS 64   // block of the trace kernel (two warps share an SM slot; 64 measured best of 32..256)
 #define SRT_WF_TRACE_REFILL 12    // idle lanes that send a trace warp back to the queue (8 / 12 / 16 measured: 1872 / 1907 / 1887 Mseg/s walking the reference BVH)
 #define SRT_WF_DESCENT_CUTOFF 5   // a_min of the trace kernel's descent phase (0, 3, 5, 7, 10 measured: 1801..1907..1862 Mseg/s)
+#ifndef SRT_WF_LOGIC_THREADS
 #define SRT_WF_LOGIC_THREADS 256
+#endif
+#ifndef SRT_WF_LOGIC_BLOCKS_PER_SM
 #define SRT_WF_LOGIC_BLOCKS_PER_SM 4  // 64 registers per thread: the kernel waits on gathers, occupancy hides them
+#endif
 #define SRT_WF_APPEND_CHUNK 256u     // most queue entries a logic warp reserves per atomic (unused ones become holes)
 #define SRT_WF_HOLE 0xFFFFFFFFu      // list entry that carries no slot
 #define SRT_WF_FETCH_MAX 2048u       // most queue entries a trace warp reserves per atomic
