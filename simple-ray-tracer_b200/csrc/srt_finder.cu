@@ -357,75 +357,100 @@ bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* node
   Rng rng{0x5EEDF1DDull};
   double cost_ref = 0.0, cost_find = 0.0;
   const int n_samples = 512;  // each costs some 300 host tests: 0.7 ms on Rubik (2048 were 3 ms of every upload)
-  std::vector<uint32_t> st;
+  // the ray parameters come from one random stream (the same rays whatever the thread count); the walks themselves run
+  // on host threads for big scenes (both costs are sums of multiples of 0.5: exact in any order)
+  struct Sample { uint32_t b, t; float dir[3]; bool use; };
+  std::vector<Sample> samples((size_t)n_samples);
   for (int s = 0; s < n_samples; ++s) {
-    const uint32_t b = rng.next() % n_bvhs;
-    const uint32_t root = bvhs[b].first_index;
-    const uint32_t t = rng.next() % n_tris;
-    if (owner[out.tri_leaf[t]] != root) { continue; }
-    const TriRecord& r = tris_ref[t];
-    float dir[3];
+    Sample& sm = samples[(size_t)s];
+    sm.b = rng.next() % n_bvhs;
+    sm.t = rng.next() % n_tris;
+    sm.use = owner[out.tri_leaf[sm.t]] == bvhs[sm.b].first_index;
+    if (!sm.use) continue;
     do {
-      for (int a = 0; a < 3; ++a) dir[a] = 2.0f * rng.uni() - 1.0f;
-    } while (dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2] > 1.0f || dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2] < 1e-4f);
-    float on[3] = {r.v0.x + 0.3f * r.e1.x + 0.3f * r.e2.x, r.v0.y + 0.3f * r.e1.y + 0.3f * r.e2.y, r.v0.z + 0.3f * r.e1.z + 0.3f * r.e2.z};
-    float o[3] = {on[0], on[1], on[2]};
-    if (s & 1) {  // from outside, aimed at the surface point
-      float ext = 0.0f;
-      for (int a = 0; a < 3; ++a) ext = std::max(ext, nodes[root].max_bounds[a] - nodes[root].min_bounds[a]);
-      for (int a = 0; a < 3; ++a) { o[a] = on[a] - 2.0f * ext * dir[a]; }
-    }
-    const float inv[3] = {1.0f / dir[0], 1.0f / dir[1], 1.0f / dir[2]};
-    // the shader's traversal
-    {
-      float best = INFINITY;
-      st.assign(1, root);
-      while (!st.empty()) {
-        const uint32_t n = st.back();
-        st.pop_back();
-        const srt_bvh_node& node = nodes[n];
-        float tn, tf;
-        cost_ref += 1.0;
-        if (!slab(o, inv, node.min_bounds, node.max_bounds, tn, tf)) continue;
-        const float d = tn >= 0.0f ? tn : tf;
-        if (!(d < best)) continue;
-        if (node.prim_count > 0) {
-          for (uint32_t k = 0; k < node.prim_count; ++k) {
-            float tt;
-            cost_ref += 1.5;
-            if (tri_hit(tris_ref[node.first_child_or_prim_index + k], o, dir, best, tt)) best = tt;
+      for (int a = 0; a < 3; ++a) sm.dir[a] = 2.0f * rng.uni() - 1.0f;
+    } while (sm.dir[0] * sm.dir[0] + sm.dir[1] * sm.dir[1] + sm.dir[2] * sm.dir[2] > 1.0f ||
+             sm.dir[0] * sm.dir[0] + sm.dir[1] * sm.dir[1] + sm.dir[2] * sm.dir[2] < 1e-4f);
+  }
+  auto walk = [&](int s0, int s1, double& cr, double& cf) {
+    std::vector<uint32_t> st;
+    for (int s = s0; s < s1; ++s) {
+      const Sample& sm = samples[(size_t)s];
+      if (!sm.use) continue;
+      const uint32_t b = sm.b, t = sm.t, root = bvhs[b].first_index;
+      const float dir[3] = {sm.dir[0], sm.dir[1], sm.dir[2]};
+      const TriRecord& r = tris_ref[t];
+      float on[3] = {r.v0.x + 0.3f * r.e1.x + 0.3f * r.e2.x, r.v0.y + 0.3f * r.e1.y + 0.3f * r.e2.y, r.v0.z + 0.3f * r.e1.z + 0.3f * r.e2.z};
+      float o[3] = {on[0], on[1], on[2]};
+      if (s & 1) {  // from outside, aimed at the surface point
+        float ext = 0.0f;
+        for (int a = 0; a < 3; ++a) ext = std::max(ext, nodes[root].max_bounds[a] - nodes[root].min_bounds[a]);
+        for (int a = 0; a < 3; ++a) { o[a] = on[a] - 2.0f * ext * dir[a]; }
+      }
+      const float inv[3] = {1.0f / dir[0], 1.0f / dir[1], 1.0f / dir[2]};
+      // the shader's traversal
+      {
+        float best = INFINITY;
+        st.assign(1, root);
+        while (!st.empty()) {
+          const uint32_t n = st.back();
+          st.pop_back();
+          const srt_bvh_node& node = nodes[n];
+          float tn, tf;
+          cr += 1.0;
+          if (!slab(o, inv, node.min_bounds, node.max_bounds, tn, tf)) continue;
+          const float d = tn >= 0.0f ? tn : tf;
+          if (!(d < best)) continue;
+          if (node.prim_count > 0) {
+            for (uint32_t k = 0; k < node.prim_count; ++k) {
+              float tt;
+              cr += 1.5;
+              if (tri_hit(tris_ref[node.first_child_or_prim_index + k], o, dir, best, tt)) best = tt;
+            }
+          } else {
+            st.push_back(node.first_child_or_prim_index);
+            st.push_back(node.first_child_or_prim_index + 1);
           }
-        } else {
-          st.push_back(node.first_child_or_prim_index);
-          st.push_back(node.first_child_or_prim_index + 1);
         }
       }
-    }
-    // finder + replay
-    {
-      st.assign(1, out.root[b]);
-      while (!st.empty()) {
-        const uint32_t n = st.back();
-        st.pop_back();
-        if (n & SRT_LEAF_BIT) {
-          uint32_t i = n & ~SRT_LEAF_BIT;
-          for (;;) {
-            float tt;
-            cost_find += 1.5;
-            if (tri_hit(out.tris[i], o, dir, INFINITY, tt)) cost_find += 1.0 + leaf_depth[out.tri_leaf[f2u_(out.tris[i].v0.w)]];
-            if (f2u_(out.tris[i].e2.w) == 0u) break;
-            ++i;
+      // finder + replay
+      {
+        st.assign(1, out.root[b]);
+        while (!st.empty()) {
+          const uint32_t n = st.back();
+          st.pop_back();
+          if (n & SRT_LEAF_BIT) {
+            uint32_t i = n & ~SRT_LEAF_BIT;
+            for (;;) {
+              float tt;
+              cf += 1.5;
+              if (tri_hit(out.tris[i], o, dir, INFINITY, tt)) cf += 1.0 + leaf_depth[out.tri_leaf[f2u_(out.tris[i].v0.w)]];
+              if (f2u_(out.tris[i].e2.w) == 0u) break;
+              ++i;
+            }
+            continue;
           }
-          continue;
+          const NodePair& p = out.pairs[n];
+          const float lmn[3] = {p.a.x, p.a.y, p.a.z}, lmx[3] = {p.a.w, p.b.x, p.b.y}, rmn[3] = {p.b.z, p.b.w, p.c.x}, rmx[3] = {p.c.y, p.c.z, p.c.w};
+          float tn, tf;
+          cf += 2.0;
+          if (slab(o, inv, lmn, lmx, tn, tf) && tf >= 0.0f) st.push_back(p.d.z);
+          if (slab(o, inv, rmn, rmx, tn, tf) && tf >= 0.0f) st.push_back(p.d.w);
         }
-        const NodePair& p = out.pairs[n];
-        const float lmn[3] = {p.a.x, p.a.y, p.a.z}, lmx[3] = {p.a.w, p.b.x, p.b.y}, rmn[3] = {p.b.z, p.b.w, p.c.x}, rmx[3] = {p.c.y, p.c.z, p.c.w};
-        float tn, tf;
-        cost_find += 2.0;
-        if (slab(o, inv, lmn, lmx, tn, tf) && tf >= 0.0f) st.push_back(p.d.z);
-        if (slab(o, inv, rmn, rmx, tn, tf) && tf >= 0.0f) st.push_back(p.d.w);
       }
+  
     }
+  };
+  {
+    const unsigned n_thr = n_tris >= (1u << 14) ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+    std::vector<double> cr(n_thr, 0.0), cf(n_thr, 0.0);
+    std::vector<std::thread> pool;
+    const int per = (n_samples + (int)n_thr - 1) / (int)n_thr;
+    for (unsigned k = 1; k < n_thr; ++k)
+      pool.emplace_back([&, k] { walk(std::min(n_samples, (int)k * per), std::min(n_samples, ((int)k + 1) * per), cr[k], cf[k]); });
+    walk(0, std::min(n_samples, per), cr[0], cf[0]);
+    for (auto& th : pool) th.join();
+    for (unsigned k = 0; k < n_thr; ++k) { cost_ref += cr[k]; cost_find += cf[k]; }
   }
   out.cost_reference = cost_ref / n_samples;
   out.cost_finder = cost_find / n_samples;
