@@ -9,6 +9,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <string>
 #include <thread>
@@ -453,19 +454,39 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
                 "(ray_intersects.glsl:100)", rl.depth, SRT_STACK_SIZE);
 
   std::vector<TriRecord> tris(n_triangles);
-  for (uint32_t i = 0; i < n_triangles; ++i) {
-    const srt_triangle& t = triangles[i];
-    if (t.v0_idx >= n_vertices || t.v1_idx >= n_vertices || t.v2_idx >= n_vertices)
-      return fail(ctx, "triangle %u: vertex index out of range", i);
-    if (t.material_idx >= n_materials) return fail(ctx, "triangle %u: material index out of range", i);
-    const float *v0 = vertices[t.v0_idx].vertex, *v1 = vertices[t.v1_idx].vertex, *v2 = vertices[t.v2_idx].vertex;
-    TriRecord r;
-    // edge_1 = v1 - v0, edge_2 = v2 - v0 (ray_intersects.glsl:69-70): IEEE subtractions, same bits as on the device
-    r.v0 = make_float4(v0[0], v0[1], v0[2], u2f(t.material_idx));
-    r.e1 = make_float4(v1[0] - v0[0], v1[1] - v0[1], v1[2] - v0[2], u2f(rl.rank[i]));
-    r.e2 = make_float4(v2[0] - v0[0], v2[1] - v0[1], v2[2] - v0[2], 0.0f);
-    memcpy(&r.e2.w, &rl.remaining[i], 4);
-    tris[i] = r;
+  {
+    // per-triangle records; a big scene (the 10 M-triangle soup) is cut over host threads.  bad_* keep the lowest
+    // offending triangle so that the message does not depend on the thread count.
+    std::atomic<uint32_t> bad_vertex{0xFFFFFFFFu}, bad_material{0xFFFFFFFFu};
+    auto lowest = [](std::atomic<uint32_t>& a, uint32_t i) {
+      uint32_t cur = a.load();
+      while (i < cur && !a.compare_exchange_weak(cur, i)) {}
+    };
+    auto fill = [&](uint32_t lo, uint32_t hi) {
+      for (uint32_t i = lo; i < hi; ++i) {
+        const srt_triangle& t = triangles[i];
+        if (t.v0_idx >= n_vertices || t.v1_idx >= n_vertices || t.v2_idx >= n_vertices) { lowest(bad_vertex, i); continue; }
+        if (t.material_idx >= n_materials) { lowest(bad_material, i); continue; }
+        const float *v0 = vertices[t.v0_idx].vertex, *v1 = vertices[t.v1_idx].vertex, *v2 = vertices[t.v2_idx].vertex;
+        TriRecord r;
+        // edge_1 = v1 - v0, edge_2 = v2 - v0 (ray_intersects.glsl:69-70): IEEE subtractions, same bits as on the device
+        r.v0 = make_float4(v0[0], v0[1], v0[2], u2f(t.material_idx));
+        r.e1 = make_float4(v1[0] - v0[0], v1[1] - v0[1], v1[2] - v0[2], u2f(rl.rank[i]));
+        r.e2 = make_float4(v2[0] - v0[0], v2[1] - v0[1], v2[2] - v0[2], 0.0f);
+        memcpy(&r.e2.w, &rl.remaining[i], 4);
+        tris[i] = r;
+      }
+    };
+    const unsigned n_thr = n_triangles >= (1u << 16) ? std::min(16u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+    const uint32_t per = (n_triangles + n_thr - 1) / n_thr;
+    std::vector<std::thread> pool;
+    for (unsigned k = 1; k < n_thr; ++k)
+      pool.emplace_back(fill, std::min(n_triangles, k * per), std::min(n_triangles, (k + 1) * per));
+    fill(0, std::min(n_triangles, per));
+    for (auto& th : pool) th.join();
+    const uint32_t bv = bad_vertex.load(), bm = bad_material.load();
+    if (bv != 0xFFFFFFFFu && bv <= bm) return fail(ctx, "triangle %u: vertex index out of range", bv);
+    if (bm != 0xFFFFFFFFu) return fail(ctx, "triangle %u: material index out of range", bm);
   }
   const auto t_relayout = now();
   // hit finder: a private tree over the same triangles + what a replay of the shader's culls needs (srt_finder.h)
