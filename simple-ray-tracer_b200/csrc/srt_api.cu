@@ -311,6 +311,8 @@ bool relayout(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_
   out.remaining.assign(n_tris, 0u);
   out.tri_bvh.assign(n_tris, 0u);
   uint32_t next_rank = 0;
+  out.pairs.reserve((size_t)n_nodes / 2 + 1);   // a full binary tree: (n - 1) / 2 inner nodes, (n + 1) / 2 leaves
+  out.leaves.reserve((size_t)n_nodes / 2 + 1);  // (no regrowth copies of a 400 MB array for the 10 M-triangle soup)
   std::vector<uint32_t> seen(n_nodes, 0);  // BVH (1-based) that reached the node
   struct Item { uint32_t node; uint32_t slot; int depth; };  // slot: where to write this node's reference
   for (uint32_t b = 0; b < n_bvhs; ++b) {
