@@ -328,6 +328,24 @@ def test_full_size_defaults_equal_the_plain_walk(pkg, ctx, tmp_path, which):
     assert np.array_equal(out, out0)
 
 
+def test_upload_rejects_bad_indices_with_the_lowest_offender(pkg, ctx, tmp_path):
+    """srt_upload_scene validates every triangle (the records are built on host threads for big scenes): the error names
+    the lowest offending triangle whatever the thread count, a vertex index before a material index on the same one."""
+    scene, _ = scenes.soup_scene(70000, str(tmp_path))  # above the threading threshold (64 Ki triangles)
+    n_vert, n_mat = len(scene["vertices"]), len(scene["materials"])
+    bad = {k: v.copy() for k, v in scene.items() if hasattr(v, "copy")}
+    bad["triangles"]["v"][69000, 1] = n_vert
+    bad["triangles"]["v"][1234, 2] = n_vert + 5
+    bad["triangles"]["material"][1234] = n_mat
+    bad["triangles"]["material"][77] = n_mat + 1
+    with pytest.raises(pkg.SrtError, match="triangle 77: material index out of range"):
+        ctx.upload_scene(bad)
+    bad["triangles"]["material"][77] = 0
+    with pytest.raises(pkg.SrtError, match="triangle 1234: vertex index out of range"):
+        ctx.upload_scene(bad)
+    ctx.upload_scene(scene)  # and a good scene still goes in afterwards
+
+
 def test_row_bands_equal_whole_image(pkg, ctx, oracle):
     """The image-tile half of the multi-GPU split: rendering two row bands gives the bits of one full render."""
     scene = scenes.rubik_scene()
