@@ -188,6 +188,12 @@ int srt_reset_counters(srt_ctx* ctx);
  * vs finder + replay).  No reference call site (the shader has one way to intersect).  Any pointer may be NULL. */
 int srt_get_finder_info(srt_ctx* ctx, int32_t* active, double* cost_reference, double* cost_finder);
 
+/* Measurement aid (no reference call site): bytes per second this GPU delivers for RANDOM 64-byte records -- the size of a
+ * device BVH node pair -- gathered from an array of `bytes` (choose it far above the 126 MB L2), with the trace kernel's
+ * launch shape.  chase = 1: each address depends on the record loaded before (a traversal's node -> child chain);
+ * chase = 0: independent addresses.  The roofline denominators for the HBM-bound configuration (configs[4]). */
+int srt_measure_gather(srt_ctx* ctx, uint64_t bytes, int32_t chase, double* gbytes_per_s);
+
 /* Device-side evaluation of the numeric decree (srt_detmath.h), for bit-for-bit checks against the host:
  * which: 0 = sin, 1 = cos, 2 = pow(x, 1/2.4), 3 = randFloat(x, y[i]) (y required), 4 = linearToSrgb. */
 int srt_eval_detmath(srt_ctx* ctx, int which, const float* x, const float* y, float* out, uint32_t n);

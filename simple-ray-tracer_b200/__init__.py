@@ -34,7 +34,7 @@ EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
            "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_build_bvh", "srt_set_texture",
-           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_version"]
+           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_version"]
 
 
 class Params(C.Structure):  # srt_params, include/srt_types.h
@@ -236,6 +236,12 @@ class Context:
         a, r, f = C.c_int32(), C.c_double(), C.c_double()
         self._ck(self._lib.srt_get_finder_info(self._h, C.byref(a), C.byref(r), C.byref(f)))
         return bool(a.value), r.value, f.value
+
+    def measure_gather(self, n_bytes, chase):
+        """GB/s of random 64 B record gathers from an n_bytes array (see srt_measure_gather)."""
+        g = C.c_double()
+        self._ck(self._lib.srt_measure_gather(self._h, C.c_uint64(n_bytes), C.c_int32(1 if chase else 0), C.byref(g)))
+        return g.value
 
     def reset_counters(self):
         self._ck(self._lib.srt_reset_counters(self._h))

@@ -1272,6 +1272,38 @@ extern "C" int srt_reset_counters(srt_ctx* ctx) {
   return 0;
 }
 
+extern "C" int srt_measure_gather(srt_ctx* ctx, uint64_t bytes, int32_t chase, double* gbytes_per_s) {
+  if (!ctx || !gbytes_per_s) return 1;
+  if (bytes < (1ull << 20) || bytes > (64ull << 30)) return fail(ctx, "srt_measure_gather: 1 MiB .. 64 GiB");
+  CU(ctx, cudaSetDevice(ctx->device));
+  const uint32_t n_records = (uint32_t)std::min<uint64_t>(bytes / 64, 0xFFFFFFFFull);
+  void* data = nullptr;
+  uint32_t* sink = nullptr;
+  CU(ctx, cudaMalloc(&data, (size_t)n_records * 64));
+  cudaError_t e = cudaMalloc(&sink, 4);
+  if (e != cudaSuccess) { cudaFree(data); return fail(ctx, "srt_measure_gather: %s", cudaGetErrorString(e)); }
+  cudaMemsetAsync(data, 0x5A, (size_t)n_records * 64, ctx->stream);
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+  const int blocks = sms * 16;
+  const uint32_t iters = 2048;
+  cudaEvent_t a, b;
+  cudaEventCreate(&a); cudaEventCreate(&b);
+  launch_gather_probe(data, n_records, 64, chase, sink, blocks, ctx->stream);  // warm-up
+  cudaEventRecord(a, ctx->stream);
+  e = launch_gather_probe(data, n_records, iters, chase, sink, blocks, ctx->stream);
+  cudaEventRecord(b, ctx->stream);
+  cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
+  float ms = 0.0f;
+  cudaEventElapsedTime(&ms, a, b);
+  cudaEventDestroy(a); cudaEventDestroy(b);
+  cudaFree(data); cudaFree(sink);
+  ctx->kernel_launches += 2;
+  if (e != cudaSuccess || e2 != cudaSuccess) return fail(ctx, "srt_measure_gather: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+  *gbytes_per_s = (double)blocks * 64.0 * iters * 64.0 / (ms * 1e-3) / 1e9;
+  return 0;
+}
+
 extern "C" int srt_eval_detmath(srt_ctx* ctx, int which, const float* x, const float* y, float* out, uint32_t n) {
   if (!ctx) return 1;
   if (n == 0) return 0;

@@ -485,6 +485,33 @@ cudaError_t launch_trace_rays(const DeviceScene& sc, int mode, int stack_cap, co
   return cudaGetLastError();
 }
 
+// Roofline denominator for a scene far larger than L2 (the soup): what this GPU delivers for RANDOM 64 B records -- the
+// size of a NodePair -- out of a big array, with the trace kernel's launch shape (64-thread CTAs, 16 per SM).
+// chase = 1: every address depends on the record before it (a traversal's node -> child chain);
+// chase = 0: addresses come from a counter hash, as many loads in flight as the hardware takes.
+__global__ void __launch_bounds__(64)
+gather_probe_kernel(const uint4* __restrict__ data, uint32_t n_records, uint32_t iters, int chase, uint32_t* __restrict__ sink) {
+  uint32_t idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u;
+  uint32_t acc = 0;
+  for (uint32_t k = 0; k < iters; ++k) {
+    idx = (idx ^ (idx >> 15)) * 2246822519u;
+    idx = (idx ^ (idx >> 13)) * 3266489917u;
+    const uint32_t r = (uint32_t)(((unsigned long long)(idx ^ (idx >> 16)) * n_records) >> 32);
+    const uint4* p = data + (size_t)r * 4;
+    const uint4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3);
+    const uint32_t x = a.x ^ b.y ^ c.z ^ d.w;
+    acc += x;
+    idx = chase ? (idx + x) : (idx + k);
+  }
+  if (acc == 0x9E3779B9u) sink[0] = acc;  // keeps the loads alive
+}
+
+cudaError_t launch_gather_probe(const void* data, uint32_t n_records, uint32_t iters, int chase, uint32_t* sink, int blocks,
+                                cudaStream_t stream) {
+  gather_probe_kernel<<<blocks, 64, 0, stream>>>(static_cast<const uint4*>(data), n_records, iters, chase, sink);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_detmath(int which, const float* x, const float* y, float* out, uint32_t n, cudaStream_t stream) {
   if (n == 0) return cudaSuccess;
   detmath_kernel<<<(n + 255) / 256, 256, 0, stream>>>(which, x, y, out, n);
