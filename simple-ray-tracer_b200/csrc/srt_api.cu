@@ -881,7 +881,7 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
   if (ctx->textures_on && !p.tex) CU(ctx, cudaMalloc(&p.tex, (size_t)ctx->pool_slots * 16));
   if (want_finder && !p.fq) {
     CU(ctx, cudaMalloc(&p.cand, (size_t)ctx->pool_slots * SRT_CAND_MAX * sizeof(uint2)));
-    CU(ctx, cudaMalloc(&p.rlist, (size_t)ctx->pool_slots * 4));
+    CU(ctx, cudaMalloc(&p.rlist, (size_t)ctx->pool_slots * sizeof(uint2)));
     CU(ctx, cudaMalloc(&p.olist, ctx->pool_list_cap * 4));
     CU(ctx, cudaMalloc(&p.fq, sizeof(FinderQueues)));
     CU(ctx, cudaMemsetAsync(p.fq, 0, sizeof(FinderQueues), ctx->stream));

@@ -180,10 +180,10 @@ struct PathPool {
   uint32_t cap;        // slots
   uint32_t list_cap;   // cap + room for the holes the logic warps' chunked reservations can leave
   WaveCounters* q;
-  // hit finder only (null otherwise): per slot SRT_CAND_MAX candidates (triangle | bvh << 26, distance bits), the
-  // list of rays to replay (slot | candidates << 28), the list of rays to trace the long way, their counters
+  // hit finder only (null otherwise): per ENTRY OF THE REPLAY LIST SRT_CAND_MAX candidates (triangle | bvh << 26, distance bits), the
+  // list of rays to replay (slot | candidates << 28, theta bits), the list of rays to trace the long way, their counters
   uint2* cand;
-  uint32_t* rlist;
+  uint2* rlist;
   uint32_t* olist;
   FinderQueues* fq;
   // one fp32 sample per path of the launch, frame-major, summed per pixel in frame order by wf_resolve_kernel

@@ -147,14 +147,16 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
         if (lane == leader) base = atomicAdd(&fq->n_replay, (unsigned int)__popc(m_r));
         base = __shfl_sync(FULL, base, leader);
         if (to_replay) {
-          uint2* dst = pool.cand + (size_t)slot * SRT_CAND_MAX;
+          // the replay's input goes where the replay reads it in order: candidates and list entry by position in
+          // the replay list, not by slot (scattered 64 B records cost 4-5x a sequential read, profiles/r01k_gather_probe)
+          const uint32_t pos = base + (uint32_t)__popc(m_r & lt_mask);
+          uint2* dst = pool.cand + (size_t)pos * SRT_CAND_MAX;
           uint32_t w = 0;
           for (uint32_t k = 0; k < n_cand; ++k) {  // an OUTSIDE ray keeps the candidates within its final theta
             const uint2 c = wf_lds(cand_base + k * cand_step);
             if (!OUTSIDE || !outside || __uint_as_float(c.y) <= tcull) dst[w++] = c;
           }
-          pool.hit[slot] = make_uint2(0u, __float_as_uint((OUTSIDE && outside) ? tcull : inf_()));  // theta, for the replay
-          pool.rlist[base + __popc(m_r & lt_mask)] = slot | (w << 28);
+          pool.rlist[pos] = make_uint2(slot | (w << 28), __float_as_uint((OUTSIDE && outside) ? tcull : inf_()));  // .y: theta
         }
       }
       const unsigned m_o = __ballot_sync(FULL, to_over);
@@ -298,15 +300,15 @@ __global__ void __launch_bounds__(128, SRT_WF_REPLAY_MIN_BLOCKS)
 wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool) {
   const uint32_t n = pool.fq->n_replay;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t entry = pool.rlist[i];
-    const uint32_t slot = entry & 0x0FFFFFFFu, n_cand = entry >> 28;
+    const uint2 entry = pool.rlist[i];
+    const uint32_t slot = entry.x & 0x0FFFFFFFu, n_cand = entry.x >> 28;
     const float4 ra = pool.ray[2 * (size_t)slot], rb = pool.ray[2 * (size_t)slot + 1];
     const V3 ray_o = v3(ra.x, ra.y, ra.z), ray_d = v3(rb.x, rb.y, rb.z);
     const bool any_hit = (__float_as_uint(rb.w) & 0xFFu) == SRT_WF_KIND_SHADOW;
     // candidates: (triangle | bvh << 26, distance); keys = bvh << 26 | visiting rank (ranks stay below 2^26 with the finder)
     uint32_t c_tri[SRT_CAND_MAX], c_key[SRT_CAND_MAX];
     float c_t[SRT_CAND_MAX];
-    const uint2* src = pool.cand + (size_t)slot * SRT_CAND_MAX;
+    const uint2* src = pool.cand + (size_t)i * SRT_CAND_MAX;
 #pragma unroll
     for (int k = 0; k < SRT_CAND_MAX; ++k) {
       if (k < (int)n_cand) {
@@ -321,7 +323,7 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
         c_key[k] = 0xFFFFFFFFu;
       }
     }
-    const float theta = __uint_as_float(pool.hit[slot].y);  // +inf unless wf_find_kernel dropped candidates beyond it
+    const float theta = __uint_as_float(entry.y);  // +inf unless wf_find_kernel dropped candidates beyond it
     bool uncertain = false;
     float best = ra.w;       // the shader's inout intersection_distance
     uint32_t hit = SRT_NO_HIT;
