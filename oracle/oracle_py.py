@@ -64,6 +64,24 @@ def lib():
     return _lib
 
 
+_ref_lib = None
+SHADER_REF_PATH = os.path.join(HERE, "_ref", "libshader_ref.so")
+
+
+def shader_ref_available():
+    """True when oracle/_ref/libshader_ref.so (the reference's own shader text compiled as C++, oracle/shader_ref.cpp)
+    has been built -- in the build container from /root/reference, on the GPU box from the prebuilt file."""
+    return os.path.exists(SHADER_REF_PATH)
+
+
+def ref_lib():
+    global _ref_lib
+    if _ref_lib is None:
+        _ref_lib = C.CDLL(SHADER_REF_PATH)
+        _ref_lib.shader_ref_render.restype = C.c_int
+    return _ref_lib
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
@@ -81,8 +99,10 @@ def make_params(width, height, cam, show_model, accum_frames=1, light_count=0, b
 
 
 def render(params, n_frames, scene, noise_unit, noise_uniform, lights, accum=None, want_out=True, want_ids=True,
-           rows=None, n_threads=0):
-    """Returns (accum[H,W,4] f32, out[H,W,4] u8 or None, ids[H,W] u32 or None, counters dict)."""
+           rows=None, n_threads=0, impl="oracle"):
+    """Returns (accum[H,W,4] f32, out[H,W,4] u8 or None, ids[H,W] u32 or None, counters dict).
+    impl = "oracle": the hand-written restatement (shader_oracle.cpp); "shader_ref": the reference's shader text
+    compiled as C++ (shader_ref.cpp) -- same signature, same decrees."""
     W, H = params.width, params.height
     if accum is None:
         accum = np.zeros((H, W, 4), np.float32)  # decree Q8
@@ -92,13 +112,14 @@ def render(params, n_frames, scene, noise_unit, noise_uniform, lights, accum=Non
     y0, y1 = rows if rows else (0, H)
     s = scene or {}
     lights = np.ascontiguousarray(lights)
-    rc = lib().oracle_render(C.byref(params), C.c_int(n_frames), _p(s.get("bvhs")), _p(s.get("nodes")),
-                             _p(s.get("materials")), _p(s.get("triangles")), _p(s.get("vertices")),
-                             _p(noise_unit), _p(noise_uniform), _p(lights), C.c_int(len(lights)),
-                             _p(accum), _p(out), _p(ids), C.c_int(y0), C.c_int(y1), C.c_int(n_threads),
-                             C.byref(cnt))
+    fn = lib().oracle_render if impl == "oracle" else ref_lib().shader_ref_render
+    rc = fn(C.byref(params), C.c_int(n_frames), _p(s.get("bvhs")), _p(s.get("nodes")),
+            _p(s.get("materials")), _p(s.get("triangles")), _p(s.get("vertices")),
+            _p(noise_unit), _p(noise_uniform), _p(lights), C.c_int(len(lights)),
+            _p(accum), _p(out), _p(ids), C.c_int(y0), C.c_int(y1), C.c_int(n_threads),
+            C.byref(cnt))
     if rc != 0:
-        raise RuntimeError("oracle_render failed: %d" % rc)
+        raise RuntimeError("%s render failed: %d" % (impl, rc))
     return accum, out, ids, cnt.as_dict()
 
 

@@ -13,10 +13,17 @@
 // Reference behaviour that is undefined is pinned by the decrees of SURVEY.md section 9 (Q1, Q2, Q7, Q8,
 // Q9, Q10), each marked "DECREE" below.
 //
-// PARITY STATUS: the shader cannot run on this box (no GL stack) and the reference's own tests for this
-// path are disabled and stale, so the shading half of this oracle is "parity unpinned"
-// by the reference; the scene half (OBJ -> BVH -> flattened arrays) IS pinned against the reference's
-// own C++ compiled in oracle/_ref (see oracle/Makefile, tests/test_scene_golden.py).
+// PARITY STATUS: PINNED to the reference's own shader text.  The shader cannot run through a graphics API on this box
+// (no GL stack), but its five .glsl files compile as C++ after a mechanical text transform: oracle/Makefile builds
+// oracle/_ref/libshader_ref.so from /root/reference/shaders/*.glsl where they lie (oracle/glsl_to_cpp.py,
+// oracle/shader_ref.cpp, oracle/shim/glsl/glsl_shim.h), and tests/test_shader_ref.py demands that THIS file produces the
+// same bits -- accumulation image, RGBA8 image, primary ids, segment / shadow-ray / box / triangle / noise-fetch
+// counts -- on BASELINE.json configs[0] (spheres 640x480x1), Rubik 640x360x4, the 20 k-triangle soup at depth 8 and a
+// two-model scene; tests/golden/shader_ref_frames.npz carries compiled-shader frames to machines without
+// /root/reference (tests/test_oracle_golden.py).  What both sides share on purpose is the decree for what GLSL leaves
+// undefined (srt_detmath.h, Q1/Q2/Q7-Q10).  The scene half (OBJ -> BVH -> flattened arrays) is pinned against the
+// reference's own C++ compiled in oracle/_ref as well (tests/test_host_loader.py), and so are the host-made inputs
+// (noise tables, camera basis: tests/test_host_inputs.py).
 //
 // Build: g++ -O2 -ffp-contract=off -mavx2 -mfma -pthread -shared -fPIC (oracle/Makefile).  Rows are handed to
 // std::thread workers through an atomic counter (dynamic schedule); no OpenMP dependency.

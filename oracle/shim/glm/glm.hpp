@@ -22,12 +22,13 @@ struct vec3 {
   union { float z, b; };
   vec3() = default;
   explicit vec3(float v) : x(v), y(v), z(v) {}
-  vec3(float a, float b_, float c) : x(a), y(b_), z(c) {}
-  vec3(double a, double b_, double c) : x((float)a), y((float)b_), z((float)c) {}
+  template <class A, class B, class C>  // glm converts each scalar argument on its own
+  vec3(A a, B b_, C c) : x((float)a), y((float)b_), z((float)c) {}
   float& operator[](int i) { return i == 0 ? x : (i == 1 ? y : z); }
   const float& operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
   vec3& operator+=(const vec3& o) { x += o.x; y += o.y; z += o.z; return *this; }
   vec3& operator-=(const vec3& o) { x -= o.x; y -= o.y; z -= o.z; return *this; }
+  vec3& operator*=(float s) { x *= s; y *= s; z *= s; return *this; }
 };
 struct vec4 {
   float x, y, z, w;
@@ -66,4 +67,15 @@ inline vec3 cross(const vec3& a, const vec3& b) {
 inline float length(const vec3& a) { return std::sqrt(dot(a, a)); }
 inline vec3 normalize(const vec3& a) { float i = 1.0f / std::sqrt(dot(a, a)); return a * i; }
 inline float radians(float d) { return d * 0.01745329251994329576923690768489f; }
+// used by the reference's camera (src/raytracer/camera.cpp) and noise helpers (include/common/utils.h)
+inline vec3 operator/(const vec3& a, const vec3& b) { return vec3(a.x / b.x, a.y / b.y, a.z / b.z); }
+inline vec3 operator*(int s, const vec3& a) { return vec3((float)s * a.x, (float)s * a.y, (float)s * a.z); }
+inline float length2(const vec3& a) { return dot(a, a); }
+inline float max(float a, float b) { return a < b ? b : a; }
+inline float min(float a, float b) { return b < a ? b : a; }
+inline float abs(float a) { return std::fabs(a); }
+inline float clamp(float v, float lo, float hi) { return min(max(v, lo), hi); }
+inline float pow(float a, int e) { return std::pow(a, (float)e); }
+inline vec3 reflect(const vec3& I, const vec3& N) { return I - N * dot(N, I) * 2.0f; }
+template <class T> inline T pi() { return (T)3.14159265358979323846264338327950288; }
 }  // namespace glm

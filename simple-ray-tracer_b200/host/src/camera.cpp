@@ -35,10 +35,18 @@ void Camera::Reset() {
 
 // front from the two angles, right/up re-derived against the fixed world up (camera.cpp:120-136).  With
 // yaw = -90 the x component is cos(-pi/2) in fp32 (about -4.37e-8), not 0; the shader sees that value.
+//
+// The reference writes `cos(glm::radians(yaw)) * cos(glm::radians(pitch))` with UNQUALIFIED cos/sin: under libstdc++
+// that is ::cos(double), so the angle (a float) is widened, both factors and their product are doubles, and the
+// result is rounded to float once, on assignment.  Spelled out here so that it does not depend on which headers
+// happen to put float overloads into the global namespace (tests/test_host_inputs.py holds the four vectors to the
+// reference's own camera.cpp compiled by the test infrastructure, bit for bit).
 void Camera::UpdateCameraVectors() {
-  const float cy = std::cos(glm::radians(yaw_)), sy = std::sin(glm::radians(yaw_));
-  const float cp = std::cos(glm::radians(pitch_)), sp = std::sin(glm::radians(pitch_));
-  front_ = glm::normalize(glm::vec3(cy * cp, sp, sy * cp));
+  const double ry = (double)glm::radians(yaw_), rp = (double)glm::radians(pitch_);
+  const float fx = (float)(::cos(ry) * ::cos(rp));
+  const float fy = (float)::sin(rp);
+  const float fz = (float)(::sin(ry) * ::cos(rp));
+  front_ = glm::normalize(glm::vec3(fx, fy, fz));
   right_ = glm::normalize(glm::cross(front_, glm::vec3(0.0f, 1.0f, 0.0f)));
   up_ = glm::normalize(glm::cross(right_, front_));
 }

@@ -56,8 +56,7 @@ void RayTracer::Render() {
     // UpdateNoiseTex (src/main.cpp:269-279): all unit vectors first, then all uniforms, from std::rand()
     noise_unit_.resize(texels);
     noise_uniform_.resize(texels);
-    for (glm::vec3& v : noise_unit_) v = Common::randomUnitVector();
-    for (glm::vec3& v : noise_uniform_) v = Common::randomVec3(0.0f, 1.0f);
+    Common::fillNoiseTables(noise_unit_, noise_uniform_);
   }
 
   compute_ = std::make_unique<Graphics::Compute>("./shaders/raytrace_compute.glsl", device_);

@@ -119,8 +119,7 @@ int main(int argc, char** argv) {
     } else {
       // UpdateNoiseTex (src/main.cpp:269-279): every unit vector first, then every uniform triple
       std::srand(o.seed);
-      for (glm::vec3& v : noise) v = Common::randomUnitVector();
-      for (glm::vec3& v : noise_uniform) v = Common::randomVec3(0.0f, 1.0f);
+      Common::fillNoiseTables(noise, noise_uniform);
     }
     compute.UploadNoise(noise.data(), noise_uniform.data(), static_cast<Graphics::uint>(texels));
 

@@ -1,10 +1,12 @@
 """CPU tests of the oracle itself: committed golden frames, schedule independence, continuation.
 
-The oracle (oracle/shader_oracle.cpp) is the checker of every GPU parity test, so it is pinned here first:
-against the golden frames of tests/golden/oracle_frames.npz (made by tests/golden/make_oracle_golden.py; "parity
-unpinned" by the reference, whose shader cannot run on this box and whose own tests do not pin the path) and against
+The oracle (oracle/shader_oracle.cpp) is the checker of every GPU parity test, so it is pinned here first: against
+tests/golden/shader_ref_frames.npz -- frames rendered by THE REFERENCE'S OWN SHADER TEXT compiled as C++
+(oracle/_ref/libshader_ref.so, made from /root/reference/shaders/*.glsl by oracle/Makefile; fixtures written by
+tests/golden/make_shader_ref_golden.py so that this test also runs where /root/reference is absent) -- and against
 properties the shader guarantees: pixels are independent (any row split / thread count gives the same bits) and
 frames accumulate in order (rendering frames 1..2 then 3..4 on the same buffer equals rendering 1..4).
+tests/test_shader_ref.py makes the same comparison live, at larger sizes, where the compiled shader is present.
 """
 import os
 import sys
@@ -15,12 +17,12 @@ import pytest
 import scenes
 
 sys.path.insert(0, os.path.join(scenes.ROOT, "tests", "golden"))
-import make_oracle_golden as G  # noqa: E402
+import make_shader_ref_golden as G  # noqa: E402
 
 
 @pytest.fixture(scope="module")
 def golden():
-    return np.load(os.path.join(scenes.GOLDEN, "oracle_frames.npz"))
+    return np.load(os.path.join(scenes.GOLDEN, "shader_ref_frames.npz"))
 
 
 def bits(a):
@@ -34,7 +36,7 @@ def test_oracle_reproduces_golden_frames(oracle, golden, name):
     assert np.array_equal(ids, golden[name + "/ids"])
     assert np.array_equal(bits(acc), bits(golden[name + "/accum"]))
     assert np.array_equal(out, golden[name + "/out"])
-    assert [cnt["segments"], cnt["shadow_rays"], cnt["nodes"], cnt["tris"]] == golden[name + "/rays"].tolist()
+    assert [cnt[k] for k in G.COUNTERS] == golden[name + "/rays"].tolist()
     assert cnt["capped_paths"] == 0
 
 
