@@ -189,10 +189,19 @@ int srt_reset_counters(srt_ctx* ctx);
 int srt_get_finder_info(srt_ctx* ctx, int32_t* active, double* cost_reference, double* cost_finder);
 
 /* Measurement aid (no reference call site): bytes per second this GPU delivers for RANDOM 64-byte records -- the size of a
- * device BVH node pair -- gathered from an array of `bytes` (choose it far above the 126 MB L2), with the trace kernel's
- * launch shape.  chase = 1: each address depends on the record loaded before (a traversal's node -> child chain);
- * chase = 0: independent addresses.  The roofline denominators for the HBM-bound configuration (configs[4]). */
+ * device BVH node pair -- gathered from an array of `bytes`, with the trace kernel's launch shape.  The array size
+ * picks the level measured: <= 64 KiB stays in every SM's L1 (Rubik's 70 KB scene), 16-64 MiB in the 126 MB L2
+ * (the stand-in's 8 MB scene, the noise tables), far above 126 MB is HBM (configs[4]).  16 KiB .. 64 GiB.
+ * chase = 1: each address depends on the record loaded before (a traversal's node -> child chain);
+ * chase = 0: independent addresses.  These are the roofline denominators bench.py quotes. */
 int srt_measure_gather(srt_ctx* ctx, uint64_t bytes, int32_t chase, double* gbytes_per_s);
+
+/* Measurement aid (no reference call site): thread-instructions per second of UN-FUSED fp32 arithmetic on this GPU
+ * (the library is built -fmad=false: the numeric decree allows only explicit fma, so box and triangle tests are FADD /
+ * FMUL / FMNMX, not FFMA).  mix 0 = FMUL + FADD, mix 1 = FMUL + FADD + 2 FMNMX (the slab test's proportions).  One
+ * fp32 operation per thread-instruction: the result is also the FP32 op/s roof for such code.  Nominal: 148 SMs x 4
+ * sub-partitions x 32 lanes x clock. */
+int srt_measure_issue(srt_ctx* ctx, int32_t mix, double* thread_ginst_per_s);
 
 /* Device-side evaluation of the numeric decree (srt_detmath.h), for bit-for-bit checks against the host:
  * which: 0 = sin, 1 = cos, 2 = pow(x, 1/2.4), 3 = randFloat(x, y[i]) (y required), 4 = linearToSrgb. */

@@ -34,7 +34,7 @@ EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
            "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_build_bvh", "srt_set_texture",
-           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_version"]
+           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_measure_issue", "srt_version"]
 
 
 class Params(C.Structure):  # srt_params, include/srt_types.h
@@ -241,6 +241,12 @@ class Context:
         """GB/s of random 64 B record gathers from an n_bytes array (see srt_measure_gather)."""
         g = C.c_double()
         self._ck(self._lib.srt_measure_gather(self._h, C.c_uint64(n_bytes), C.c_int32(1 if chase else 0), C.byref(g)))
+        return g.value
+
+    def measure_issue(self, mix):
+        """Thread-instructions per second (in units of 1e9) of un-fused fp32 arithmetic (see srt_measure_issue)."""
+        g = C.c_double()
+        self._ck(self._lib.srt_measure_issue(self._h, C.c_int32(mix), C.byref(g)))
         return g.value
 
     def reset_counters(self):

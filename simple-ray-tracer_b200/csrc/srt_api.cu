@@ -1274,7 +1274,7 @@ extern "C" int srt_reset_counters(srt_ctx* ctx) {
 
 extern "C" int srt_measure_gather(srt_ctx* ctx, uint64_t bytes, int32_t chase, double* gbytes_per_s) {
   if (!ctx || !gbytes_per_s) return 1;
-  if (bytes < (1ull << 20) || bytes > (64ull << 30)) return fail(ctx, "srt_measure_gather: 1 MiB .. 64 GiB");
+  if (bytes < (16ull << 10) || bytes > (64ull << 30)) return fail(ctx, "srt_measure_gather: 16 KiB .. 64 GiB");
   CU(ctx, cudaSetDevice(ctx->device));
   const uint32_t n_records = (uint32_t)std::min<uint64_t>(bytes / 64, 0xFFFFFFFFull);
   void* data = nullptr;
@@ -1301,6 +1301,33 @@ extern "C" int srt_measure_gather(srt_ctx* ctx, uint64_t bytes, int32_t chase, d
   ctx->kernel_launches += 2;
   if (e != cudaSuccess || e2 != cudaSuccess) return fail(ctx, "srt_measure_gather: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
   *gbytes_per_s = (double)blocks * 64.0 * iters * 64.0 / (ms * 1e-3) / 1e9;
+  return 0;
+}
+
+extern "C" int srt_measure_issue(srt_ctx* ctx, int32_t mix, double* thread_ginst_per_s) {
+  if (!ctx || !thread_ginst_per_s) return 1;
+  if (mix != 0 && mix != 1) return fail(ctx, "srt_measure_issue: mix 0 or 1");
+  CU(ctx, cudaSetDevice(ctx->device));
+  float* sink = nullptr;
+  CU(ctx, cudaMalloc(&sink, 4));
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+  const int blocks = sms * 8;  // 8 x 256 threads = 64 warps per SM
+  const uint32_t iters = 1u << 14;
+  cudaEvent_t a, b;
+  cudaEventCreate(&a); cudaEventCreate(&b);
+  launch_issue_probe(mix, 256, blocks, sink, ctx->stream);  // warm-up
+  cudaEventRecord(a, ctx->stream);
+  cudaError_t e = launch_issue_probe(mix, iters, blocks, sink, ctx->stream);
+  cudaEventRecord(b, ctx->stream);
+  cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
+  float ms = 0.0f;
+  cudaEventElapsedTime(&ms, a, b);
+  cudaEventDestroy(a); cudaEventDestroy(b);
+  cudaFree(sink);
+  ctx->kernel_launches += 2;
+  if (e != cudaSuccess || e2 != cudaSuccess) return fail(ctx, "srt_measure_issue: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+  *thread_ginst_per_s = (double)blocks * 256.0 * (double)iters * 8.0 * (mix == 1 ? 4.0 : 2.0) / (ms * 1e-3) / 1e9;
   return 0;
 }
 
