@@ -37,7 +37,11 @@ typedef struct srt_counters {
 #define SRT_OPT_TRAVERSAL 1      /* 0 = the shader's visiting order everywhere (bit-exact by construction)
                                     1 = nearer child first where neither child's box contains the ray origin, the
                                         shader's order elsewhere (default; same hits bar documented grazing ties) */
-#define SRT_OPT_COUNT_TRAVERSAL 2 /* 1 = count nodes/tris (slower; for the roofline figures) */
+#define SRT_OPT_COUNT_TRAVERSAL 2 /* for the roofline figures (slower; the tail kernel is not used while counting):
+                                     1 = count the box / triangle tests of the SHADER's walk (every ray through the
+                                         reference BVH in its visiting order; the hit finder is switched off)
+                                     2 = count the box / triangle tests the DEFAULT path really executes (hit finder +
+                                         replay + overflow walk, primary cull) */
 #define SRT_OPT_L2_PERSIST 3     /* 1 = pin BVH top levels + noise tables in L2 with an access-policy window (default 1) */
 #define SRT_OPT_BLOCK_THREADS 4  /* threads per block of the path kernel (multiple of 32) */
 #define SRT_OPT_SCHEDULE 5       /* 0 = one path at a time per lane (the shader's schedule)

@@ -95,7 +95,7 @@ struct srt_ctx {
 
   // options
   int traversal = TRAV_ORDERED;
-  bool count_traversal = false;
+  int count_traversal = 0;  // SRT_OPT_COUNT_TRAVERSAL: 0 off, 1 the shader's walk (finder off), 2 what the default path executes
   bool l2_persist = true;
   int block_threads = 64;
   int schedule = SCHED_WAVEFRONT;
@@ -231,7 +231,10 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
       if (value != TRAV_REFERENCE && value != TRAV_ORDERED) return fail(ctx, "SRT_OPT_TRAVERSAL: 0 or 1");
       ctx->traversal = value;
       return 0;
-    case SRT_OPT_COUNT_TRAVERSAL: ctx->count_traversal = value != 0; return 0;
+    case SRT_OPT_COUNT_TRAVERSAL:
+      if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_COUNT_TRAVERSAL: 0, 1 or 2");
+      ctx->count_traversal = value;
+      return 0;
     case SRT_OPT_L2_PERSIST: ctx->l2_persist = value != 0; return 0;
     case SRT_OPT_BLOCK_THREADS:
       if (value < 32 || value > SRT_MAX_BLOCK_THREADS || value % 32) return fail(ctx, "SRT_OPT_BLOCK_THREADS: 32..%d, multiple of 32", SRT_MAX_BLOCK_THREADS);
@@ -858,7 +861,7 @@ int check_ready(srt_ctx* ctx) {
 namespace {
 
 bool finder_active(const srt_ctx* ctx) {
-  return ctx->finder_ready && !ctx->count_traversal && (ctx->finder_mode == 1 || (ctx->finder_mode == 2 && ctx->finder_worthwhile));
+  return ctx->finder_ready && ctx->count_traversal != 1 && (ctx->finder_mode == 1 || (ctx->finder_mode == 2 && ctx->finder_worthwhile));
 }
 
 int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_finder) {

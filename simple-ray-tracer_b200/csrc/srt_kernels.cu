@@ -340,12 +340,12 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
 namespace {
 // the trace step through the hit finder (srt_wf_find.cuh): candidates, then the replay of the shader's culls, then the
 // rays with too many candidates (or a replay that could not be sure) the long way
-template <bool OUTSIDE>
+template <bool OUTSIDE, bool COUNT>
 cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
                            DeviceCounters* counters, int block, cudaStream_t stream) {
   static int per_sm = 0, sms = 0;
   static size_t smem_set = 0;
-  auto k = wf_find_kernel<OUTSIDE>;
+  auto k = wf_find_kernel<OUTSIDE, COUNT>;
   const size_t smem = (size_t)fp.stack_cap * SRT_WF_FIND_THREADS * 4u + (size_t)SRT_CAND_MAX * SRT_WF_FIND_THREADS * 8u;
   cudaError_t e;
   if (per_sm == 0 || smem_set != smem) {
@@ -363,17 +363,17 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
   long need = ((long)pool.cap / 32 + 1) / 2;
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  k<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill > 0 ? refill : SRT_WF_FIND_REFILL);
+  k<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill > 0 ? refill : SRT_WF_FIND_REFILL, counters);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   long blocks = ((long)pool.cap + 127) / 128;
   if (blocks > (long)sms * 16) blocks = (long)sms * 16;
-  wf_replay_kernel<<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool);
+  wf_replay_kernel<COUNT><<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool, counters);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   PathPool over = pool;  // the overflow list (the replay may have added to it), seen through the trace kernel's own interface
   over.q = &pool.fq->over;
   over.list[0] = pool.olist;
   over.list[1] = pool.olist;
-  if ((e = wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, over, 0, refill, counters, block, stream)) != cudaSuccess) return e;
+  if ((e = wf_trace_launch<TRAV_REFERENCE, COUNT>(sc, fp, over, 0, refill, counters, block, stream)) != cudaSuccess) return e;
   return cudaGetLastError();
 }
 }  // namespace
@@ -383,9 +383,11 @@ cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const P
                            cudaEvent_t after_trace, int finder) {
   cudaError_t e;
   if (finder == 2)  // a wave that may hold camera rays
-    e = wf_find_launch<true>(sc, fp, pool, parity, refill, counters, block, stream);
+    e = count ? wf_find_launch<true, true>(sc, fp, pool, parity, refill, counters, block, stream)
+              : wf_find_launch<true, false>(sc, fp, pool, parity, refill, counters, block, stream);
   else if (finder)
-    e = wf_find_launch<false>(sc, fp, pool, parity, refill, counters, block, stream);
+    e = count ? wf_find_launch<false, true>(sc, fp, pool, parity, refill, counters, block, stream)
+              : wf_find_launch<false, false>(sc, fp, pool, parity, refill, counters, block, stream);
   else if (mode == TRAV_REFERENCE)
     e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, refill, counters, block, stream)
               : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, refill, counters, block, stream);

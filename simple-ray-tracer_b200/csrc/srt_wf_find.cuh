@@ -62,9 +62,12 @@ __device__ __forceinline__ bool wf_find_box_t(V3 o, V3 inv, float tmax, float mn
 
 // OUTSIDE = false: the kernel without the outside-ray handling (every ray walks the finder tree without distance
 // culling, as an inside ray does either way); the host uses it for the waves that cannot hold camera rays.
-template <bool OUTSIDE>
+// COUNT (SRT_OPT_COUNT_TRAVERSAL = 2, bench.py's untimed pass): box and triangle tests this kernel really executes go to
+// counters->nodes / counters->tris -- the work behind the roofline's FP32-issue figure.
+template <bool OUTSIDE, bool COUNT>
 __global__ void __launch_bounds__(SRT_WF_FIND_THREADS, SRT_WF_FIND_MIN_BLOCKS)
-wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity, int refill_threshold) {
+wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity, int refill_threshold,
+               DeviceCounters* __restrict__ counters) {
   extern __shared__ uint32_t s_find[];  // [stack_cap][64] node references, then [SRT_CAND_MAX][64] candidates (8 B)
   const uint32_t sp_base = (uint32_t)__cvta_generic_to_shared(s_find + threadIdx.x);
   constexpr uint32_t sp_step = SRT_WF_FIND_THREADS * 4u;
@@ -83,6 +86,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
     q->n_shadow[parity ^ 1] = 0;
   }
 
+  unsigned int n_nodes = 0, n_tris = 0;
   bool trav = false, pending = false, overflow = false;
   uint32_t slot = 0, cur = 0, bvh_i = 0, n_cand = 0;
   V3 to = v3(0.0f), td = v3(0.0f), inv = v3(0.0f);
@@ -112,9 +116,17 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
       const float pad = bvh->finder_pad;
       tcull = tmax;
-      outside = OUTSIDE && fp.bvh_count == 1u && (to.x < bvh->root_min[0] || to.x > bvh->root_max[0] || to.y < bvh->root_min[1] ||
-                                       to.y > bvh->root_max[1] || to.z < bvh->root_min[2] || to.z > bvh->root_max[2]);
+      // An axis-parallel ray (a zero direction component: 1/0 = inf) is NOT handled as an outside ray: where its origin
+      // lies on a slab plane of a node the shader's IntersectsBox turns 0 * inf = NaN into a cull (Q17), so the shader
+      // may pass over the nearest triangle and accept a farther one -- its culls are then no closest-hit culls, and
+      // dropping candidates beyond theta would drop the one it accepts (tests/test_adversarial_gpu.py found exactly
+      // that).  Such a ray collects every candidate like an inside ray and the replay applies the NaN culls exactly.
+      const bool finite_inv = fabsf(inv.x) < inf_() && fabsf(inv.y) < inf_() && fabsf(inv.z) < inf_();  // false for NaN too
+      outside = OUTSIDE && fp.bvh_count == 1u && finite_inv &&
+                (to.x < bvh->root_min[0] || to.x > bvh->root_max[0] || to.y < bvh->root_min[1] ||
+                 to.y > bvh->root_max[1] || to.z < bvh->root_min[2] || to.z > bvh->root_max[2]);
       if (outside) tpad = 4.0f * pad * rsqrtf(td.x * td.x + td.y * td.y + td.z * td.z);
+      if (COUNT) n_nodes++;
       if (wf_find_box(to, inv, tmax, bvh->root_min[0] - pad, bvh->root_min[1] - pad, bvh->root_min[2] - pad,
                       bvh->root_max[0] + pad, bvh->root_max[1] + pad, bvh->root_max[2] + pad)) {
         cur = bvh->finder_root;
@@ -224,6 +236,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           float tl, tr;
           const bool pl = wf_find_box_t(to, inv, OUTSIDE ? tcull : tmax, na.x, na.y, na.z, na.w, nb.x, nb.y, tl);
           const bool pr = wf_find_box_t(to, inv, OUTSIDE ? tcull : tmax, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, tr);
+          if (COUNT) n_nodes += 2;
           if (pl && pr) {
             const bool left_first = !OUTSIDE || tl <= tr;  // nearer child first: an OUTSIDE ray's theta drops early
             wf_sts1(sp, left_first ? nd.w : nd.z);
@@ -241,6 +254,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           // IntersectsTriangle (ray_intersects.glsl:61-96) against the ray's INITIAL intersection_distance
           const float4* p = reinterpret_cast<const float4*>(sc.ftris + (cur & ~SRT_LEAF_BIT));
           const float4 r0 = __ldg(p), r1 = __ldg(p + 1), r2 = __ldg(p + 2);
+          if (COUNT) n_tris++;
           const V3 edge_1 = v3(r1.x, r1.y, r1.z), edge_2 = v3(r2.x, r2.y, r2.z);
           const V3 h = cross_(td, edge_2);
           const float a = dot_(edge_1, h);
@@ -290,15 +304,28 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       if (!exhausted && n_idle - (32 - lane_cap) >= refill_at) break;
     }
   }
+  if (COUNT) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      n_nodes += __shfl_down_sync(FULL, n_nodes, o);
+      n_tris += __shfl_down_sync(FULL, n_tris, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&counters->nodes, (unsigned long long)n_nodes);
+      atomicAdd(&counters->tris, (unsigned long long)n_tris);
+    }
+  }
 }
 
 // ---- replay: the shader's culls above each candidate, candidates in the shader's visiting order ------------------------
 #ifndef SRT_WF_REPLAY_MIN_BLOCKS
 #define SRT_WF_REPLAY_MIN_BLOCKS 8  // 64 registers (88 B of spills): 1 / 6 / 8 measured 36.56 / 36.38 / 36.25 ms per Rubik step
 #endif
+template <bool COUNT>
 __global__ void __launch_bounds__(128, SRT_WF_REPLAY_MIN_BLOCKS)
-wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool) {
+wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, DeviceCounters* __restrict__ counters) {
   const uint32_t n = pool.fq->n_replay;
+  unsigned int n_nodes = 0;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint2 entry = pool.rlist[i];
     const uint32_t slot = entry.x & 0x0FFFFFFFu, n_cand = entry.x >> 28;
@@ -365,6 +392,7 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
       for (uint32_t node = __ldg(sc.tri_leaf + tri);;) {
         const float4 na = __ldg(&sc.rnodes[node].a), nb = __ldg(&sc.rnodes[node].b);
         const uint32_t first_rank = __float_as_uint(nb.w);
+        if (COUNT) n_nodes++;
         float at_pop = best_in;
 #pragma unroll
         for (int j = 0; j < SRT_CAND_MAX; ++j)
@@ -401,6 +429,7 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
       pool.hit[slot] = make_uint2(hit, __float_as_uint(best));
     }
   }
+  if (COUNT && n_nodes) atomicAdd(&counters->nodes, (unsigned long long)n_nodes);
 }
 
 }  // namespace srt

@@ -83,6 +83,7 @@ int main(int argc,char**argv){
     if(h2!=hit||(hit!=0xFFFFFFFFu&&b2!=best)){if(mism<5)printf("mismatch ray %ld: ref %u %g finder %u %g (cands %zu)\n",it,hit,best,h2,b2,cs.size());mism++;}
     // ---- OUTSIDE mode: origin outside the root box on some axis: nearest-first finder walk with distance culling
     {auto&rn=nodes[bvhs[0].first_index]; bool outside=false; for(int k=0;k<3;++k) if(o[k]<rn.min_bounds[k]||o[k]>rn.max_bounds[k]) outside=true;
+     for(int k=0;k<3;++k) if(!(fabsf(inv[k])<INFINITY)) outside=false;  // axis-parallel rays are not handled as outside rays (srt_wf_find.cuh)
      if(outside){ n_out++;
       const float pad=fo.pad[0]; const float tpad=4.0f*pad/sqrtf(d[0]*d[0]+d[1]*d[1]+d[2]*d[2]);
       float tcull=tmax; std::vector<C> k2;
