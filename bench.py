@@ -125,24 +125,34 @@ def workload_inputs(name, soup_tris=10_000_000):
             "lights": scenes.model_lights() if show_model else scenes.sphere_lights(), "cam": cam}
 
 
+def cpu_kind():
+    """("reference", "shader_ref") when oracle/_ref/libshader_ref.so -- the reference's OWN shader text compiled as C++
+    (oracle/shader_ref.cpp) -- travelled with the repo, else ("port", "oracle"): the hand-written restatement."""
+    import __graft_entry__ as g
+    O = g.load_oracle()
+    return ("reference", "shader_ref") if O.shader_ref_available() else ("port", "oracle")
+
+
 def oracle_run(inp, first_frame, n_frames, threads=0):
-    """TEST-INFRASTRUCTURE leg: the CPU oracle (oracle/) timed on the host cores.  Returns (Mseg/s, seconds, counters)."""
+    """TEST-INFRASTRUCTURE leg: the reference's CPU implementation of the path (oracle/) timed on the host cores.
+    Returns (Mseg/s, seconds, counters)."""
     import __graft_entry__ as g
     O = g.load_oracle()
     p = O.make_params(inp["W"], inp["H"], inp["cam"], inp["show_model"], first_frame, len(inp["lights"]),
                       1 if inp["show_model"] else 0, inp["max_depth"])
     t0 = time.perf_counter()
     _, _, _, cnt = O.render(p, n_frames, inp["scene"], inp["unit"], inp["uniform"], inp["lights"], want_out=False,
-                            want_ids=False, n_threads=threads)
+                            want_ids=False, n_threads=threads, impl=cpu_kind()[1])
     dt = time.perf_counter() - t0
     return cnt["segments"] / dt / 1e6, dt, cnt
 
 
 def run_reference(args):
-    """--impl reference: the reference's own implementation of the path cannot run here (GLSL, no GL stack), so this
-    arm times the committed CPU restatement of the shader (kind "port") on all host cores; each step is a bounded
-    sample of the workload: as many whole 1920x1080 frames (1 spp each; per-frame cost is stationary) as fit about five
-    seconds, sized from one calibration frame."""
+    """--impl reference: the reference's shader cannot run through a graphics API here (GLSL, no GL stack: "unavailable
+    on this box"), so this arm times its CPU form on all host cores: the reference's own shader text compiled as C++
+    (oracle/_ref/libshader_ref.so, kind "reference") when that file travelled with the repo, else the hand-written
+    restatement pinned to it (kind "port").  Each step is a bounded sample of the workload: as many whole frames (1 spp
+    each; per-frame cost is stationary) as fit about five seconds, sized from one calibration frame."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -158,13 +168,13 @@ def run_reference(args):
         secs += dt
         segs += cnt["segments"]
     value = segs / secs / 1e6
-    sample = "%d frame(s) (1 spp each) of the %d-spp workload per step, whole 1920x1080 image" % (per_step, inp["spp"])
+    sample = "%d frame(s) (1 spp each) of the %d-spp workload per step, whole %dx%d image" % (per_step, inp["spp"], inp["W"], inp["H"])
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": inp["desc"], "step": sample, "host_threads": cores},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": cpu_kind()[0], "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
@@ -302,24 +312,34 @@ def run_gpu(args):
     ms_per_step = total_ms / args.steps
     value = segments / (total_ms * 1e-3) / 1e6
 
-    # ---- traversal work per ray for the roofline's algorithmic bytes: an untimed counting pass (4 frames) in the
-    # SHADER's visiting order (Nn, Nt "as executed by the reference traversal order"); shadow rays stop at
-    # the first accepted triangle here, the shader runs them to the end, so the figure is a lower bound of the shader's
-    nodes_per_ray = tris_per_ray = 0.0
-    if show_model:
-        ctx.set_option(pkg.OPT_TRAVERSAL, pkg.TRAV_REFERENCE)
-        ctx.set_option(pkg.OPT_COUNT_TRAVERSAL, 1)
-        ctx.reset_counters()
-        ctx.set_params(params(1)); ctx.render(1)
-        ctx.set_params(params(0)); ctx.render(4)
-        c2 = ctx.counters()
-        ctx.set_option(pkg.OPT_COUNT_TRAVERSAL, 0)
-        ctx.set_option(pkg.OPT_TRAVERSAL, mode)
-        w2 = torch.tensor([c2["nodes"], c2["tris"], c2["segments"] + c2["shadow_rays"]], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(w2, op=dist.ReduceOp.SUM)
-        n2, t2, r2 = w2.tolist()
-        nodes_per_ray, tris_per_ray = n2 / max(r2, 1), t2 / max(r2, 1)
+    # ---- work per ray for the roofline, from two untimed counting passes over the SAME frames as a timed step:
+    #   reference: box / triangle tests of the SHADER's walk (Nn, Nt "as executed by the reference traversal
+    #              order"; shadow rays stop at the first accepted triangle here, the shader runs them on: a lower bound)
+    #   executed : box / triangle tests the default path really makes (hit finder + replay + overflow walk + primary
+    #              cull; the counting build makes waves to the end instead of the tail kernel, which carries the last
+    #              ~1 % of the rays through the reference BVH)
+    ref_nodes_per_ray = ref_tris_per_ray = exe_nodes_per_ray = exe_tris_per_ray = 0.0
+    culled_per_step = 0.0
+    if show_model and wavefront:
+        def count_pass(kind):
+            ctx.set_option(pkg.OPT_COUNT_TRAVERSAL, kind)
+            if kind == 1:
+                ctx.set_option(pkg.OPT_TRAVERSAL, pkg.TRAV_REFERENCE)
+            ctx.reset_counters()
+            ctx.set_params(params(1)); ctx.render(1)
+            ctx.set_params(params(0)); ctx.render(spp)
+            c = ctx.counters()
+            ctx.set_option(pkg.OPT_COUNT_TRAVERSAL, 0)
+            ctx.set_option(pkg.OPT_TRAVERSAL, mode)
+            w = torch.tensor([c["nodes"], c["tris"], c["segments"] + c["shadow_rays"], c["culled_primaries"]],
+                             dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(w, op=dist.ReduceOp.SUM)
+            return w.tolist()
+        n1, t1, r1, _ = count_pass(1)
+        ref_nodes_per_ray, ref_tris_per_ray = n1 / max(r1, 1), t1 / max(r1, 1)
+        n2, t2, r2, culled_per_step = count_pass(2)
+        exe_nodes_per_ray, exe_tris_per_ray = n2 / max(r2, 1), t2 / max(r2, 1)
 
     # ---- end to end through the C-ABI with host buffers: upload everything, render, (reduce,) read the image back
     out_host = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory().numpy()
@@ -361,52 +381,79 @@ def run_gpu(args):
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel: algorithmic gather bytes per ray over its CUDA-event time
+    # ---- roofline of the kernels that answer rays: which roof binds depends on where the scene lives
     peaks, which = measured_peaks()
     rays = segments + shadow
-    bytes_per_ray = 32.0 * nodes_per_ray + 52.0 * tris_per_ray
     finder_on = bool(show_model and wavefront and ctx.finder_info()[0])
     if wavefront:
-        # wf_trace_kernel does ALL box and triangle tests; its launches of one step differ in size (one per wave), so
-        # bytes per launch and duration per launch are both averages over the timed region's launches
-        # (with the hit finder the same tests are answered by wf_find_kernel + wf_replay_kernel, overflow rays by
-        # wf_trace_kernel; with the primary cull the root-box tests of culled primary rays by wf_init_kernel; the last
-        # paths by wf_tail_kernel: trace_ms brackets them all, shading of the tail included)
-        kname = "wf_find_kernel+wf_replay_kernel (+wf_trace_kernel overflow, wf_init_kernel cull, wf_tail_kernel)" if finder_on else "wf_trace_kernel"
+        # SRT_OPT_TIME_KERNELS brackets every launch that answers rays: wf_init_kernel's cull, wf_find_kernel,
+        # wf_replay_kernel, the overflow wf_trace_kernel, wf_tail_kernel (its shading included); launches of one step
+        # differ in size (one per wave), so per-launch figures are averages over the timed region's launches
+        kname = "wf_find_kernel+wf_replay_kernel (+wf_trace_kernel overflow, wf_init_kernel cull, wf_tail_kernel)" if finder_on else "wf_trace_kernel (+wf_init_kernel cull, wf_tail_kernel)"
         k_ms, k_launches = trace_ms, max(n_waves, 1.0)
     else:
         kname, k_ms, k_launches = "pathtrace_persistent_kernel" if args.schedule == "persistent" else "pathtrace_kernel", kernel_ms, float(args.steps * world)
-    achieved = rays * bytes_per_ray / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
-    scene_mb = 0.0
+    k_s = max(k_ms, 1e-9) * 1e-3
+    scene_mb = finder_mb = 0.0
     if inp["scene"] is not None:
-        scene_mb = (32 * len(inp["scene"]["nodes"]) + 48 * len(inp["scene"]["triangles"])) / 1e6
-    # DRAM bytes per launch of the same kernel from the committed ncu pass over one step's launches (never measured in
-    # this run: numbers taken under a profiler are not bench values; the pass is per workload)
+        n_inner = int((inp["scene"]["nodes"]["count"] == 0).sum())
+        scene_mb = (64 * n_inner + 48 * len(inp["scene"]["triangles"])) / 1e6  # NodePair + TriRecord arrays as the kernels read them
+    # roofs measured now, on this GPU, through the C-ABI (srt_measure_gather / srt_measure_issue)
+    roofs = {"issue_fmul_fadd_Gop_s": ctx.measure_issue(0), "issue_fmul_fadd_2fmnmx_Gop_s": ctx.measure_issue(1),
+             "l1_gather_GBps": ctx.measure_gather(48 << 10, 1), "l2_gather_GBps": ctx.measure_gather(32 << 20, 1),
+             "hbm_gather_GBps": ctx.measure_gather(1 << 30, 1), "hbm_copy_GBps": peaks["hbm_gbs"]}
+    # algorithmic work of the tests the kernels EXECUTE (SURVEY.md 8d per-test figures: 28 fp32 ops per box test, 50 per
+    # triangle test; 32 B per node, 52 B per triangle), and of the shader's own walk for comparison across designs
+    exe_flops_per_ray = 28.0 * exe_nodes_per_ray + 50.0 * exe_tris_per_ray
+    exe_bytes_per_ray = 32.0 * exe_nodes_per_ray + 52.0 * exe_tris_per_ray
+    ref_bytes_per_ray = 32.0 * ref_nodes_per_ray + 52.0 * ref_tris_per_ray
+    achieved_tflops = rays * exe_flops_per_ray / k_s / 1e12
+    achieved_gbs = rays * exe_bytes_per_ray / k_s / 1e9
+    issue_peak_tflops = roofs["issue_fmul_fadd_Gop_s"] * world / 1e3
+    level = "l1" if scene_mb <= 0.2 else ("l2" if scene_mb <= 100.0 else "hbm")
+    mem_peak = {"l1": roofs["l1_gather_GBps"], "l2": roofs["l2_gather_GBps"], "hbm": peaks["hbm_gbs"]}[level] * world
+    frac_issue = achieved_tflops / issue_peak_tflops
+    frac_mem = achieved_gbs / mem_peak
+    # DRAM bytes per launch from the committed ncu pass of this command (never measured in this run: numbers taken under
+    # a profiler are not bench values); one file per workload and build
     traffic, traffic_extra = None, {}
-    tf = os.path.join(ROOT, "profiles", "r01i_trace_dram_bytes.json" if finder_on else "r01f_trace_dram_bytes.json")
-    if wavefront and world == 1 and args.workload == "rubik" and os.path.exists(tf):
+    tf = os.path.join(ROOT, "profiles", "r02_traffic_%s.json" % args.workload)
+    if wavefront and world == 1 and os.path.exists(tf):
         t = json.load(open(tf))
         traffic = t["dram_bytes_per_launch"]
-        traffic_extra = {"traffic_source": "profiles/%s (dram__bytes_read.sum + dram__bytes_write.sum of the kernels that "
-                                           "answer rays, per trace launch as SRT_OPT_TIME_KERNELS counts them, from an ncu "
-                                           "pass of this command)" % os.path.basename(tf),
-                         "l2_bytes_per_launch": t["l2_bytes_per_launch"], "l1_bytes_per_launch": t["l1_bytes_per_launch"]}
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"] * world, "unit": "GB/s",
-                "frac": achieved / (peaks["hbm_gbs"] * world), "traffic": traffic,
-                "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs, burst copy figure, x n_gpus)",
-                "kernel": kname, "kernel_launches": k_launches, "kernel_ms_total": k_ms,
-                "bytes_per_launch": rays * bytes_per_ray / k_launches, "ms_per_launch": k_ms / k_launches,
-                "logic_kernel_ms_total": logic_ms,
-                "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
-                "rays_per_step": rays / args.steps, "scene_mb": scene_mb,
-                "note": "algorithmic bytes = rays x (32 B x nodes box-tested + 52 B x triangles tested), counted in the "
-                        "shader's visiting order; duration = sum of CUDA-event times around the kernel's launches on the "
-                        "launching stream (max over ranks; achieved and peak are whole-job). A scene smaller than the "
-                        "126 MB L2 is served from L1/L2, so the figure is then on-chip gather bandwidth quoted against the "
-                        "HBM copy peak (it may exceed 1), not DRAM traffic; see profiles/ for dram__bytes. With the hit "
-                        "finder the same rays are answered with a fraction of those tests, so the figure is a rate of "
-                        "reference work answered; what binds the kernels is instruction issue (ncu: 68-80 % of issue slots "
-                        "busy at 25-27 of 32 lanes, profiles/r01i_ncu_full_summary.txt)"}
+        algorithmic_dram = (12.0 * W * H + 36.0 * W * H) * spp / max(k_launches / args.steps, 1.0)  # noise gathers + accumulate/output streaming
+        traffic_extra = {"traffic_source": "profiles/%s (dram__bytes_read.sum + dram__bytes_write.sum over the launches of one "
+                                           "step from an ncu pass of this command, divided by the ray-answering launches)" % os.path.basename(tf),
+                         "traffic_per_step": t.get("dram_bytes_per_step"), "traffic_build": t.get("build"),
+                         "wasted_ratio_vs_algorithmic_dram": (t.get("dram_bytes_per_step") or 0.0) / ((12.0 + 36.0) * W * H * spp) if show_model else None}
+    if frac_mem > frac_issue:
+        roofline = {"bound": level if level != "l1" else "l1", "achieved": achieved_gbs, "peak": mem_peak, "unit": "GB/s", "frac": frac_mem}
+    else:
+        roofline = {"bound": "issue", "achieved": achieved_tflops, "peak": issue_peak_tflops, "unit": "TFLOP/s", "frac": frac_issue}
+    roofline.update({
+        "traffic": traffic,
+        "peak_source": ("measured in this run through the C-ABI: srt_measure_issue(FMUL+FADD, un-fused: the library is built "
+                        "-fmad=false) x n_gpus" if roofline["bound"] == "issue" else
+                        ("%s (MEASURED_PEAKS.json hbm_gbs, burst copy figure) x n_gpus" % which if level == "hbm" else
+                         "measured in this run through the C-ABI: srt_measure_gather(%s-resident array, 64 B records) x n_gpus" % level.upper())),
+        "kernel": kname, "kernel_launches": k_launches, "kernel_ms_total": k_ms, "ms_per_launch": k_ms / k_launches,
+        "logic_kernel_ms_total": logic_ms,
+        "frac_issue": frac_issue, "frac_memory": frac_mem, "memory_level": level,
+        "achieved_tflops": achieved_tflops, "achieved_GBps": achieved_gbs,
+        "flops_per_launch": rays * exe_flops_per_ray / k_launches, "bytes_per_launch": rays * exe_bytes_per_ray / k_launches,
+        "executed_per_ray": {"box_tests": exe_nodes_per_ray, "triangle_tests": exe_tris_per_ray,
+                             "flops": exe_flops_per_ray, "bytes": exe_bytes_per_ray},
+        "reference_walk_per_ray": {"box_tests": ref_nodes_per_ray, "triangle_tests": ref_tris_per_ray, "bytes": ref_bytes_per_ray,
+                                   "answered_GBps": rays * ref_bytes_per_ray / k_s / 1e9},
+        "rays_per_step": rays / args.steps, "scene_mb": scene_mb, "roofs": roofs,
+        "note": "achieved = rays x algorithmic work of the box and triangle tests the kernels EXECUTE (28 fp32 ops / 32 B per "
+                "box test, 50 ops / 52 B per triangle test, counted by an untimed pass over the same frames with "
+                "SRT_OPT_COUNT_TRAVERSAL = 2) / sum of CUDA-event durations around every ray-answering launch on the "
+                "launching stream (max over ranks).  Both fractions are reported; the larger names the bound.  frac_issue "
+                "counts only the tests' own arithmetic against the issue rate of un-fused FP32 instructions: address, "
+                "stack, queue and control instructions use the other slots (ncu: profiles/).  reference_walk_per_ray is "
+                "what the shader's own traversal does for the same rays (answered_GBps: reference work answered per "
+                "second, comparable across designs, not bytes moved)."})
     roofline.update(traffic_extra)
 
     cpu_baseline = None
@@ -416,7 +463,7 @@ def run_gpu(args):
             _, t1, _ = oracle_run(inp, 1, 1)
             n_cpu = max(1, min(inp["spp"], int(15.0 / max(t1, 1e-3))))
         v, dt, c = oracle_run(inp, 1, n_cpu)
-        cpu_baseline = {"value": v, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": cpu_kind()[0],
                         "sample": "%d of the workload's %d frames (1 spp each), whole image, %.1f s" % (n_cpu, inp["spp"], dt),
                         "ms_per_frame": dt / n_cpu * 1e3}
 
@@ -424,7 +471,10 @@ def run_gpu(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": inp["desc"], "traversal": args.traversal, "schedule": args.schedule, "block_threads": args.block,
+        "config": {"workload": inp["desc"], "traversal_requested": args.traversal,
+                   "traversal": "reference (the shader's visiting order: the hit finder answers the rays, and every kernel beside it walks "
+                                "in that order)" if finder_on else args.traversal,
+                   "schedule": args.schedule, "block_threads": args.block,
                    "split": "interleaved 8-row bands over %d GPU(s), NCCL reduce of the fp32 accumulation image to rank 0" % world
                             if world > 1 else "single GPU",
                    "l2": "512 MB device buffer rewritten between timed steps (L2 flush)",
@@ -434,6 +484,11 @@ def run_gpu(args):
                    "ms_per_frame": ms_per_step / spp},
         "segments_per_step": segments / args.steps, "shadow_rays_per_step": shadow / args.steps,
         "mrays_incl_shadow": rays / (total_ms * 1e-3) / 1e6,
+        # `value` counts every CheckHit of the path loop, as the shader and the CPU arm do; most camera rays of this view
+        # miss the model's root box (ended by the primary cull).  The rates of the rays that do reach a BVH:
+        "paths_per_step": paths / args.steps, "culled_primaries_per_step": culled_per_step,
+        "segments_reaching_bvh_per_s_M": (segments / args.steps - culled_per_step) / (ms_per_step * 1e-3) / 1e6,
+        "bounce_segments_per_s_M": (segments - paths) / args.steps / (ms_per_step * 1e-3) / 1e6,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": float(e2.item()) / e2e_steps * 1e3},
         "gpu_launches": gpu_launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,

@@ -31,6 +31,8 @@ typedef struct srt_counters {
   uint64_t kernel_launches; /* kernels launched by this context (all kinds) */
   uint64_t nodes;        /* BVH nodes box-tested   (only counted when SRT_FLAG_COUNT_TRAVERSAL is set) */
   uint64_t tris;         /* triangles tested       (only counted when SRT_FLAG_COUNT_TRAVERSAL is set) */
+  uint64_t culled_primaries; /* camera rays that missed every root box and ended where they were generated
+                                (SRT_OPT_PRIMARY_CULL; only counted when SRT_OPT_COUNT_TRAVERSAL is set) */
 } srt_counters;
 
 /* srt_set_option keys */

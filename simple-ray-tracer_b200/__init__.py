@@ -48,7 +48,7 @@ class Params(C.Structure):  # srt_params, include/srt_types.h
 class Counters(C.Structure):  # srt_counters, include/srt_b200.h
     _fields_ = [("segments", C.c_uint64), ("shadow_rays", C.c_uint64), ("paths", C.c_uint64),
                 ("capped_paths", C.c_uint64), ("kernel_launches", C.c_uint64), ("nodes", C.c_uint64),
-                ("tris", C.c_uint64)]
+                ("tris", C.c_uint64), ("culled_primaries", C.c_uint64)]
 
 
 def build():

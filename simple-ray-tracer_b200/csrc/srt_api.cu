@@ -1235,7 +1235,7 @@ extern "C" int srt_get_counters(srt_ctx* ctx, srt_counters* out) {
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   out->segments = h.segments; out->shadow_rays = h.shadow_rays; out->paths = h.paths;
   out->capped_paths = h.capped_paths; out->kernel_launches = ctx->kernel_launches;
-  out->nodes = h.nodes; out->tris = h.tris;
+  out->nodes = h.nodes; out->tris = h.tris; out->culled_primaries = h.culled;
   return 0;
 }
 

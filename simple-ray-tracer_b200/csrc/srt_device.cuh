@@ -142,6 +142,7 @@ struct FrameParams {
 
 struct DeviceCounters {
   unsigned long long segments, shadow_rays, paths, capped_paths, nodes, tris;
+  unsigned long long culled;  // camera rays ended by the primary cull (counted with SRT_OPT_COUNT_TRAVERSAL only)
   unsigned int next_tile;  // work counter of the persistent kernel (zeroed before each launch)
   unsigned int _pad;
 };

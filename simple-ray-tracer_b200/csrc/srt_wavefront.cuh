@@ -160,6 +160,7 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
         const unsigned long long start = (unsigned long long)blockIdx.x * blockDim.x;
         const uint32_t here = start >= first ? 0u : (first - start < blockDim.x ? (uint32_t)(first - start) : blockDim.x);
         atomicAdd(&counters->nodes, (unsigned long long)(here - total) * fp.bvh_count);
+        atomicAdd(&counters->culled, (unsigned long long)(here - total));
       }
     }
     __syncthreads();
