@@ -5,9 +5,10 @@
 
 A "step" is one pass of the hot path over the workload: 64 progressive frames (64 spp) of the reference's Rubik
 scene at 1920x1080 (BASELINE.json metric "1080p 64spp" on configs[1]'s scene; the Airplane OBJ of configs[2]
-is absent from the reference mount) rendered by ONE kernel launch.  With N GPUs the frame is split by
-interleaved 8-row bands (bit-identical to one GPU) and the fp32 accumulation image is reduced to rank 0 with
-one NCCL reduce per step (strong scaling: total work fixed).
+is absent from the reference mount) rendered by ONE srt_render call (about 36 kernel launches).  With N GPUs the library splits
+the frame itself (srt_group_join; --split bands: interleaved 8-row bands, bit-identical to one GPU, each rank's rows
+gathered on rank 0; --split samples: every rank renders the whole image for 1/N of the frames, one ncclReduce) with one
+NCCL collective per step inside srt_render (strong scaling: total work fixed).
   value : path segments / s, inputs resident in HBM, CUDA events on the launching stream, max over ranks
   e2e   : the same through the C-ABI with HOST buffers: scene + noise + lights + uniforms uploaded, 64 frames
           rendered, (reduced,) RGBA8 image read back -- every step, wall clock, max over ranks
@@ -179,13 +180,6 @@ def run_reference(args):
         "gpu_launches": 0}))
 
 
-class _DevPtr:
-    """Lets torch wrap the context-owned accumulation image (srt_accum_device_ptr) without copying."""
-
-    def __init__(self, ptr, n):
-        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 2}
-
-
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -203,6 +197,15 @@ def run_gpu(args):
     mode = pkg.TRAV_REFERENCE if args.traversal == "reference" else pkg.TRAV_ORDERED
 
     ctx = pkg.Context(local)
+    if world > 1:
+        # the product's own multi-GPU layer (srt_group_join: partition + one NCCL collective inside srt_render);
+        # torch.distributed is only the launcher's channel for the 128-byte group id
+        idt = torch.zeros(pkg.GROUP_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt = torch.tensor(list(pkg.group_unique_id()), dtype=torch.uint8, device="cuda")
+        dist.broadcast(idt, 0)
+        ctx.group_join(rank, world, bytes(idt.cpu().numpy().tobytes()))
+        ctx.set_option(pkg.OPT_SPLIT, pkg.SPLIT_SAMPLES if args.split == "samples" else pkg.SPLIT_BANDS)
     stream = torch.cuda.Stream()  # a real (non-NULL) stream: kernels, events and NCCL ordering all go through it
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
@@ -235,9 +238,6 @@ def run_gpu(args):
 
     upload_all()
     ctx.resize(W, H)
-    ctx.set_stripe(rank, world)
-    ptr, nfl = ctx.accum_device_ptr()
-    accum_t = torch.as_tensor(_DevPtr(ptr, nfl), device="cuda")
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def params(reset):
@@ -247,7 +247,8 @@ def run_gpu(args):
     launches = [0]
 
     def step(ev_kernel=None):
-        """One fresh 64-spp frame: clear (the shader's reset dispatch), 64 frames, reduce + tonemap when split."""
+        """One fresh 64-spp frame: clear (the shader's reset dispatch), then 64 frames in one srt_render -- which, in a
+        group, ends with the call's one collective and rank 0's tonemap, all queued on the stream by the library."""
         ctx.set_params(params(1))
         ctx.render_async(1)
         ctx.set_params(params(0))
@@ -257,11 +258,6 @@ def run_gpu(args):
         if ev_kernel:
             ev_kernel[1].record(stream)
         launches[0] += 2
-        if world > 1:
-            dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
-            if rank == 0:
-                ctx.tonemap(spp)
-                launches[0] += 1
 
     def barrier():
         if world > 1:
@@ -300,6 +296,7 @@ def run_gpu(args):
         trace_ms, logic_ms, n_waves = ctx.kernel_times()
         ctx.set_option(pkg.OPT_TIME_KERNELS, 0)
     cnt = ctx.counters()
+    coll_ms, coll_n = ctx.collective_ms() if world > 1 else (0.0, 0)
     gpu_launches = cnt["kernel_launches"]  # every kernel this context launched in the timed region (clear, init, waves, resolve, tonemap)
 
     tot = torch.tensor([sum(step_ms), sum(kern_ms), trace_ms, logic_ms, float(n_waves)], dtype=torch.float64, device="cuda")
@@ -475,8 +472,11 @@ def run_gpu(args):
                    "traversal": "reference (the shader's visiting order: the hit finder answers the rays, and every kernel beside it walks "
                                 "in that order)" if finder_on else args.traversal,
                    "schedule": args.schedule, "block_threads": args.block,
-                   "split": "interleaved 8-row bands over %d GPU(s), NCCL reduce of the fp32 accumulation image to rank 0" % world
-                            if world > 1 else "single GPU",
+                   "split": ("single GPU" if world == 1 else
+                             ("sample ranges: each of %d GPUs renders the whole image for 1/%d of the frames; one ncclReduce(sum) of the "
+                              "fp32 accumulation images to rank 0 per step, inside srt_render" % (world, world)) if args.split == "samples" else
+                             ("interleaved 8-row bands over %d GPUs; each rank's own rows (P*16/%d bytes) gathered on rank 0 with "
+                              "ncclSend/ncclRecv once per step, inside srt_render" % (world, world))),
                    "l2": "512 MB device buffer rewritten between timed steps (L2 flush)",
                    "tail_paths": "library default" if args.tail_paths < 0 else args.tail_paths,
                    "primary_cull": "library default (on)" if args.primary_cull < 0 else args.primary_cull,
@@ -491,6 +491,7 @@ def run_gpu(args):
         "bounce_segments_per_s_M": (segments - paths) / args.steps / (ms_per_step * 1e-3) / 1e6,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": float(e2.item()) / e2e_steps * 1e3},
+        "collective_ms_per_step": (coll_ms / max(coll_n, 1)) if world > 1 else None,
         "gpu_launches": gpu_launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "wall_s_timed_region": wall,
     }
@@ -521,6 +522,8 @@ def main():
                     help="hit finder of the wavefront schedule: 0 off, 1 on, 2 auto (-1 = library default, auto)")
     ap.add_argument("--tail-paths", type=int, default=-1,
                     help="live paths at which the wavefront schedule's tail kernel takes over (-1 = library default, 0 = never)")
+    ap.add_argument("--split", default="bands", choices=["bands", "samples"],
+                    help="multi-GPU partition (SRT_OPT_SPLIT): interleaved image bands (bit-identical to one GPU) or sample ranges")
     ap.add_argument("--wave-slots", type=int, default=0, help="path slots of the wavefront schedule (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -184,6 +184,38 @@ int srt_build_bvh(srt_ctx* ctx, const float* centre_xyz, const float* min_xyz, c
                   srt_bvh_node* nodes_out, uint32_t* n_nodes_out, uint32_t* order_out, uint32_t* depth_out,
                   float* device_ms_out);
 
+/* ---- several B200s behind one srt_render (no reference call site: src/main.cpp:706 is a single dispatch) ---------------
+ * the frame shards by image tile and by sample range with full replicas of scene and noise tables on
+ * every GPU and no exchange inside the path loop; ONE collective over NVLink per srt_render call.  In a group
+ *   - srt_render / srt_render_async render this rank's share and then run the collective + rank 0's tonemap, all on the
+ *     context's stream;
+ *   - rank 0 holds the picture: srt_read_output / srt_read_accum / srt_accum_device_ptr / srt_tonemap there act on the
+ *     GATHERED accumulation image; every rank's own image only holds what that rank rendered, so progressive rendering
+ *     without resets never counts a contribution twice;
+ *   - every rank must be given the same scene, noise tables, lights, uniforms and image size, and make the same calls.
+ * SRT_OPT_SPLIT picks the partition:
+ *   SRT_SPLIT_BANDS   (default) rank r renders the interleaved 8-row bands b = r (mod world); the collective gathers every
+ *                     rank's own rows (Width*Height*16/world bytes each) on rank 0: the bits of a single-GPU render
+ *   SRT_SPLIT_SAMPLES rank r renders the whole image for the r-th of `world` consecutive ranges of the call's frames; the
+ *                     collective is one ncclReduce(sum) of the fp32 images: fp32 additions re-ordered, equal to the
+ *                     single-GPU image within tolerance (1e-4 relative), not in bits
+ * NCCL is loaded with dlopen("libnccl.so.2") when the first group is formed; without it these calls fail, the rest of
+ * the library does not need it. */
+#define SRT_OPT_SPLIT 14
+#define SRT_SPLIT_BANDS 0
+#define SRT_SPLIT_SAMPLES 1
+#define SRT_GROUP_ID_BYTES 128
+/* One process per GPU (torchrun / mpirun): rank 0 calls srt_group_unique_id, the launcher's own channel carries the
+ * SRT_GROUP_ID_BYTES bytes to every rank, every rank calls srt_group_join with them (collective: returns when all have). */
+int srt_group_unique_id(void* id, uint64_t bytes);
+int srt_group_join(srt_ctx* ctx, int32_t rank, int32_t world, const void* id, uint64_t bytes);
+/* One process, n GPUs: *out is a HEAD context (rank 0, devices[0]).  Options, uploads, uniforms, resize, render, sync
+ * and counter calls on it act on every device (srt_render on one host thread per device); reads come from rank 0;
+ * srt_destroy(head) destroys all.  n = 1 is srt_create. */
+int srt_create_multi(srt_ctx** out, const int* devices, int32_t n);
+/* Sum of the CUDA-event durations of this rank's collectives since the last call, and how many there were. */
+int srt_get_collective_ms(srt_ctx* ctx, double* ms, uint64_t* calls);
+
 int srt_get_counters(srt_ctx* ctx, srt_counters* out);
 /* Sums of the CUDA-event durations of the wavefront schedule's trace and logic launches since the last call
  * (needs SRT_OPT_TIME_KERNELS = 1); waves = launches of each kind.  Synchronises the stream. */

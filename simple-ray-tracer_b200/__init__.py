@@ -16,6 +16,9 @@ LIB_PATH = os.path.join(HERE, "libsrt_b200.so")
 OPT_TRAVERSAL, OPT_COUNT_TRAVERSAL, OPT_L2_PERSIST, OPT_BLOCK_THREADS, OPT_SCHEDULE = 1, 2, 3, 4, 5
 OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS, OPT_TEXTURES, OPT_TAIL_PATHS, OPT_FINDER = 6, 7, 8, 9, 10, 11, 12
 OPT_PRIMARY_CULL = 13
+OPT_SPLIT = 14
+SPLIT_BANDS, SPLIT_SAMPLES = 0, 1
+GROUP_ID_BYTES = 128
 SCHED_PER_PATH, SCHED_REGEN, SCHED_PERSISTENT, SCHED_WAVEFRONT = 0, 1, 2, 3
 TRAV_REFERENCE, TRAV_ORDERED = 0, 1
 NO_HIT = 0xFFFFFFFF
@@ -34,7 +37,8 @@ EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
            "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_build_bvh", "srt_set_texture",
-           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_measure_issue", "srt_version"]
+           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_measure_issue", "srt_group_unique_id", "srt_group_join",
+           "srt_create_multi", "srt_get_collective_ms", "srt_version"]
 
 
 class Params(C.Structure):  # srt_params, include/srt_types.h
@@ -81,15 +85,40 @@ class SrtError(RuntimeError):
     pass
 
 
+def group_unique_id():
+    """The id rank 0 hands to every rank's Context.group_join (srt_group_unique_id)."""
+    buf = (C.c_ubyte * GROUP_ID_BYTES)()
+    if lib().srt_group_unique_id(buf, C.c_uint64(GROUP_ID_BYTES)) != 0:
+        raise SrtError(lib().srt_last_error(None).decode())
+    return bytes(buf)
+
+
 class Context:
     """One srt_ctx: the stand-in for the reference's GL context + compute program + bound buffers."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, devices=None):
+        """device: one GPU (srt_create).  devices=[...]: one process driving several GPUs through a head context
+        (srt_create_multi)."""
         self._h = C.c_void_p()
         self._lib = lib()
-        if self._lib.srt_create(C.byref(self._h), C.c_int(device)) != 0:
+        if devices is not None:
+            arr = (C.c_int * len(devices))(*devices)
+            rc = self._lib.srt_create_multi(C.byref(self._h), arr, C.c_int32(len(devices)))
+        else:
+            rc = self._lib.srt_create(C.byref(self._h), C.c_int(device))
+        if rc != 0:
             raise SrtError(self._lib.srt_last_error(None).decode())
         self.width = self.height = 0
+
+    def group_join(self, rank, world, group_id):
+        """One process per GPU: joins the group whose id rank 0 got from group_unique_id() (collective call)."""
+        buf = (C.c_ubyte * GROUP_ID_BYTES).from_buffer_copy(bytes(group_id))
+        self._ck(self._lib.srt_group_join(self._h, C.c_int32(rank), C.c_int32(world), buf, C.c_uint64(GROUP_ID_BYTES)))
+
+    def collective_ms(self):
+        ms, n = C.c_double(), C.c_uint64()
+        self._ck(self._lib.srt_get_collective_ms(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     def close(self):
         if self._h:

@@ -9,6 +9,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <functional>
 #include <atomic>
 #include <chrono>
 #include <string>
@@ -20,113 +21,13 @@
 #include "srt_kernels.h"
 #include "srt_bvh_build.h"
 #include "srt_finder.h"
+#include "srt_ctx.h"
 
 using namespace srt;
 
-struct srt_ctx {
-  int device = 0;
-  cudaStream_t own_stream = nullptr;
-  cudaStream_t stream = nullptr;
-  std::string error;
-
-  // host copies of what the reference keeps in its file-static vectors (gpu_loader.cpp:44-52)
-  std::vector<srt_bvh> h_bvhs;
-  std::vector<BvhRecord> h_bvh_records;
-  uint32_t n_nodes = 0, n_tris = 0, n_mats = 0;
-  int tree_depth = 0;
-  bool have_scene = false;
-  size_t top_pair_bytes = 0;             // breadth-first prefix of d_pairs (top BVH levels)
-  cudaStream_t l2_window_stream = nullptr;  // stream the access-policy window is currently set on
-  bool l2_window_on = false;
-  const void* l2_window_ptr = nullptr;      // what the window covers
-  size_t l2_window_bytes = 0;
-  size_t l2_limit_set = (size_t)-1;         // last cudaLimitPersistingL2CacheSize this context asked for
-  int l2_max_window = -1, l2_max_persist = -1;  // device limits (-1: not asked yet)
-
-  // device scene
-  NodePair* d_pairs = nullptr;
-  uint2* d_leaves = nullptr;
-  TriRecord* d_tris = nullptr;
-  MatRecord* d_mats = nullptr;
-  BvhRecord* d_bvhs = nullptr;
-  // hit finder (srt_finder.h): built at upload unless SRT_OPT_FINDER is 0
-  NodePair* d_fpairs = nullptr;
-  TriRecord* d_ftris = nullptr;
-  RefNode* d_rnodes = nullptr;
-  uint32_t* d_tri_leaf = nullptr;
-  int finder_mode = 2;           // SRT_OPT_FINDER: 0 off, 1 on, 2 where the sample rays say it pays
-  bool finder_ready = false;     // the arrays above describe the uploaded scene
-  bool finder_worthwhile = false;
-  int finder_depth = 0;
-  double finder_cost = 0.0, reference_cost = 0.0;
-  // textured-albedo option (SRT_OPT_TEXTURES; include/srt_texmath.h)
-  bool textures_on = false;
-  TexTri* d_tex_tris = nullptr;            // built by srt_upload_scene when a material says use_texture
-  TexInfo* d_tex_info = nullptr;
-  unsigned char* d_texels = nullptr;
-  std::vector<unsigned char> h_texels;     // RGBA8 of every texture set so far
-  std::vector<TexInfo> h_tex_info;
-  std::vector<uint32_t> h_mat_tex;         // per material: 1 + texture index, 0 = none
-  std::vector<MatRecord> h_mats;
-  bool textures_dirty = false;
-  float2* d_noise_xy = nullptr;
-  float* d_noise_x = nullptr;
-  uint32_t noise_count = 0;
-  char* noise_stage = nullptr;  // pinned staging buffer of the packed noise tables
-  size_t noise_stage_bytes = 0;
-  std::map<void**, size_t> dev_capacity;  // bytes allocated behind the scene's device pointers (upload_vec)
-  float* d_noise_raw = nullptr; // device copy of the two tables as given (pinned callers: packed on the device)
-  size_t noise_raw_bytes = 0;
-
-  // images
-  int width = 0, height = 0;
-  float4* d_accum = nullptr;
-  uchar4* d_out = nullptr;
-  uint32_t* d_ids = nullptr;
-  bool ids_enabled = false;
-  int row0 = 0, row1 = 0;
-  int stripe_rank = 0, stripe_world = 1;
-
-  // uniforms + lights
-  srt_params params;
-  bool have_params = false;
-  srt_light lights[SRT_MAX_LIGHTS];
-  int light_count = 0;
-
-  // options
-  int traversal = TRAV_ORDERED;
-  int count_traversal = 0;  // SRT_OPT_COUNT_TRAVERSAL: 0 off, 1 the shader's walk (finder off), 2 what the default path executes
-  bool l2_persist = true;
-  int block_threads = 64;
-  int schedule = SCHED_WAVEFRONT;
-
-  // wavefront schedule: path slots + queues (sized for the pixels this context renders), polling state
-  PathPool pool;
-  uint32_t pool_slots = 0;
-  size_t pool_list_cap = 0;
-  WaveCounters* h_live = nullptr;  // pinned ring the device reports its wave counters into (live slots, paths handed out)
-  cudaEvent_t wave_events[4] = {nullptr, nullptr, nullptr, nullptr};
-  uint64_t waves = 0;
-  uint64_t tail_launches = 0;
-  // optional per-kernel timing of the wavefront schedule (SRT_OPT_TIME_KERNELS): three events per wave
-  bool time_kernels = false;
-  std::vector<cudaEvent_t> timing_events;
-  size_t timing_used = 0;
-  int refill_threshold = 0;                    // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL; 0 = each kernel's own default)
-  uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
-  bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
-  uint32_t* d_culled = nullptr;                 // bit map of the paths the cull ended (one bit per sample entry)
-  uint32_t tail_paths = 1u << 20;               // live paths at which the tail kernel takes over (SRT_OPT_TAIL_PATHS, 0 = never)
-  size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
-  size_t sample_budget_bytes = (size_t)4 << 30;  // sample buffer budget per frame chunk (SRT_OPT_SAMPLE_BUDGET_MB)
-
-  DeviceCounters* d_counters = nullptr;
-  uint64_t kernel_launches = 0;
-};
-
 static thread_local std::string g_create_error;
 
-static int fail(srt_ctx* ctx, const char* fmt, ...) {
+int srt_fail(srt_ctx* ctx, const char* fmt, ...) {
   char buf[512];
   va_list ap;
   va_start(ap, fmt);
@@ -135,6 +36,22 @@ static int fail(srt_ctx* ctx, const char* fmt, ...) {
   if (ctx) ctx->error = buf; else g_create_error = buf;
   return 1;
 }
+#define fail srt_fail
+
+// srt_multi.cu
+int srt_group_fanout(srt_ctx* ctx, bool parallel, const std::function<int(srt_ctx*)>& call);
+int srt_group_set_split(srt_ctx* ctx, int value);
+int srt_group_peer_count(const srt_ctx* ctx);
+srt_ctx* srt_group_peer(const srt_ctx* ctx, int i);
+float4* srt_group_display_accum(srt_ctx* ctx);
+bool srt_group_is_sample_split(const srt_ctx* ctx);
+int srt_group_rank(const srt_ctx* ctx);
+// a head context of srt_create_multi hands the call to every device's context (srt_multi.cu)
+#define FANOUT(ctx, parallel, expr)                                                          \
+  do {                                                                                       \
+    const int f_ = srt_group_fanout(ctx, parallel, [&](srt_ctx* c) -> int { return expr; });  \
+    if (f_ >= 0) return f_;                                                                  \
+  } while (0)
 
 #define CU(ctx, call)                                                                       \
   do {                                                                                      \
@@ -200,6 +117,8 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  srt_group_release(ctx);  // a head context takes its other devices' contexts with it
+  cudaSetDevice(ctx->device);
   dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris); dfree(ctx->d_mats); dfree(ctx->d_bvhs);
   dfree(ctx->d_fpairs); dfree(ctx->d_ftris); dfree(ctx->d_rnodes); dfree(ctx->d_tri_leaf);
   dfree(ctx->d_tex_tris); dfree(ctx->d_tex_info); dfree(ctx->d_texels);
@@ -226,6 +145,8 @@ extern "C" int srt_set_stream(srt_ctx* ctx, void* cuda_stream) {
 
 extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (!ctx) return 1;
+  FANOUT(ctx, false, srt_set_option(c, key, value));
+  if (key == SRT_OPT_SPLIT) return srt_group_set_split(ctx, value);
   switch (key) {
     case SRT_OPT_TRAVERSAL:
       if (value != TRAV_REFERENCE && value != TRAV_ORDERED) return fail(ctx, "SRT_OPT_TRAVERSAL: 0 or 1");
@@ -294,6 +215,7 @@ namespace {
 // Inner nodes of the first SRT_TOP_LEVELS levels are laid out breadth-first at the front of the NodePair array (every
 // ray walks them; that prefix is what the L2 access-policy window pins), deeper subtrees depth-first behind it.
 #define SRT_TOP_LEVELS 14
+#define SRT_TIMING_WAVES 16384  // launches whose CUDA events SRT_OPT_TIME_KERNELS keeps until srt_get_kernel_times reads them
 
 struct Relayout {
   size_t top_pairs = 0;  // NodePair records of the breadth-first prefix (all BVHs)
@@ -443,6 +365,7 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
                                 const srt_triangle* triangles, uint32_t n_triangles, const srt_vertex* vertices,
                                 uint32_t n_vertices) {
   if (!ctx) return 1;
+  FANOUT(ctx, true, srt_upload_scene(c, bvhs, n_bvhs, nodes, n_nodes, materials, n_materials, triangles, n_triangles, vertices, n_vertices));
   if (!bvhs || !nodes || !materials || !triangles || !vertices) return fail(ctx, "srt_upload_scene: NULL array");
   if (n_bvhs == 0 || n_bvhs > SRT_MAX_BVHS) return fail(ctx, "srt_upload_scene: n_bvhs must be 1..%d", SRT_MAX_BVHS);
   CU(ctx, cudaSetDevice(ctx->device));
@@ -574,6 +497,7 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
 
 extern "C" int srt_update_frame(srt_ctx* ctx, uint32_t index, const float* m) {
   if (!ctx || !m) return 1;
+  FANOUT(ctx, false, srt_update_frame(c, index, m));
   if (!ctx->have_scene || index >= ctx->h_bvhs.size()) return fail(ctx, "srt_update_frame: index %u out of range", index);
   CU(ctx, cudaSetDevice(ctx->device));
   memcpy(ctx->h_bvhs[index].frame, m, 64);
@@ -586,6 +510,7 @@ extern "C" int srt_update_frame(srt_ctx* ctx, uint32_t index, const float* m) {
 // ---- noise, lights, uniforms, images -----------------------------------------------------------
 extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const float* uniform_vec3, uint32_t count) {
   if (!ctx) return 1;
+  FANOUT(ctx, false, srt_upload_noise(c, unit_vec3, uniform_vec3, count));
   if (!unit_vec3 || !uniform_vec3 || count == 0) return fail(ctx, "srt_upload_noise: NULL table or count 0");
   CU(ctx, cudaSetDevice(ctx->device));
   // the shader reads noiseTex.xy (raytrace_utils.glsl:15) and noiseUniformTex.x (:52) only: keep those, packed.
@@ -669,6 +594,7 @@ extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const floa
 
 extern "C" int srt_set_lights(srt_ctx* ctx, const srt_light* lights, int32_t count) {
   if (!ctx) return 1;
+  FANOUT(ctx, false, srt_set_lights(c, lights, count));
   if (count < 0 || count > SRT_MAX_LIGHTS) return fail(ctx, "srt_set_lights: count %d not in 0..%d", count, SRT_MAX_LIGHTS);
   if (count > 0 && !lights) return fail(ctx, "srt_set_lights: NULL lights");
   memset(ctx->lights, 0, sizeof ctx->lights);  // decree Q2: zero-padded to MAX_LIGHTS
@@ -679,6 +605,7 @@ extern "C" int srt_set_lights(srt_ctx* ctx, const srt_light* lights, int32_t cou
 
 extern "C" int srt_set_params(srt_ctx* ctx, const srt_params* p) {
   if (!ctx || !p) return 1;
+  FANOUT(ctx, false, srt_set_params(c, p));
   if (p->width <= 0 || p->height <= 0 || (p->width % 8) || (p->height % 8))
     return fail(ctx, "srt_set_params: Width/Height must be positive multiples of 8 (src/main.cpp:706), got %dx%d", p->width, p->height);
   if ((int64_t)p->width * p->height >= (1 << 30)) return fail(ctx, "srt_set_params: Width*Height must be < 2^30");
@@ -691,6 +618,7 @@ extern "C" int srt_set_params(srt_ctx* ctx, const srt_params* p) {
 
 extern "C" int srt_resize(srt_ctx* ctx, int32_t width, int32_t height) {
   if (!ctx) return 1;
+  FANOUT(ctx, false, srt_resize(c, width, height));
   if (width <= 0 || height <= 0 || (width % 8) || (height % 8))
     return fail(ctx, "srt_resize: width/height must be positive multiples of 8, got %dx%d", width, height);
   CU(ctx, cudaSetDevice(ctx->device));
@@ -732,6 +660,7 @@ extern "C" int srt_set_stripe(srt_ctx* ctx, int32_t rank, int32_t world) {
 
 extern "C" int srt_enable_primary_ids(srt_ctx* ctx, int enable) {
   if (!ctx) return 1;
+  FANOUT(ctx, false, srt_enable_primary_ids(c, enable));
   CU(ctx, cudaSetDevice(ctx->device));
   ctx->ids_enabled = enable != 0;
   if (ctx->ids_enabled && !ctx->d_ids && ctx->width > 0) {
@@ -759,10 +688,24 @@ int flush_textures(srt_ctx* ctx) {
 
 extern "C" int srt_set_texture(srt_ctx* ctx, uint32_t material_index, const uint8_t* rgba8, uint32_t width, uint32_t height) {
   if (!ctx) return 1;
+  FANOUT(ctx, false, srt_set_texture(c, material_index, rgba8, width, height));
   if (!ctx->have_scene) return fail(ctx, "srt_set_texture: no scene uploaded");
   if (material_index >= ctx->n_mats) return fail(ctx, "srt_set_texture: material %u out of range", material_index);
   if (!rgba8 || width == 0 || height == 0 || width > 32768u || height > 32768u) return fail(ctx, "srt_set_texture: bad image");
   if (!ctx->d_tex_tris) return fail(ctx, "srt_set_texture: no material of the uploaded scene has use_texture set");
+  // a material that already has an image: the old texels leave the buffer (later images move down), nothing piles up
+  if (const uint32_t had = ctx->h_mat_tex[material_index]) {
+    const TexInfo old = ctx->h_tex_info[had - 1];
+    const size_t old_bytes = (size_t)old.width * old.height * 4, at = (size_t)old.offset * 4;
+    ctx->h_texels.erase(ctx->h_texels.begin() + (ptrdiff_t)at, ctx->h_texels.begin() + (ptrdiff_t)(at + old_bytes));
+    ctx->h_tex_info.erase(ctx->h_tex_info.begin() + (had - 1));
+    for (TexInfo& t : ctx->h_tex_info)
+      if (t.offset > old.offset) t.offset -= (uint32_t)(old_bytes / 4);
+    for (uint32_t& m : ctx->h_mat_tex) {
+      if (m == had) m = 0;
+      else if (m > had) --m;
+    }
+  }
   TexInfo ti;
   ti.offset = (uint32_t)(ctx->h_texels.size() / 4);
   ti.width = width;
@@ -1001,6 +944,9 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     unsigned long long live = n_paths < (unsigned long long)slots ? n_paths : (unsigned long long)slots;
     bool all_out = n_paths <= (unsigned long long)slots;
     auto timing_events = [&](cudaEvent_t* ev) -> int {
+      // at most SRT_TIMING_WAVES launches are remembered between two srt_get_kernel_times calls: a caller that switches
+      // the option on and never reads starts over from the oldest instead of growing without bound
+      if (ctx->timing_used + 3 > 3 * (size_t)SRT_TIMING_WAVES) ctx->timing_used = 0;
       while (ctx->timing_events.size() < ctx->timing_used + 3) {
         cudaEvent_t e;
         CU(ctx, cudaEventCreate(&e));
@@ -1083,6 +1029,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
 
 extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
   if (!ctx) return 1;
+  FANOUT(ctx, true, srt_render_async(c, n_frames));
   if (n_frames < 0) return fail(ctx, "srt_render: n_frames < 0");
   if (check_ready(ctx)) return 1;
   CU(ctx, cudaSetDevice(ctx->device));
@@ -1096,23 +1043,31 @@ extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
   if (ctx->textures_on && flush_textures(ctx)) return 1;
   if (ctx->textures_on && ctx->d_texels && ctx->params.show_model && ctx->schedule != SCHED_WAVEFRONT && ctx->schedule != SCHED_PER_PATH)
     return fail(ctx, "SRT_OPT_TEXTURES: schedules 0 (per path) and 3 (wavefront) sample textures; 1 and 2 do not");
-  FrameParams fp;
-  fill_frame_params(ctx, n_frames, fp);
-  if (ctx->params.show_model && ctx->schedule == SCHED_WAVEFRONT) {
-    if (render_wavefront(ctx, fp)) return 1;
-    ctx->params.accum_frames += n_frames;
-    return 0;
+  // in a multi-GPU group this rank renders its bands of every frame, or the whole image for its share of the frames
+  // (srt_multi.cu); alone it renders the call as it is
+  const int32_t call_first = ctx->params.accum_frames;
+  int32_t first = call_first, mine = n_frames;
+  if (srt_group_before_render(ctx, n_frames, &first, &mine)) return 1;
+  if (mine > 0) {
+    ctx->params.accum_frames = first;
+    FrameParams fp;
+    fill_frame_params(ctx, mine, fp);
+    if (ctx->params.show_model && ctx->schedule == SCHED_WAVEFRONT) {
+      if (render_wavefront(ctx, fp)) return 1;
+    } else {
+      CU(ctx, launch_pathtrace(device_scene(ctx), fp, ctx->params.show_model != 0, ctx->traversal, ctx->count_traversal != 0, ctx->schedule,
+                               ctx->d_accum, ctx->d_out, ctx->ids_enabled ? ctx->d_ids : nullptr, ctx->d_counters, &ctx->d_counters->next_tile,
+                               ctx->block_threads, ctx->stream));
+      ctx->kernel_launches++;
+    }
   }
-  CU(ctx, launch_pathtrace(device_scene(ctx), fp, ctx->params.show_model != 0, ctx->traversal, ctx->count_traversal, ctx->schedule,
-                           ctx->d_accum, ctx->d_out, ctx->ids_enabled ? ctx->d_ids : nullptr, ctx->d_counters, &ctx->d_counters->next_tile,
-                           ctx->block_threads, ctx->stream));
-  ctx->kernel_launches++;
-  ctx->params.accum_frames += n_frames;
-  return 0;
+  ctx->params.accum_frames = call_first + n_frames;
+  return srt_group_after_render(ctx, call_first + n_frames - 1);
 }
 
 extern "C" int srt_sync(srt_ctx* ctx) {
   if (!ctx) return 1;
+  FANOUT(ctx, false, srt_sync(c));
   CU(ctx, cudaSetDevice(ctx->device));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   return 0;
@@ -1127,7 +1082,7 @@ extern "C" int srt_tonemap(srt_ctx* ctx, int32_t accum_frames) {
   if (!ctx || !ctx->d_accum) return 1;
   if (accum_frames < 1) return fail(ctx, "srt_tonemap: accum_frames < 1");
   CU(ctx, cudaSetDevice(ctx->device));
-  CU(ctx, launch_tonemap(ctx->d_accum, ctx->d_out, (size_t)ctx->width * ctx->height, (float)accum_frames, ctx->stream));
+  CU(ctx, launch_tonemap(srt_group_display_accum(ctx), ctx->d_out, (size_t)ctx->width * ctx->height, (float)accum_frames, ctx->stream));
   ctx->kernel_launches++;
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   return 0;
@@ -1147,16 +1102,22 @@ extern "C" int srt_read_accum(srt_ctx* ctx, float* rgba32f) {
   if (!ctx || !rgba32f) return 1;
   if (!ctx->d_accum) return fail(ctx, "srt_read_accum: no image (call srt_resize)");
   CU(ctx, cudaSetDevice(ctx->device));
-  CU(ctx, cudaMemcpyAsync(rgba32f, ctx->d_accum, (size_t)ctx->width * ctx->height * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(rgba32f, srt_group_display_accum(ctx), (size_t)ctx->width * ctx->height * 16, cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   return 0;
 }
 
 extern "C" int srt_write_accum(srt_ctx* ctx, const float* rgba32f) {
   if (!ctx || !rgba32f) return 1;
+  FANOUT(ctx, false, srt_write_accum(c, rgba32f));
   if (!ctx->d_accum) return fail(ctx, "srt_write_accum: no image (call srt_resize)");
   CU(ctx, cudaSetDevice(ctx->device));
-  CU(ctx, cudaMemcpyAsync(ctx->d_accum, rgba32f, (size_t)ctx->width * ctx->height * 16, cudaMemcpyHostToDevice, ctx->stream));
+  // In a group every rank is handed the same image.  Image bands: a rank only ever reads and gathers its own rows of
+  // it.  Sample ranges: the images are SUMMED, so rank 0 keeps the restored image and the other ranks start from zero.
+  if (srt_group_is_sample_split(ctx) && srt_group_rank(ctx) != 0)
+    CU(ctx, cudaMemsetAsync(ctx->d_accum, 0, (size_t)ctx->width * ctx->height * 16, ctx->stream));
+  else
+    CU(ctx, cudaMemcpyAsync(ctx->d_accum, rgba32f, (size_t)ctx->width * ctx->height * 16, cudaMemcpyHostToDevice, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   return 0;
 }
@@ -1164,7 +1125,7 @@ extern "C" int srt_write_accum(srt_ctx* ctx, const float* rgba32f) {
 extern "C" int srt_accum_device_ptr(srt_ctx* ctx, void** device_ptr, uint64_t* n_floats) {
   if (!ctx || !device_ptr) return 1;
   if (!ctx->d_accum) return fail(ctx, "srt_accum_device_ptr: no image (call srt_resize)");
-  *device_ptr = ctx->d_accum;
+  *device_ptr = srt_group_display_accum(ctx);
   if (n_floats) *n_floats = (uint64_t)ctx->width * ctx->height * 4;
   return 0;
 }
@@ -1229,6 +1190,20 @@ extern "C" int srt_build_bvh(srt_ctx* ctx, const float* centre_xyz, const float*
 
 extern "C" int srt_get_counters(srt_ctx* ctx, srt_counters* out) {
   if (!ctx || !out) return 1;
+  if (srt_group_peer_count(ctx) > 1) {  // a head context of srt_create_multi: the sum over its devices
+    memset(out, 0, sizeof *out);
+    for (int i = 0; i < srt_group_peer_count(ctx); ++i) {
+      srt_ctx* c = srt_group_peer(ctx, i);
+      CU(c, cudaSetDevice(c->device));
+      DeviceCounters h;
+      CU(c, cudaMemcpyAsync(&h, c->d_counters, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+      CU(c, cudaStreamSynchronize(c->stream));
+      out->segments += h.segments; out->shadow_rays += h.shadow_rays; out->paths += h.paths;
+      out->capped_paths += h.capped_paths; out->kernel_launches += c->kernel_launches;
+      out->nodes += h.nodes; out->tris += h.tris; out->culled_primaries += h.culled;
+    }
+    return 0;
+  }
   CU(ctx, cudaSetDevice(ctx->device));
   DeviceCounters h;
   CU(ctx, cudaMemcpyAsync(&h, ctx->d_counters, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1269,6 +1244,7 @@ extern "C" int srt_get_finder_info(srt_ctx* ctx, int32_t* active, double* cost_r
 
 extern "C" int srt_reset_counters(srt_ctx* ctx) {
   if (!ctx) return 1;
+  FANOUT(ctx, false, srt_reset_counters(c));
   CU(ctx, cudaSetDevice(ctx->device));
   CU(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(DeviceCounters), ctx->stream));
   ctx->kernel_launches = 0;

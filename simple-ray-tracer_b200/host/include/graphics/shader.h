@@ -13,6 +13,7 @@
 #pragma once
 
 #include <string>
+#include <vector>
 
 #include <glm/glm.hpp>
 
@@ -48,11 +49,16 @@ class Shader {
   srt_ctx* m_ctx = nullptr;
   srt_params m_params;
   int m_device = 0;
+  std::vector<int> m_devices;  // more than one: Init() makes a head context over them (srt_create_multi)
 };
 
 class Compute : public Shader {
  public:
   explicit Compute(const char* path, int device = 0) : Shader(path) { m_device = device; }
+  // several GPUs behind this one program (no reference call site): Init() then creates a head context over `devices`;
+  // the frame is split inside every Dispatch (image bands by default, SetSplitBySamples(true) for sample ranges)
+  void SetDevices(const std::vector<int>& devices) { m_devices = devices; }
+  void SetSplitBySamples(bool by_samples);
 
   void Init() override;
 

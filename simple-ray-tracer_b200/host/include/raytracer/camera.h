@@ -53,6 +53,9 @@ class Camera {
                      float movementSpeed);
   // headless replacement for mouse input: place the camera directly
   void SetPose(const glm::vec3& position, float yaw_degrees, float pitch_degrees);
+  // puts back a basis read earlier (the scripted front end renders a batch with the vectors of BEFORE a
+  // MoveAndRotate call that re-orthonormalised them)
+  void SetBasis(const glm::vec3& front, const glm::vec3& up, const glm::vec3& right) { front_ = front; up_ = up; right_ = right; }
 
  private:
   void UpdateCameraVectors();

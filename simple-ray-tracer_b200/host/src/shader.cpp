@@ -71,9 +71,15 @@ void Shader::SetVec3(const std::string& name, glm::vec3 val) {
   }
 }
 
+void Compute::SetSplitBySamples(bool by_samples) {
+  SrtHost::Check(srt_set_option(m_ctx, SRT_OPT_SPLIT, by_samples ? SRT_SPLIT_SAMPLES : SRT_SPLIT_BANDS), m_ctx, "SetSplitBySamples");
+}
+
 void Compute::Init() {
   if (m_ctx != nullptr) return;
-  if (srt_create(&m_ctx, m_device) != 0) {
+  const int rc = m_devices.size() > 1 ? srt_create_multi(&m_ctx, m_devices.data(), static_cast<int>(m_devices.size()))
+                                      : srt_create(&m_ctx, m_devices.size() == 1 ? m_devices[0] : m_device);
+  if (rc != 0) {
     // the reference terminates when its program does not compile or link (Shader.cpp:134-141,149-156)
     std::cerr << "Compute::Init failed: " << srt_last_error(nullptr) << std::endl;
     std::terminate();

@@ -11,12 +11,29 @@
 //                [--accum FILE]   also write the RGBA32F accumulation image as raw fp32
 //                [--device-bvh]   build the model's BVH on the device (same bytes as the host builder)
 //                [--textures]     sample the map_Kd PNGs at the OBJ's vt coordinates (default: albedo = Kd, decree Q7)
+//                [--obj PATH]     PATH = <objects dir>/<NAME>/<NAME>.obj: the same as --objects <objects dir> --model <NAME>
+//                [--gpus N]       one process driving N GPUs (devices 0..N-1) through a head context (srt_create_multi);
+//                [--split bands|samples]  how the frame is split across them (default: interleaved image bands)
+//                [--script FILE]  replaces the reference's InputHandler (input_handler.cpp:4-172) by a list of events, one
+//                                 per line, run through the reference's own per-frame sequence (src/main.cpp:622-725):
+//                     frames N                        N frames without input (the picture accumulates)
+//                     move DT MX MY MZ RYAW RPITCH    one frame with this movement / rotation delta
+//                     click                           one frame with the left mouse button held
+//                     reset                           one frame with InputHandler::ShouldResetBuffer() raised
+//                     write FILE.ppm                  writes the picture as it stands
+//                   Any input raises resetAccumBuffer and sets accumFrames = 0 before the frame's accumFrames++, so that
+//                   dispatch only clears with accumFrames = 1 and the first sample after it is taken at accumFrames = 2
+//                   and divided by 2 ((n-1)/n too dark after any reset) -- reproduced, not fixed.
+//                   Camera::MoveAndRotate runs every frame, as in the reference (its 120-call re-orthonormalisation too).
+//                   Without --script the loop is the reference's start-up: --frames frames without input.
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <exception>
+#include <fstream>
 #include <memory>
+#include <sstream>
 #include <stdexcept>
 #include <algorithm>
 #include <iostream>
@@ -46,7 +63,49 @@ struct Options {
   bool textures = false;    // decode map_Kd images, honour vt lines, sample them (default: decree Q7, albedo = Kd)
   bool device_bvh = false;  // build the model's BVH with srt_build_bvh instead of on the host
   float px = 0, py = 0, pz = 0, yaw = -90, pitch = 0;
+  int gpus = 1;
+  bool split_samples = false;
+  std::string script;
 };
+
+// one frame of the scripted loop
+struct Event {
+  enum Kind { Idle, Move, Click, Reset, Write } kind = Idle;
+  int count = 1;  // Idle: frames
+  float dt = 0.016f;
+  glm::vec3 move = glm::vec3(0.0f, 0.0f, 0.0f);
+  glm::vec2 rot = glm::vec2(0.0f, 0.0f);
+  std::string file;
+};
+
+std::vector<Event> read_script(const std::string& path) {
+  std::ifstream in(path);
+  if (!in) throw std::runtime_error("cannot read script " + path);
+  std::vector<Event> events;
+  std::string line;
+  int lineno = 0;
+  while (std::getline(in, line)) {
+    ++lineno;
+    const auto hash = line.find('#');
+    if (hash != std::string::npos) line.erase(hash);
+    std::istringstream ss(line);
+    std::string op;
+    if (!(ss >> op)) continue;
+    Event e;
+    bool ok = true;
+    if (op == "frames") { e.kind = Event::Idle; ok = static_cast<bool>(ss >> e.count) && e.count >= 0; }
+    else if (op == "move") { e.kind = Event::Move; ok = static_cast<bool>(ss >> e.dt >> e.move.x >> e.move.y >> e.move.z >> e.rot.x >> e.rot.y); }
+    else if (op == "click") e.kind = Event::Click;
+    else if (op == "reset") e.kind = Event::Reset;
+    else if (op == "write") { e.kind = Event::Write; ok = static_cast<bool>(ss >> e.file); }
+    else ok = false;
+    if (!ok) throw std::runtime_error(path + ":" + std::to_string(lineno) + ": bad script line");
+    events.push_back(e);
+  }
+  return events;
+}
+
+bool same_bits(const glm::vec3& a, const glm::vec3& b) { return std::memcmp(&a, &b, sizeof a) == 0; }
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -75,6 +134,27 @@ int main(int argc, char** argv) {
     else if (a == "--accum") { o.accum_file = val(); ++i; }
     else if (a == "--device-bvh") o.device_bvh = true;
     else if (a == "--textures") o.textures = true;
+    else if (a == "--gpus") { o.gpus = std::atoi(val()); ++i; }
+    else if (a == "--split") { o.split_samples = std::string(val()) == "samples"; ++i; }
+    else if (a == "--script") { o.script = val(); ++i; }
+    else if (a == "--obj") {
+      // <objects dir>/<NAME>/<NAME>.obj, the layout LoadObject expects (model_loader.cpp:14,24-26)
+      std::string path = val();
+      ++i;
+      const auto slash = path.find_last_of('/');
+      const std::string dir = slash == std::string::npos ? "." : path.substr(0, slash);
+      std::string file = slash == std::string::npos ? path : path.substr(slash + 1);
+      if (file.size() > 4 && file.substr(file.size() - 4) == ".obj") file.erase(file.size() - 4);
+      const auto up = dir.find_last_of('/');
+      const std::string folder = up == std::string::npos ? dir : dir.substr(up + 1);
+      if (folder != file) {
+        std::fprintf(stderr, "--obj: expected <objects dir>/%s/%s.obj (LoadObject's layout), got %s\n", file.c_str(), file.c_str(), path.c_str());
+        return 2;
+      }
+      o.objects = (up == std::string::npos ? std::string(".") : dir.substr(0, up)) + "/";
+      o.model = file;
+      o.show_model = true;
+    }
     else if (a == "--pose") {
       o.pose = true;
       o.px = std::atof(val(1)); o.py = std::atof(val(2)); o.pz = std::atof(val(3));
@@ -97,8 +177,14 @@ int main(int argc, char** argv) {
     if (o.pose) camera.SetPose(glm::vec3(o.px, o.py, o.pz), o.yaw, o.pitch);
 
     Graphics::Compute compute("./shaders/raytrace_compute.glsl", o.device);
+    if (o.gpus > 1) {
+      std::vector<int> devices;
+      for (int d = 0; d < o.gpus; ++d) devices.push_back(d);
+      compute.SetDevices(devices);
+    }
     compute.Init();
     compute.Use();
+    if (o.gpus > 1 && o.split_samples) compute.SetSplitBySamples(true);
 
     Graphics::Texture texture;
     texture.setWidth(o.width);
@@ -149,18 +235,26 @@ int main(int argc, char** argv) {
       lights.emplace_back(glm::vec3(-2.5f, 2.0f, 0.0f), glm::vec3(1.0f, 1.0f, 1.0f), 3.0f);
     }
 
+    std::vector<Event> events;
+    if (!o.script.empty()) {
+      events = read_script(o.script);
+    } else {
+      Event e;
+      e.count = o.frames;
+      events.push_back(e);
+    }
+
     srt_reset_counters(compute.GetProgram());
-    int accumFrames = 0;
-    const auto t0 = std::chrono::steady_clock::now();
-    while (accumFrames < o.frames) {
-      const int n = std::min(o.batch, o.frames - accumFrames);
+    int accumFrames = 0, frames_run = 0, resets = 0;
+    // one dispatch of n frames with the uniforms of src/main.cpp:668-685; accumFrames is the value of the FIRST of them
+    const auto dispatch = [&](bool reset_buffer, int first_accum_frames, int n) {
       compute.Use();
-      compute.SetBool("resetAccumBuffer", false);
+      compute.SetBool("resetAccumBuffer", reset_buffer);
       compute.SetVec3("cameraOrigin", camera.getOrigin());
       compute.SetVec3("cameraDirection", camera.getForward());
       compute.SetVec3("cameraUp", camera.getUpVector());
       compute.SetVec3("cameraRight", camera.getRightVector());
-      compute.SetInt("accumFrames", accumFrames + 1);
+      compute.SetInt("accumFrames", first_accum_frames);
       compute.SetInt("Width", o.width);
       compute.SetInt("Height", o.height);
       compute.SetUInt("bvh_count", o.show_model ? 1u : 0u);  // models in scene (decree Q1; the reference passes 2)
@@ -169,9 +263,55 @@ int main(int argc, char** argv) {
       if (o.max_depth > 0) compute.SetInt("maxDepth", o.max_depth);
       compute.SetLights(lights.data(), static_cast<Graphics::uint>(lights.size()));
       compute.DispatchFrames(o.width / 8, o.height / 8, n);
-      accumFrames += n;
+      frames_run += n;
+    };
+    const auto t0 = std::chrono::steady_clock::now();
+    for (const Event& e : events) {
+      if (e.kind == Event::Write) {
+        texture.updateImageDataFromGPU();
+        RayTracer::WritePPM(e.file, texture.getImageData(), o.width, o.height);
+        continue;
+      }
+      if (e.kind == Event::Idle) {
+        // frames without input: accumFrames++ and one dispatch each (src/main.cpp:657-706).  Consecutive frames whose
+        // camera vectors stay the same bits go out as one batch (MoveAndRotate still runs once per frame: every 120th
+        // call re-orthonormalises the basis, camera.cpp:174-184, which may move a bit)
+        int pending = 0, pending_first = 0;
+        for (int k = 0; k < e.count; ++k) {
+          const glm::vec3 f0 = camera.getForward(), u0 = camera.getUpVector(), r0 = camera.getRightVector();
+          camera.MoveAndRotate(e.dt, glm::vec3(0.0f, 0.0f, 0.0f), glm::vec2(0.0f, 0.0f), 1.0f);
+          const bool moved = !same_bits(f0, camera.getForward()) || !same_bits(u0, camera.getUpVector()) || !same_bits(r0, camera.getRightVector());
+          if (pending > 0 && (moved || pending >= o.batch)) {
+            // the batch was rendered with the vectors before this call
+            const glm::vec3 f1 = camera.getForward(), u1 = camera.getUpVector(), r1 = camera.getRightVector();
+            if (moved) camera.SetBasis(f0, u0, r0);
+            dispatch(false, pending_first, pending);
+            if (moved) camera.SetBasis(f1, u1, r1);
+            pending = 0;
+          }
+          ++accumFrames;
+          if (pending == 0) pending_first = accumFrames;
+          ++pending;
+        }
+        if (pending > 0) dispatch(false, pending_first, pending);
+        continue;
+      }
+      // a frame with input (src/main.cpp:622-659): resetBuffer, accumFrames = 0, the camera moves, accumFrames++ -> 1,
+      // and the dispatch only clears (raytrace_compute.glsl:390-393)
+      const bool any_input = e.kind == Event::Click || e.kind == Event::Reset || glm::length(e.move) > 0.0001f ||
+                             glm::length(e.rot) > 0.0001f;
+      bool reset_buffer = false;
+      if (any_input) {
+        reset_buffer = true;
+        accumFrames = 0;
+        ++resets;
+      }
+      camera.MoveAndRotate(e.dt, e.move, e.rot, 1.0f);
+      ++accumFrames;
+      dispatch(reset_buffer, accumFrames, 1);
     }
     const double render_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    o.frames = frames_run > 0 ? frames_run : 1;
 
     texture.updateImageDataFromGPU();
     RayTracer::WritePPM(o.out, texture.getImageData(), o.width, o.height);
@@ -184,10 +324,10 @@ int main(int argc, char** argv) {
     srt_counters c;
     srt_get_counters(compute.GetProgram(), &c);
     std::printf("{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"frames\": %d, \"ms_per_frame\": %.4f, "
-                "\"segments\": %llu, \"shadow_rays\": %llu, \"mseg_per_s\": %.2f, \"load_s\": %.3f, \"bvh\": \"%s\", \"out\": \"%s\"}\n",
+                "\"segments\": %llu, \"shadow_rays\": %llu, \"mseg_per_s\": %.2f, \"load_s\": %.3f, \"bvh\": \"%s\", \"gpus\": %d, \"resets\": %d, \"accum_frames\": %d, \"out\": \"%s\"}\n",
                 o.show_model ? o.model.c_str() : "spheres", o.width, o.height, o.frames, render_s * 1e3 / o.frames,
                 (unsigned long long)c.segments, (unsigned long long)c.shadow_rays, c.segments / render_s / 1e6, load_s,
-                o.device_bvh ? "device" : "host", o.out.c_str());
+                o.device_bvh ? "device" : "host", o.gpus, resets, accumFrames, o.out.c_str());
   } catch (const std::exception& e) {
     std::fprintf(stderr, "srt_headless: %s\n", e.what());
     return 1;

@@ -105,3 +105,92 @@ def test_headless_textures_option_matches_oracle(oracle, tmp_path):
     finally:
         oracle.set_textures([])
     assert_bit_exact(acc_tex, oacc_tex)
+
+
+def _camera_after(script_lines):
+    """Camera vectors after every line of a srt_host_probe script (the product's RayTracer::Camera, which
+    tests/test_host_inputs.py holds to the reference's camera.cpp bit for bit)."""
+    probe = scenes._host_tool("srt_host_probe")
+    path = os.path.join(scenes.ROOT, "tests", ".probe_script.tmp")
+    with open(path, "w") as f:
+        f.write("\n".join(script_lines) + "\n")
+    try:
+        out = subprocess.run([probe, "camera", path], check=True, capture_output=True, text=True).stdout.splitlines()
+    finally:
+        os.remove(path)
+    cams = []
+    for ln in out:
+        v = np.array([int(h, 16) for h in ln.split()], np.uint32).view(np.float32)
+        cams.append({"origin": tuple(map(float, v[0:3])), "direction": tuple(map(float, v[3:6])), "up": tuple(map(float, v[6:9])),
+                     "right": tuple(map(float, v[9:12]))})
+    return cams
+
+
+def test_scripted_camera_path_with_the_references_reset_semantics(oracle, tmp_path):
+    """--script replaces the InputHandler.  Any input raises resetAccumBuffer and sets
+    accumFrames = 0 before the frame's accumFrames++ (src/main.cpp:629-659), so that dispatch only clears with
+    accumFrames = 1 (raytrace_compute.glsl:390-393) and the first sample after it is taken at accumFrames = 2 and divided
+    by 2.  The oracle is driven through the same sequence of (reset, accumFrames, camera) dispatches."""
+    W, H = 192, 104
+    name, _ = scenes.write_airplane_standin(str(tmp_path), detail=24)
+    unit, uniform = scenes.noise_tables(W, H)
+    with open(tmp_path / "noise.bin", "wb") as f:
+        f.write(unit.tobytes())
+        f.write(uniform.tobytes())
+    mid = str(tmp_path / "mid.ppm")
+    script = tmp_path / "path.txt"
+    script.write_text("frames 3\n"
+                      "move 0.016 0.5 0 1 4.0 -2.0   # walk forward/right while turning: a reset frame\n"
+                      "frames 2\n"
+                      "write %s\n"
+                      "click\n"
+                      "frames 4\n" % mid)
+    acc, ppm, info = run_headless(tmp_path, name, W, H, 0, "scripted", ["--script", str(script)])
+    assert info["resets"] == 2 and info["accum_frames"] == 5 and info["frames"] == 3 + 1 + 2 + 1 + 4
+
+    # the same camera, call by call: Reset, 3 idle MoveAndRotate calls, the move, 2 idle, the click (no deltas), 4 idle
+    idle = "moverot 0.016 0 0 0 0 0 1"
+    cams = _camera_after(["reset 1"] + [idle] * 3 + ["moverot 0.016 0.5 0 1 4.0 -2.0 1"] + [idle] * 2 + [idle] + [idle] * 4)
+    cam0, cam1 = cams[0], cams[4]
+    assert cams[3] == cam0 and cams[-1] == cam1 and cam1 != cam0
+    scene = scenes.load_obj_scene(str(tmp_path), name, str(tmp_path))
+    lights = scenes.model_lights()
+
+    def run(accum, cam, first, n, reset=0):
+        p = oracle.make_params(W, H, cam, True, first, len(lights), 1, 0, reset=reset)
+        a, out, _, _ = oracle.render(p, n, scene, unit, uniform, lights, accum=accum)
+        return a, out
+
+    a, _ = run(None, cam0, 1, 3)                 # frames 3: accumFrames 1..3
+    a, _ = run(a, cam1, 1, 1, reset=1)           # the move: clears, accumFrames = 1
+    a, out_mid = run(a, cam1, 2, 2)              # frames 2: accumFrames 2, 3 (two samples divided by 3)
+    a, _ = run(a, cam1, 1, 1, reset=1)           # the click: clears again
+    a, out_end = run(a, cam1, 2, 4)              # frames 4: accumFrames 2..5 (four samples divided by 5)
+    assert_bit_exact(acc, a)
+
+    def ppm_rgb(text):
+        tok = text.split()
+        return np.array(tok[4:], np.int64).reshape(H, W, 3)
+
+    assert np.array_equal(ppm_rgb(ppm), out_end[..., :3].astype(np.int64)[::-1])
+    assert np.array_equal(ppm_rgb(open(mid).read()), out_mid[..., :3].astype(np.int64)[::-1])
+    # Q11 made visible: one more sample would NOT be divided by the number of samples taken
+    full, _ = run(None, cam1, 1, 4)
+    assert np.allclose(a[..., :3], full[..., :3], rtol=0.5) and not np.array_equal(out_end, run(None, cam1, 1, 4)[1])
+
+
+def test_obj_option_is_the_objects_and_model_pair(oracle, tmp_path):
+    W, H = 128, 64
+    name, _ = scenes.write_airplane_standin(str(tmp_path), detail=16)
+    unit, uniform = scenes.noise_tables(W, H)
+    with open(tmp_path / "noise.bin", "wb") as f:
+        f.write(unit.tobytes())
+        f.write(uniform.tobytes())
+    a, _, _ = run_headless(tmp_path, name, W, H, 2, "pair")
+    exe = os.path.join(HOST, "srt_headless")
+    accum = str(tmp_path / "obj.accum")
+    r = subprocess.run([exe, "--obj", str(tmp_path / name / (name + ".obj")), "--width", str(W), "--height", str(H), "--frames", "2",
+                        "--noise", str(tmp_path / "noise.bin"), "--accum", accum, "--out", str(tmp_path / "obj.ppm")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert np.fromfile(accum, np.float32).tobytes() == a.tobytes()

@@ -114,3 +114,27 @@ def test_textures_need_schedule_0_or_3(pkg, ctx, tmp_path):
     ctx.set_params(pkg.make_params(64, 32, scenes.reset_camera(True), True, accum_frames=1, bvh_count=1))
     with pytest.raises(RuntimeError, match="SRT_OPT_TEXTURES"):
         ctx.render(1)
+
+
+@pytest.mark.gpu
+def test_setting_a_materials_texture_again_replaces_it(pkg, ctx, oracle, tmp_path):
+    """srt_set_texture for a material that already has an image: the new image replaces the old one (of another size, and
+    with an image of a LATER material behind it in the texel buffer), nothing is appended beside it."""
+    from test_parity_gpu import assert_bit_exact, cpu_render, gpu_render
+    scene, images = textured_scene(tmp_path)
+    W, H = 192, 96
+    rng = np.random.default_rng(5)
+    first = [(0, rng.integers(0, 256, (7, 3, 4), dtype=np.uint8)), images[1]]  # material 0's first image, then material 3's
+    ctx.set_option(pkg.OPT_TEXTURES, 1)
+    gpu_render(pkg, ctx, W, H, True, 1, pkg.TRAV_REFERENCE, scene=scene, schedule=3, textures=first)
+    ctx.set_texture(images[0][0], images[0][1])  # replace material 0's image by a larger one
+    ctx.resize(W, H)
+    ctx.set_params(pkg.make_params(W, H, scenes.reset_camera(True), True, accum_frames=1, bvh_count=1))
+    ctx.render(2)
+    got = ctx.read_accum()
+    try:
+        oracle.set_textures(images)
+        want, _, _, _ = cpu_render(oracle, W, H, True, 2, scene=scene)
+    finally:
+        oracle.set_textures([])
+    assert_bit_exact(got, want)
