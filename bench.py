@@ -238,6 +238,8 @@ def run_gpu(args):
 
     upload_all()
     ctx.resize(W, H)
+    if args.stripe_of > 1 and world == 1:
+        ctx.set_stripe(0, args.stripe_of)  # study aid: this GPU renders what rank 0 of `stripe_of` GPUs would (no collective)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def params(reset):
@@ -267,6 +269,8 @@ def run_gpu(args):
     for _ in range(max(args.warmup, 0)):
         step()
     barrier()
+    if world > 1:
+        ctx.collective_ms()  # forget the warm-up's collectives (the first one sets the NCCL connections up)
 
     # ---- timed region: K steps, device time by CUDA events on the launching stream, L2 flushed between steps
     ctx.reset_counters()
@@ -491,6 +495,7 @@ def run_gpu(args):
         "bounce_segments_per_s_M": (segments - paths) / args.steps / (ms_per_step * 1e-3) / 1e6,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": float(e2.item()) / e2e_steps * 1e3},
+        "emulated_rank_of": args.stripe_of if (args.stripe_of > 1 and world == 1) else None,
         "collective_ms_per_step": (coll_ms / max(coll_n, 1)) if world > 1 else None,
         "gpu_launches": gpu_launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "wall_s_timed_region": wall,
@@ -524,6 +529,9 @@ def main():
                     help="live paths at which the wavefront schedule's tail kernel takes over (-1 = library default, 0 = never)")
     ap.add_argument("--split", default="bands", choices=["bands", "samples"],
                     help="multi-GPU partition (SRT_OPT_SPLIT): interleaved image bands (bit-identical to one GPU) or sample ranges")
+    ap.add_argument("--stripe-of", type=int, default=1,
+                    help="study aid (1 GPU only): render only the bands rank 0 of this many GPUs would own -- the per-rank step of a "
+                         "multi-GPU run without its collective; the line is marked emulated_rank_of")
     ap.add_argument("--wave-slots", type=int, default=0, help="path slots of the wavefront schedule (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
