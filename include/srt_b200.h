@@ -184,6 +184,19 @@ int srt_build_bvh(srt_ctx* ctx, const float* centre_xyz, const float* min_xyz, c
                   srt_bvh_node* nodes_out, uint32_t* n_nodes_out, uint32_t* order_out, uint32_t* depth_out,
                   float* device_ms_out);
 
+/* srt_trace_rays without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same results (bit for bit) as srt_trace_rays, but the device staging of the rays and of the two result
+ * arrays lives in a file-scope `static __device__` array inside the library instead of per-call cudaMalloc'ed buffers:
+ *   - at most SRT_TRACE_STATIC_MAX_RAYS rays per call; more is rejected with an error that names the limit;
+ *   - the array is 40 B x SRT_TRACE_STATIC_MAX_RAYS = 2.5 MiB and every GPU that loads the library holds it until exit;
+ *   - the call makes no cudaMalloc / cudaFree / allocating library call (copies, two memsets, one kernel, a synchronise);
+ *   - every call on a device shares the array, which keeps the last call's contents: the result words are cleared before
+ *     the kernel runs, and calls whose GPU work OVERLAPS on one device (two contexts or streams) race -- serialise them. */
+#define SRT_TRACE_STATIC_MAX_RAYS 65536u
+int srt_trace_rays_static(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, uint32_t bvh_count, uint32_t* hit_tri,
+                          float* hit_t);
+
 /* ---- several B200s behind one srt_render (no reference call site: src/main.cpp:706 is a single dispatch) ---------------
  * the frame shards by image tile and by sample range with full replicas of scene and noise tables on
  * every GPU and no exchange inside the path loop; ONE collective over NVLink per srt_render call.  In a group

@@ -19,6 +19,7 @@ OPT_PRIMARY_CULL = 13
 OPT_SPLIT = 14
 SPLIT_BANDS, SPLIT_SAMPLES = 0, 1
 GROUP_ID_BYTES = 128
+TRACE_STATIC_MAX_RAYS = 65536
 SCHED_PER_PATH, SCHED_REGEN, SCHED_PERSISTENT, SCHED_WAVEFRONT = 0, 1, 2, 3
 TRAV_REFERENCE, TRAV_ORDERED = 0, 1
 NO_HIT = 0xFFFFFFFF
@@ -36,7 +37,7 @@ RAY_DT = np.dtype([("origin", "<f4", 3), ("_pad0", "<f4"), ("direction", "<f4", 
 EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt_set_option", "srt_upload_scene",
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
-           "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_build_bvh", "srt_set_texture",
+           "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_trace_rays_static", "srt_build_bvh", "srt_set_texture",
            "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_measure_issue", "srt_group_unique_id", "srt_group_join",
            "srt_create_multi", "srt_get_collective_ms", "srt_version"]
 
@@ -227,6 +228,17 @@ class Context:
         hit = np.empty(len(rays), np.uint32)
         t = np.empty(len(rays), np.float32)
         self._ck(self._lib.srt_trace_rays(self._h, _p(rays), C.c_uint32(len(rays)), C.c_uint32(bvh_count), _p(hit), _p(t)))
+        return hit, t
+
+    def trace_rays_static(self, rays, bvh_count=1):
+        """srt_trace_rays_static: the same results through the library's static device scratch (no allocation; at most
+        TRACE_STATIC_MAX_RAYS rays)."""
+        rays = np.ascontiguousarray(rays)
+        assert rays.dtype.itemsize == 32
+        n = len(rays)
+        hit = np.zeros(n, np.uint32)
+        t = np.zeros(n, np.float32)
+        self._ck(self._lib.srt_trace_rays_static(self._h, _p(rays), C.c_uint32(n), C.c_uint32(bvh_count), _p(hit), _p(t)))
         return hit, t
 
     def set_texture(self, material_index, image):

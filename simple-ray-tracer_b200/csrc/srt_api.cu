@@ -1169,6 +1169,28 @@ extern "C" int srt_trace_rays(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays
   return rc;
 }
 
+// No counterpart in the reference: srt_trace_rays with its device staging
+// in a static __device__ array of srt_kernels.cu -- no cudaMalloc / cudaFree on this path.
+extern "C" int srt_trace_rays_static(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, uint32_t bvh_count, uint32_t* hit_tri,
+                                     float* hit_t) {
+  if (!ctx) return 1;
+  if (!ctx->have_scene) return fail(ctx, "srt_trace_rays_static: no scene uploaded");
+  if (bvh_count > ctx->h_bvhs.size()) return fail(ctx, "srt_trace_rays_static: bvh_count %u exceeds the uploaded BVHs", bvh_count);
+  if (n_rays > SRT_TRACE_STATIC_MAX_RAYS)
+    return fail(ctx, "srt_trace_rays_static: %u rays exceed the static scratch's limit of %u (SRT_TRACE_STATIC_MAX_RAYS); "
+                "split the batch or use srt_trace_rays", n_rays, SRT_TRACE_STATIC_MAX_RAYS);
+  if (n_rays == 0) return 0;
+  if (!rays || !hit_tri) return fail(ctx, "srt_trace_rays_static: NULL array");
+  CU(ctx, cudaSetDevice(ctx->device));
+  const int cap = ctx->tree_depth + 1 < 2 ? 2 : ctx->tree_depth + 1;
+  const char* what = "";
+  const cudaError_t e = launch_trace_rays_static(device_scene(ctx), ctx->traversal, cap, rays, n_rays, bvh_count, hit_tri, hit_t,
+                                                 ctx->stream, &what);
+  ctx->kernel_launches++;
+  if (e != cudaSuccess) return fail(ctx, "srt_trace_rays_static: %s: %s", what, cudaGetErrorString(e));
+  return 0;
+}
+
 extern "C" int srt_build_bvh(srt_ctx* ctx, const float* centre_xyz, const float* min_xyz, const float* max_xyz,
                              uint32_t n_prims, srt_bvh_node* nodes_out, uint32_t* n_nodes_out, uint32_t* order_out,
                              uint32_t* depth_out, float* device_ms_out) {

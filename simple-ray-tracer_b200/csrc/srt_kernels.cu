@@ -6,6 +6,8 @@
 // (prev + c1) + c2 + ... (raytrace_compute.glsl:404-406) and the accumulation image is read and written once
 // per launch instead of once per frame.  A warp covers an 8x4 pixel tile (primary rays stay coherent; the
 // reference's work group is 8x8, raytrace_compute.glsl:12).
+#include <mutex>
+
 #include "srt_kernels.h"
 #include "srt_path.cuh"
 #include "srt_regen.cuh"
@@ -485,6 +487,68 @@ cudaError_t launch_trace_rays(const DeviceScene& sc, int mode, int stack_cap, co
     trace_rays_kernel<TRAV_ORDERED><<<grid, block, smem, stream>>>(sc, rays, n_rays, bvh_count, hit_tri, hit_t);
   }
   return cudaGetLastError();
+}
+
+// ---- srt_trace_rays_static: the same kernel with its device scratch in a file-scope array (no allocation per call) ----
+// launch_trace_rays' caller stages the rays and the two result arrays in device memory it cudaMallocs per call.  Callers
+// that may not allocate get the same staging out of the array below: SRT_TRACE_STATIC_MAX_RAYS x (32 B ray + 4 B hit + 4 B
+// distance) = 2.5 MiB, held by every GPU that loads the library until the process exits.
+//   * In HOST code `g_trace_scratch` is a host-side stand-in for the symbol, not a device address: a kernel handed that
+//     value faults (or, where the GPU can reach host memory, quietly uses the wrong memory).  The device address comes
+//     from cudaGetSymbolAddress, asked once per device with that device current, here, in the array's own file.
+//   * Every call on a device shares the array, and it keeps the last call's contents: the result words a call will read
+//     back are cleared first, and two calls whose GPU work overlaps (two contexts / streams on one device) race.
+static __device__ __align__(256) unsigned char g_trace_scratch[(size_t)SRT_TRACE_STATIC_MAX_RAYS * 40u];
+
+namespace {
+std::mutex g_trace_scratch_mutex;
+unsigned char* g_trace_scratch_ptr[SRT_MAX_DEVICES] = {};  // per device: the array's DEVICE address
+}  // namespace
+
+cudaError_t launch_trace_rays_static(const DeviceScene& sc, int mode, int stack_cap, const srt_ray* host_rays, uint32_t n_rays,
+                                     uint32_t bvh_count, uint32_t* host_hit_tri, float* host_hit_t, cudaStream_t stream,
+                                     const char** what) {
+  *what = "";
+  if (n_rays == 0) return cudaSuccess;
+  if (n_rays > SRT_TRACE_STATIC_MAX_RAYS) {
+    *what = "more rays than the static scratch holds";
+    return cudaErrorInvalidValue;
+  }
+  cudaError_t e;
+  int dev = -1;
+  *what = "cudaGetDevice";
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if (dev < 0 || dev >= SRT_MAX_DEVICES) {
+    *what = "device ordinal beyond SRT_MAX_DEVICES";
+    return cudaErrorInvalidDevice;
+  }
+  unsigned char* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_trace_scratch_mutex);
+    if (g_trace_scratch_ptr[dev] == nullptr) {  // set-up, once per device, that device current
+      void* p = nullptr;
+      *what = "cudaGetSymbolAddress(g_trace_scratch)";
+      if ((e = cudaGetSymbolAddress(&p, g_trace_scratch)) != cudaSuccess) return e;
+      g_trace_scratch_ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    base = g_trace_scratch_ptr[dev];
+  }
+  srt_ray* d_rays = reinterpret_cast<srt_ray*>(base);
+  uint32_t* d_hit = reinterpret_cast<uint32_t*>(base + (size_t)SRT_TRACE_STATIC_MAX_RAYS * 32u);
+  float* d_t = reinterpret_cast<float*>(base + (size_t)SRT_TRACE_STATIC_MAX_RAYS * 36u);
+  *what = "cudaMemcpyAsync(rays)";
+  if ((e = cudaMemcpyAsync(d_rays, host_rays, (size_t)n_rays * sizeof(srt_ray), cudaMemcpyHostToDevice, stream)) != cudaSuccess) return e;
+  // what this call reads back starts from "no hit" / 0, never from the previous call's results
+  *what = "cudaMemsetAsync(results)";
+  if ((e = cudaMemsetAsync(d_hit, 0xFF, (size_t)n_rays * 4u, stream)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(d_t, 0, (size_t)n_rays * 4u, stream)) != cudaSuccess) return e;
+  *what = "trace_rays_kernel";
+  if ((e = launch_trace_rays(sc, mode, stack_cap, d_rays, n_rays, bvh_count, d_hit, d_t, stream)) != cudaSuccess) return e;
+  *what = "cudaMemcpyAsync(results)";
+  if ((e = cudaMemcpyAsync(host_hit_tri, d_hit, (size_t)n_rays * 4u, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return e;
+  if (host_hit_t && (e = cudaMemcpyAsync(host_hit_t, d_t, (size_t)n_rays * 4u, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return e;
+  *what = "cudaStreamSynchronize";
+  return cudaStreamSynchronize(stream);
 }
 
 // Roofline denominator for a scene far larger than L2 (the soup): what this GPU delivers for RANDOM 64 B records -- the

@@ -3,6 +3,7 @@
 
 #include <cuda_runtime.h>
 
+#include "srt_b200.h"
 #include "srt_device.cuh"
 
 #define SRT_MAX_BLOCK_THREADS 128
@@ -34,6 +35,12 @@ cudaError_t launch_clear(float4* accum, int width, int y0, int y1, cudaStream_t 
 cudaError_t launch_tonemap(const float4* accum, uchar4* out, size_t n, float frames, cudaStream_t stream);
 cudaError_t launch_trace_rays(const DeviceScene& sc, int mode, int stack_cap, const srt_ray* rays, uint32_t n_rays,
                               uint32_t bvh_count, uint32_t* hit_tri, float* hit_t, cudaStream_t stream);
+// the same kernel fed from a file-scope static __device__ scratch array in srt_kernels.cu: no allocation (host pointers
+// in and out, at most SRT_TRACE_STATIC_MAX_RAYS rays; synchronises the stream).  *what names the step that failed.
+#define SRT_MAX_DEVICES 64
+cudaError_t launch_trace_rays_static(const DeviceScene& sc, int mode, int stack_cap, const srt_ray* host_rays, uint32_t n_rays,
+                                     uint32_t bvh_count, uint32_t* host_hit_tri, float* host_hit_t, cudaStream_t stream,
+                                     const char** what);
 cudaError_t launch_detmath(int which, const float* x, const float* y, float* out, uint32_t n, cudaStream_t stream);
 
 }  // namespace srt
