@@ -103,13 +103,28 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def workload_inputs(name, soup_tris=10_000_000):
+def workload_inputs(name, soup_tris=10_000_000, obj=None):
     import tempfile
     show_model, W, H, spp, max_depth, desc = WORKLOADS[name]
     unit, uniform = scenes.noise_tables(W, H)
     cam = scenes.reset_camera(show_model)
     scene = None
-    if name == "rubik":
+    if obj:
+        # --obj <objects dir>/<NAME>/<NAME>.obj (LoadObject's layout, model_loader.cpp:14,24-26): the scene of the chosen
+        # workload is replaced by this file, loaded by the product's own loader + BVH builder; the line carries the
+        # file's own name (BASELINE.json configs[2]/[3] name objects/11803_Airplane_v1_l1, absent from the reference mount)
+        path = os.path.abspath(obj)
+        folder, base = os.path.split(path)
+        obj_name = os.path.splitext(base)[0]
+        if os.path.basename(folder) != obj_name or not os.path.isfile(path):
+            raise SystemExit("--obj: expected <objects dir>/%s/%s.obj, got %s" % (obj_name, obj_name, obj))
+        with tempfile.TemporaryDirectory() as d:
+            scene = scenes.load_obj_scene(os.path.dirname(folder), obj_name, d)
+        show_model = True
+        desc = "objects/%s (%d tris, %d nodes, BVH by the reference algorithm, 6 lights) %dx%d, %d spp per step, maxDepth %d" % (
+            obj_name, len(scene["triangles"]), len(scene["nodes"]), W, H, spp, max_depth or 5)
+        cam = scenes.reset_camera(True)
+    elif name == "rubik":
         scene = scenes.rubik_scene()
     elif name in ("airplane-standin", "airplane-standin-4k"):
         with tempfile.TemporaryDirectory() as d:
@@ -157,7 +172,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    inp = workload_inputs(args.workload, args.soup_tris)
+    inp = workload_inputs(args.workload, args.soup_tris, args.obj)
     cores = os.cpu_count() or 1
     _, t1, _ = oracle_run(inp, 1, 1)  # calibration (also the first warm-up)
     per_step = max(1, min(inp["spp"], int(5.0 / max(t1, 1e-3))))
@@ -192,7 +207,7 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = g.load_package()
-    inp = workload_inputs(args.workload, args.soup_tris)
+    inp = workload_inputs(args.workload, args.soup_tris, args.obj)
     W, H, spp, show_model = inp["W"], inp["H"], inp["spp"], inp["show_model"]
     mode = pkg.TRAV_REFERENCE if args.traversal == "reference" else pkg.TRAV_ORDERED
 
@@ -518,6 +533,9 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=0,
                     help="frames of the workload the CPU baseline renders (0 = as many as fit about 15 s)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--obj", default=None,
+                    help="<objects dir>/<NAME>/<NAME>.obj: render this model instead of the workload's scene (size, spp and depth stay "
+                         "the workload's), e.g. the Airplane OBJ of BASELINE.json configs[2] where someone supplies it")
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
     ap.add_argument("--l2-persist", type=int, default=-1, help="1/0: pin the BVH top levels in L2 (default: library default, on)")
     ap.add_argument("--refill", type=int, default=0, help="refill threshold of the wavefront trace kernel (0 = default)")

@@ -33,6 +33,8 @@ typedef struct srt_counters {
   uint64_t tris;         /* triangles tested       (only counted when SRT_FLAG_COUNT_TRAVERSAL is set) */
   uint64_t culled_primaries; /* camera rays that missed every root box and ended where they were generated
                                 (SRT_OPT_PRIMARY_CULL; only counted when SRT_OPT_COUNT_TRAVERSAL is set) */
+  uint64_t check_flags;  /* always 0 in the normal build; in the checked build (libsrt_b200_checked.so, -DSRT_CHECKED) one
+                            bit per kind of out-of-bounds access the kernels' own checks saw (csrc/srt_device.cuh SRT_CHK_*) */
 } srt_counters;
 
 /* srt_set_option keys */
@@ -253,6 +255,12 @@ int srt_measure_gather(srt_ctx* ctx, uint64_t bytes, int32_t chase, double* gbyt
  * fp32 operation per thread-instruction: the result is also the FP32 op/s roof for such code.  Nominal: 148 SMs x 4
  * sub-partitions x 32 lanes x clock. */
 int srt_measure_issue(srt_ctx* ctx, int32_t mix, double* thread_ginst_per_s);
+
+/* Checked build (libsrt_b200_checked.so, built -DSRT_CHECKED: the wavefront kernels bounds-check every stack push and
+ * every queue / slot / sample index into srt_counters.check_flags; compute-sanitizer is not available on the pool this
+ * was developed on).  srt_check_selftest raises bit 31 of check_flags through the same macro, which proves the checks are
+ * compiled in; in the normal build it launches an empty kernel and check_flags stays 0.  No reference call site. */
+int srt_check_selftest(srt_ctx* ctx);
 
 /* Device-side evaluation of the numeric decree (srt_detmath.h), for bit-for-bit checks against the host:
  * which: 0 = sin, 1 = cos, 2 = pow(x, 1/2.4), 3 = randFloat(x, y[i]) (y required), 4 = linearToSrgb. */

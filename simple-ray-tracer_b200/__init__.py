@@ -11,7 +11,9 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsrt_b200.so")
+# SRT_LIB picks another build of the same C-ABI, e.g. the bounds-checked one (libsrt_b200_checked.so) in tests
+LIB_PATH = os.environ.get("SRT_LIB") or os.path.join(HERE, "libsrt_b200.so")
+CHECKED_LIB_PATH = os.path.join(HERE, "libsrt_b200_checked.so")
 
 OPT_TRAVERSAL, OPT_COUNT_TRAVERSAL, OPT_L2_PERSIST, OPT_BLOCK_THREADS, OPT_SCHEDULE = 1, 2, 3, 4, 5
 OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS, OPT_TEXTURES, OPT_TAIL_PATHS, OPT_FINDER = 6, 7, 8, 9, 10, 11, 12
@@ -38,7 +40,7 @@ EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
            "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_trace_rays_static", "srt_build_bvh", "srt_set_texture",
-           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_measure_issue", "srt_group_unique_id", "srt_group_join",
+           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_measure_issue", "srt_check_selftest", "srt_group_unique_id", "srt_group_join",
            "srt_create_multi", "srt_get_collective_ms", "srt_version"]
 
 
@@ -53,7 +55,7 @@ class Params(C.Structure):  # srt_params, include/srt_types.h
 class Counters(C.Structure):  # srt_counters, include/srt_b200.h
     _fields_ = [("segments", C.c_uint64), ("shadow_rays", C.c_uint64), ("paths", C.c_uint64),
                 ("capped_paths", C.c_uint64), ("kernel_launches", C.c_uint64), ("nodes", C.c_uint64),
-                ("tris", C.c_uint64), ("culled_primaries", C.c_uint64)]
+                ("tris", C.c_uint64), ("culled_primaries", C.c_uint64), ("check_flags", C.c_uint64)]
 
 
 def build():
@@ -283,6 +285,9 @@ class Context:
         g = C.c_double()
         self._ck(self._lib.srt_measure_gather(self._h, C.c_uint64(n_bytes), C.c_int32(1 if chase else 0), C.byref(g)))
         return g.value
+
+    def check_selftest(self):
+        self._ck(self._lib.srt_check_selftest(self._h))
 
     def measure_issue(self, mix):
         """Thread-instructions per second (in units of 1e9) of un-fused fp32 arithmetic (see srt_measure_issue)."""

@@ -77,7 +77,11 @@ static void free_pool(srt_ctx* ctx) {
   ctx->sample_entries = 0;
 }
 
+#ifdef SRT_CHECKED
+extern "C" const char* srt_version(void) { return "srt_b200 0.1 sm_100a checked"; }
+#else
 extern "C" const char* srt_version(void) { return "srt_b200 0.1 sm_100a"; }
+#endif
 
 extern "C" const char* srt_last_error(const srt_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
 
@@ -1222,7 +1226,7 @@ extern "C" int srt_get_counters(srt_ctx* ctx, srt_counters* out) {
       CU(c, cudaStreamSynchronize(c->stream));
       out->segments += h.segments; out->shadow_rays += h.shadow_rays; out->paths += h.paths;
       out->capped_paths += h.capped_paths; out->kernel_launches += c->kernel_launches;
-      out->nodes += h.nodes; out->tris += h.tris; out->culled_primaries += h.culled;
+      out->nodes += h.nodes; out->tris += h.tris; out->culled_primaries += h.culled; out->check_flags |= h.check_flags;
     }
     return 0;
   }
@@ -1232,7 +1236,7 @@ extern "C" int srt_get_counters(srt_ctx* ctx, srt_counters* out) {
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   out->segments = h.segments; out->shadow_rays = h.shadow_rays; out->paths = h.paths;
   out->capped_paths = h.capped_paths; out->kernel_launches = ctx->kernel_launches;
-  out->nodes = h.nodes; out->tris = h.tris; out->culled_primaries = h.culled;
+  out->nodes = h.nodes; out->tris = h.tris; out->culled_primaries = h.culled; out->check_flags = h.check_flags;
   return 0;
 }
 
@@ -1302,6 +1306,15 @@ extern "C" int srt_measure_gather(srt_ctx* ctx, uint64_t bytes, int32_t chase, d
   ctx->kernel_launches += 2;
   if (e != cudaSuccess || e2 != cudaSuccess) return fail(ctx, "srt_measure_gather: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
   *gbytes_per_s = (double)blocks * 64.0 * iters * 64.0 / (ms * 1e-3) / 1e9;
+  return 0;
+}
+
+extern "C" int srt_check_selftest(srt_ctx* ctx) {
+  if (!ctx) return 1;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, launch_check_selftest(ctx->d_counters, ctx->stream));
+  ctx->kernel_launches++;
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
   return 0;
 }
 

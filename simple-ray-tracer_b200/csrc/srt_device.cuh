@@ -144,8 +144,30 @@ struct DeviceCounters {
   unsigned long long segments, shadow_rays, paths, capped_paths, nodes, tris;
   unsigned long long culled;  // camera rays ended by the primary cull (counted with SRT_OPT_COUNT_TRAVERSAL only)
   unsigned int next_tile;  // work counter of the persistent kernel (zeroed before each launch)
-  unsigned int _pad;
+  unsigned int check_flags;  // checked build (-DSRT_CHECKED) only: one bit per kind of bounds violation seen (SRT_CHK_*)
 };
+
+// Checked build (make libsrt_b200_checked.so): compute-sanitizer is not available on this pool, so the kernels of the
+// wavefront schedule carry their own bounds checks -- every push on a shared-memory traversal stack, every index into a
+// queue / list / slot array / sample buffer.  A violation sets its bit in DeviceCounters::check_flags (read through
+// srt_get_counters) and the access is still made, as in the normal build.  The normal build compiles the checks away.
+#define SRT_CHK_STACK 0      // traversal stack deeper than fp.stack_cap
+#define SRT_CHK_LIST_READ 1  // queue entry read beyond pool.list_cap
+#define SRT_CHK_SLOT 2       // slot index beyond pool.cap
+#define SRT_CHK_LIST_WRITE 3 // queue entry written beyond pool.list_cap
+#define SRT_CHK_STASH 4      // logic kernel's put-aside list beyond its 64 entries
+#define SRT_CHK_SAMPLE 5     // sample written beyond the launch's paths
+#define SRT_CHK_CAND 6       // candidate index beyond SRT_CAND_MAX / replay position beyond the slots
+#define SRT_CHK_OVERFLOW 7   // overflow list written beyond pool.list_cap
+#define SRT_CHK_PIXEL 8      // pixel / texel index beyond the image
+#ifdef SRT_CHECKED
+#define SRT_CHECK(cond, bit)                                        \
+  do {                                                              \
+    if (!(cond)) atomicOr(&counters->check_flags, 1u << (bit));     \
+  } while (0)
+#else
+#define SRT_CHECK(cond, bit) ((void)0)
+#endif
 
 // ---- wavefront schedule (srt_wavefront.cuh): queues, path slots, per-frame sample buffer ---------------------------
 struct WaveCounters {

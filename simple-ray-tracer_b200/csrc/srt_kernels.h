@@ -14,6 +14,7 @@ cudaError_t launch_pathtrace(const DeviceScene& sc, const FrameParams& fp, bool 
                              float4* accum, uchar4* out, uint32_t* ids, DeviceCounters* counters,
                              unsigned int* next_tile, int block, cudaStream_t stream);
 // Wavefront schedule (srt_wavefront.cuh): one init launch, then trace+logic pairs queued by the caller.
+cudaError_t launch_check_selftest(DeviceCounters* counters, cudaStream_t stream);  // srt_probes.cu
 cudaError_t launch_issue_probe(int mix, uint32_t iters, int blocks, float* sink, cudaStream_t stream);  // srt_probes.cu
 cudaError_t launch_gather_probe(const void* data, uint32_t n_records, uint32_t iters, int chase, uint32_t* sink, int blocks,
                                 cudaStream_t stream);

@@ -48,4 +48,14 @@ cudaError_t launch_issue_probe(int mix, uint32_t iters, int blocks, float* sink,
   return cudaGetLastError();
 }
 
+// Raises bit 31 of check_flags through the very macro the kernels use: set in the checked build, a no-op in the normal one.
+__global__ void check_selftest_kernel(DeviceCounters* counters) {
+  SRT_CHECK(threadIdx.x > 1024u, 31);
+  (void)counters;
+}
+cudaError_t launch_check_selftest(DeviceCounters* counters, cudaStream_t stream) {
+  check_selftest_kernel<<<1, 32, 0, stream>>>(counters);
+  return cudaGetLastError();
+}
+
 }  // namespace srt

@@ -173,6 +173,8 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       primary_ids[(size_t)y * fp.width + x] = SRT_NO_HIT;
     if (!keep) return;
   }
+  SRT_CHECK(slot < pool.cap && slot < pool.list_cap, SRT_CHK_SLOT);
+  SRT_CHECK(x >= 0 && x < fp.width && y >= 0 && y < fp.height, SRT_CHK_PIXEL);
   pool.ray[2 * (size_t)slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
   pool.ray[2 * (size_t)slot + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
   pool.pst[2 * (size_t)slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
@@ -317,9 +319,11 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       const int my_rank = __popc(idle & ((1u << lane) - 1u));
       if (!trav && my_rank < n_take) {
         const uint32_t idx = r_next + my_rank;
+        SRT_CHECK((idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)) < pool.list_cap, SRT_CHK_LIST_READ);
         const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
         if (entry != SRT_WF_HOLE) {
           slot = entry;
+          SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
           const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1];
           ray_o = v3(a.x, a.y, a.z);
           ray_d = v3(b.x, b.y, b.z);
@@ -367,6 +371,7 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           const bool pr = (nr <= fr) && (dr < best) && (dr != -inf_());
           if (pl && pr) {
             const bool right_first = (MODE == TRAV_REFERENCE || !front_l || !front_r) ? true : !(dl < dr);
+            SRT_CHECK((sp - sp_base) / sp_step < (uint32_t)fp.stack_cap, SRT_CHK_STACK);
             wf_sts(sp, right_first ? nd.z : nd.w, __float_as_uint(right_first ? dl : dr));
             sp += sp_step;
             cur = right_first ? nd.w : nd.z;
@@ -463,11 +468,13 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       region_a = g < chunks_a;
       const uint32_t idx = (region_a ? g : g - chunks_a) * 32u + lane;
       const bool in_range = idx < (region_a ? n_a : n_b);
+      SRT_CHECK(!in_range || (region_a ? idx : pool.list_cap - 1u - idx) < pool.list_cap, SRT_CHK_LIST_READ);
       if (in_range) entry = __ldg(list_in + (region_a ? idx : pool.list_cap - 1u - idx));
       g += n_warps;
     }
     const bool valid = entry != SRT_WF_HOLE;
     const uint32_t slot = valid ? entry : 0u;
+    SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
     const uint2 path = valid ? pool.path[slot] : make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
     int x = 0, y = 0;
     tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
@@ -494,6 +501,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       if (region_a) {
         // ---- a closest-hit ray came back (raytrace_compute.glsl:225-236) ----
         dir = v3(b.x, b.y, b.z);
+        SRT_CHECK(x >= 0 && x < fp.width && y >= 0 && y < fp.height, SRT_CHK_PIXEL);
         if (primary_ids != nullptr && iter == 0 && path.y == (uint32_t)(fp.n_frames - 1))
           primary_ids[(size_t)y * fp.width + x] = h.x;
         if (h.x == SRT_NO_HIT) {
@@ -546,6 +554,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     {
       const unsigned m_p = __ballot_sync(FULL, put_aside);
       if (m_p) {  // at most 31 entries are waiting here, so 64 hold them all
+        SRT_CHECK(stash_n + (uint32_t)__popc(m_p) <= 64u, SRT_CHK_STASH);
         if (put_aside) stash[stash_n + __popc(m_p & lt_mask)] = slot;
         stash_n += (uint32_t)__popc(m_p);
         __syncwarp();
@@ -622,6 +631,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       if (finish) {
         color = color + throughput * sky;  // Q19
         const V3 pixel_color = v3(0.0f) + color;  // main(): pixelColor = vec3(0) + GetRayColor(...)
+        SRT_CHECK((unsigned long long)path.y * pool.n_pixels + path.x < pool.n_paths && path.x < pool.n_pixels, SRT_CHK_SAMPLE);
         pool.samples[(size_t)path.y * pool.n_pixels + path.x] = make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f);
         const unsigned long long next = base + (unsigned long long)__popc(m_f & lt_mask);
         if (next < pool.n_paths) {
@@ -655,6 +665,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         c_next = __shfl_sync(FULL, base, 0);
         c_end = c_next + want;
       }
+      SRT_CHECK(c_next + m <= pool.list_cap && c_end <= pool.list_cap, SRT_CHK_LIST_WRITE);
       if (emit_closest) list_out[c_next + __popc(m_c & lt_mask)] = slot;
       c_next += m;
     }
@@ -669,12 +680,14 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         s_next = __shfl_sync(FULL, base, 0);
         s_end = s_next + want;
       }
+      SRT_CHECK(s_next + m <= pool.list_cap && s_end <= pool.list_cap, SRT_CHK_LIST_WRITE);
       if (emit_shadow) list_out[pool.list_cap - 1u - (s_next + __popc(m_s & lt_mask))] = slot;
       s_next += m;
     }
   }
   for (uint32_t i = c_next + lane; i < c_end; i += 32) list_out[i] = SRT_WF_HOLE;
   for (uint32_t i = s_next + lane; i < s_end; i += 32) list_out[pool.list_cap - 1u - i] = SRT_WF_HOLE;
+  SRT_CHECK((unsigned long long)c_end + s_end <= pool.list_cap, SRT_CHK_LIST_WRITE);  // front and back never meet
 
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {

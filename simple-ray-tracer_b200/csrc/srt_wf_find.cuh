@@ -162,6 +162,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           // the replay's input goes where the replay reads it in order: candidates and list entry by position in
           // the replay list, not by slot (scattered 64 B records cost 4-5x a sequential read, profiles/r01k_gather_probe)
           const uint32_t pos = base + (uint32_t)__popc(m_r & lt_mask);
+          SRT_CHECK(pos < pool.cap && n_cand <= SRT_CAND_MAX, SRT_CHK_CAND);
           uint2* dst = pool.cand + (size_t)pos * SRT_CAND_MAX;
           uint32_t w = 0;
           for (uint32_t k = 0; k < n_cand; ++k) {  // an OUTSIDE ray keeps the candidates within its final theta
@@ -177,6 +178,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
         const int leader = __ffs(m_o) - 1;
         if (lane == leader) base = atomicAdd(&fq->over.n_closest[0], (unsigned int)__popc(m_o));
         base = __shfl_sync(FULL, base, leader);
+        SRT_CHECK(base + (uint32_t)__popc(m_o) <= pool.list_cap, SRT_CHK_OVERFLOW);
         if (to_over) pool.olist[base + __popc(m_o & lt_mask)] = slot;
       }
       pending = false;
@@ -205,9 +207,11 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       const int my_rank = __popc(idle & lt_mask);
       if (!trav && !pending && my_rank < n_take) {
         const uint32_t idx = r_next + my_rank;
+        SRT_CHECK((idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)) < pool.list_cap, SRT_CHK_LIST_READ);
         const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
         if (entry != SRT_WF_HOLE) {
           slot = entry;
+          SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
           tmax = pool.ray[2 * (size_t)slot].w;
           n_cand = 0;
           overflow = false;
@@ -239,6 +243,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           if (COUNT) n_nodes += 2;
           if (pl && pr) {
             const bool left_first = !OUTSIDE || tl <= tr;  // nearer child first: an OUTSIDE ray's theta drops early
+            SRT_CHECK((sp - sp_base) / sp_step < (uint32_t)fp.stack_cap, SRT_CHK_STACK);
             wf_sts1(sp, left_first ? nd.w : nd.z);
             sp += sp_step;
             cur = left_first ? nd.z : nd.w;
@@ -288,6 +293,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
                     trav = false;
                     pending = true;
                   } else {
+                    SRT_CHECK(n_cand < SRT_CAND_MAX, SRT_CHK_CAND);
                     wf_sts(cand_base + n_cand * cand_step, __float_as_uint(r0.w) | (bvh_i << SRT_CAND_BVH_SHIFT), __float_as_uint(t));
                     n_cand++;
                   }
@@ -329,6 +335,8 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint2 entry = pool.rlist[i];
     const uint32_t slot = entry.x & 0x0FFFFFFFu, n_cand = entry.x >> 28;
+    SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
+    SRT_CHECK(n_cand <= SRT_CAND_MAX && i < pool.cap, SRT_CHK_CAND);
     const float4 ra = pool.ray[2 * (size_t)slot], rb = pool.ray[2 * (size_t)slot + 1];
     const V3 ray_o = v3(ra.x, ra.y, ra.z), ray_d = v3(rb.x, rb.y, rb.z);
     const bool any_hit = (__float_as_uint(rb.w) & 0xFFu) == SRT_WF_KIND_SHADOW;
@@ -424,7 +432,9 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
       n_acc++;
     }
     if (uncertain) {  // the long way (wf_trace_kernel over the overflow list, launched after this kernel)
-      pool.olist[atomicAdd(&pool.fq->over.n_closest[0], 1u)] = slot;
+      const uint32_t at = atomicAdd(&pool.fq->over.n_closest[0], 1u);
+      SRT_CHECK(at < pool.list_cap, SRT_CHK_OVERFLOW);
+      pool.olist[at] = slot;
     } else {
       pool.hit[slot] = make_uint2(hit, __float_as_uint(best));
     }

@@ -202,6 +202,7 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       if (finish) {
         color = color + throughput * sky;  // Q19
         const V3 pixel_color = v3(0.0f) + color;  // main(): pixelColor = vec3(0) + GetRayColor(...)
+        SRT_CHECK((unsigned long long)path.y * pool.n_pixels + path.x < pool.n_paths && path.x < pool.n_pixels, SRT_CHK_SAMPLE);
         pool.samples[(size_t)path.y * pool.n_pixels + path.x] = make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f);
         has_path = false;
         n_done++;
@@ -232,9 +233,11 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       const int my_rank = __popc(idle & ((1u << lane) - 1u));
       if (!has_path && my_rank < n_take) {
         const uint32_t idx = r_next + my_rank;
+        SRT_CHECK((idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)) < pool.list_cap, SRT_CHK_LIST_READ);
         const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
         if (entry != SRT_WF_HOLE) {
           const size_t slot = entry;
+          SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
           const float4 a = pool.ray[2 * slot], b = pool.ray[2 * slot + 1], t0 = pool.pst[2 * slot], c1 = pool.pst[2 * slot + 1];
           path = pool.path[slot];
           int x, y;
@@ -290,6 +293,7 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           const bool pr = (nr <= fr) && (dr < best) && (dr != -inf_());
           if (pl && pr) {
             const bool right_first = (MODE == TRAV_REFERENCE || !front_l || !front_r) ? true : !(dl < dr);
+            SRT_CHECK((sp - sp_base) / sp_step < (uint32_t)fp.stack_cap, SRT_CHK_STACK);
             wf_sts(sp, right_first ? nd.z : nd.w, __float_as_uint(right_first ? dl : dr));
             sp += sp_step;
             cur = right_first ? nd.w : nd.z;
