@@ -239,11 +239,23 @@ def run_gpu(args):
         ctx.set_option(pkg.OPT_FINDER, args.finder)
     if args.primary_cull >= 0:
         ctx.set_option(pkg.OPT_PRIMARY_CULL, args.primary_cull)
+    if args.sort_rays >= 0:
+        ctx.set_option(pkg.OPT_SORT_RAYS, args.sort_rays)
 
-    # the step's host inputs: the two noise tables live in pinned host memory (the library then DMAs them as they are
-    # and packs on the device; pageable tables are packed by host threads first), the scene arrays are pageable
+    # the step's host inputs live in pinned host memory: the two noise tables (the library DMAs them as they are and packs
+    # on the device; pageable tables are packed by host threads first) and the five scene arrays (a scene of more than
+    # 2 Mi triangles goes to the device as it is and is re-laid out there, csrc/srt_relayout.cu; smaller ones are walked
+    # on the host, where pinning changes nothing)
     pinned = [torch.from_numpy(np.ascontiguousarray(inp[k], np.float32)).pin_memory() for k in ("unit", "uniform")]
     noise_unit, noise_uniform = pinned[0].numpy(), pinned[1].numpy()
+    if inp["scene"] is not None:
+        for k in ("bvhs", "nodes", "materials", "triangles", "vertices"):
+            a = np.ascontiguousarray(inp["scene"][k])
+            t = torch.from_numpy(a.view(np.uint8).reshape(-1)).pin_memory()
+            pinned.append(t)
+            inp["scene"][k] = t.numpy().view(a.dtype).reshape(a.shape)
+    if args.device_relayout >= 0:
+        ctx.set_option(pkg.OPT_DEVICE_RELAYOUT, args.device_relayout)
 
     def upload_all():
         ctx.upload_noise(noise_unit, noise_uniform)  # queued DMA: runs while the host prepares the scene
@@ -389,7 +401,13 @@ def run_gpu(args):
     if inp["scene"] is not None:
         n_inner = int((inp["scene"]["nodes"]["count"] == 0).sum())
         n_leaf = int((inp["scene"]["nodes"]["count"] > 0).sum())
-        h2d += 64 * n_inner + 8 * n_leaf + 48 * len(inp["scene"]["triangles"]) + 32 * len(inp["scene"]["materials"]) + 96
+        relayout_on_device, relayout_ms = ctx.upload_info()
+        if relayout_on_device:  # the reference's arrays as they are (re-laid out by kernels on the device)
+            h2d += sum(int(inp["scene"][k].nbytes) for k in ("bvhs", "nodes", "triangles", "vertices")) + 32 * len(inp["scene"]["materials"])
+        else:                   # the records the host walk made
+            h2d += 64 * n_inner + 8 * n_leaf + 48 * len(inp["scene"]["triangles"]) + 32 * len(inp["scene"]["materials"]) + 96
+    else:
+        relayout_on_device, relayout_ms = False, 0.0
     d2h = W * H * 4
 
     if rank != 0:
@@ -422,6 +440,12 @@ def run_gpu(args):
     # triangle test; 32 B per node, 52 B per triangle), and of the shader's own walk for comparison across designs
     exe_flops_per_ray = 28.0 * exe_nodes_per_ray + 50.0 * exe_tris_per_ray
     exe_bytes_per_ray = 32.0 * exe_nodes_per_ray + 52.0 * exe_tris_per_ray
+    if not show_model:
+        # the sphere scene (configs[0]) has no BVH: CheckHit is SphereHit on the 5 spheres of main() (raytrace_compute.glsl:
+        # 93-141), about 30 fp32 operations each (two lengths, two dots, the discriminant, one sqrt, a divide, the interval
+        # test) on constants held in registers -- no scene bytes at all, so the bound can only be instruction issue; the
+        # one-thread-per-pixel kernel's whole duration (traversal + shading) is the denominator
+        exe_flops_per_ray, exe_bytes_per_ray = 5.0 * 30.0, 0.0
     ref_bytes_per_ray = 32.0 * ref_nodes_per_ray + 52.0 * ref_tris_per_ray
     achieved_tflops = rays * exe_flops_per_ray / k_s / 1e12
     achieved_gbs = rays * exe_bytes_per_ray / k_s / 1e9
@@ -457,7 +481,7 @@ def run_gpu(args):
         "frac_issue": frac_issue, "frac_memory": frac_mem, "memory_level": level,
         "achieved_tflops": achieved_tflops, "achieved_GBps": achieved_gbs,
         "flops_per_launch": rays * exe_flops_per_ray / k_launches, "bytes_per_launch": rays * exe_bytes_per_ray / k_launches,
-        "executed_per_ray": {"box_tests": exe_nodes_per_ray, "triangle_tests": exe_tris_per_ray,
+        "executed_per_ray": {"box_tests": exe_nodes_per_ray, "triangle_tests": exe_tris_per_ray, "sphere_tests": 0.0 if show_model else 5.0,
                              "flops": exe_flops_per_ray, "bytes": exe_bytes_per_ray},
         "reference_walk_per_ray": {"box_tests": ref_nodes_per_ray, "triangle_tests": ref_tris_per_ray, "bytes": ref_bytes_per_ray,
                                    "answered_GBps": rays * ref_bytes_per_ray / k_s / 1e9},
@@ -499,6 +523,7 @@ def run_gpu(args):
                    "l2": "512 MB device buffer rewritten between timed steps (L2 flush)",
                    "tail_paths": "library default" if args.tail_paths < 0 else args.tail_paths,
                    "primary_cull": "library default (on)" if args.primary_cull < 0 else args.primary_cull,
+                   "sort_rays": "library default (off)" if args.sort_rays < 0 else args.sort_rays,
                    "hit_finder": dict(zip(("active", "cost_reference", "cost_finder"), ctx.finder_info())) if show_model else None,
                    "ms_per_frame": ms_per_step / spp},
         "segments_per_step": segments / args.steps, "shadow_rays_per_step": shadow / args.steps,
@@ -509,7 +534,8 @@ def run_gpu(args):
         "segments_reaching_bvh_per_s_M": (segments / args.steps - culled_per_step) / (ms_per_step * 1e-3) / 1e6,
         "bounce_segments_per_s_M": (segments - paths) / args.steps / (ms_per_step * 1e-3) / 1e6,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": float(e2.item()) / e2e_steps * 1e3},
+                "ms_per_step": float(e2.item()) / e2e_steps * 1e3,
+                "scene_relayout": ("device kernels, %.1f ms" % relayout_ms) if relayout_on_device else "host walk"},
         "emulated_rank_of": args.stripe_of if (args.stripe_of > 1 and world == 1) else None,
         "collective_ms_per_step": (coll_ms / max(coll_n, 1)) if world > 1 else None,
         "gpu_launches": gpu_launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
@@ -537,10 +563,14 @@ def main():
                     help="<objects dir>/<NAME>/<NAME>.obj: render this model instead of the workload's scene (size, spp and depth stay "
                          "the workload's), e.g. the Airplane OBJ of BASELINE.json configs[2] where someone supplies it")
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
+    ap.add_argument("--device-relayout", type=int, default=-1, help="0/1/2: SRT_OPT_DEVICE_RELAYOUT (default: library default, 2)")
     ap.add_argument("--l2-persist", type=int, default=-1, help="1/0: pin the BVH top levels in L2 (default: library default, on)")
     ap.add_argument("--refill", type=int, default=0, help="refill threshold of the wavefront trace kernel (0 = default)")
     ap.add_argument("--primary-cull", type=int, default=-1,
                     help="1/0: primary rays that miss every root box end in the init kernel (-1 = library default, on)")
+    ap.add_argument("--sort-rays", type=int, default=-1,
+                    help="ray queues regrouped by origin cell before each wave: 0 off, 1 on (-1 = library default, off: measured "
+                         "slower on the soup)")
     ap.add_argument("--finder", type=int, default=-1,
                     help="hit finder of the wavefront schedule: 0 off, 1 on, 2 auto (-1 = library default, auto)")
     ap.add_argument("--tail-paths", type=int, default=-1,

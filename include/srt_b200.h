@@ -216,6 +216,19 @@ int srt_trace_rays_static(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, ui
  *                     single-GPU image within tolerance (1e-4 relative), not in bits
  * NCCL is loaded with dlopen("libnccl.so.2") when the first group is formed; without it these calls fail, the rest of
  * the library does not need it. */
+#define SRT_OPT_SORT_RAYS 16       /* wavefront schedule: 1 = before a wave is traced its two queues are regrouped by the cell the
+                                     rays start in (15-bit Morton code in the first BVH's root box; counting sort, 8 small
+                                     launches).  Another order of answering rays, never another result (parity-tested).
+                                     Default 0: measured on configs[4] (10 M-triangle soup) it is SLOWER, 354 vs 215 ms per
+                                     step -- the queues come out of the logic kernel in pixel order, which is already a finer
+                                     grouping by origin than any cell grid; what diverges there is the rays' directions */
+#define SRT_OPT_DEVICE_RELAYOUT 15 /* where srt_upload_scene turns the reference's arrays into this library's records: 0 = a serial walk
+                                     on the host, 1 = kernels on the device (the raw arrays are copied over as they are: DMA
+                                     when the caller's arrays are page-locked), 2 (default) = on the device for scenes of more
+                                     than 2 Mi triangles.  The device version needs the reference's node numbering (children
+                                     after their parent, bvh.h:96-131) and valid indices; anything else goes to the host walk,
+                                     which handles or reports it.  Same records up to where a node pair sits in its array: no
+                                     ray result depends on it (parity-tested).  srt_get_upload_info says what the last upload did */
 #define SRT_OPT_SPLIT 14
 #define SRT_SPLIT_BANDS 0
 #define SRT_SPLIT_SAMPLES 1
@@ -230,6 +243,10 @@ int srt_group_join(srt_ctx* ctx, int32_t rank, int32_t world, const void* id, ui
 int srt_create_multi(srt_ctx** out, const int* devices, int32_t n);
 /* Sum of the CUDA-event durations of this rank's collectives since the last call, and how many there were. */
 int srt_get_collective_ms(srt_ctx* ctx, double* ms, uint64_t* calls);
+
+/* What the last srt_upload_scene did: *on_device = 1 when the records were built by kernels (SRT_OPT_DEVICE_RELAYOUT),
+ * *device_ms = their CUDA-event time.  No reference counterpart (the reference uploads its arrays as they are). */
+int srt_get_upload_info(srt_ctx* ctx, int32_t* on_device, float* device_ms);
 
 int srt_get_counters(srt_ctx* ctx, srt_counters* out);
 /* Sums of the CUDA-event durations of the wavefront schedule's trace and logic launches since the last call

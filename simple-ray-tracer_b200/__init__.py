@@ -19,6 +19,8 @@ OPT_TRAVERSAL, OPT_COUNT_TRAVERSAL, OPT_L2_PERSIST, OPT_BLOCK_THREADS, OPT_SCHED
 OPT_WAVE_SLOTS, OPT_SAMPLE_BUDGET_MB, OPT_REFILL, OPT_TIME_KERNELS, OPT_TEXTURES, OPT_TAIL_PATHS, OPT_FINDER = 6, 7, 8, 9, 10, 11, 12
 OPT_PRIMARY_CULL = 13
 OPT_SPLIT = 14
+OPT_SORT_RAYS = 16
+OPT_DEVICE_RELAYOUT = 15
 SPLIT_BANDS, SPLIT_SAMPLES = 0, 1
 GROUP_ID_BYTES = 128
 TRACE_STATIC_MAX_RAYS = 65536
@@ -40,7 +42,7 @@ EXPORTS = ["srt_create", "srt_destroy", "srt_last_error", "srt_set_stream", "srt
            "srt_update_frame", "srt_upload_noise", "srt_set_lights", "srt_set_params", "srt_resize", "srt_set_rows", "srt_set_stripe",
            "srt_render", "srt_render_async", "srt_sync", "srt_read_output", "srt_read_accum", "srt_write_accum",
            "srt_tonemap", "srt_accum_device_ptr", "srt_enable_primary_ids", "srt_read_primary_ids", "srt_trace_rays", "srt_trace_rays_static", "srt_build_bvh", "srt_set_texture",
-           "srt_get_counters", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_measure_issue", "srt_check_selftest", "srt_group_unique_id", "srt_group_join",
+           "srt_get_counters", "srt_get_upload_info", "srt_get_kernel_times", "srt_get_finder_info", "srt_reset_counters", "srt_eval_detmath", "srt_measure_gather", "srt_measure_issue", "srt_check_selftest", "srt_group_unique_id", "srt_group_join",
            "srt_create_multi", "srt_get_collective_ms", "srt_version"]
 
 
@@ -288,6 +290,12 @@ class Context:
 
     def check_selftest(self):
         self._ck(self._lib.srt_check_selftest(self._h))
+
+    def upload_info(self):
+        """(on_device, device_ms) of the last upload_scene (see srt_get_upload_info)."""
+        on, ms = C.c_int32(), C.c_float()
+        self._ck(self._lib.srt_get_upload_info(self._h, C.byref(on), C.byref(ms)))
+        return bool(on.value), ms.value
 
     def measure_issue(self, mix):
         """Thread-instructions per second (in units of 1e9) of un-fused fp32 arithmetic (see srt_measure_issue)."""

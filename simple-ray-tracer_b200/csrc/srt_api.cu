@@ -21,6 +21,7 @@
 #include "srt_kernels.h"
 #include "srt_bvh_build.h"
 #include "srt_finder.h"
+#include "srt_relayout.h"
 #include "srt_ctx.h"
 
 using namespace srt;
@@ -70,6 +71,7 @@ static void free_pool(srt_ctx* ctx) {
   dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.path); dfree(p.p3);
   dfree(p.list[0]); dfree(p.list[1]); dfree(p.q); dfree(p.samples); dfree(p.tex);
   dfree(p.cand); dfree(p.rlist); dfree(p.olist); dfree(p.fq);
+  dfree(p.sort_bins); dfree(p.sort_keys); dfree(p.sort_tmp);
   dfree(ctx->d_culled);
   p.culled = nullptr;
   p.cap = 0;
@@ -188,6 +190,16 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_PRIMARY_CULL) {
     if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_PRIMARY_CULL: 0 or 1");
     ctx->primary_cull = value != 0;
+    return 0;
+  }
+  if (key == SRT_OPT_SORT_RAYS) {
+    if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_SORT_RAYS: 0 (off) or 1 (on)");
+    ctx->sort_rays = value;
+    return 0;
+  }
+  if (key == SRT_OPT_DEVICE_RELAYOUT) {
+    if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_DEVICE_RELAYOUT: 0 (host), 1 (device) or 2 (device for huge scenes)");
+    ctx->device_relayout = value;
     return 0;
   }
   if (key == SRT_OPT_TAIL_PATHS) {
@@ -379,14 +391,68 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
     return std::chrono::duration<double, std::milli>(b - a).count();
   };
   const auto t_start = now();
+  bool any_textured = false;
+  for (uint32_t i = 0; i < n_materials; ++i) any_textured = any_textured || materials[i].use_texture != 0;
   Relayout rl;
-  if (!relayout(ctx, bvhs, n_bvhs, nodes, n_nodes, n_triangles, rl)) return 1;
+  std::vector<TriRecord> tris;
+  // Huge scenes (or SRT_OPT_DEVICE_RELAYOUT 1): the raw arrays go to the device as they are and srt_relayout.cu builds the
+  // records there.  Anything it does not like -- a numbering that is not the reference's, or any invalid index -- comes
+  // back as "use the host walk", which then handles it or reports it in its own words.
+  bool on_device = false;
+  ctx->relayout_on_device = false;
+  ctx->relayout_device_ms = 0.0f;
+  if (ctx->device_relayout == 1 || (ctx->device_relayout == 2 && n_triangles > SRT_FINDER_MAX_TRIS)) {
+    srt_bvh_node* d_nodes = nullptr;
+    srt_triangle* d_tin = nullptr;
+    srt_vertex* d_vin = nullptr;
+    DeviceRelayoutOut dev;
+    std::string why;
+    int rc = 1;
+    // (the old records stay until the new ones stand: a refused upload leaves the previous scene in place, as on the host path)
+    cudaError_t e = cudaMalloc(&d_nodes, ((size_t)n_nodes ? n_nodes : 1) * sizeof(srt_bvh_node));
+    if (e == cudaSuccess) e = cudaMalloc(&d_tin, ((size_t)n_triangles ? n_triangles : 1) * sizeof(srt_triangle));
+    if (e == cudaSuccess) e = cudaMalloc(&d_vin, ((size_t)n_vertices ? n_vertices : 1) * sizeof(srt_vertex));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_nodes, nodes, (size_t)n_nodes * sizeof(srt_bvh_node), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_tin, triangles, (size_t)n_triangles * sizeof(srt_triangle), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_vin, vertices, (size_t)n_vertices * sizeof(srt_vertex), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess)
+      rc = relayout_on_device(bvhs, n_bvhs, d_nodes, n_nodes, d_tin, n_triangles, d_vin, n_vertices, n_materials, any_textured,
+                              &dev, ctx->stream, &why);
+    else
+      why = std::string("device re-layout: ") + cudaGetErrorString(e);
+    cudaFree(d_nodes); cudaFree(d_tin); cudaFree(d_vin);
+    if (rc == 1) return fail(ctx, "srt_upload_scene: %s", why.c_str());
+    if (rc == 0) {
+      on_device = true;
+      dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris);
+      ctx->d_pairs = dev.d_pairs; ctx->d_leaves = dev.d_leaves; ctx->d_tris = dev.d_tris;
+      ctx->dev_capacity[(void**)&ctx->d_pairs] = (dev.n_pairs ? dev.n_pairs : 1) * sizeof(NodePair);
+      ctx->dev_capacity[(void**)&ctx->d_leaves] = (dev.n_leaves ? dev.n_leaves : 1) * sizeof(uint2);
+      ctx->dev_capacity[(void**)&ctx->d_tris] = ((size_t)n_triangles ? n_triangles : 1) * sizeof(TriRecord);
+      rl.bvhs = dev.bvh_records;
+      rl.depth = dev.depth;
+      rl.top_pairs = 0;  // the pairs are in the reference's node order, not breadth-first: nothing to pin
+      if (any_textured) {
+        rl.tri_bvh.resize(n_triangles);
+        CU(ctx, cudaMemcpyAsync(rl.tri_bvh.data(), dev.d_tri_bvh, (size_t)n_triangles * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+      }
+      if (ctx->finder_mode != 0 && n_triangles > 0 && n_triangles <= SRT_FINDER_MAX_TRIS) {  // the finder build reads the records
+        tris.resize(n_triangles);
+        CU(ctx, cudaMemcpyAsync(tris.data(), dev.d_tris, (size_t)n_triangles * sizeof(TriRecord), cudaMemcpyDeviceToHost, ctx->stream));
+      }
+      CU(ctx, cudaStreamSynchronize(ctx->stream));
+      cudaFree(dev.d_tri_bvh);
+      ctx->relayout_on_device = true;
+      ctx->relayout_device_ms = dev.device_ms;
+    }
+  }
+  if (!on_device && !relayout(ctx, bvhs, n_bvhs, nodes, n_nodes, n_triangles, rl)) return 1;
   if (rl.depth > SRT_STACK_SIZE - 1)
     return fail(ctx, "srt_upload_scene: BVH depth %d overflows the shader's %d-entry traversal stack "
                 "(ray_intersects.glsl:100)", rl.depth, SRT_STACK_SIZE);
 
-  std::vector<TriRecord> tris(n_triangles);
-  {
+  if (!on_device) {
+    tris.resize(n_triangles);
     // per-triangle records; a big scene (the 10 M-triangle soup) is cut over host threads.  bad_* keep the lowest
     // offending triangle so that the message does not depend on the thread count.
     std::atomic<uint32_t> bad_vertex{0xFFFFFFFFu}, bad_material{0xFFFFFFFFu};
@@ -455,8 +521,6 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
     mats[i].b = make_float4(m.specular[0], m.specular[1], m.specular[2], 0.0f);
   }
   // textured-albedo option: texture coordinates per triangle + the BVH whose frame gives the model-space hit point
-  bool any_textured = false;
-  for (uint32_t i = 0; i < n_materials; ++i) any_textured = any_textured || materials[i].use_texture != 0;
   dfree(ctx->d_tex_tris);
   if (any_textured) {
     std::vector<TexTri> tt(n_triangles);
@@ -481,9 +545,10 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   dfree(ctx->d_tex_info);
   dfree(ctx->d_texels);
   CU(ctx, cudaStreamSynchronize(ctx->stream));
-  if (upload_vec(ctx, ctx->d_pairs, rl.pairs) || upload_vec(ctx, ctx->d_leaves, rl.leaves) ||
-      upload_vec(ctx, ctx->d_tris, tris) || upload_vec(ctx, ctx->d_mats, mats) || upload_vec(ctx, ctx->d_bvhs, rl.bvhs))
+  if (!on_device && (upload_vec(ctx, ctx->d_pairs, rl.pairs) || upload_vec(ctx, ctx->d_leaves, rl.leaves) ||
+                     upload_vec(ctx, ctx->d_tris, tris)))
     return 1;
+  if (upload_vec(ctx, ctx->d_mats, mats) || upload_vec(ctx, ctx->d_bvhs, rl.bvhs)) return 1;
   CU(ctx, cudaStreamSynchronize(ctx->stream));  // host vectors go out of scope
   ctx->h_bvhs.assign(bvhs, bvhs + n_bvhs);
   ctx->h_bvh_records = rl.bvhs;
@@ -496,6 +561,14 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   if (log)
     fprintf(stderr, "srt_upload_scene: relayout + records %.2f ms, finder build + upload %.2f ms, rest %.2f ms\n",
             ms(t_start, t_relayout), ms(t_relayout, t_finder), ms(t_finder, now()));
+  return 0;
+}
+
+extern "C" int srt_get_upload_info(srt_ctx* ctx, int32_t* on_device, float* device_ms) {
+  if (!ctx) return 1;
+  if (!ctx->have_scene) return fail(ctx, "srt_get_upload_info: no scene uploaded");
+  if (on_device) *on_device = ctx->relayout_on_device ? 1 : 0;
+  if (device_ms) *device_ms = ctx->relayout_device_ms;
   return 0;
 }
 
@@ -811,6 +884,8 @@ bool finder_active(const srt_ctx* ctx) {
   return ctx->finder_ready && ctx->count_traversal != 1 && (ctx->finder_mode == 1 || (ctx->finder_mode == 2 && ctx->finder_worthwhile));
 }
 
+bool sort_active(const srt_ctx* ctx) { return ctx->sort_rays == 1; }
+
 int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_finder) {
   PathPool& p = ctx->pool;
   if (!(ctx->pool_slots >= slots && p.q)) {
@@ -835,6 +910,12 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
     CU(ctx, cudaMalloc(&p.olist, ctx->pool_list_cap * 4));
     CU(ctx, cudaMalloc(&p.fq, sizeof(FinderQueues)));
     CU(ctx, cudaMemsetAsync(p.fq, 0, sizeof(FinderQueues), ctx->stream));
+  }
+  if (sort_active(ctx) && !p.sort_bins) {
+    CU(ctx, cudaMalloc(&p.sort_bins, SRT_SORT_BINS_HOST * sizeof(uint32_t)));
+    CU(ctx, cudaMemsetAsync(p.sort_bins, 0, SRT_SORT_BINS_HOST * sizeof(uint32_t), ctx->stream));
+    CU(ctx, cudaMalloc(&p.sort_keys, ctx->pool_list_cap * 4));
+    CU(ctx, cudaMalloc(&p.sort_tmp, ctx->pool_list_cap * 4));
   }
   p.cap = slots;
   p.list_cap = (uint32_t)ctx->pool_list_cap;
@@ -924,6 +1005,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
   // the hit finder gives the reference visiting order's result (bit for bit); so does every kernel beside it then
   const bool finder = finder_active(ctx);
   const int traversal = finder ? (int)TRAV_REFERENCE : ctx->traversal;
+  const bool sort = sort_active(ctx);
 
   for (int done = 0; done < fp_all.n_frames; done += chunk_frames) {
     FrameParams fp = fp_all;
@@ -985,6 +1067,10 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
           if (timing_events(ev)) return 1;
           CU(ctx, cudaEventRecord(ev[0], ctx->stream));
         }
+        if (sort && batch > 0) {  // the paths the tail starts from, grouped like a wave's (inside the timed bracket)
+          CU(ctx, launch_wf_sort(sc, ctx->pool, parity, ctx->stream));
+          ctx->kernel_launches += 8;
+        }
         CU(ctx, launch_wf_tail(sc, fp, ctx->pool, parity, traversal, chunk_ids, ctx->d_counters, ctx->stream));
         if (ctx->time_kernels) {
           CU(ctx, cudaEventRecord(ev[1], ctx->stream));
@@ -1002,6 +1088,11 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
         if (ctx->time_kernels) {
           if (timing_events(ev)) return 1;
           CU(ctx, cudaEventRecord(ev[0], ctx->stream));
+        }
+        // every wave but the camera rays' (one origin): queues regrouped by the cell the rays start in (srt_wf_sort.cuh)
+        if (sort && !(batch == 0 && w == 0)) {
+          CU(ctx, launch_wf_sort(sc, ctx->pool, parity, ctx->stream));
+          ctx->kernel_launches += 8;
         }
         // camera rays are in the chunk's first wave and, while slots still take new paths, in any later one
         const int finder_kind = !finder ? 0 : ((batch == 0 && w == 0) || !all_out) ? 2 : 1;

@@ -461,4 +461,10 @@ cudaError_t build_bvh_device(const float* centre, const float* lo, const float* 
   return cudaSuccess;
 }
 
+// the file's exclusive scan for other translation units (srt_relayout.cu): out[i] = in[0] + ... + in[i-1]
+cudaError_t device_exclusive_scan(const uint32_t* in, uint32_t* out, uint32_t n, uint32_t* scratch, cudaStream_t stream) {
+  return exclusive_scan(in, out, n, scratch, stream);
+}
+size_t device_scan_scratch_entries(uint32_t n) { return scan_scratch_entries(n); }
+
 }  // namespace srt

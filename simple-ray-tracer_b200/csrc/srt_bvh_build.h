@@ -26,4 +26,9 @@ struct BvhBuildResult {
 cudaError_t build_bvh_device(const float* centre, const float* lo, const float* hi, uint32_t n, srt_bvh_node* nodes_out,
                              uint32_t* order_out, BvhBuildResult* result, cudaStream_t stream, const char** what);
 
+// Exclusive scan of n uint32 on the device (tiles of 2048, tile sums scanned recursively); scratch must hold
+// device_scan_scratch_entries(n) uint32.  in and out may not alias.
+cudaError_t device_exclusive_scan(const uint32_t* in, uint32_t* out, uint32_t n, uint32_t* scratch, cudaStream_t stream);
+size_t device_scan_scratch_entries(uint32_t n);
+
 }  // namespace srt

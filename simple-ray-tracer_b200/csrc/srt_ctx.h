@@ -107,6 +107,10 @@ struct srt_ctx {
   size_t timing_used = 0;
   int refill_threshold = 0;                    // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL; 0 = each kernel's own default)
   uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
+  int device_relayout = 2;                      // SRT_OPT_DEVICE_RELAYOUT: 0 host walk, 1 device, 2 device above SRT_FINDER_MAX_TRIS triangles
+  bool relayout_on_device = false;              // what the last upload did
+  float relayout_device_ms = 0.0f;
+  int sort_rays = 0;                            // SRT_OPT_SORT_RAYS: 0 off (default: measured slower, see srt_b200.h), 1 on
   bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
   uint32_t* d_culled = nullptr;                 // bit map of the paths the cull ended (one bit per sample entry)
   uint32_t tail_paths = 1u << 20;               // live paths at which the tail kernel takes over (SRT_OPT_TAIL_PATHS, 0 = never)

@@ -214,6 +214,11 @@ struct PathPool {
   // primary cull only (null otherwise): one bit per path of the launch, frame-major like `samples`; a set bit says the
   // path ended in wf_init_kernel with the sky sample, which is then NOT stored (wf_resolve_kernel adds the constant)
   uint32_t* culled;
+  // SRT_OPT_SORT_RAYS only (null otherwise; srt_wf_sort.cuh): the bins of the counting sort, per queue entry its key, and
+  // the sorted copy of the queue
+  uint32_t* sort_bins;
+  uint32_t* sort_keys;
+  uint32_t* sort_tmp;
   uint32_t n_pixels;           // pixel slots of this launch (8x4 tiles x 32)
   unsigned long long n_paths;  // n_pixels * frames of this launch
 };

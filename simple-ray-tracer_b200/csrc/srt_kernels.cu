@@ -15,6 +15,7 @@
 #include "srt_wavefront.cuh"
 #include "srt_wf_tail.cuh"
 #include "srt_wf_find.cuh"
+#include "srt_wf_sort.cuh"
 
 namespace srt {
 
@@ -435,6 +436,25 @@ cudaError_t wf_tail_launch(const DeviceScene& sc, const FrameParams& fp, const P
   return cudaGetLastError();
 }
 }  // namespace
+
+// Both queues of the wave `parity` regrouped by the cell their rays start in (srt_wf_sort.cuh): 8 small launches.
+cudaError_t launch_wf_sort(const DeviceScene& sc, const PathPool& pool, int parity, cudaStream_t stream) {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaError_t e;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+  }
+  const unsigned grid = (unsigned)sms * 8u;
+  for (int shadow = 0; shadow < 2; ++shadow) {
+    wf_sort_hist_kernel<<<grid, SRT_SORT_THREADS, 0, stream>>>(sc, pool, parity, shadow);
+    wf_sort_scan_kernel<<<1, 1024, 0, stream>>>(pool);
+    wf_sort_scatter_kernel<<<grid, SRT_SORT_THREADS, 0, stream>>>(pool, parity, shadow);
+    wf_sort_copy_kernel<<<grid, SRT_SORT_THREADS, 0, stream>>>(pool, parity, shadow);
+  }
+  return cudaGetLastError();
+}
 
 cudaError_t launch_wf_tail(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            uint32_t* ids, DeviceCounters* counters, cudaStream_t stream) {

@@ -175,11 +175,11 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   }
   SRT_CHECK(slot < pool.cap && slot < pool.list_cap, SRT_CHK_SLOT);
   SRT_CHECK(x >= 0 && x < fp.width && y >= 0 && y < fp.height, SRT_CHK_PIXEL);
-  pool.ray[2 * (size_t)slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
-  pool.ray[2 * (size_t)slot + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
-  pool.pst[2 * (size_t)slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-  pool.pst[2 * (size_t)slot + 1] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0)));
-  pool.path[slot] = make_uint2(pixel, f);
+  __stcs(pool.ray + 2 * (size_t)slot, make_float4(fp.center.x, fp.center.y, fp.center.z, inf_()));
+  __stcs(pool.ray + 2 * (size_t)slot + 1, make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
+  __stcs(pool.pst + 2 * (size_t)slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
+  __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0))));
+  __stcs(pool.path + slot, make_uint2(pixel, f));
   pool.list[0][slot] = slot;
 }
 
@@ -475,7 +475,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     const bool valid = entry != SRT_WF_HOLE;
     const uint32_t slot = valid ? entry : 0u;
     SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
-    const uint2 path = valid ? pool.path[slot] : make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
+    const uint2 path = valid ? __ldcs(pool.path + slot) : make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
     int x = 0, y = 0;
     tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
     const int pix = y * fp.height + x;  // Q4
@@ -489,8 +489,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     bool shade = false, have_light = false, finish = false, emit_closest = false, emit_shadow = false, put_aside = false;
 
     if (valid) {
-      const uint2 h = pool.hit[slot];
-      const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1], t0 = pool.pst[2 * (size_t)slot], c1 = pool.pst[2 * (size_t)slot + 1];
+      // slot records stream through once per wave (gigabytes, no reuse within L2's reach): evict-first loads and stores keep
+      // them from pushing the noise table (8 MB, ~10 random gathers per shaded path) out of L2 -- profiles/r02h_ncu_full_summary.txt
+      const uint2 h = __ldcs(pool.hit + slot);
+      const float4 a = __ldcs(pool.ray + 2 * (size_t)slot), b = __ldcs(pool.ray + 2 * (size_t)slot + 1), t0 = __ldcs(pool.pst + 2 * (size_t)slot), c1 = __ldcs(pool.pst + 2 * (size_t)slot + 1);
       origin = v3(a.x, a.y, a.z);
       throughput = v3(t0.x, t0.y, t0.z);
       color = v3(c1.x, c1.y, c1.z);
@@ -522,11 +524,11 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
             const V3 lpos = v3(l.px, l.py, l.pz);
             const V3 sd = normalize_(lpos - origin);  // :168
             const float len = length_(lpos - origin);  // :169
-            pool.ray[2 * (size_t)slot] = make_float4(origin.x, origin.y, origin.z, len);
-            pool.ray[2 * (size_t)slot + 1] = make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8)));
-            pool.p3[slot] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(hit_prim));
-            pool.pst[2 * (size_t)slot] = make_float4(throughput.x, throughput.y, throughput.z, light_weight);
-            if (sc.tex_tris != nullptr) pool.tex[slot] = make_float4(tex_albedo.x, tex_albedo.y, tex_albedo.z, has_tex ? 1.0f : 0.0f);
+            __stcs(pool.ray + 2 * (size_t)slot, make_float4(origin.x, origin.y, origin.z, len));
+            __stcs(pool.ray + 2 * (size_t)slot + 1, make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8))));
+            __stcs(pool.p3 + slot, make_float4(dir.x, dir.y, dir.z, __uint_as_float(hit_prim)));
+            __stcs(pool.pst + 2 * (size_t)slot, make_float4(throughput.x, throughput.y, throughput.z, light_weight));
+            if (sc.tex_tris != nullptr) __stcs(pool.tex + slot, make_float4(tex_albedo.x, tex_albedo.y, tex_albedo.z, has_tex ? 1.0f : 0.0f));
             emit_shadow = true;
             n_shadow++;
           } else {
@@ -535,14 +537,14 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         }
       } else {
         // ---- a shadow ray came back (:235-246): the path still stands at the ray's origin ----
-        const float4 c3 = pool.p3[slot];
+        const float4 c3 = __ldcs(pool.p3 + slot);
         dir = v3(c3.x, c3.y, c3.z);
         hit_prim = __float_as_uint(c3.w);
         li = (int)(__float_as_uint(b.w) >> 8);
         light_weight = t0.w;
         shadow_mult = (h.x != SRT_NO_HIT) ? 0.0f : 1.0f;
         if (sc.tex_tris != nullptr) {
-          const float4 ta = pool.tex[slot];
+          const float4 ta = __ldcs(pool.tex + slot);
           tex_albedo = v3(ta.x, ta.y, ta.z);
           has_tex = ta.w != 0.0f;
         }
@@ -604,10 +606,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           n_capped++;
           finish = true;
         } else {
-          pool.ray[2 * (size_t)slot] = make_float4(p.x, p.y, p.z, inf_());
-          pool.ray[2 * (size_t)slot + 1] = make_float4(new_dir.x, new_dir.y, new_dir.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
-          pool.pst[2 * (size_t)slot] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
-          pool.pst[2 * (size_t)slot + 1] = make_float4(color.x, color.y, color.z, __uint_as_float(wf_pack(depth, rand_index, iter)));
+          __stcs(pool.ray + 2 * (size_t)slot, make_float4(p.x, p.y, p.z, inf_()));
+          __stcs(pool.ray + 2 * (size_t)slot + 1, make_float4(new_dir.x, new_dir.y, new_dir.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
+          __stcs(pool.pst + 2 * (size_t)slot, make_float4(throughput.x, throughput.y, throughput.z, 0.0f));
+          __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(color.x, color.y, color.z, __uint_as_float(wf_pack(depth, rand_index, iter))));
           emit_closest = true;
           n_seg++;
         }
@@ -632,7 +634,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         color = color + throughput * sky;  // Q19
         const V3 pixel_color = v3(0.0f) + color;  // main(): pixelColor = vec3(0) + GetRayColor(...)
         SRT_CHECK((unsigned long long)path.y * pool.n_pixels + path.x < pool.n_paths && path.x < pool.n_pixels, SRT_CHK_SAMPLE);
-        pool.samples[(size_t)path.y * pool.n_pixels + path.x] = make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f);
+        __stcs(pool.samples + (size_t)path.y * pool.n_pixels + path.x, make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f));
         const unsigned long long next = base + (unsigned long long)__popc(m_f & lt_mask);
         if (next < pool.n_paths) {
           uint32_t pixel, f;
@@ -640,11 +642,11 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           int nx, ny;
           tile_pixel(fp, pixel >> 5, pixel & 31, nx, ny);
           const V3 d = wf_primary_dir(sc, fp, nx, ny, ny * fp.height + nx, (int)f);
-          pool.ray[2 * (size_t)slot] = make_float4(fp.center.x, fp.center.y, fp.center.z, inf_());
-          pool.ray[2 * (size_t)slot + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST));
-          pool.pst[2 * (size_t)slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-          pool.pst[2 * (size_t)slot + 1] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0)));
-          pool.path[slot] = make_uint2(pixel, f);
+          __stcs(pool.ray + 2 * (size_t)slot, make_float4(fp.center.x, fp.center.y, fp.center.z, inf_()));
+          __stcs(pool.ray + 2 * (size_t)slot + 1, make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
+          __stcs(pool.pst + 2 * (size_t)slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
+          __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0))));
+          __stcs(pool.path + slot, make_uint2(pixel, f));
           emit_closest = true;
           n_seg++;
         } else {

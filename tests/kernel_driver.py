@@ -68,6 +68,8 @@ def main():
         ("wavefront, plain walk, no cull, no tail", {pkg.OPT_TAIL_PATHS: 0, pkg.OPT_FINDER: 0, pkg.OPT_PRIMARY_CULL: 0}),
         ("wavefront, small pool (slots regenerate)", {pkg.OPT_WAVE_SLOTS: 2048, pkg.OPT_TAIL_PATHS: 256}),
         ("wavefront, ordered traversal, finder off", {pkg.OPT_FINDER: 0, pkg.OPT_TRAVERSAL: pkg.TRAV_ORDERED}),
+        ("wavefront, queues sorted by origin cell", {pkg.OPT_SORT_RAYS: 1, pkg.OPT_TAIL_PATHS: 1024}),
+        ("wavefront, sorted queues, plain walk, no tail", {pkg.OPT_SORT_RAYS: 1, pkg.OPT_FINDER: 0, pkg.OPT_TAIL_PATHS: 0}),
         ("persistent schedule", {pkg.OPT_SCHEDULE: pkg.SCHED_PERSISTENT}),
         ("regeneration schedule", {pkg.OPT_SCHEDULE: pkg.SCHED_REGEN}),
         ("per-path schedule", {pkg.OPT_SCHEDULE: pkg.SCHED_PER_PATH}),

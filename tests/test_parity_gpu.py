@@ -414,3 +414,29 @@ def test_trace_rays_reference_fixture_shape(pkg, ctx, oracle):
     ohit2, _, _ = oracle.trace_rays(scene2, rays)
     assert np.array_equal(hit, ohit2)
     assert (hit == pkg.NO_HIT).all()
+
+
+@pytest.mark.parametrize("schedule", [3, 30, 31])
+def test_sorted_ray_queues_change_no_bit(pkg, ctx, oracle, tmp_path, schedule):
+    """SRT_OPT_SORT_RAYS: the wave's queues regrouped by the cell the rays start in (counting sort by a 15-bit Morton code,
+    csrc/srt_wf_sort.cuh) -- another ORDER of answering independent rays, the same picture: soup at depth 8 (the case it is
+    for), Rubik from inside, and a small pool whose slots regenerate (holes in the queues)."""
+    ctx.set_option(pkg.OPT_SORT_RAYS, 1)
+    scene, _ = scenes.soup_scene(20000, str(tmp_path))
+    cam = scenes.reset_camera(True, origin=(0.0, 0.0, 120.0))
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 256, 144, True, 2, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8,
+                                    schedule=schedule)
+    oacc, oout, oids, ocnt = cpu_render(oracle, 256, 144, True, 2, scene=scene, cam=cam, max_depth=8)
+    assert np.array_equal(ids, oids)
+    assert_bit_exact(acc, oacc)
+    assert cnt["segments"] == ocnt["segments"] and cnt["shadow_rays"] == ocnt["shadow_rays"]
+    rubik = scenes.rubik_scene()
+    inside = scenes.look_camera((0.3, 9.1, 12.0), -70.0, -12.0)
+    ctx.set_option(pkg.OPT_WAVE_SLOTS, 8192)
+    acc, out, ids, cnt = gpu_render(pkg, ctx, 256, 256, True, 3, pkg.TRAV_REFERENCE, scene=rubik, cam=inside, max_depth=8,
+                                    schedule=schedule)
+    oacc, oout, oids, ocnt = cpu_render(oracle, 256, 256, True, 3, scene=rubik, cam=inside, max_depth=8)
+    assert np.array_equal(ids, oids)
+    assert_bit_exact(acc, oacc)
+    assert np.array_equal(out, oout)
+    assert cnt["segments"] == ocnt["segments"] and cnt["shadow_rays"] == ocnt["shadow_rays"]
