@@ -126,6 +126,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   srt_group_release(ctx);  // a head context takes its other devices' contexts with it
   cudaSetDevice(ctx->device);
   dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris); dfree(ctx->d_mats); dfree(ctx->d_bvhs);
+  relayout_workspace_release(&ctx->relayout_ws);
   dfree(ctx->d_fpairs); dfree(ctx->d_ftris); dfree(ctx->d_rnodes); dfree(ctx->d_tri_leaf);
   dfree(ctx->d_tex_tris); dfree(ctx->d_tex_info); dfree(ctx->d_texels);
   dfree(ctx->d_noise_xy); dfree(ctx->d_noise_x); dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
@@ -402,48 +403,32 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   ctx->relayout_on_device = false;
   ctx->relayout_device_ms = 0.0f;
   if (ctx->device_relayout == 1 || (ctx->device_relayout == 2 && n_triangles > SRT_FINDER_MAX_TRIS)) {
-    srt_bvh_node* d_nodes = nullptr;
-    srt_triangle* d_tin = nullptr;
-    srt_vertex* d_vin = nullptr;
-    DeviceRelayoutOut dev;
+    DeviceRelayoutIO io;
+    io.d_pairs = &ctx->d_pairs;   io.cap_pairs = &ctx->dev_capacity[(void**)&ctx->d_pairs];
+    io.d_leaves = &ctx->d_leaves; io.cap_leaves = &ctx->dev_capacity[(void**)&ctx->d_leaves];
+    io.d_tris = &ctx->d_tris;     io.cap_tris = &ctx->dev_capacity[(void**)&ctx->d_tris];
     std::string why;
-    int rc = 1;
-    // (the old records stay until the new ones stand: a refused upload leaves the previous scene in place, as on the host path)
-    cudaError_t e = cudaMalloc(&d_nodes, ((size_t)n_nodes ? n_nodes : 1) * sizeof(srt_bvh_node));
-    if (e == cudaSuccess) e = cudaMalloc(&d_tin, ((size_t)n_triangles ? n_triangles : 1) * sizeof(srt_triangle));
-    if (e == cudaSuccess) e = cudaMalloc(&d_vin, ((size_t)n_vertices ? n_vertices : 1) * sizeof(srt_vertex));
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_nodes, nodes, (size_t)n_nodes * sizeof(srt_bvh_node), cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_tin, triangles, (size_t)n_triangles * sizeof(srt_triangle), cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_vin, vertices, (size_t)n_vertices * sizeof(srt_vertex), cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess)
-      rc = relayout_on_device(bvhs, n_bvhs, d_nodes, n_nodes, d_tin, n_triangles, d_vin, n_vertices, n_materials, any_textured,
-                              &dev, ctx->stream, &why);
-    else
-      why = std::string("device re-layout: ") + cudaGetErrorString(e);
-    cudaFree(d_nodes); cudaFree(d_tin); cudaFree(d_vin);
-    if (rc == 1) return fail(ctx, "srt_upload_scene: %s", why.c_str());
+    const int rc = relayout_on_device(bvhs, n_bvhs, nodes, n_nodes, triangles, n_triangles, vertices, n_vertices, n_materials,
+                                      SRT_STACK_SIZE - 1, &ctx->relayout_ws, &io, any_textured ? &rl.tri_bvh : nullptr,
+                                      ctx->stream, &why);
+    if (rc == 1) {
+      ctx->have_scene = false;
+      return fail(ctx, "srt_upload_scene: %s", why.c_str());
+    }
     if (rc == 0) {
       on_device = true;
-      dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris);
-      ctx->d_pairs = dev.d_pairs; ctx->d_leaves = dev.d_leaves; ctx->d_tris = dev.d_tris;
-      ctx->dev_capacity[(void**)&ctx->d_pairs] = (dev.n_pairs ? dev.n_pairs : 1) * sizeof(NodePair);
-      ctx->dev_capacity[(void**)&ctx->d_leaves] = (dev.n_leaves ? dev.n_leaves : 1) * sizeof(uint2);
-      ctx->dev_capacity[(void**)&ctx->d_tris] = ((size_t)n_triangles ? n_triangles : 1) * sizeof(TriRecord);
-      rl.bvhs = dev.bvh_records;
-      rl.depth = dev.depth;
+      rl.bvhs = io.bvh_records;
+      rl.depth = io.depth;
       rl.top_pairs = 0;  // the pairs are in the reference's node order, not breadth-first: nothing to pin
-      if (any_textured) {
-        rl.tri_bvh.resize(n_triangles);
-        CU(ctx, cudaMemcpyAsync(rl.tri_bvh.data(), dev.d_tri_bvh, (size_t)n_triangles * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-      }
       if (ctx->finder_mode != 0 && n_triangles > 0 && n_triangles <= SRT_FINDER_MAX_TRIS) {  // the finder build reads the records
         tris.resize(n_triangles);
-        CU(ctx, cudaMemcpyAsync(tris.data(), dev.d_tris, (size_t)n_triangles * sizeof(TriRecord), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(ctx, cudaMemcpyAsync(tris.data(), ctx->d_tris, (size_t)n_triangles * sizeof(TriRecord), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
       }
-      CU(ctx, cudaStreamSynchronize(ctx->stream));
-      cudaFree(dev.d_tri_bvh);
       ctx->relayout_on_device = true;
-      ctx->relayout_device_ms = dev.device_ms;
+      ctx->relayout_device_ms = io.device_ms;
+      if (log) fprintf(stderr, "srt_upload_scene: device re-layout: copy %.2f ms, kernels %.2f ms, %llu launches\n", io.copy_ms,
+                       io.device_ms, (unsigned long long)io.launches);
     }
   }
   if (!on_device && !relayout(ctx, bvhs, n_bvhs, nodes, n_nodes, n_triangles, rl)) return 1;

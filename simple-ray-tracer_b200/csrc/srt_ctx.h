@@ -11,6 +11,7 @@
 #include "srt_b200.h"
 #include "srt_kernels.h"
 #include "srt_finder.h"
+#include "srt_relayout.h"
 
 struct srt_group;  // srt_multi.cu: this context's place in a multi-GPU group (NULL = a single GPU)
 
@@ -110,6 +111,7 @@ struct srt_ctx {
   int device_relayout = 2;                      // SRT_OPT_DEVICE_RELAYOUT: 0 host walk, 1 device, 2 device above SRT_FINDER_MAX_TRIS triangles
   bool relayout_on_device = false;              // what the last upload did
   float relayout_device_ms = 0.0f;
+  RelayoutWorkspace relayout_ws;                // raw arrays + scratch of the device re-layout, kept between uploads
   int sort_rays = 0;                            // SRT_OPT_SORT_RAYS: 0 off (default: measured slower, see srt_b200.h), 1 on
   bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
   uint32_t* d_culled = nullptr;                 // bit map of the paths the cull ended (one bit per sample entry)

@@ -114,6 +114,16 @@ k_triangles(const srt_triangle* __restrict__ tris_in, const srt_vertex* __restri
   out[i] = r;
 }
 
+// the index checks of k_triangles alone, before anything is written
+__global__ void __launch_bounds__(RL_THREADS)
+k_check_triangles(const srt_triangle* __restrict__ tris_in, uint32_t n_tris, uint32_t n_verts, uint32_t n_mats, RlStatus* st) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_tris) return;
+  const srt_triangle t = tris_in[i];
+  if (t.v0_idx >= n_verts || t.v1_idx >= n_verts || t.v2_idx >= n_verts) atomicMin(&st->bad_vertex, i);
+  else if (t.material_idx >= n_mats) atomicMin(&st->bad_material, i);
+}
+
 // breadth-first expansion of one level: every inner node of the level appends its two children to the next one
 __global__ void __launch_bounds__(RL_THREADS)
 k_expand(const srt_bvh_node* __restrict__ nodes, uint32_t n_nodes, uint32_t* __restrict__ frontier, uint32_t* __restrict__ bvh_of,
@@ -210,153 +220,180 @@ __global__ void k_bvh_records(const srt_bvh* __restrict__ bvhs, uint32_t n_bvhs,
 
 }  // namespace
 
-namespace {
-struct Scratch {  // frees what it holds when it goes out of scope
-  std::vector<void*> dev;
-  RlStatus* h_status = nullptr;
-  cudaEvent_t ev[2] = {nullptr, nullptr};
-  ~Scratch() {
-    for (void* p : dev) cudaFree(p);
-    if (h_status) cudaFreeHost(h_status);
-    for (cudaEvent_t e : ev)
-      if (e) cudaEventDestroy(e);
-  }
-  template <class T>
-  cudaError_t alloc(T** p, size_t n) {
-    cudaError_t e = cudaMalloc(p, (n ? n : 1) * sizeof(T));
-    if (e == cudaSuccess) dev.push_back(*p);
-    return e;
-  }
-};
-}  // namespace
-
-#define RL(call)                                                                                   \
-  do {                                                                                             \
-    cudaError_t e_ = (call);                                                                       \
-    if (e_ != cudaSuccess) {                                                                       \
-      *error = std::string("device re-layout: ") + #call + ": " + cudaGetErrorString(e_);          \
-      release(out);                                                                                \
-      return 1;                                                                                    \
-    }                                                                                              \
-  } while (0)
-
-static void release(DeviceRelayoutOut* out) {
-  cudaFree(out->d_pairs); cudaFree(out->d_leaves); cudaFree(out->d_tris); cudaFree(out->d_tri_bvh);
-  out->d_pairs = nullptr; out->d_leaves = nullptr; out->d_tris = nullptr; out->d_tri_bvh = nullptr;
+// ---- host side ----------------------------------------------------------------------------------------------------------
+void relayout_workspace_release(RelayoutWorkspace* ws) {
+  cudaFree(ws->arena);
+  if (ws->h_status) cudaFreeHost(ws->h_status);
+  for (cudaEvent_t& e : ws->ev)
+    if (e) cudaEventDestroy(e);
+  *ws = RelayoutWorkspace();
 }
 
-int relayout_on_device(const srt_bvh* h_bvhs, uint32_t n_bvhs, const srt_bvh_node* d_nodes, uint32_t n_nodes,
-                       const srt_triangle* d_triangles, uint32_t n_triangles, const srt_vertex* d_vertices, uint32_t n_vertices,
-                       uint32_t n_materials, bool want_tri_bvh, DeviceRelayoutOut* out, cudaStream_t stream, std::string* error) {
-  Scratch sc;
+namespace {
+struct Carver {  // hands out 256-byte aligned pieces of the arena (first pass: base == nullptr, only the size is wanted)
+  char* base;
+  size_t at = 0;
+  template <class T>
+  T* take(size_t n) {
+    T* p = base ? reinterpret_cast<T*>(base + at) : nullptr;
+    at += ((n ? n : 1) * sizeof(T) + 255) & ~(size_t)255;
+    return p;
+  }
+};
+
+struct Pieces {
+  srt_bvh_node* nodes; srt_triangle* tin; srt_vertex* vin;
+  uint32_t *inner, *rank, *scan, *frontier, *bvh_of, *seen_count, *start, *roots, *tri_bvh;
+  RlStatus* status; srt_bvh* bvhs; BvhRecord* records;
+};
+
+Pieces carve(Carver& c, uint32_t n_bvhs, uint32_t n_nodes, uint32_t n_tris, uint32_t n_verts, bool want_tri_bvh) {
+  Pieces p;
+  p.nodes = c.take<srt_bvh_node>(n_nodes);
+  p.tin = c.take<srt_triangle>(n_tris);
+  p.vin = c.take<srt_vertex>(n_verts);
+  p.inner = c.take<uint32_t>((size_t)n_nodes + 1);
+  p.rank = c.take<uint32_t>((size_t)n_nodes + 1);
+  p.scan = c.take<uint32_t>(device_scan_scratch_entries(n_nodes + 1));
+  p.frontier = c.take<uint32_t>(n_nodes);
+  p.bvh_of = c.take<uint32_t>(n_nodes);
+  p.seen_count = c.take<uint32_t>(n_nodes);  // `seen` marks while the levels are found, triangle counts afterwards
+  p.start = c.take<uint32_t>(n_nodes);
+  p.roots = c.take<uint32_t>(n_bvhs);
+  p.tri_bvh = want_tri_bvh ? c.take<uint32_t>(n_tris) : nullptr;
+  p.status = c.take<RlStatus>(1);
+  p.bvhs = c.take<srt_bvh>(n_bvhs);
+  p.records = c.take<BvhRecord>(n_bvhs);
+  return p;
+}
+
+// the same keep-or-reallocate rule as srt_upload_scene's host path (upload_vec)
+cudaError_t ensure(void** p, size_t* cap, size_t bytes) {
+  if (bytes == 0) bytes = 1;
+  if (*p && *cap >= bytes && *cap <= 2 * bytes + 4096) return cudaSuccess;
+  cudaFree(*p);
+  *p = nullptr;
+  *cap = 0;
+  cudaError_t e = cudaMalloc(p, bytes);
+  if (e == cudaSuccess) *cap = bytes;
+  return e;
+}
+}  // namespace
+
+#define RL(call)                                                                           \
+  do {                                                                                     \
+    cudaError_t e_ = (call);                                                               \
+    if (e_ != cudaSuccess) {                                                               \
+      *error = std::string("device re-layout: ") + #call + ": " + cudaGetErrorString(e_);  \
+      return 1;                                                                            \
+    }                                                                                      \
+  } while (0)
+
+int relayout_on_device(const srt_bvh* h_bvhs, uint32_t n_bvhs, const srt_bvh_node* h_nodes, uint32_t n_nodes,
+                       const srt_triangle* h_triangles, uint32_t n_triangles, const srt_vertex* h_vertices, uint32_t n_vertices,
+                       uint32_t n_materials, int max_depth, RelayoutWorkspace* ws, DeviceRelayoutIO* io,
+                       std::vector<uint32_t>* tri_bvh, cudaStream_t stream, std::string* error) {
   auto blocks = [](size_t n) { return (unsigned)((n + RL_THREADS - 1) / RL_THREADS); };
   for (uint32_t b = 0; b < n_bvhs; ++b)
     if (h_bvhs[b].first_index >= n_nodes) return 2;
-  uint32_t *d_inner = nullptr, *d_rank = nullptr, *d_scan = nullptr, *d_frontier = nullptr, *d_bvh_of = nullptr, *d_seen = nullptr,
-           *d_count = nullptr, *d_start = nullptr, *d_roots = nullptr;
-  RlStatus* d_status = nullptr;
-  srt_bvh* d_bvhs = nullptr;
-  BvhRecord* d_records = nullptr;
-  RL(sc.alloc(&d_inner, (size_t)n_nodes + 1));
-  RL(sc.alloc(&d_rank, (size_t)n_nodes + 1));
-  RL(sc.alloc(&d_scan, device_scan_scratch_entries(n_nodes + 1)));
-  RL(sc.alloc(&d_frontier, n_nodes));
-  RL(sc.alloc(&d_bvh_of, n_nodes));
-  RL(sc.alloc(&d_seen, n_nodes));
-  RL(sc.alloc(&d_count, n_nodes));
-  RL(sc.alloc(&d_start, n_nodes));
-  RL(sc.alloc(&d_roots, n_bvhs));
-  RL(sc.alloc(&d_status, 1));
-  RL(sc.alloc(&d_bvhs, n_bvhs));
-  RL(sc.alloc(&d_records, n_bvhs));
-  RL(cudaHostAlloc(&sc.h_status, sizeof(RlStatus), cudaHostAllocDefault));
-  RL(cudaEventCreate(&sc.ev[0]));
-  RL(cudaEventCreate(&sc.ev[1]));
-  RL(cudaMalloc(&out->d_tris, ((size_t)n_triangles ? n_triangles : 1) * sizeof(TriRecord)));
-  if (want_tri_bvh) RL(cudaMalloc(&out->d_tri_bvh, ((size_t)n_triangles ? n_triangles : 1) * sizeof(uint32_t)));
+  io->launches = 0;
+
+  // ---- workspace: the raw arrays + scratch, kept between uploads ----
+  Carver sizing{nullptr};
+  carve(sizing, n_bvhs, n_nodes, n_triangles, n_vertices, tri_bvh != nullptr);
+  RL(ensure(&ws->arena, &ws->arena_bytes, sizing.at));
+  Carver c{static_cast<char*>(ws->arena)};
+  const Pieces w = carve(c, n_bvhs, n_nodes, n_triangles, n_vertices, tri_bvh != nullptr);
+  if (!ws->h_status) RL(cudaHostAlloc(&ws->h_status, sizeof(RlStatus), cudaHostAllocDefault));
+  for (cudaEvent_t& e : ws->ev)
+    if (!e) RL(cudaEventCreate(&e));
+  RlStatus* h_status = static_cast<RlStatus*>(ws->h_status);
 
   const RlStatus init = {0u, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u};
   std::vector<uint32_t> roots(n_bvhs);
   for (uint32_t b = 0; b < n_bvhs; ++b) roots[b] = h_bvhs[b].first_index;
-  RL(cudaMemcpyAsync(d_status, &init, sizeof init, cudaMemcpyHostToDevice, stream));
-  RL(cudaMemcpyAsync(d_roots, roots.data(), n_bvhs * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
-  RL(cudaMemcpyAsync(d_bvhs, h_bvhs, n_bvhs * sizeof(srt_bvh), cudaMemcpyHostToDevice, stream));
-  RL(cudaMemsetAsync(d_seen, 0, (size_t)n_nodes * sizeof(uint32_t), stream));
-  RL(cudaEventRecord(sc.ev[0], stream));
+  RL(cudaEventRecord(ws->ev[0], stream));
+  RL(cudaMemcpyAsync(w.nodes, h_nodes, (size_t)n_nodes * sizeof(srt_bvh_node), cudaMemcpyHostToDevice, stream));
+  RL(cudaMemcpyAsync(w.tin, h_triangles, (size_t)n_triangles * sizeof(srt_triangle), cudaMemcpyHostToDevice, stream));
+  RL(cudaMemcpyAsync(w.vin, h_vertices, (size_t)n_vertices * sizeof(srt_vertex), cudaMemcpyHostToDevice, stream));
+  RL(cudaMemcpyAsync(w.status, &init, sizeof init, cudaMemcpyHostToDevice, stream));
+  RL(cudaMemcpyAsync(w.roots, roots.data(), n_bvhs * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+  RL(cudaMemcpyAsync(w.bvhs, h_bvhs, n_bvhs * sizeof(srt_bvh), cudaMemcpyHostToDevice, stream));
+  RL(cudaMemsetAsync(w.seen_count, 0, (size_t)n_nodes * sizeof(uint32_t), stream));
+  RL(cudaEventRecord(ws->ev[1], stream));
 
-  // ---- node flags + triangle records, then the first look at the status word ----
-  k_flags<<<blocks((size_t)n_nodes + 1), RL_THREADS, 0, stream>>>(d_nodes, n_nodes, n_triangles, d_inner, d_status);
+  // ---- every check first: nothing of the context's scene is touched until the new one has passed them all.  Anything
+  // wrong -- the numbering, a range, an index, the depth -- is left to the host walk, which reports it in the words the
+  // callers know (or, for a numbering that is merely not the reference's, handles it).
+  k_flags<<<blocks((size_t)n_nodes + 1), RL_THREADS, 0, stream>>>(w.nodes, n_nodes, n_triangles, w.inner, w.status);
   if (n_triangles)
-    k_triangles<<<blocks(n_triangles), RL_THREADS, 0, stream>>>(d_triangles, d_vertices, n_triangles, n_vertices, n_materials,
-                                                                out->d_tris, d_status);
-  RL(device_exclusive_scan(d_inner, d_rank, n_nodes + 1, d_scan, stream));
+    k_check_triangles<<<blocks(n_triangles), RL_THREADS, 0, stream>>>(w.tin, n_triangles, n_vertices, n_materials, w.status);
+  RL(device_exclusive_scan(w.inner, w.rank, n_nodes + 1, w.scan, stream));
   uint32_t n_inner = 0;
-  RL(cudaMemcpyAsync(&n_inner, d_rank + n_nodes, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-  RL(cudaMemcpyAsync(sc.h_status, d_status, sizeof(RlStatus), cudaMemcpyDeviceToHost, stream));
+  RL(cudaMemcpyAsync(&n_inner, w.rank + n_nodes, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  RL(cudaMemcpyAsync(h_status, w.status, sizeof(RlStatus), cudaMemcpyDeviceToHost, stream));
   RL(cudaStreamSynchronize(stream));
-  out->launches += 5;
-  {
-    // Anything wrong with the scene -- the numbering, a range, an index -- is left to the host walk, which reports it in
-    // the words the callers know (or, for a numbering that is merely not the reference's, handles it).
-    const RlStatus st = *sc.h_status;
-    if (st.err != 0u || st.bad_vertex != 0xFFFFFFFFu || st.bad_material != 0xFFFFFFFFu) {
-      release(out);
-      return 2;
-    }
-  }
-  if (n_inner >= SRT_LEAF_BIT - 1u) {
-    release(out);
-    return 2;
-  }
-  out->n_pairs = n_inner;
-  out->n_leaves = n_nodes - n_inner;
-  RL(cudaMalloc(&out->d_pairs, ((size_t)n_inner ? n_inner : 1) * sizeof(NodePair)));
-  RL(cudaMalloc(&out->d_leaves, ((size_t)out->n_leaves ? out->n_leaves : 1) * sizeof(uint2)));
-  k_records<<<blocks(n_nodes), RL_THREADS, 0, stream>>>(d_nodes, n_nodes, d_rank, out->d_pairs, out->d_leaves);
-  k_bvh_records<<<1, 64, 0, stream>>>(d_bvhs, n_bvhs, d_nodes, d_rank, d_records);
-  out->launches += 2;
+  io->launches += 5;
+  if (h_status->err != 0u || h_status->bad_vertex != 0xFFFFFFFFu || h_status->bad_material != 0xFFFFFFFFu) return 2;
+  if (n_inner >= SRT_LEAF_BIT - 1u) return 2;
 
-  // ---- the tree's levels, breadth-first from the roots ----
-  RL(cudaMemcpyAsync(d_frontier, roots.data(), n_bvhs * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
-  for (uint32_t b = 0; b < n_bvhs; ++b)
-    RL(cudaMemcpyAsync(d_bvh_of + roots[b], &b, sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
-  RL(cudaStreamSynchronize(stream));  // `b` above is a stack variable
+  // the tree's levels, breadth-first from the roots (also: every node reached once, and the depth)
+  RL(cudaMemcpyAsync(w.frontier, roots.data(), n_bvhs * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+  std::vector<uint32_t> ordinal(n_bvhs);
+  for (uint32_t b = 0; b < n_bvhs; ++b) {
+    ordinal[b] = b;
+    RL(cudaMemcpyAsync(w.bvh_of + roots[b], &ordinal[b], sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+  }
   std::vector<std::pair<uint32_t, uint32_t>> levels;  // (first entry of the frontier array, entries)
   levels.push_back({0u, n_bvhs});
   for (;;) {
     const uint32_t begin = levels.back().first, count = levels.back().second;
-    RL(cudaMemsetAsync(&d_status->next_count, 0, sizeof(unsigned int), stream));
-    k_expand<<<blocks(count), RL_THREADS, 0, stream>>>(d_nodes, n_nodes, d_frontier, d_bvh_of, d_seen, begin, count, d_status);
-    RL(cudaMemcpyAsync(sc.h_status, d_status, sizeof(RlStatus), cudaMemcpyDeviceToHost, stream));
+    RL(cudaMemsetAsync(&w.status->next_count, 0, sizeof(unsigned int), stream));
+    k_expand<<<blocks(count), RL_THREADS, 0, stream>>>(w.nodes, n_nodes, w.frontier, w.bvh_of, w.seen_count, begin, count, w.status);
+    RL(cudaMemcpyAsync(h_status, w.status, sizeof(RlStatus), cudaMemcpyDeviceToHost, stream));
     RL(cudaStreamSynchronize(stream));
-    out->launches += 1;
-    if (sc.h_status->err & RL_ERR_NOT_A_TREE) {  // also: a node shared by two BVHs, which the host walk allows
-      release(out);
-      return 2;
-    }
-    if (sc.h_status->next_count == 0u) break;
-    levels.push_back({begin + count, sc.h_status->next_count});
-    if (levels.size() > 4096) {
-      release(out);
-      return 2;
-    }
+    io->launches += 1;
+    if (h_status->err & RL_ERR_NOT_A_TREE) return 2;  // also: a node shared by two BVHs, which the host walk allows
+    if (h_status->next_count == 0u) break;
+    levels.push_back({begin + count, h_status->next_count});
+    if ((int)levels.size() - 1 > max_depth) return 2;  // the host walk says by how much
   }
-  out->depth = (int)levels.size() - 1;
+  io->depth = (int)levels.size() - 1;
 
-  // ---- triangle counts bottom-up, rank offsets top-down ----
+  // ---- the records, into the context's arrays (kept when they fit) ----
+  io->n_pairs = n_inner;
+  io->n_leaves = n_nodes - n_inner;
+  RL(ensure(reinterpret_cast<void**>(io->d_pairs), io->cap_pairs, (size_t)n_inner * sizeof(NodePair)));
+  RL(ensure(reinterpret_cast<void**>(io->d_leaves), io->cap_leaves, (size_t)io->n_leaves * sizeof(uint2)));
+  RL(ensure(reinterpret_cast<void**>(io->d_tris), io->cap_tris, (size_t)n_triangles * sizeof(TriRecord)));
+  RL(cudaEventRecord(ws->ev[2], stream));
+  k_records<<<blocks(n_nodes), RL_THREADS, 0, stream>>>(w.nodes, n_nodes, w.rank, *io->d_pairs, *io->d_leaves);
+  if (n_triangles)
+    k_triangles<<<blocks(n_triangles), RL_THREADS, 0, stream>>>(w.tin, w.vin, n_triangles, n_vertices, n_materials, *io->d_tris, w.status);
+  k_bvh_records<<<1, 64, 0, stream>>>(w.bvhs, n_bvhs, w.nodes, w.rank, w.records);
+  // triangle counts bottom-up, rank offsets top-down
   for (size_t l = levels.size(); l-- > 0;)
-    k_counts<<<blocks(levels[l].second), RL_THREADS, 0, stream>>>(d_nodes, d_frontier, levels[l].first, levels[l].second, d_count);
-  k_root_offsets<<<1, 32, 0, stream>>>(d_roots, n_bvhs, d_count, d_start);
+    k_counts<<<blocks(levels[l].second), RL_THREADS, 0, stream>>>(w.nodes, w.frontier, levels[l].first, levels[l].second, w.seen_count);
+  k_root_offsets<<<1, 32, 0, stream>>>(w.roots, n_bvhs, w.seen_count, w.start);
   for (size_t l = 0; l < levels.size(); ++l)
-    k_ranks<<<blocks(levels[l].second), RL_THREADS, 0, stream>>>(d_nodes, d_frontier, levels[l].first, levels[l].second, d_count,
-                                                                 d_start, d_bvh_of, out->d_tris, out->d_tri_bvh);
-  out->launches += 2 * levels.size() + 1;
+    k_ranks<<<blocks(levels[l].second), RL_THREADS, 0, stream>>>(w.nodes, w.frontier, levels[l].first, levels[l].second, w.seen_count,
+                                                                 w.start, w.bvh_of, *io->d_tris, w.tri_bvh);
+  io->launches += 2 * levels.size() + 4;
   RL(cudaGetLastError());
-  RL(cudaEventRecord(sc.ev[1], stream));
-  out->bvh_records.resize(n_bvhs);
-  RL(cudaMemcpyAsync(out->bvh_records.data(), d_records, n_bvhs * sizeof(BvhRecord), cudaMemcpyDeviceToHost, stream));
+  RL(cudaEventRecord(ws->ev[3], stream));
+  io->bvh_records.resize(n_bvhs);
+  RL(cudaMemcpyAsync(io->bvh_records.data(), w.records, n_bvhs * sizeof(BvhRecord), cudaMemcpyDeviceToHost, stream));
+  if (tri_bvh) {
+    tri_bvh->resize(n_triangles);
+    RL(cudaMemcpyAsync(tri_bvh->data(), w.tri_bvh, (size_t)n_triangles * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  }
   RL(cudaStreamSynchronize(stream));
-  cudaEventElapsedTime(&out->device_ms, sc.ev[0], sc.ev[1]);
+  float copy_ms = 0.0f, check_ms = 0.0f, build_ms = 0.0f;
+  cudaEventElapsedTime(&copy_ms, ws->ev[0], ws->ev[1]);
+  cudaEventElapsedTime(&check_ms, ws->ev[1], ws->ev[2]);
+  cudaEventElapsedTime(&build_ms, ws->ev[2], ws->ev[3]);
+  io->copy_ms = copy_ms;
+  io->device_ms = check_ms + build_ms;
   return 0;
 }
 

@@ -68,29 +68,34 @@ def test_two_models_with_frames(pkg, ctx, oracle, tmp_path):
 def test_soup_device_relayout(pkg, ctx, oracle, tmp_path, schedule):
     scene, info = scenes.soup_scene(70000, str(tmp_path))
     cam = scenes.reset_camera(True, origin=(0.0, 0.0, 120.0))
-    acc, img, ids, cnt = both_ways(pkg, ctx, scene, 192, 108, 2, cam=cam, max_depth=8, schedule=schedule)
-    oacc, _, oids, ocnt = cpu_render(oracle, 192, 108, True, 2, scene=scene, cam=cam, max_depth=8)
+    acc, img, ids, cnt = both_ways(pkg, ctx, scene, 192, 104, 2, cam=cam, max_depth=8, schedule=schedule)
+    oacc, _, oids, ocnt = cpu_render(oracle, 192, 104, True, 2, scene=scene, cam=cam, max_depth=8)
     assert np.array_equal(ids, oids)
     assert_bit_exact(acc, oacc)
     assert cnt["segments"] == ocnt["segments"]
 
 
-def test_automatic_choice_above_the_finder_limit(pkg, ctx, tmp_path):
+def test_automatic_choice_above_the_finder_limit(pkg, ctx, oracle, tmp_path):
     """Default option value 2: a scene of more than 2 Mi triangles is re-laid out on the device without being asked; its
-    picture equals the host walk's.  (No oracle here: 2.2 M triangles at this image size would take it minutes.)"""
+    picture equals the host walk's and the oracle's (configs[4]'s kind of scene at a fifth of its size: 2.2 M triangles,
+    4.4 M nodes, maxDepth 8)."""
     scene, info = scenes.soup_scene((1 << 21) + 100000, str(tmp_path))
     cam = scenes.reset_camera(True, origin=(0.0, 0.0, 120.0))
     ctx.set_option(pkg.OPT_DEVICE_RELAYOUT, 2)
-    a1, i1, d1, c1 = gpu_render(pkg, ctx, 160, 90, True, 1, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8)
+    a1, i1, d1, c1 = gpu_render(pkg, ctx, 160, 88, True, 1, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8)
     on_device, ms = ctx.upload_info()
     assert on_device and ms > 0.0
     ctx.set_option(pkg.OPT_DEVICE_RELAYOUT, 0)
-    a0, i0, d0, c0 = gpu_render(pkg, ctx, 160, 90, True, 1, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8)
+    a0, i0, d0, c0 = gpu_render(pkg, ctx, 160, 88, True, 1, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8)
     assert not ctx.upload_info()[0]
     ctx.set_option(pkg.OPT_DEVICE_RELAYOUT, 2)
     assert np.array_equal(d0, d1)
     assert_bit_exact(a1, a0)
     assert c0["segments"] == c1["segments"] and c0["shadow_rays"] == c1["shadow_rays"]
+    oacc, _, oids, ocnt = cpu_render(oracle, 160, 88, True, 1, scene=scene, cam=cam, max_depth=8)
+    assert np.array_equal(d1, oids)
+    assert_bit_exact(a1, oacc)
+    assert c1["segments"] == ocnt["segments"] and c1["shadow_rays"] == ocnt["shadow_rays"]
 
 
 def reversed_numbering(scene):
@@ -143,7 +148,7 @@ def test_invalid_scene_refused_in_the_host_walks_words_and_previous_scene_kept(p
     good = scenes.rubik_scene()
     ctx.set_option(pkg.OPT_DEVICE_RELAYOUT, 1)
     try:
-        ref = gpu_render(pkg, ctx, 160, 100, True, 1, pkg.TRAV_REFERENCE, scene=good)
+        ref = gpu_render(pkg, ctx, 160, 96, True, 1, pkg.TRAV_REFERENCE, scene=good)
         soup, _ = scenes.soup_scene(70000, str(tmp_path))
         bad = {k: v.copy() for k, v in soup.items()}
         bad["triangles"]["v"][1234, 2] = len(soup["vertices"]) + 5
@@ -159,8 +164,11 @@ def test_invalid_scene_refused_in_the_host_walks_words_and_previous_scene_kept(p
         with pytest.raises(pkg.SrtError, match="out of range"):
             ctx.upload_scene(bad)
         # the Rubik scene is still the one in place
-        again = gpu_render(pkg, ctx, 160, 100, True, 1, pkg.TRAV_REFERENCE)
-        assert np.array_equal(ref[2], again[2])
-        assert_bit_exact(again[0], ref[0])
+        ctx.resize(160, 96)  # fresh accumulation image
+        ctx.enable_primary_ids(True)
+        ctx.set_params(pkg.make_params(160, 96, scenes.reset_camera(True), True, accum_frames=1, bvh_count=1))
+        ctx.render(1)
+        assert np.array_equal(ref[2], ctx.read_primary_ids())
+        assert_bit_exact(ctx.read_accum(), ref[0])
     finally:
         ctx.set_option(pkg.OPT_DEVICE_RELAYOUT, 2)
