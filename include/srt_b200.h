@@ -46,7 +46,9 @@ typedef struct srt_counters {
                                          reference BVH in its visiting order; the hit finder is switched off)
                                      2 = count the box / triangle tests the DEFAULT path really executes (hit finder +
                                          replay + overflow walk, primary cull) */
-#define SRT_OPT_L2_PERSIST 3     /* 1 = pin BVH top levels + noise tables in L2 with an access-policy window (default 1) */
+#define SRT_OPT_L2_PERSIST 3     /* which array an L2 access-policy window (persisting hits) is put on for the context's stream:
+                                    0 = none, 1 (default) and 2 = the BVH's top levels, 3 = the two noise tables (12 B per pixel, read at
+                                    hashed positions ~10 times per shaded path).  Measured: no gain from either; 3 is slower on Rubik */
 #define SRT_OPT_BLOCK_THREADS 4  /* threads per block of the path kernel (multiple of 32) */
 #define SRT_OPT_SCHEDULE 5       /* 0 = one path at a time per lane (the shader's schedule)
                                     1 = per-lane state machine with path regeneration + warp-synchronous traversal

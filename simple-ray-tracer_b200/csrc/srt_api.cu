@@ -68,8 +68,8 @@ static void dfree(T*& p) {
 
 static void free_pool(srt_ctx* ctx) {
   PathPool& p = ctx->pool;
-  dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.path); dfree(p.p3);
-  dfree(p.list[0]); dfree(p.list[1]); dfree(p.q); dfree(p.samples); dfree(p.tex);
+  dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.path); dfree(p.pend);
+  dfree(p.list[0]); dfree(p.list[1]); dfree(p.dlist[0]); dfree(p.dlist[1]); dfree(p.q); dfree(p.samples);
   dfree(p.cand); dfree(p.rlist); dfree(p.olist); dfree(p.fq);
   dfree(p.sort_bins); dfree(p.sort_keys); dfree(p.sort_tmp);
   dfree(ctx->d_culled);
@@ -129,7 +129,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   relayout_workspace_release(&ctx->relayout_ws);
   dfree(ctx->d_fpairs); dfree(ctx->d_ftris); dfree(ctx->d_rnodes); dfree(ctx->d_tri_leaf);
   dfree(ctx->d_tex_tris); dfree(ctx->d_tex_info); dfree(ctx->d_texels);
-  dfree(ctx->d_noise_xy); dfree(ctx->d_noise_x); dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
+  dfree(ctx->d_noise_xy); ctx->d_noise_x = nullptr; dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
   dfree(ctx->d_counters);
   free_pool(ctx);
   for (cudaEvent_t e : ctx->timing_events) cudaEventDestroy(e);
@@ -138,6 +138,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   dfree(ctx->d_noise_raw);
   for (cudaEvent_t& e : ctx->wave_events)
     if (e) cudaEventDestroy(e);
+  if (ctx->fork.aux) { cudaStreamDestroy(ctx->fork.aux); cudaEventDestroy(ctx->fork.forked); cudaEventDestroy(ctx->fork.joined); }
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -163,7 +164,10 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
       if (value < 0 || value > 2) return fail(ctx, "SRT_OPT_COUNT_TRAVERSAL: 0, 1 or 2");
       ctx->count_traversal = value;
       return 0;
-    case SRT_OPT_L2_PERSIST: ctx->l2_persist = value != 0; return 0;
+    case SRT_OPT_L2_PERSIST:
+      if (value < 0 || value > 3) return fail(ctx, "SRT_OPT_L2_PERSIST: 0 (off), 1 (automatic), 2 (BVH top levels) or 3 (noise tables)");
+      ctx->l2_persist = value;
+      return 0;
     case SRT_OPT_BLOCK_THREADS:
       if (value < 32 || value > SRT_MAX_BLOCK_THREADS || value % 32) return fail(ctx, "SRT_OPT_BLOCK_THREADS: 32..%d, multiple of 32", SRT_MAX_BLOCK_THREADS);
       ctx->block_threads = value;
@@ -581,10 +585,11 @@ extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const floa
   if (ctx->noise_count != count || !ctx->d_noise_xy) {
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     dfree(ctx->d_noise_xy);
-    dfree(ctx->d_noise_x);
+    ctx->d_noise_x = nullptr;  // second part of the same allocation
     ctx->noise_count = 0;
-    CU(ctx, cudaMalloc(&ctx->d_noise_xy, (size_t)count * sizeof(float2)));
-    CU(ctx, cudaMalloc(&ctx->d_noise_x, (size_t)count * sizeof(float)));
+    // one allocation, .xy table first: a single L2 access-policy window can cover both (apply_l2_window)
+    CU(ctx, cudaMalloc(&ctx->d_noise_xy, (size_t)count * (sizeof(float2) + sizeof(float))));
+    ctx->d_noise_x = reinterpret_cast<float*>(ctx->d_noise_xy + count);
   }
   // Tables in page-locked host memory (cudaHostAlloc / cudaHostRegister): both go to the device as they are, by DMA,
   // and a kernel packs them there; the call returns with the copies queued, so the tables must stay as they are until
@@ -879,19 +884,23 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
     p.samples = nullptr;
     free_pool(ctx);
     p.samples = keep;
-    CU(ctx, cudaMalloc(&p.ray, (size_t)slots * 32)); CU(ctx, cudaMalloc(&p.hit, (size_t)slots * 8));
+    // per slot: two rays (closest-hit + shadow, 32 B each) and their two answers (8 B each), path state, pixel/frame, the
+    // direct-light term put aside for the shadow ray
+    CU(ctx, cudaMalloc(&p.ray, (size_t)slots * 64)); CU(ctx, cudaMalloc(&p.hit, (size_t)slots * 16));
     CU(ctx, cudaMalloc(&p.pst, (size_t)slots * 32)); CU(ctx, cudaMalloc(&p.path, (size_t)slots * 8));
-    // every logic warp can leave one partly used reservation per queue: room for those holes beside the slots
-    ctx->pool_list_cap = (size_t)slots + 2u * (size_t)launch_wf_max_logic_warps() * 256u;
+    CU(ctx, cudaMalloc(&p.pend, (size_t)slots * 16));
+    // a wave holds up to two rays per slot; every logic warp can leave one partly used reservation per queue: room for
+    // those holes beside the rays
+    ctx->pool_list_cap = 2u * (size_t)slots + 2u * (size_t)launch_wf_max_logic_warps() * 256u;
     if (ctx->pool_list_cap >= 0xFFFFFFFFull) return fail(ctx, "wavefront pool too large");
-    CU(ctx, cudaMalloc(&p.p3, (size_t)slots * 16)); CU(ctx, cudaMalloc(&p.list[0], ctx->pool_list_cap * 4));
-    CU(ctx, cudaMalloc(&p.list[1], ctx->pool_list_cap * 4)); CU(ctx, cudaMalloc(&p.q, sizeof(WaveCounters)));
+    CU(ctx, cudaMalloc(&p.list[0], ctx->pool_list_cap * 4)); CU(ctx, cudaMalloc(&p.list[1], ctx->pool_list_cap * 4));
+    CU(ctx, cudaMalloc(&p.dlist[0], (size_t)slots * 4)); CU(ctx, cudaMalloc(&p.dlist[1], (size_t)slots * 4));
+    CU(ctx, cudaMalloc(&p.q, sizeof(WaveCounters)));
     ctx->pool_slots = slots;
   }
-  if (ctx->textures_on && !p.tex) CU(ctx, cudaMalloc(&p.tex, (size_t)ctx->pool_slots * 16));
-  if (want_finder && !p.fq) {
-    CU(ctx, cudaMalloc(&p.cand, (size_t)ctx->pool_slots * SRT_CAND_MAX * sizeof(uint2)));
-    CU(ctx, cudaMalloc(&p.rlist, (size_t)ctx->pool_slots * sizeof(uint2)));
+  if (want_finder && !p.fq) {  // sized by rays: 2 per slot
+    CU(ctx, cudaMalloc(&p.cand, 2u * (size_t)ctx->pool_slots * SRT_CAND_MAX * sizeof(uint2)));
+    CU(ctx, cudaMalloc(&p.rlist, 2u * (size_t)ctx->pool_slots * sizeof(uint2)));
     CU(ctx, cudaMalloc(&p.olist, ctx->pool_list_cap * 4));
     CU(ctx, cudaMalloc(&p.fq, sizeof(FinderQueues)));
     CU(ctx, cudaMemsetAsync(p.fq, 0, sizeof(FinderQueues), ctx->stream));
@@ -903,6 +912,7 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
     CU(ctx, cudaMalloc(&p.sort_tmp, ctx->pool_list_cap * 4));
   }
   p.cap = slots;
+  p.ray_cap = 2u * slots;
   p.list_cap = (uint32_t)ctx->pool_list_cap;
   if (ctx->sample_entries < sample_entries) {
     CU(ctx, cudaStreamSynchronize(ctx->stream));
@@ -915,6 +925,12 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
   if (!ctx->h_live) CU(ctx, cudaHostAlloc(&ctx->h_live, 4 * sizeof(WaveCounters), cudaHostAllocDefault));
   for (cudaEvent_t& e : ctx->wave_events)
     if (!e) CU(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  if (!ctx->fork.aux) {
+    CU(ctx, cudaStreamCreateWithFlags(&ctx->fork.aux, cudaStreamNonBlocking));
+    CU(ctx, cudaEventCreateWithFlags(&ctx->fork.forked, cudaEventDisableTiming));
+    CU(ctx, cudaEventCreateWithFlags(&ctx->fork.joined, cudaEventDisableTiming));
+    ctx->use_fork = getenv("SRT_NO_FORK") == nullptr;
+  }
   return 0;
 }
 
@@ -922,7 +938,10 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
 // the launching stream; the rest of the scene streams through the remaining L2.  Matters when the scene is far larger
 // than the 126 MB L2 (the 10 M-triangle soup); a scene that fits L2 entirely is resident anyway.
 int apply_l2_window(srt_ctx* ctx) {
-  const bool want = ctx->l2_persist && ctx->have_scene && ctx->top_pair_bytes > 0;
+  // What the window covers (one contiguous range per stream): the breadth-first top levels of the node pairs (1, 2) or the
+  // two packed noise tables (3) -- 12 B per pixel, read at hashed positions some ten times per shaded path
+  // (raytrace_utils.glsl:15,52) while gigabytes of path-slot records stream through L2.  Measured on one B200
+  // (profiles/r02m_l2_window.txt): neither helps; the noise window costs 0.8 ms per Rubik step.
   if (ctx->l2_max_window < 0) {  // device limits, asked once (cudaGetDeviceProperties is slow)
     int w = 0, p = 0;
     CU(ctx, cudaDeviceGetAttribute(&w, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device));
@@ -931,14 +950,28 @@ int apply_l2_window(srt_ctx* ctx) {
     ctx->l2_max_persist = p;
   }
   if (ctx->l2_max_window <= 0 || ctx->l2_max_persist <= 0) return 0;
+  const void* ptr = nullptr;
   size_t bytes = 0;
-  if (want) {
-    bytes = std::min(ctx->top_pair_bytes, (size_t)ctx->l2_max_window);
+  if (ctx->l2_persist != 0) {
+    const bool model = ctx->have_scene && ctx->params.show_model;
+    const size_t scene_bytes = model ? (size_t)ctx->n_nodes / 2 * sizeof(NodePair) + (size_t)ctx->n_tris * sizeof(TriRecord) : 0;
+    const size_t noise_bytes = (size_t)ctx->noise_count * 12;
+    (void)scene_bytes;
+    const bool noise = ctx->l2_persist == 3;  // measured: slower (Rubik logic kernel 11.1 vs 10.2 ms per step), so never automatic
+    if (noise && ctx->d_noise_xy && noise_bytes > 0) {
+      ptr = ctx->d_noise_xy;
+      bytes = noise_bytes;
+    } else if (!noise && model && ctx->top_pair_bytes > 0) {
+      ptr = ctx->d_pairs;
+      bytes = ctx->top_pair_bytes;
+    }
+    bytes = std::min(bytes, (size_t)ctx->l2_max_window);
     bytes = std::min(bytes, (size_t)ctx->l2_max_persist);
   }
+  const bool want = bytes > 0;
   // nothing to do when the window that is set already covers the same bytes of the same array on the same stream (a
   // frame loop that re-uploads its scene lands in the kept allocation: cudaDeviceSetLimit alone costs milliseconds)
-  if (want == ctx->l2_window_on && (!want || (ctx->l2_window_stream == ctx->stream && ctx->l2_window_ptr == (const void*)ctx->d_pairs &&
+  if (want == ctx->l2_window_on && (!want || (ctx->l2_window_stream == ctx->stream && ctx->l2_window_ptr == ptr &&
                                               ctx->l2_window_bytes == bytes)))
     return 0;
   cudaStreamAttrValue attr;
@@ -948,11 +981,12 @@ int apply_l2_window(srt_ctx* ctx) {
       CU(ctx, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes));
       ctx->l2_limit_set = bytes;
     }
-    attr.accessPolicyWindow.base_ptr = ctx->d_pairs;
+    attr.accessPolicyWindow.base_ptr = const_cast<void*>(ptr);
     attr.accessPolicyWindow.num_bytes = bytes;
     attr.accessPolicyWindow.hitRatio = 1.0f;
     attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    // outside the window: the tree itself must not become evict-first when the window is spent on the noise tables
+    attr.accessPolicyWindow.missProp = ptr == (const void*)ctx->d_pairs ? cudaAccessPropertyStreaming : cudaAccessPropertyNormal;
   } else {
     attr.accessPolicyWindow.num_bytes = 0;
     attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
@@ -961,7 +995,7 @@ int apply_l2_window(srt_ctx* ctx) {
   CU(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
   ctx->l2_window_on = want;
   ctx->l2_window_stream = want ? ctx->stream : nullptr;
-  ctx->l2_window_ptr = want ? (const void*)ctx->d_pairs : nullptr;
+  ctx->l2_window_ptr = ptr;
   ctx->l2_window_bytes = bytes;
   return 0;
 }
@@ -1000,7 +1034,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     uint32_t slots = ctx->wave_slots;
     if ((unsigned long long)slots > n_paths) slots = (uint32_t)n_paths;
     slots = (slots + 31u) & ~31u;
-    if (finder && slots >= (1u << 28)) return fail(ctx, "SRT_OPT_FINDER: at most 2^28 - 1 path slots (SRT_OPT_WAVE_SLOTS)");
+    if (finder && slots >= (1u << 27)) return fail(ctx, "SRT_OPT_FINDER: at most 2^27 - 1 path slots (SRT_OPT_WAVE_SLOTS)");
     if (ensure_pool(ctx, slots, (size_t)n_pixels * (size_t)chunk_frames, finder)) return 1;
     ctx->pool.n_pixels = n_pixels;
     ctx->pool.n_paths = n_paths;
@@ -1082,7 +1116,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
         // camera rays are in the chunk's first wave and, while slots still take new paths, in any later one
         const int finder_kind = !finder ? 0 : ((batch == 0 && w == 0) || !all_out) ? 2 : 1;
         CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
-                               ctx->block_threads, ctx->stream, ev[1], finder_kind));
+                               ctx->block_threads, ctx->stream, ev[1], finder_kind, ctx->use_fork ? &ctx->fork : nullptr));
         if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], ctx->stream));
         parity ^= 1;
       }
@@ -1119,7 +1153,7 @@ extern "C" int srt_render_async(srt_ctx* ctx, int32_t n_frames) {
     return 0;
   }
   if (n_frames == 0 || ctx->row1 == ctx->row0) return 0;
-  if (ctx->params.show_model && apply_l2_window(ctx)) return 1;
+  if (apply_l2_window(ctx)) return 1;
   if (ctx->textures_on && flush_textures(ctx)) return 1;
   if (ctx->textures_on && ctx->d_texels && ctx->params.show_model && ctx->schedule != SCHED_WAVEFRONT && ctx->schedule != SCHED_PER_PATH)
     return fail(ctx, "SRT_OPT_TEXTURES: schedules 0 (per path) and 3 (wavefront) sample textures; 1 and 2 do not");

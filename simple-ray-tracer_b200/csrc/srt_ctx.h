@@ -90,7 +90,7 @@ struct srt_ctx {
   // options
   int traversal = TRAV_ORDERED;
   int count_traversal = 0;  // SRT_OPT_COUNT_TRAVERSAL: 0 off, 1 the shader's walk (finder off), 2 what the default path executes
-  bool l2_persist = true;
+  int l2_persist = 1;  // SRT_OPT_L2_PERSIST: 0 off, 1 automatic, 2 node pairs' top levels, 3 noise tables
   int block_threads = 64;
   int schedule = SCHED_WAVEFRONT;
 
@@ -100,6 +100,8 @@ struct srt_ctx {
   size_t pool_list_cap = 0;
   WaveCounters* h_live = nullptr;  // pinned ring the device reports its wave counters into (live slots, paths handed out)
   cudaEvent_t wave_events[4] = {nullptr, nullptr, nullptr, nullptr};
+  WaveFork fork = {nullptr, nullptr, nullptr};  // second stream of the finder waves (launch_wf_wave); SRT_NO_FORK=1 in the environment keeps it unused
+  bool use_fork = true;
   uint64_t waves = 0;
   uint64_t tail_launches = 0;
   // optional per-kernel timing of the wavefront schedule (SRT_OPT_TIME_KERNELS): three events per wave
@@ -107,7 +109,7 @@ struct srt_ctx {
   std::vector<cudaEvent_t> timing_events;
   size_t timing_used = 0;
   int refill_threshold = 0;                    // idle lanes that send a trace warp back to the queue (SRT_OPT_REFILL; 0 = each kernel's own default)
-  uint32_t wave_slots = 128u << 20;             // path slots of the pool (SRT_OPT_WAVE_SLOTS)
+  uint32_t wave_slots = (128u << 20) - 32u;     // path slots of the pool (SRT_OPT_WAVE_SLOTS); ray ids (2 per slot) stay below 2^28
   int device_relayout = 2;                      // SRT_OPT_DEVICE_RELAYOUT: 0 host walk, 1 device, 2 device above SRT_FINDER_MAX_TRIS triangles
   bool relayout_on_device = false;              // what the last upload did
   float relayout_device_ms = 0.0f;

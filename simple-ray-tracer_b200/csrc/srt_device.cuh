@@ -176,6 +176,8 @@ struct WaveCounters {
   unsigned int cursor;        // fetch cursor of wf_trace_kernel
   unsigned int live_slots;    // slots that still carry a path
   unsigned long long next_path;  // next path (frame-major: frame * n_pixels + pixel slot) to hand to a free slot
+  unsigned int n_dying[2];    // entries of dlist[parity]
+  unsigned int _pad[2];
 };
 
 // Queues between wf_find_kernel and its two consumers (srt_wf_find.cuh); zeroed by wf_init_kernel / wf_logic_kernel.
@@ -187,21 +189,29 @@ struct FinderQueues {
   unsigned int _pad[2];
 };
 
-// Per-slot records (SoA, 16 B each unless noted).  A slot carries ONE path at a time; when the path ends the slot
-// takes the next path of the launch from WaveCounters::next_path.
+// Per-slot records (SoA).  A slot carries ONE path at a time; when the path ends the slot takes the next path of the
+// launch from WaveCounters::next_path.  A path has up to TWO rays in flight per wave: the closest-hit ray of its next
+// segment and the shadow ray of the surface it has just left (the direct-light term that ray decides is computed when
+// the ray is emitted and added when its answer is in: `pend`).  What the queues and the trace kernels handle are RAY IDS,
+//   ray id = 2 * slot (the slot's closest-hit ray) or 2 * slot + 1 (its shadow ray),
+// which index `ray` and `hit`; to those kernels a ray id is an opaque record number.
 struct PathPool {
-  // records that are always read together share one 32 B sector (slots are gathered through the queues)
-  float4* ray;   // [2*slot]   ray origin.xyz, tmax (initial intersection_distance)
-                 // [2*slot+1] ray direction.xyz, bits: kind | light index << 8
-  uint2* hit;    // result: primitive (or SRT_NO_HIT), distance bits
-  float4* pst;   // [2*slot]   throughput.xyz, light weight of the pending shadow ray
+  // records that are always read together share one 32 B sector (they are gathered through the queues)
+  float4* ray;   // [2*id]   ray origin.xyz, tmax (initial intersection_distance)
+                 // [2*id+1] ray direction.xyz, bits: kind (SRT_WF_KIND_*)
+  uint2* hit;    // [id] result: primitive (or SRT_NO_HIT), distance bits.  hit[2*slot+1].x = SRT_WF_NOT_PENDING while the
+                 // slot has no shadow ray in flight (written by whoever decides not to emit one)
+  float4* pst;   // [2*slot]   throughput.xyz, unused
                  // [2*slot+1] colour.xyz, bits: depth | rand_index << 8 | iter << 20
   uint2* path;   // (pixel slot, frame of the launch) of the path in this slot  (8 B)
-  float4* tex;   // textured-albedo option only: albedo.xyz of the surface the path stands on, w != 0 when it is textured
-  float4* p3;    // while a shadow ray is out: incoming direction.xyz, bits: primitive the path stands on
+  float4* pend;  // while a shadow ray is out: the term `throughput * SampleDirect * weight` for an unoccluded light (.xyz), and
+                 // in .w two bits per channel saying what the occluded term is (+0, -0 or NaN: 0 * anything)
+  uint32_t* dlist[2];  // cap entries each: SLOTS whose path ends as soon as its last shadow ray is answered (no closest-hit
+                       // ray of theirs is in the wave, so the closest queue does not lead the logic kernel to them)
   uint32_t* list[2];   // list_cap entries each: closest-hit queue from the front, shadow queue from the back
   uint32_t cap;        // slots
-  uint32_t list_cap;   // cap + room for the holes the logic warps' chunked reservations can leave
+  uint32_t ray_cap;    // ray ids: 2 * cap
+  uint32_t list_cap;   // 2 * cap + room for the holes the logic warps' chunked reservations can leave
   WaveCounters* q;
   // hit finder only (null otherwise): per ENTRY OF THE REPLAY LIST SRT_CAND_MAX candidates (triangle | bvh << 26, distance bits), the
   // list of rays to replay (slot | candidates << 28, theta bits), the list of rays to trace the long way, their counters

@@ -345,7 +345,7 @@ namespace {
 // rays with too many candidates (or a replay that could not be sure) the long way
 template <bool OUTSIDE, bool COUNT>
 cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
-                           DeviceCounters* counters, int block, cudaStream_t stream) {
+                           DeviceCounters* counters, int block, cudaStream_t stream, const WaveFork* fork) {
   static int per_sm = 0, sms = 0;
   static size_t smem_set = 0;
   auto k = wf_find_kernel<OUTSIDE, COUNT>;
@@ -370,27 +370,41 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   long blocks = ((long)pool.cap + 127) / 128;
   if (blocks > (long)sms * 16) blocks = (long)sms * 16;
-  wf_replay_kernel<COUNT><<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool, counters);
-  if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  PathPool over = pool;  // the overflow list (the replay may have added to it), seen through the trace kernel's own interface
+  PathPool over = pool;  // the overflow list, seen through the trace kernel's own interface
   over.q = &pool.fq->over;
   over.list[0] = pool.olist;
   over.list[1] = pool.olist;
-  if ((e = wf_trace_launch<TRAV_REFERENCE, COUNT>(sc, fp, over, 0, refill, counters, block, stream)) != cudaSuccess) return e;
+  // Only the replay of an OUTSIDE ray (finite theta) can add to the overflow list; in any other wave the list is final
+  // when the find kernel ends, and the walk over it (a latency-bound launch: a few thousand long rays in lock step,
+  // ~0.1 ms whatever its size) runs beside the replay instead of after it.
+  const bool side_by_side = !OUTSIDE && fork != nullptr && fork->aux != nullptr;
+  if (side_by_side) {
+    if ((e = cudaEventRecord(fork->forked, stream)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(fork->aux, fork->forked, 0)) != cudaSuccess) return e;
+    if ((e = wf_trace_launch<TRAV_REFERENCE, COUNT>(sc, fp, over, 0, refill, counters, block, fork->aux)) != cudaSuccess) return e;
+    if ((e = cudaEventRecord(fork->joined, fork->aux)) != cudaSuccess) return e;
+  }
+  wf_replay_kernel<COUNT><<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool, counters);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  if (side_by_side) {
+    if ((e = cudaStreamWaitEvent(stream, fork->joined, 0)) != cudaSuccess) return e;
+  } else {
+    if ((e = wf_trace_launch<TRAV_REFERENCE, COUNT>(sc, fp, over, 0, refill, counters, block, stream)) != cudaSuccess) return e;
+  }
   return cudaGetLastError();
 }
 }  // namespace
 
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
-                           cudaEvent_t after_trace, int finder) {
+                           cudaEvent_t after_trace, int finder, const WaveFork* fork) {
   cudaError_t e;
   if (finder == 2)  // a wave that may hold camera rays
-    e = count ? wf_find_launch<true, true>(sc, fp, pool, parity, refill, counters, block, stream)
-              : wf_find_launch<true, false>(sc, fp, pool, parity, refill, counters, block, stream);
+    e = count ? wf_find_launch<true, true>(sc, fp, pool, parity, refill, counters, block, stream, fork)
+              : wf_find_launch<true, false>(sc, fp, pool, parity, refill, counters, block, stream, fork);
   else if (finder)
-    e = count ? wf_find_launch<false, true>(sc, fp, pool, parity, refill, counters, block, stream)
-              : wf_find_launch<false, false>(sc, fp, pool, parity, refill, counters, block, stream);
+    e = count ? wf_find_launch<false, true>(sc, fp, pool, parity, refill, counters, block, stream, fork)
+              : wf_find_launch<false, false>(sc, fp, pool, parity, refill, counters, block, stream, fork);
   else if (mode == TRAV_REFERENCE)
     e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, refill, counters, block, stream)
               : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, refill, counters, block, stream);

@@ -22,9 +22,16 @@ cudaError_t launch_pack_noise(const float* unit3, const float* uniform3, float2*
                               cudaStream_t stream);
 cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, bool cull,
                            uint32_t* primary_ids, bool count_nodes, DeviceCounters* counters, cudaStream_t stream);
+// A second stream + two events: in a finder wave without camera rays the overflow walk (rays with too many candidates) and
+// the replay are independent -- only an OUTSIDE ray's replay can add to the overflow list -- and run side by side.
+struct WaveFork {
+  cudaStream_t aux;
+  cudaEvent_t forked, joined;
+};
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
-                           cudaEvent_t after_trace = nullptr, int finder = 0);  // finder: 0 = walk the reference BVH, 1 = hit finder, 2 = hit finder with its outside-ray walk (waves that may hold camera rays)
+                           cudaEvent_t after_trace = nullptr, int finder = 0,  // finder: 0 = walk the reference BVH, 1 = hit finder, 2 = hit finder with its outside-ray walk (waves that may hold camera rays)
+                           const WaveFork* fork = nullptr);
 // SRT_OPT_SORT_RAYS: both queues of wave `parity` regrouped by the cell their rays start in (pool.sort_* must be allocated)
 cudaError_t launch_wf_sort(const DeviceScene& sc, const PathPool& pool, int parity, cudaStream_t stream);
 #define SRT_SORT_BINS_HOST 32768u

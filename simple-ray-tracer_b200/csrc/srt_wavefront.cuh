@@ -10,11 +10,16 @@
 //   * wf_trace_kernel : persistent warps; a lane whose ray ended FETCHES the next ray of the wave from a queue
 //     (32 B load + root-box test) instead of shading, so the warp keeps traversing with full lanes; results go back to
 //     the slot as (primitive, distance)
-//   * wf_logic_kernel : consumes the wave's results queue by queue -- all lanes of a warp are either "closest-hit
-//     came back" (hit point, light sampling, emit shadow ray) or "shadow ray came back" (direct light, lobe choice,
-//     roulette, bounce) -- and appends the next wave's rays to the closest / shadow queue; a finished path writes its
-//     sample to samples[frame][pixel] and its slot takes the next path of the launch (regeneration), so waves stay
-//     millions of rays wide until the launch runs out of paths
+//   * wf_logic_kernel : one visit per path and wave.  A path has up to two rays in a wave -- the closest-hit ray of its
+//     next segment and the shadow ray of the surface it has just left -- and the visit takes both answers in the
+//     shader's order: the direct light of the surface left behind (its value was computed when the shadow ray was
+//     emitted; the answer picks the lit or the occluded one), then the new hit: light sampling, shadow ray, lobe
+//     choice, roulette, bounce (raytrace_compute.glsl:225-285), none of which waits for the new shadow ray.  Hits are
+//     put aside per warp and shaded 32 at a time; misses end their path at once.  A finished path writes its sample to
+//     samples[frame][pixel] and its slot takes the next path of the launch (regeneration), so waves stay millions of
+//     rays wide until the launch runs out of paths.  (Round 1 visited a path twice per segment -- closest hit, then
+//     shadow answer -- with the surface state parked in slot records in between: 28 GB of DRAM traffic per Rubik step
+//     and twice the waves.)
 //   * wf_resolve_kernel : per pixel, accum + sample[0] + sample[1] + ... in frame order -- the shader's own
 //     accumulation order (raytrace_compute.glsl:404-406) -- so results stay bit-identical to the shader's schedule.
 //     The sample buffer is what 180 GB of HBM buys: 16 B per path (2.1 GB for 64 frames at 1080p; longer launches
@@ -43,6 +48,7 @@ namespace srt {
 #define SRT_WF_NEED_POP 0x7FFFFFFFu  // a lane's `cur` between the end of its leaf and its pop (never a NodePair index)
 #define SRT_WF_KIND_CLOSEST 0u
 #define SRT_WF_KIND_SHADOW 1u
+#define SRT_WF_NOT_PENDING 0xFFFFFFFEu  // PathPool::hit[2*slot+1].x while no shadow ray of the slot is in flight (never a primitive)
 
 __device__ __forceinline__ uint32_t wf_pack(int depth, int rand_index, int iter) {
   return (uint32_t)depth | ((uint32_t)rand_index << 8) | ((uint32_t)iter << 20);
@@ -77,6 +83,17 @@ __device__ __forceinline__ void wf_path_id(const PathPool& pool, unsigned long l
   }
 }
 
+// a new path moves into `slot`: its camera ray, unit throughput, no colour, no shadow ray in flight
+__device__ __forceinline__ void wf_store_primary(const PathPool& pool, const FrameParams& fp, uint32_t slot, V3 d, uint32_t pixel, uint32_t f) {
+  const size_t id = 2 * (size_t)slot;
+  __stcs(pool.ray + 2 * id, make_float4(fp.center.x, fp.center.y, fp.center.z, inf_()));
+  __stcs(pool.ray + 2 * id + 1, make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
+  __stcs(pool.pst + 2 * (size_t)slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
+  __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0))));
+  __stcs(pool.path + slot, make_uint2(pixel, f));
+  pool.hit[id + 1] = make_uint2(SRT_WF_NOT_PENDING, 0u);
+}
+
 // ---- wave 0: the first pool.cap paths of the launch -----------------------------------------------------------------
 // CULL (SRT_OPT_PRIMARY_CULL, only when every path of the launch starts here): a primary ray whose CheckHit would end
 // at the root of every BVH -- the very test the trace kernel's enter() makes, IntersectsBox on the root against an
@@ -99,6 +116,8 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
     pool.q->n_shadow[0] = 0;
     pool.q->n_closest[1] = 0;
     pool.q->n_shadow[1] = 0;
+    pool.q->n_dying[0] = 0;
+    pool.q->n_dying[1] = 0;
     pool.q->cursor = 0;
     pool.q->next_path = first;
     if (pool.fq != nullptr) memset(pool.fq, 0, sizeof(FinderQueues));
@@ -175,12 +194,8 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   }
   SRT_CHECK(slot < pool.cap && slot < pool.list_cap, SRT_CHK_SLOT);
   SRT_CHECK(x >= 0 && x < fp.width && y >= 0 && y < fp.height, SRT_CHK_PIXEL);
-  __stcs(pool.ray + 2 * (size_t)slot, make_float4(fp.center.x, fp.center.y, fp.center.z, inf_()));
-  __stcs(pool.ray + 2 * (size_t)slot + 1, make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
-  __stcs(pool.pst + 2 * (size_t)slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
-  __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0))));
-  __stcs(pool.path + slot, make_uint2(pixel, f));
-  pool.list[0][slot] = slot;
+  wf_store_primary(pool, fp, slot, d, pixel, f);
+  pool.list[0][slot] = 2u * slot;  // ray id of the slot's closest-hit ray
 }
 
 // The traversal stack lives in shared memory, one column per thread; addressed by 32-bit shared addresses so that a
@@ -228,6 +243,7 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   if (blockIdx.x == 0 && threadIdx.x == 0) {  // the logic kernel of this wave fills the other list from empty
     q->n_closest[parity ^ 1] = 0;
     q->n_shadow[parity ^ 1] = 0;
+    q->n_dying[parity ^ 1] = 0;
   }
 
   unsigned int n_nodes = 0, n_tris = 0;
@@ -323,7 +339,7 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
         if (entry != SRT_WF_HOLE) {
           slot = entry;
-          SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
+          SRT_CHECK(slot < pool.ray_cap, SRT_CHK_SLOT);
           const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1];
           ray_o = v3(a.x, a.y, a.z);
           ray_d = v3(b.x, b.y, b.z);
@@ -417,6 +433,36 @@ wf_trace_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   }
 }
 
+// ---- the direct-light term of a shadow ray that is still out ------------------------------------------------------------
+// GetRayColor adds  throughput * SampleDirect(..., shadow_mult) * weight  once CheckLightOccluded has answered
+// (raytrace_compute.glsl:235-246; shadow_mult is 1 or 0).  Both values are computed when the ray is emitted: the lit one
+// is stored as it is; the occluded one is 0 * (finite or not) per channel, i.e. +0, -0 or NaN, and two bits say which.
+__device__ __forceinline__ uint32_t wf_zero_code(V3 t0) {
+  uint32_t code = 0;
+  const float c[3] = {t0.x, t0.y, t0.z};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const uint32_t bits = __float_as_uint(c[k]);
+    code |= (bits == 0u ? 0u : (bits == 0x80000000u ? 1u : 2u)) << (2 * k);
+  }
+  return code;
+}
+__device__ __forceinline__ V3 wf_zero_term(uint32_t code) {
+  float c[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const uint32_t two = (code >> (2 * k)) & 3u;
+    c[k] = __uint_as_float(two == 0u ? 0u : (two == 1u ? 0x80000000u : 0x7FC00000u));
+  }
+  return v3(c[0], c[1], c[2]);
+}
+// colour after the answer of the shadow ray that was out (hit_s: PathPool::hit[2*slot+1])
+__device__ __forceinline__ V3 wf_add_pending(const PathPool& pool, uint32_t slot, uint2 hit_s, V3 color) {
+  if (hit_s.x == SRT_WF_NOT_PENDING) return color;
+  const float4 pe = __ldcs(pool.pend + slot);
+  return color + (hit_s.x != SRT_NO_HIT ? wf_zero_term(__float_as_uint(pe.w)) : v3(pe.x, pe.y, pe.z));
+}
+
 // ---- logic: everything GetRayColor does between two CheckHit calls (raytrace_compute.glsl:225-292) -----------------
 __global__ void __launch_bounds__(SRT_WF_LOGIC_THREADS, SRT_WF_LOGIC_BLOCKS_PER_SM)
 wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity,
@@ -427,10 +473,14 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
   WaveCounters* q = pool.q;
-  const uint32_t n_a = q->n_closest[parity], n_b = q->n_shadow[parity];
-  const uint32_t chunks_a = (n_a + 31u) >> 5, chunks_b = (n_b + 31u) >> 5;
+  // region a: the closest queue (one entry per path that has a next segment); region d: paths that only wait for their
+  // last shadow ray.  The shadow queue itself is the trace kernels' business: its rays belong to slots met in a or d.
+  const uint32_t n_a = q->n_closest[parity], n_d = q->n_dying[parity];
+  const uint32_t chunks_a = (n_a + 31u) >> 5, chunks_d = (n_d + 31u) >> 5;
   const uint32_t* __restrict__ list_in = parity ? pool.list[1] : pool.list[0];
+  const uint32_t* __restrict__ dying_in = parity ? pool.dlist[1] : pool.dlist[0];
   uint32_t* __restrict__ list_out = parity ? pool.list[0] : pool.list[1];
+  uint32_t* __restrict__ dying_out = parity ? pool.dlist[0] : pool.dlist[1];
   if (blockIdx.x == 0 && threadIdx.x == 0) {  // for the next wave's trace kernels
     q->cursor = 0;
     if (pool.fq != nullptr) memset(pool.fq, 0, sizeof(FinderQueues));
@@ -443,116 +493,51 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   uint32_t c_next = 0, c_end = 0, s_next = 0, s_end = 0;
   // a warp that makes no more than four turns reserves exactly what each turn emits (append_chunk = 0): no holes in
   // the small waves, whose atomics do not contend anyway
-  const uint32_t append_chunk = (chunks_a + chunks_b) > 4u * n_warps ? SRT_WF_APPEND_CHUNK : 0u;
+  const uint32_t total_chunks = chunks_a + chunks_d;
+  const uint32_t append_chunk = total_chunks > 4u * n_warps ? SRT_WF_APPEND_CHUNK : 0u;
 
-  // Paths whose closest hit came back and for which SampleLights selects no light (1 in 12 on Rubik) go straight on to
-  // the lobe choice and the bounce (raytrace_compute.glsl:232-234 skipped): alone among 32 lanes that wait for their
-  // shadow rays' results, that code ran 2.8 lanes wide and was 45 % of the first wave's instructions
-  // (profiles/r01i_*).  Their slots are put aside per warp instead and shaded 32 at a time.
+  // Paths whose ray hit something are put aside per warp and shaded 32 at a time: in a chunk of the queue hits and misses
+  // are mixed, and the shading code (some 2 800 thread-instructions per path) would run as wide as the hits are dense.
   __shared__ uint32_t s_stash[SRT_WF_LOGIC_THREADS / 32][64];
   uint32_t* stash = s_stash[threadIdx.x >> 5];
   uint32_t stash_n = 0;  // warp-uniform
-  const uint32_t total_chunks = chunks_a + chunks_b;
 
   for (uint32_t g = warp;;) {
     const bool stashed = stash_n >= 32u || (g >= total_chunks && stash_n > 0u);  // this turn shades put-aside paths
     if (!stashed && g >= total_chunks) break;
-    bool region_a = true;  // warp-uniform: which queue this chunk belongs to
-    uint32_t entry = SRT_WF_HOLE;
+    bool region_a = true;  // warp-uniform
+    uint32_t slot = 0;
+    bool valid = false;
     if (stashed) {
       const uint32_t take = stash_n < 32u ? stash_n : 32u;
-      if ((uint32_t)lane < take) entry = stash[stash_n - take + lane];
+      if ((uint32_t)lane < take) {
+        slot = stash[stash_n - take + lane];
+        valid = true;
+      }
       stash_n -= take;
       __syncwarp();
     } else {
       region_a = g < chunks_a;
       const uint32_t idx = (region_a ? g : g - chunks_a) * 32u + lane;
-      const bool in_range = idx < (region_a ? n_a : n_b);
-      SRT_CHECK(!in_range || (region_a ? idx : pool.list_cap - 1u - idx) < pool.list_cap, SRT_CHK_LIST_READ);
-      if (in_range) entry = __ldg(list_in + (region_a ? idx : pool.list_cap - 1u - idx));
+      if (idx < (region_a ? n_a : n_d)) {
+        SRT_CHECK(region_a ? idx < pool.list_cap : idx < pool.cap, SRT_CHK_LIST_READ);
+        const uint32_t entry = __ldg(region_a ? list_in + idx : dying_in + idx);
+        if (entry != SRT_WF_HOLE) {
+          slot = region_a ? entry >> 1 : entry;  // the closest queue holds ray ids (2 * slot)
+          valid = true;
+        }
+      }
       g += n_warps;
     }
-    const bool valid = entry != SRT_WF_HOLE;
-    const uint32_t slot = valid ? entry : 0u;
     SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
-    const uint2 path = valid ? __ldcs(pool.path + slot) : make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
-    int x = 0, y = 0;
-    tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
-    const int pix = y * fp.height + x;  // Q4
 
-    V3 origin = v3(0.0f), dir = v3(0.0f), throughput = v3(0.0f), color = v3(0.0f);
-    int depth = 0, rand_index = 0, iter = 0, li = 0;
-    uint32_t hit_prim = SRT_NO_HIT;
-    V3 tex_albedo = v3(0.0f);
-    bool has_tex = false;
-    float light_weight = 0.0f, shadow_mult = 1.0f;
-    bool shade = false, have_light = false, finish = false, emit_closest = false, emit_shadow = false, put_aside = false;
-
-    if (valid) {
-      // slot records stream through once per wave (gigabytes, no reuse within L2's reach): evict-first loads and stores keep
-      // them from pushing the noise table (8 MB, ~10 random gathers per shaded path) out of L2 -- profiles/r02h_ncu_full_summary.txt
-      const uint2 h = __ldcs(pool.hit + slot);
-      const float4 a = __ldcs(pool.ray + 2 * (size_t)slot), b = __ldcs(pool.ray + 2 * (size_t)slot + 1), t0 = __ldcs(pool.pst + 2 * (size_t)slot), c1 = __ldcs(pool.pst + 2 * (size_t)slot + 1);
-      origin = v3(a.x, a.y, a.z);
-      throughput = v3(t0.x, t0.y, t0.z);
-      color = v3(c1.x, c1.y, c1.z);
-      const uint32_t packed = __float_as_uint(c1.w);
-      depth = (int)(packed & 0xFFu);
-      rand_index = (int)((packed >> 8) & 0xFFFu);
-      iter = (int)(packed >> 20);
-      if (region_a) {
-        // ---- a closest-hit ray came back (raytrace_compute.glsl:225-236) ----
-        dir = v3(b.x, b.y, b.z);
-        SRT_CHECK(x >= 0 && x < fp.width && y >= 0 && y < fp.height, SRT_CHK_PIXEL);
-        if (primary_ids != nullptr && iter == 0 && path.y == (uint32_t)(fp.n_frames - 1))
-          primary_ids[(size_t)y * fp.width + x] = h.x;
-        if (h.x == SRT_NO_HIT) {
-          finish = true;  // :287-289
-        } else {
-          hit_prim = h.x;
-          if (sc.tex_tris != nullptr) {  // textured-albedo option: needs the ray as it was traced, so it happens here
-            const float4* tp = reinterpret_cast<const float4*>(sc.tris + hit_prim);
-            const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
-            const float4 mb = __ldg(reinterpret_cast<const float4*>(sc.mats + __float_as_uint(r0.w)) + 1);
-            has_tex = textured_albedo(sc, hit_prim, r0, r1, r2, mb, origin, dir, __uint_as_float(h.y), tex_albedo);
-          }
-          origin = (__uint_as_float(h.y) * dir) + origin;  // rec.p (:155)
-          if (stashed) {
-            shade = true;  // put aside in an earlier turn: no light was selected; the slot still holds the traced ray
-          } else if (sample_lights(sc, fp, pix, origin, light_weight, li)) {
-            const DeviceLight& l = fp.lights[li];
-            const V3 lpos = v3(l.px, l.py, l.pz);
-            const V3 sd = normalize_(lpos - origin);  // :168
-            const float len = length_(lpos - origin);  // :169
-            __stcs(pool.ray + 2 * (size_t)slot, make_float4(origin.x, origin.y, origin.z, len));
-            __stcs(pool.ray + 2 * (size_t)slot + 1, make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8))));
-            __stcs(pool.p3 + slot, make_float4(dir.x, dir.y, dir.z, __uint_as_float(hit_prim)));
-            __stcs(pool.pst + 2 * (size_t)slot, make_float4(throughput.x, throughput.y, throughput.z, light_weight));
-            if (sc.tex_tris != nullptr) __stcs(pool.tex + slot, make_float4(tex_albedo.x, tex_albedo.y, tex_albedo.z, has_tex ? 1.0f : 0.0f));
-            emit_shadow = true;
-            n_shadow++;
-          } else {
-            put_aside = true;
-          }
-        }
-      } else {
-        // ---- a shadow ray came back (:235-246): the path still stands at the ray's origin ----
-        const float4 c3 = __ldcs(pool.p3 + slot);
-        dir = v3(c3.x, c3.y, c3.z);
-        hit_prim = __float_as_uint(c3.w);
-        li = (int)(__float_as_uint(b.w) >> 8);
-        light_weight = t0.w;
-        shadow_mult = (h.x != SRT_NO_HIT) ? 0.0f : 1.0f;
-        if (sc.tex_tris != nullptr) {
-          const float4 ta = __ldcs(pool.tex + slot);
-          tex_albedo = v3(ta.x, ta.y, ta.z);
-          has_tex = ta.w != 0.0f;
-        }
-        have_light = true;
-        shade = true;
-      }
+    bool shade = false, finish = false, emit_closest = false, emit_shadow = false, emit_dying = false, put_aside = false;
+    uint4 h = make_uint4(SRT_NO_HIT, 0u, SRT_WF_NOT_PENDING, 0u);  // .xy: the closest-hit ray's answer, .zw: the shadow ray's
+    if (valid) h = __ldcs(reinterpret_cast<const uint4*>(pool.hit) + slot);
+    if (valid && !stashed) {
+      if (region_a && h.x != SRT_NO_HIT) put_aside = true;  // shaded when 32 are waiting
+      else finish = true;  // a miss (:287-289), or a path that only waited for its last shadow ray
     }
-
     {
       const unsigned m_p = __ballot_sync(FULL, put_aside);
       if (m_p) {  // at most 31 entries are waiting here, so 64 hold them all
@@ -562,25 +547,72 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         __syncwarp();
       }
     }
+    shade = valid && stashed;
+
+    uint2 path = make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
+    int x = 0, y = 0, pix = 0;
+    V3 throughput = v3(0.0f), color = v3(0.0f);
+    int depth = 0, rand_index = 0, iter = 0;
+    if (shade || finish) {
+      // slot records stream through once per wave (gigabytes, no reuse within L2's reach): evict-first loads and stores
+      path = __ldcs(pool.path + slot);
+      tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
+      pix = y * fp.height + x;  // Q4
+      SRT_CHECK(x >= 0 && x < fp.width && y >= 0 && y < fp.height, SRT_CHK_PIXEL);
+      const float4 t0 = __ldcs(pool.pst + 2 * (size_t)slot), c1 = __ldcs(pool.pst + 2 * (size_t)slot + 1);
+      throughput = v3(t0.x, t0.y, t0.z);
+      color = v3(c1.x, c1.y, c1.z);
+      const uint32_t packed = __float_as_uint(c1.w);
+      depth = (int)(packed & 0xFFu);
+      rand_index = (int)((packed >> 8) & 0xFFFu);
+      iter = (int)(packed >> 20);
+      // the direct light of the surface the path left last (:235-246) comes before anything the new segment adds
+      color = wf_add_pending(pool, slot, make_uint2(h.z, h.w), color);
+      if ((stashed || region_a) && primary_ids != nullptr && iter == 0 && path.y == (uint32_t)(fp.n_frames - 1))
+        primary_ids[(size_t)y * fp.width + x] = h.x;
+    }
 
     if (shade) {
-      // ---- direct light, lobe choice, roulette, bounce (:238-285) ----
+      // ---- the closest-hit ray found a surface (:225-285) ----
+      const size_t id = 2 * (size_t)slot;
+      const float4 a = __ldcs(pool.ray + 2 * id), b = __ldcs(pool.ray + 2 * id + 1);
+      const V3 ray_o = v3(a.x, a.y, a.z), dir = v3(b.x, b.y, b.z);
+      const uint32_t hit_prim = h.x;
       const float4* tp = reinterpret_cast<const float4*>(sc.tris + hit_prim);
       const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
-      const V3 N = normalize_(cross_(v3(r1.x, r1.y, r1.z), v3(r2.x, r2.y, r2.z)));  // ray_intersects.glsl:90
       const float4* mp = reinterpret_cast<const float4*>(sc.mats + __float_as_uint(r0.w));
       const float4 ma = __ldg(mp), mb = __ldg(mp + 1);
+      V3 tex_albedo = v3(0.0f);
+      bool has_tex = false;
+      if (sc.tex_tris != nullptr)  // textured-albedo option: needs the ray as it was traced
+        has_tex = textured_albedo(sc, hit_prim, r0, r1, r2, mb, ray_o, dir, __uint_as_float(h.y), tex_albedo);
+      const V3 p = (__uint_as_float(h.y) * dir) + ray_o;  // rec.p (:155)
+      const V3 N = normalize_(cross_(v3(r1.x, r1.y, r1.z), v3(r2.x, r2.y, r2.z)));  // ray_intersects.glsl:90
       SurfMat mat;
       mat.albedo = has_tex ? tex_albedo : v3(ma.x, ma.y, ma.z);
       mat.roughness = ma.w;
       mat.specular = v3(mb.x, mb.y, mb.z);
       mat.metalness = 0.1f;  // raytrace_utils.glsl:172-173
       mat.use_spec = true;
-      const V3 p = origin;
       const V3 V = -dir;
-      if (have_light) {
+      float light_weight = 0.0f;
+      int li = 0;
+      if (sample_lights(sc, fp, pix, p, light_weight, li)) {
+        // the shadow ray (:168-169) and both values of the term its answer will add (:238-246, useSpec)
         const DeviceLight& l = fp.lights[li];
-        color = color + throughput * sample_direct(p, N, mat, V, l, shadow_mult) * light_weight;  // useSpec
+        const V3 lpos = v3(l.px, l.py, l.pz);
+        const V3 sd = normalize_(lpos - p);
+        const float len = length_(lpos - p);
+        const V3 lit = throughput * sample_direct(p, N, mat, V, l, 1.0f) * light_weight;
+        const V3 occluded = throughput * sample_direct(p, N, mat, V, l, 0.0f) * light_weight;
+        __stcs(pool.ray + 2 * (id + 1), make_float4(p.x, p.y, p.z, len));
+        __stcs(pool.ray + 2 * (id + 1) + 1, make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8))));
+        __stcs(pool.pend + slot, make_float4(lit.x, lit.y, lit.z, __uint_as_float(wf_zero_code(occluded))));
+        pool.hit[id + 1] = make_uint2(SRT_NO_HIT, 0u);  // "out": what wf_tail_kernel looks at when it takes the path over untraced
+        emit_shadow = true;
+        n_shadow++;
+      } else {
+        pool.hit[id + 1] = make_uint2(SRT_WF_NOT_PENDING, 0u);
       }
       const float prob = brdf_probability(mat, V, N);  // metalness 0.1 != 1: the lobe is always drawn (:249-264)
       const float fd = (float)depth;
@@ -600,21 +632,25 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         depth--;
       }
       V3 new_dir, weight;
+      bool goes_on = false;
       if (alive && sample_indirect(sc, fp, pix, p, N, V, mat, specular_lobe, new_dir, weight)) {
         throughput = throughput * weight;
-        if (++iter >= SRT_MAX_PATH_ITERS) {  // decree Q9
-          n_capped++;
-          finish = true;
-        } else {
-          __stcs(pool.ray + 2 * (size_t)slot, make_float4(p.x, p.y, p.z, inf_()));
-          __stcs(pool.ray + 2 * (size_t)slot + 1, make_float4(new_dir.x, new_dir.y, new_dir.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
-          __stcs(pool.pst + 2 * (size_t)slot, make_float4(throughput.x, throughput.y, throughput.z, 0.0f));
-          __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(color.x, color.y, color.z, __uint_as_float(wf_pack(depth, rand_index, iter))));
-          emit_closest = true;
-          n_seg++;
-        }
+        if (++iter >= SRT_MAX_PATH_ITERS) n_capped++;  // decree Q9
+        else goes_on = true;
+      }
+      if (goes_on) {
+        __stcs(pool.ray + 2 * id, make_float4(p.x, p.y, p.z, inf_()));
+        __stcs(pool.ray + 2 * id + 1, make_float4(new_dir.x, new_dir.y, new_dir.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
+        emit_closest = true;
+        n_seg++;
+      } else if (emit_shadow) {
+        emit_dying = true;  // the path is over, but its colour still lacks the light this surface receives
       } else {
         finish = true;
+      }
+      if (goes_on || emit_dying) {
+        __stcs(pool.pst + 2 * (size_t)slot, make_float4(throughput.x, throughput.y, throughput.z, 0.0f));
+        __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(color.x, color.y, color.z, __uint_as_float(wf_pack(depth, rand_index, iter))));
       }
     }
 
@@ -642,11 +678,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           int nx, ny;
           tile_pixel(fp, pixel >> 5, pixel & 31, nx, ny);
           const V3 d = wf_primary_dir(sc, fp, nx, ny, ny * fp.height + nx, (int)f);
-          __stcs(pool.ray + 2 * (size_t)slot, make_float4(fp.center.x, fp.center.y, fp.center.z, inf_()));
-          __stcs(pool.ray + 2 * (size_t)slot + 1, make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
-          __stcs(pool.pst + 2 * (size_t)slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
-          __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0))));
-          __stcs(pool.path + slot, make_uint2(pixel, f));
+          wf_store_primary(pool, fp, slot, d, pixel, f);
           emit_closest = true;
           n_seg++;
         } else {
@@ -655,7 +687,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       }
     }
 
-    // ---- next wave's queues: closest-hit rays at the front, shadow rays at the back ----
+    // ---- next wave's queues: closest-hit rays at the front, shadow rays at the back, both as ray ids ----
     const unsigned m_c = __ballot_sync(FULL, emit_closest);
     if (m_c) {
       const uint32_t m = (uint32_t)__popc(m_c);
@@ -668,7 +700,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         c_end = c_next + want;
       }
       SRT_CHECK(c_next + m <= pool.list_cap && c_end <= pool.list_cap, SRT_CHK_LIST_WRITE);
-      if (emit_closest) list_out[c_next + __popc(m_c & lt_mask)] = slot;
+      if (emit_closest) list_out[c_next + __popc(m_c & lt_mask)] = 2u * slot;
       c_next += m;
     }
     const unsigned m_s = __ballot_sync(FULL, emit_shadow);
@@ -683,8 +715,17 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         s_end = s_next + want;
       }
       SRT_CHECK(s_next + m <= pool.list_cap && s_end <= pool.list_cap, SRT_CHK_LIST_WRITE);
-      if (emit_shadow) list_out[pool.list_cap - 1u - (s_next + __popc(m_s & lt_mask))] = slot;
+      if (emit_shadow) list_out[pool.list_cap - 1u - (s_next + __popc(m_s & lt_mask))] = 2u * slot + 1u;
       s_next += m;
+    }
+    const unsigned m_d = __ballot_sync(FULL, emit_dying);
+    if (m_d) {  // few: one atomic per turn that has any
+      uint32_t base = 0;
+      const int leader = __ffs(m_d) - 1;
+      if (lane == leader) base = atomicAdd(&q->n_dying[parity ^ 1], (unsigned int)__popc(m_d));
+      base = __shfl_sync(FULL, base, leader);
+      SRT_CHECK(base + (uint32_t)__popc(m_d) <= pool.cap, SRT_CHK_LIST_WRITE);
+      if (emit_dying) dying_out[base + __popc(m_d & lt_mask)] = slot;
     }
   }
   for (uint32_t i = c_next + lane; i < c_end; i += 32) list_out[i] = SRT_WF_HOLE;

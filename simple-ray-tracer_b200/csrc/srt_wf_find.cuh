@@ -84,6 +84,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   if (blockIdx.x == 0 && threadIdx.x == 0) {  // the logic kernel of this wave fills the other list from empty
     q->n_closest[parity ^ 1] = 0;
     q->n_shadow[parity ^ 1] = 0;
+    q->n_dying[parity ^ 1] = 0;
   }
 
   unsigned int n_nodes = 0, n_tris = 0;
@@ -162,7 +163,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           // the replay's input goes where the replay reads it in order: candidates and list entry by position in
           // the replay list, not by slot (scattered 64 B records cost 4-5x a sequential read, profiles/r01k_gather_probe)
           const uint32_t pos = base + (uint32_t)__popc(m_r & lt_mask);
-          SRT_CHECK(pos < pool.cap && n_cand <= SRT_CAND_MAX, SRT_CHK_CAND);
+          SRT_CHECK(pos < pool.ray_cap && n_cand <= SRT_CAND_MAX, SRT_CHK_CAND);
           uint2* dst = pool.cand + (size_t)pos * SRT_CAND_MAX;
           uint32_t w = 0;
           for (uint32_t k = 0; k < n_cand; ++k) {  // an OUTSIDE ray keeps the candidates within its final theta
@@ -211,7 +212,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
         const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
         if (entry != SRT_WF_HOLE) {
           slot = entry;
-          SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
+          SRT_CHECK(slot < pool.ray_cap, SRT_CHK_SLOT);
           tmax = pool.ray[2 * (size_t)slot].w;
           n_cand = 0;
           overflow = false;
@@ -335,8 +336,8 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint2 entry = pool.rlist[i];
     const uint32_t slot = entry.x & 0x0FFFFFFFu, n_cand = entry.x >> 28;
-    SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
-    SRT_CHECK(n_cand <= SRT_CAND_MAX && i < pool.cap, SRT_CHK_CAND);
+    SRT_CHECK(slot < pool.ray_cap, SRT_CHK_SLOT);
+    SRT_CHECK(n_cand <= SRT_CAND_MAX && i < pool.ray_cap, SRT_CHK_CAND);
     const float4 ra = pool.ray[2 * (size_t)slot], rb = pool.ray[2 * (size_t)slot + 1];
     const V3 ray_o = v3(ra.x, ra.y, ra.z), ray_d = v3(rb.x, rb.y, rb.z);
     const bool any_hit = (__float_as_uint(rb.w) & 0xFFu) == SRT_WF_KIND_SHADOW;

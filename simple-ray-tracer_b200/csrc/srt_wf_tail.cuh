@@ -7,9 +7,12 @@
 // Here a lane keeps ONE path until it ends -- closest-hit ray, light sampling, shadow ray, direct light, lobe choice,
 // roulette, bounce (raytrace_compute.glsl:225-292), exactly the statements of wf_logic_kernel with the path state in
 // registers instead of slot records -- so a path costs the sum of ITS OWN rays, not the sum over waves of the slowest
-// ray of each wave.  Lanes whose path ended take the next entry of the wave's queues (either kind: the slot says what
-// the path was waiting for).  Traversal is the two-phase lock-step loop of wf_trace_kernel; lanes whose ray ended wait
-// until enough of them can run the (divergent) shading code together, as in srt_persistent.cuh.
+// ray of each wave.  Lanes whose path ended take the next path of the wave: an entry of the closest queue, or of the
+// list of paths that only wait for their last shadow ray.  Such a path arrives as wf_logic_kernel left it, with up to
+// two rays that nobody has traced yet: the lane first answers the shadow ray and adds the direct-light term that was
+// put aside for it (PathPool::pend), then goes on with the closest-hit ray (or ends the path), and from there on does
+// one thing after the other as the shader does.  Traversal is the two-phase lock-step loop of wf_trace_kernel; lanes
+// whose ray ended wait until enough of them can run the (divergent) shading code together, as in srt_persistent.cuh.
 //
 // The per-path arithmetic is the same functions in the same order as the wave kernels, so the samples are the same
 // bits; tests run every parity case with the tail on and off.  Not used with the textured-albedo option or the
@@ -38,8 +41,9 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   const int lane = threadIdx.x & 31;
   WaveCounters* q = pool.q;
   const uint32_t n_front = q->n_closest[parity];
-  const uint32_t n_total = n_front + q->n_shadow[parity];
+  const uint32_t n_total = n_front + q->n_dying[parity];
   const uint32_t* __restrict__ list = parity ? pool.list[1] : pool.list[0];
+  const uint32_t* __restrict__ dying = parity ? pool.dlist[1] : pool.dlist[0];
   const V3 sky = v3(0.05f);
 
   // path
@@ -50,6 +54,10 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   int depth = 0, rand_index = 0, iter = 0, li = 0;
   uint32_t hit_prim = SRT_NO_HIT;
   float light_weight = 0.0f;
+  // a path taken over from the waves with a shadow ray still to answer: its slot, and what follows the answer
+  // (1 = the slot's closest-hit ray, 2 = the end of the path)
+  uint32_t my_slot = 0;
+  int resume = 0;
   // ray in flight (it starts at `origin`)
   bool trav = false, any_hit = false, exact_box = false;
   V3 ray_d = v3(0.0f), to = v3(0.0f), td = v3(0.0f), inv = v3(0.0f);
@@ -115,7 +123,23 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
     if (has_path && !trav) {
       bool shade = false, have_light = false, finish = false;
       float shadow_mult = 1.0f;
-      if (any_hit) {
+      if (resume != 0) {
+        // the shadow ray the waves left behind is answered: the term put aside for it, lit or occluded
+        color = wf_add_pending(pool, my_slot, make_uint2(hit, 0u), color);
+        if (resume == 1) {
+          const size_t id = 2 * (size_t)my_slot;
+          const float4 a = pool.ray[2 * id], b = pool.ray[2 * id + 1];
+          origin = v3(a.x, a.y, a.z);
+          ray_d = v3(b.x, b.y, b.z);
+          dir = ray_d;
+          best = a.w;
+          any_hit = false;
+          start_ray();  // counted as a segment when wf_logic_kernel emitted it
+        } else {
+          finish = true;
+        }
+        resume = 0;
+      } else if (any_hit) {
         // a shadow ray came back (:235-246): the path still stands at the ray's origin
         shadow_mult = (hit != SRT_NO_HIT) ? 0.0f : 1.0f;
         have_light = true;
@@ -233,37 +257,36 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       const int my_rank = __popc(idle & ((1u << lane) - 1u));
       if (!has_path && my_rank < n_take) {
         const uint32_t idx = r_next + my_rank;
-        SRT_CHECK((idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)) < pool.list_cap, SRT_CHK_LIST_READ);
-        const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
+        SRT_CHECK(idx < n_front ? idx < pool.list_cap : idx - n_front < pool.cap, SRT_CHK_LIST_READ);
+        const uint32_t entry = __ldg(idx < n_front ? list + idx : dying + (idx - n_front));
         if (entry != SRT_WF_HOLE) {
-          const size_t slot = entry;
+          const bool is_dying = idx >= n_front;
+          my_slot = is_dying ? entry : entry >> 1;  // the closest queue holds ray ids (2 * slot)
+          const size_t slot = my_slot;
           SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
-          const float4 a = pool.ray[2 * slot], b = pool.ray[2 * slot + 1], t0 = pool.pst[2 * slot], c1 = pool.pst[2 * slot + 1];
+          const float4 t0 = pool.pst[2 * slot], c1 = pool.pst[2 * slot + 1];
           path = pool.path[slot];
           int x, y;
           tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
           pix = y * fp.height + x;  // Q4
-          origin = v3(a.x, a.y, a.z);
-          ray_d = v3(b.x, b.y, b.z);
-          best = a.w;
           throughput = v3(t0.x, t0.y, t0.z);
-          light_weight = t0.w;
           color = v3(c1.x, c1.y, c1.z);
           const uint32_t packed = __float_as_uint(c1.w);
           depth = (int)(packed & 0xFFu);
           rand_index = (int)((packed >> 8) & 0xFFFu);
           iter = (int)(packed >> 20);
-          any_hit = (__float_as_uint(b.w) & 0xFFu) == SRT_WF_KIND_SHADOW;
-          if (any_hit) {
-            const float4 c3 = pool.p3[slot];
-            dir = v3(c3.x, c3.y, c3.z);
-            hit_prim = __float_as_uint(c3.w);
-            li = (int)(__float_as_uint(b.w) >> 8);
-          } else {
-            dir = ray_d;
-          }
+          const bool shadow_out = is_dying || pool.hit[2 * slot + 1].x != SRT_WF_NOT_PENDING;
+          // the ray to answer first: the slot's shadow ray if one is out, else its closest-hit ray
+          const size_t id = 2 * slot + (shadow_out ? 1u : 0u);
+          const float4 a = pool.ray[2 * id], b = pool.ray[2 * id + 1];
+          origin = v3(a.x, a.y, a.z);
+          ray_d = v3(b.x, b.y, b.z);
+          best = a.w;
+          any_hit = shadow_out;
+          resume = shadow_out ? (is_dying ? 2 : 1) : 0;
+          dir = ray_d;  // (of a shadow ray: replaced when the closest-hit ray is taken up)
           has_path = true;
-          start_ray();  // may end at once (root box missed): the lane shades in the next round
+          start_ray();  // may end at once (root box missed): the lane goes on in the next round
         }
       }
       r_next += n_take;
