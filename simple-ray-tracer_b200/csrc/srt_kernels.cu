@@ -420,7 +420,10 @@ cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const P
   long max_blocks = (long)launch_wf_max_logic_warps() / warps_per_block;
   if (blocks > max_blocks) blocks = max_blocks;
   if (blocks < 1) blocks = 1;
-  wf_logic_kernel<<<(unsigned)blocks, SRT_WF_LOGIC_THREADS, 0, stream>>>(sc, fp, pool, parity, ids, counters);
+  if (sc.tex_tris != nullptr)
+    wf_logic_kernel<true><<<(unsigned)blocks, SRT_WF_LOGIC_THREADS, 0, stream>>>(sc, fp, pool, parity, ids, counters);
+  else
+    wf_logic_kernel<false><<<(unsigned)blocks, SRT_WF_LOGIC_THREADS, 0, stream>>>(sc, fp, pool, parity, ids, counters);
   return cudaGetLastError();
 }
 

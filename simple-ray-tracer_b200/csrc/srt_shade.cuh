@@ -89,12 +89,12 @@ __device__ __forceinline__ bool sample_lights(const DeviceScene& sc, const Frame
       if (!selected) {
         float fi = (float)i;
         float r = rand_uniform(sc, fp, pix, p.y + fi, p.z + fi);
-        if (r < div_(ris_weight, total)) selected = true;
+        if (r < div0_(ris_weight, total)) selected = true;  // (the clamped index beyond the list is a light of no intensity: 0 / 0)
       }
     }
   }
   float sample_pdf = selected ? light_pdf : 0.0f;
-  sample_weight = div_(div_(total, fp.light_count_f), max_(0.001f, sample_pdf));
+  sample_weight = div0_(div0_(total, fp.light_count_f), max_(0.001f, sample_pdf));
   return selected;
 }
 
@@ -107,7 +107,9 @@ __device__ __forceinline__ V3 light_dir(const DeviceLight& l, V3 p) {
 
 // SampleDirect (brdf.glsl:200-224) with the 7-output GetAllBRDFValues (brdf.glsl:154-171),
 // ggxNormalDistribution (:8-12), ggxSchlickMaskingTerm (:21-31), schlickFresnel (:34-36) inlined.
-__device__ __forceinline__ V3 sample_direct(V3 p, V3 N, const SurfMat& m, V3 V, const DeviceLight& l, float shadow_mult) {
+// Everything of SampleDirect but the light's own term: brdf = ggx + NdotL * albedo / pi, and the light's intensity at p.
+__device__ __forceinline__ void sample_direct_terms(V3 p, V3 N, const SurfMat& m, V3 V, const DeviceLight& l, V3& brdf,
+                                                    float& light_intensity) {
   V3 L = light_dir(l, p);
   V3 VL = V + L;
   V3 H = length_(VL) > 0.0f ? normalize_(VL) : VL;
@@ -122,16 +124,30 @@ __device__ __forceinline__ V3 sample_direct(V3 p, V3 N, const SurfMat& m, V3 V, 
   float D = div_(a2, max_(0.001f, (dd * dd * SRT_PI_F)));
   // G
   float k = div_(rough * rough, 2.0f);
-  float g_v = div_(NdotV, max_(0.001f, (NdotV * (1.0f - k) + k)));
-  float g_l = div_(NdotL, max_(0.001f, (NdotL * (1.0f - k) + k)));
+  float g_v = div0_(NdotV, max_(0.001f, (NdotV * (1.0f - k) + k)));
+  float g_l = div0_(NdotL, max_(0.001f, (NdotL * (1.0f - k) + k)));
   float G = abs_(g_v * g_l);
   // F
   V3 F = m.specular + (v3(1.0f) - m.specular) * pow5_(max_(0.001f, 1.0f - LdotH));
   float falloff = light_falloff(p, l);
-  float light_intensity = l.intensity * falloff;
-  V3 ggx = (D * G) * F / (4.0f * max_(0.001f, NdotV));
+  light_intensity = l.intensity * falloff;
+  V3 ggx = div0_((D * G) * F, 4.0f * max_(0.001f, NdotV));
+  brdf = ggx + div0_(NdotL * m.albedo, SRT_PI_F);
+}
+__device__ __forceinline__ V3 sample_direct(V3 p, V3 N, const SurfMat& m, V3 V, const DeviceLight& l, float shadow_mult) {
+  V3 brdf;
+  float light_intensity;
+  sample_direct_terms(p, N, m, V, l, brdf, light_intensity);
   V3 light_term = shadow_mult * v3(l.cx, l.cy, l.cz) * light_intensity;
-  return light_term * (ggx + NdotL * m.albedo / SRT_PI_F);
+  return light_term * brdf;
+}
+// SampleDirect for both answers of the shadow ray at once (shadow_mult = 1 and 0): the same expressions, the shared part once
+__device__ __forceinline__ void sample_direct_both(V3 p, V3 N, const SurfMat& m, V3 V, const DeviceLight& l, V3& lit, V3& occluded) {
+  V3 brdf;
+  float light_intensity;
+  sample_direct_terms(p, N, m, V, l, brdf, light_intensity);
+  lit = (1.0f * v3(l.cx, l.cy, l.cz) * light_intensity) * brdf;
+  occluded = (0.0f * v3(l.cx, l.cy, l.cz) * light_intensity) * brdf;
 }
 
 // SmithGAlpha / SmithGLambdaGGX / Smith_G2_Height_Correlated (brdf.glsl:44-57)

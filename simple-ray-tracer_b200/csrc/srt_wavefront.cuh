@@ -464,14 +464,23 @@ __device__ __forceinline__ V3 wf_add_pending(const PathPool& pool, uint32_t slot
 }
 
 // ---- logic: everything GetRayColor does between two CheckHit calls (raytrace_compute.glsl:225-292) -----------------
+// TEX: the textured-albedo option (SRT_OPT_TEXTURES with a texture set); its 9 KB of code stay out of the other instance.
+//
+// A block works in PHASES that all of its warps enter together.  Phase A: every warp takes one 32-entry chunk of the
+// wave, ends the paths whose ray missed (little code) and puts the slots whose ray hit something on a list in shared
+// memory.  Phase B, once a block's worth of hits is waiting: every thread shades one.  The shading code is ~60 KB of
+// straight-line arithmetic, twice the 32 KB instruction cache of an SM: warps that walk through it at 32 unrelated places
+// wait for instructions more than for anything else (6.6 warps per issue in the capture of profiles/r02n_*), warps of
+// a block that start it together fetch each line once for all of them.
+template <bool TEX>
 __global__ void __launch_bounds__(SRT_WF_LOGIC_THREADS, SRT_WF_LOGIC_BLOCKS_PER_SM)
 wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity,
                 uint32_t* __restrict__ primary_ids, DeviceCounters* __restrict__ counters) {
   const unsigned FULL = 0xFFFFFFFFu;
   const int lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
-  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+  constexpr uint32_t warps_per_block = SRT_WF_LOGIC_THREADS / 32;
+  const uint32_t n_warps = gridDim.x * warps_per_block;
   WaveCounters* q = pool.q;
   // region a: the closest queue (one entry per path that has a next segment); region d: paths that only wait for their
   // last shadow ray.  The shadow queue itself is the trace kernels' business: its rays belong to slots met in a or d.
@@ -496,38 +505,47 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
   const uint32_t total_chunks = chunks_a + chunks_d;
   const uint32_t append_chunk = total_chunks > 4u * n_warps ? SRT_WF_APPEND_CHUNK : 0u;
 
-  // Paths whose ray hit something are put aside per warp and shaded 32 at a time: in a chunk of the queue hits and misses
-  // are mixed, and the shading code (some 2 800 thread-instructions per path) would run as wide as the hits are dense.
-  __shared__ uint32_t s_stash[SRT_WF_LOGIC_THREADS / 32][64];
-  uint32_t* stash = s_stash[threadIdx.x >> 5];
-  uint32_t stash_n = 0;  // warp-uniform
+  // slots whose ray hit something, waiting to be shaded: fewer than a block's worth are left over by a phase B, a phase A
+  // adds at most one per thread
+  __shared__ uint32_t s_stash[2 * SRT_WF_LOGIC_THREADS];
+  __shared__ uint32_t s_stash_n;
+  if (threadIdx.x == 0) s_stash_n = 0;
+  __syncthreads();
 
-  for (uint32_t g = warp;;) {
-    const bool stashed = stash_n >= 32u || (g >= total_chunks && stash_n > 0u);  // this turn shades put-aside paths
-    if (!stashed && g >= total_chunks) break;
+  for (uint32_t turn = 0;; ++turn) {
+    // block-uniform: phase A while the wave has chunks for this block and fewer than a block's worth of hits wait
+    const uint32_t first_chunk = (turn * gridDim.x + blockIdx.x) * warps_per_block;  // this block's chunks of this turn
+    const uint32_t waiting = s_stash_n;
+    const bool more = first_chunk < total_chunks;
+    const bool stashed = waiting >= SRT_WF_LOGIC_THREADS || (!more && waiting > 0u);  // this turn shades put-aside paths
+    if (!stashed && !more) break;
+    __syncthreads();  // everyone has read s_stash_n
     bool region_a = true;  // warp-uniform
     uint32_t slot = 0;
     bool valid = false;
     if (stashed) {
-      const uint32_t take = stash_n < 32u ? stash_n : 32u;
-      if ((uint32_t)lane < take) {
-        slot = stash[stash_n - take + lane];
+      --turn;  // the chunks of this turn are still to come
+      const uint32_t take = waiting < SRT_WF_LOGIC_THREADS ? waiting : SRT_WF_LOGIC_THREADS;
+      if (threadIdx.x < take) {
+        slot = s_stash[waiting - take + threadIdx.x];
         valid = true;
       }
-      stash_n -= take;
-      __syncwarp();
+      __syncthreads();
+      if (threadIdx.x == 0) s_stash_n = waiting - take;
     } else {
-      region_a = g < chunks_a;
-      const uint32_t idx = (region_a ? g : g - chunks_a) * 32u + lane;
-      if (idx < (region_a ? n_a : n_d)) {
-        SRT_CHECK(region_a ? idx < pool.list_cap : idx < pool.cap, SRT_CHK_LIST_READ);
-        const uint32_t entry = __ldg(region_a ? list_in + idx : dying_in + idx);
-        if (entry != SRT_WF_HOLE) {
-          slot = region_a ? entry >> 1 : entry;  // the closest queue holds ray ids (2 * slot)
-          valid = true;
+      const uint32_t g = first_chunk + (threadIdx.x >> 5);
+      if (g < total_chunks) {
+        region_a = g < chunks_a;
+        const uint32_t idx = (region_a ? g : g - chunks_a) * 32u + lane;
+        if (idx < (region_a ? n_a : n_d)) {
+          SRT_CHECK(region_a ? idx < pool.list_cap : idx < pool.cap, SRT_CHK_LIST_READ);
+          const uint32_t entry = __ldg(region_a ? list_in + idx : dying_in + idx);
+          if (entry != SRT_WF_HOLE) {
+            slot = region_a ? entry >> 1 : entry;  // the closest queue holds ray ids (2 * slot)
+            valid = true;
+          }
         }
       }
-      g += n_warps;
     }
     SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
 
@@ -535,16 +553,18 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
     uint4 h = make_uint4(SRT_NO_HIT, 0u, SRT_WF_NOT_PENDING, 0u);  // .xy: the closest-hit ray's answer, .zw: the shadow ray's
     if (valid) h = __ldcs(reinterpret_cast<const uint4*>(pool.hit) + slot);
     if (valid && !stashed) {
-      if (region_a && h.x != SRT_NO_HIT) put_aside = true;  // shaded when 32 are waiting
+      if (region_a && h.x != SRT_NO_HIT) put_aside = true;  // shaded in a phase B
       else finish = true;  // a miss (:287-289), or a path that only waited for its last shadow ray
     }
-    {
+    if (!stashed) {
       const unsigned m_p = __ballot_sync(FULL, put_aside);
-      if (m_p) {  // at most 31 entries are waiting here, so 64 hold them all
-        SRT_CHECK(stash_n + (uint32_t)__popc(m_p) <= 64u, SRT_CHK_STASH);
-        if (put_aside) stash[stash_n + __popc(m_p & lt_mask)] = slot;
-        stash_n += (uint32_t)__popc(m_p);
-        __syncwarp();
+      if (m_p) {
+        uint32_t base = 0;
+        const int leader = __ffs(m_p) - 1;
+        if (lane == leader) base = atomicAdd(&s_stash_n, (uint32_t)__popc(m_p));
+        base = __shfl_sync(FULL, base, leader);
+        SRT_CHECK(base + (uint32_t)__popc(m_p) <= 2u * SRT_WF_LOGIC_THREADS, SRT_CHK_STASH);
+        if (put_aside) s_stash[base + __popc(m_p & lt_mask)] = slot;
       }
     }
     shade = valid && stashed;
@@ -584,7 +604,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       const float4 ma = __ldg(mp), mb = __ldg(mp + 1);
       V3 tex_albedo = v3(0.0f);
       bool has_tex = false;
-      if (sc.tex_tris != nullptr)  // textured-albedo option: needs the ray as it was traced
+      if (TEX && sc.tex_tris != nullptr)  // textured-albedo option: needs the ray as it was traced
         has_tex = textured_albedo(sc, hit_prim, r0, r1, r2, mb, ray_o, dir, __uint_as_float(h.y), tex_albedo);
       const V3 p = (__uint_as_float(h.y) * dir) + ray_o;  // rec.p (:155)
       const V3 N = normalize_(cross_(v3(r1.x, r1.y, r1.z), v3(r2.x, r2.y, r2.z)));  // ray_intersects.glsl:90
@@ -603,8 +623,10 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         const V3 lpos = v3(l.px, l.py, l.pz);
         const V3 sd = normalize_(lpos - p);
         const float len = length_(lpos - p);
-        const V3 lit = throughput * sample_direct(p, N, mat, V, l, 1.0f) * light_weight;
-        const V3 occluded = throughput * sample_direct(p, N, mat, V, l, 0.0f) * light_weight;
+        V3 sd_lit, sd_occluded;
+        sample_direct_both(p, N, mat, V, l, sd_lit, sd_occluded);
+        const V3 lit = throughput * sd_lit * light_weight;
+        const V3 occluded = throughput * sd_occluded * light_weight;
         __stcs(pool.ray + 2 * (id + 1), make_float4(p.x, p.y, p.z, len));
         __stcs(pool.ray + 2 * (id + 1) + 1, make_float4(sd.x, sd.y, sd.z, __uint_as_float(SRT_WF_KIND_SHADOW | ((uint32_t)li << 8))));
         __stcs(pool.pend + slot, make_float4(lit.x, lit.y, lit.z, __uint_as_float(wf_zero_code(occluded))));
@@ -727,6 +749,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       SRT_CHECK(base + (uint32_t)__popc(m_d) <= pool.cap, SRT_CHK_LIST_WRITE);
       if (emit_dying) dying_out[base + __popc(m_d & lt_mask)] = slot;
     }
+    __syncthreads();  // the list of waiting hits is complete (phase A) / its count is set (phase B) before the next turn looks
   }
   for (uint32_t i = c_next + lane; i < c_end; i += 32) list_out[i] = SRT_WF_HOLE;
   for (uint32_t i = s_next + lane; i < s_end; i += 32) list_out[pool.list_cap - 1u - i] = SRT_WF_HOLE;
