@@ -116,7 +116,7 @@ SRT_HD float div0_(float a, float b) {
 #if defined(__CUDA_ARCH__)
   const uint32_t ub = f2u(b) & 0x7fffffffu;
   const bool zero = (a == 0.0f) && (ub <= 0x7f800000u);
-  const float q = __fdiv_rn(zero ? 1.0f : a, b);  /* (a zero numerator never reaches the divider) */
+  const float q = __fdiv_rn(zero ? 1.0f : a, zero ? 1.0f : b);  /* (a zero numerator never reaches the divider, nor does 0 / 0) */
   const float z = ub == 0u ? u2f(0x7fffffffu) : u2f((f2u(a) ^ f2u(b)) & 0x80000000u);
   return zero ? z : q;
 #else
