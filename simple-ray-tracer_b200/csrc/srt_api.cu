@@ -127,6 +127,7 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   cudaSetDevice(ctx->device);
   dfree(ctx->d_pairs); dfree(ctx->d_leaves); dfree(ctx->d_tris); dfree(ctx->d_mats); dfree(ctx->d_bvhs);
   relayout_workspace_release(&ctx->relayout_ws);
+  finder_build_workspace_release(&ctx->finder_ws);
   dfree(ctx->d_fpairs); dfree(ctx->d_ftris); dfree(ctx->d_rnodes); dfree(ctx->d_tri_leaf);
   dfree(ctx->d_tex_tris); dfree(ctx->d_tex_info); dfree(ctx->d_texels);
   dfree(ctx->d_noise_xy); ctx->d_noise_x = nullptr; dfree(ctx->d_accum); dfree(ctx->d_out); dfree(ctx->d_ids);
@@ -200,6 +201,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_SORT_RAYS) {
     if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_SORT_RAYS: 0 (off) or 1 (on)");
     ctx->sort_rays = value;
+    return 0;
+  }
+  if (key == SRT_OPT_DEVICE_FINDER_BUILD) {
+    if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_DEVICE_FINDER_BUILD: 0 (host threads) or 1 (device)");
+    ctx->device_finder_build = value;
     return 0;
   }
   if (key == SRT_OPT_DEVICE_RELAYOUT) {
@@ -482,7 +488,7 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   for (BvhRecord& r : rl.bvhs) r.finder_root = r.root_node = 0u;
   if (ctx->finder_mode != 0) {
     FinderOut fo;
-    if (build_finder(bvhs, n_bvhs, nodes, n_nodes, triangles, vertices, tris, fo)) {
+    if (build_finder(bvhs, n_bvhs, nodes, n_nodes, triangles, vertices, tris, fo, ctx->device_finder_build ? &ctx->finder_ws : nullptr, ctx->stream)) {
       for (uint32_t b = 0; b < n_bvhs; ++b) {
         rl.bvhs[b].finder_root = fo.root[b];
         rl.bvhs[b].root_node = bvhs[b].first_index;

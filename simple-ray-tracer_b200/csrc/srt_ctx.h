@@ -113,6 +113,8 @@ struct srt_ctx {
   int device_relayout = 2;                      // SRT_OPT_DEVICE_RELAYOUT: 0 host walk, 1 device, 2 device above SRT_FINDER_MAX_TRIS triangles
   bool relayout_on_device = false;              // what the last upload did
   float relayout_device_ms = 0.0f;
+  int device_finder_build = 1;                  // SRT_OPT_DEVICE_FINDER_BUILD: the hit finder's trees are built by kernels (srt_finder_build.cu)
+  FinderBuildWorkspace finder_ws;
   RelayoutWorkspace relayout_ws;                // raw arrays + scratch of the device re-layout, kept between uploads
   int sort_rays = 0;                            // SRT_OPT_SORT_RAYS: 0 off (default: measured slower, see srt_b200.h), 1 on
   bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL

@@ -2,6 +2,8 @@
 // Host code only; compiled by nvcc because the records are the device's.
 #include "srt_finder.h"
 
+#include <cuda_runtime.h>
+
 #include <math.h>
 #include <string.h>
 
@@ -9,6 +11,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <string>
 #include <chrono>
 #include <atomic>
 #include <thread>
@@ -258,7 +261,7 @@ inline bool tri_hit(const TriRecord& r, const float* o, const float* d, float li
 
 bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* nodes, uint32_t n_nodes,
                   const srt_triangle* triangles, const srt_vertex* vertices, const std::vector<TriRecord>& tris_ref,
-                  FinderOut& out) {
+                  FinderOut& out, FinderBuildWorkspace* device_ws, cudaStream_t stream) {
   const uint32_t n_tris = (uint32_t)tris_ref.size();
   out = FinderOut();
   const bool log = getenv("SRT_UPLOAD_LOG") != nullptr;
@@ -269,8 +272,9 @@ bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* node
   const auto t0 = now();
   double ms_tree = 0.0;
   if (n_tris == 0 || n_tris > SRT_FINDER_MAX_TRIS) return false;
-  std::vector<Box> tb(n_tris);
-  for (uint32_t i = 0; i < n_tris; ++i) {
+  // the triangles' boxes are the host builder's input; the device builder (srt_finder_build.cu) makes its own
+  std::vector<Box> tb(device_ws ? 0 : n_tris);
+  for (uint32_t i = 0; i < (device_ws ? 0u : n_tris); ++i) {
     const float* v[3] = {vertices[triangles[i].v0_idx].vertex, vertices[triangles[i].v1_idx].vertex,
                          vertices[triangles[i].v2_idx].vertex};
     // the device tests v0, v0 + edge_1, v0 + edge_2 in effect; the box takes the vertices AND those sums
@@ -285,6 +289,9 @@ bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* node
   out.tri_leaf.assign(n_tris, 0xFFFFFFFFu);
   out.root.assign(n_bvhs, 0u);
   out.pad.assign(n_bvhs, 0.0f);
+  std::vector<uint32_t> tree_of;                 // finder tree k belongs to BVH tree_of[k]
+  std::vector<float> tree_pads;
+  std::vector<std::vector<uint32_t>> tree_tris;  // its triangles, in the reference tree's pre-order
   std::vector<uint32_t> owner(n_nodes, 0xFFFFFFFFu);  // root that reached the node
   std::vector<int> leaf_depth(n_nodes, 0);
   for (uint32_t b = 0; b < n_bvhs; ++b) {
@@ -344,11 +351,50 @@ bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* node
     for (int a = 0; a < 3; ++a) ext = std::max(ext, nodes[root].max_bounds[a] - nodes[root].min_bounds[a]);
     if (!(ext > 0.0f) || !std::isfinite(ext)) return false;
     const float pad = ext * (1.0f / 4096.0f);
-    const auto tt = now();
-    out.root[b] = build_tree(tris_ref, tb, mine, pad, out);
-    ms_tree += ms(tt, now());
     out.pad[b] = pad;
+    tree_of.push_back(b);
+    tree_pads.push_back(pad);
+    tree_tris.push_back(std::move(mine));
   }
+  {
+    const auto tt = now();
+    bool on_device = false;
+    if (device_ws) {  // all trees in one go, a level per turn (srt_finder_build.cu); anything it refuses is built here
+      std::vector<uint32_t> roots;
+      std::string why;
+      const int rc = build_finder_trees_device(tris_ref, tree_tris, tree_pads, device_ws, stream, &out.pairs, &out.tris, &roots,
+                                               &out.depth, &why);
+      if (rc == 0) {
+        for (size_t k = 0; k < tree_of.size(); ++k) out.root[tree_of[k]] = roots[k];
+        on_device = true;
+      } else if (rc == 1 && log) {
+        fprintf(stderr, "build_finder: %s; building on the host\n", why.c_str());
+      }
+    }
+    if (!on_device) {
+      if (tb.empty()) {
+        tb.resize(n_tris);
+        for (uint32_t i = 0; i < n_tris; ++i) {
+          const TriRecord& r = tris_ref[i];
+          const float w0[3] = {r.v0.x, r.v0.y, r.v0.z};
+          const float w1[3] = {r.v0.x + r.e1.x, r.v0.y + r.e1.y, r.v0.z + r.e1.z}, w2[3] = {r.v0.x + r.e2.x, r.v0.y + r.e2.y, r.v0.z + r.e2.z};
+          for (int a = 0; a < 3; ++a) {
+            tb[i].mn[a] = std::min(w0[a], std::min(w1[a], w2[a]));
+            tb[i].mx[a] = std::max(w0[a], std::max(w1[a], w2[a]));
+          }
+        }
+      }
+      out.pairs.clear();
+      out.tris.clear();
+      out.depth = 0;
+      for (size_t k = 0; k < tree_of.size(); ++k) out.root[tree_of[k]] = build_tree(tris_ref, tb, tree_tris[k], tree_pads[k], out);
+    }
+    ms_tree += ms(tt, now());
+  }
+  // the same tree under another frame: filled in now that the first one's root is known
+  for (uint32_t b = 0; b < n_bvhs; ++b)
+    for (uint32_t p = 0; p < b; ++p)
+      if (bvhs[p].first_index == bvhs[b].first_index) { out.root[b] = out.root[p]; out.pad[b] = out.pad[p]; break; }
   if (out.pairs.size() >= SRT_LEAF_BIT - 1u || out.depth > SRT_STACK_SIZE - 1) return false;
 
   const auto t1 = now();

@@ -24,6 +24,7 @@
 #include <vector>
 
 #include "srt_device.cuh"
+#include "srt_finder_build.h"
 #include "srt_types.h"
 
 namespace srt {
@@ -42,8 +43,10 @@ struct FinderOut {
 
 // tris_ref: the device records of the triangles in reference order (e1.w = visiting rank).  Returns false (and leaves
 // out.worthwhile false) when the scene is out of the finder's range (too many triangles, shared subtrees).
+// device_ws: non-null = the trees are built on the device (srt_finder_build.cu) with that workspace, on `stream`; null = on
+// host threads.  The reference-side tables (RefNode, tri_leaf) and the sample-ray costing are host work either way.
 bool build_finder(const srt_bvh* bvhs, uint32_t n_bvhs, const srt_bvh_node* nodes, uint32_t n_nodes,
                   const srt_triangle* triangles, const srt_vertex* vertices, const std::vector<TriRecord>& tris_ref,
-                  FinderOut& out);
+                  FinderOut& out, FinderBuildWorkspace* device_ws = nullptr, cudaStream_t stream = nullptr);
 
 }  // namespace srt

@@ -1,0 +1,482 @@
+// srt_finder_build.cu -- the hit finder's private tree (srt_finder.h) built ON THE DEVICE.
+//
+// No reference counterpart: the finder is this library's own structure (the reference walks its midpoint-split BVH and
+// nothing else).  Any conservative tree gives the same pictures -- the finder only collects candidate triangles, the
+// replay of the shader's own culls decides -- so this builder shares the host builder's rules (binned SAH over three axes,
+// 16 bins, leaves of at most 4 triangles, split by count where the bins have nothing to offer, boxes padded by `pad`) but
+// not its bits: it looks at every triangle of a node where the host samples the big ones.
+//
+// Why: the host builder (srt_finder.cu: build_tree) takes 14 ms for the 110 k-triangle stand-in on 16 host threads, every
+// srt_upload_scene -- a third of that scene's end-to-end step.  Here the tree grows one LEVEL per turn
+// for all nodes of all BVHs at once:
+//   k_bounds   per triangle: the centre bounds and the box of its node, by atomics (ordered-integer min / max)
+//   k_bin      per triangle: its bin on each axis; count and box of that bin, by atomics
+//   k_split    per node: leaf (<= 4 triangles), or the best of the 3 x 15 SAH planes, or the middle of the range
+//   scan       of the inner flags: pair indices and the numbers of the child nodes, in node order (deterministic)
+//   k_side     per triangle: left or right of the plane; scan of the left flags
+//   k_scatter  per triangle: its place in the child's range (stable); triangles of leaves stay and become records
+//   k_link     per node: its reference and padded box into its parent's NodePair half (or the BVH's root reference)
+// about a dozen launches and one 8-byte read-back per level, ~20 levels.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "srt_bvh_build.h"
+#include "srt_finder_build.h"
+
+namespace srt {
+namespace {
+
+#define FB_THREADS 256
+constexpr int kBins = 16;
+constexpr uint32_t kLeafMax = 4;
+constexpr uint32_t kNone = 0xFFFFFFFFu;
+
+// float <-> int whose signed order is the floats' order (for atomicMin / atomicMax)
+__device__ __forceinline__ int ord(float f) {
+  const int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7FFFFFFF;
+}
+__device__ __forceinline__ float unord(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7FFFFFFF); }
+#define ORD_PLUS_INF 0x7F800000
+#define ORD_MINUS_INF ((int)0x807FFFFF)  // ord(-inf)
+
+struct Node {           // a node of the level being split
+  uint32_t lo, hi;      // its triangles: positions [lo, hi) of idx
+  uint32_t parent;      // pair that holds its reference: pair * 2 + side; kNone | bvh for a root (see k_link)
+  uint32_t mid;         // k_split: first position of the right child (inner nodes)
+  int axis, bin;        // k_split: the plane (axis < 0: split by position)
+  uint32_t inner;       // k_split: 1 when the node is split
+  uint32_t tree;        // which BVH's finder tree the node belongs to (its pad)
+};
+struct NodeBounds {     // ordered ints
+  int cmin[3], cmax[3];  // of the triangles' centres
+  int bmin[3], bmax[3];  // of the triangles' boxes
+};
+struct Bin {
+  int bmin[3], bmax[3];
+  unsigned int count;
+  unsigned int _pad;
+};
+
+__device__ __forceinline__ void tri_box(const TriRecord& r, float mn[3], float mx[3]) {
+  // the device tests v0, v0 + edge_1, v0 + edge_2 in effect
+  const float v0[3] = {r.v0.x, r.v0.y, r.v0.z};
+  const float w1[3] = {r.v0.x + r.e1.x, r.v0.y + r.e1.y, r.v0.z + r.e1.z};
+  const float w2[3] = {r.v0.x + r.e2.x, r.v0.y + r.e2.y, r.v0.z + r.e2.z};
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    mn[a] = fminf(v0[a], fminf(w1[a], w2[a]));
+    mx[a] = fmaxf(v0[a], fmaxf(w1[a], w2[a]));
+  }
+}
+
+__global__ void __launch_bounds__(FB_THREADS)
+k_clear(NodeBounds* nb, Bin* bins, uint32_t n_nodes) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_nodes) {
+    NodeBounds b;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      b.cmin[a] = ORD_PLUS_INF; b.cmax[a] = ORD_MINUS_INF;
+      b.bmin[a] = ORD_PLUS_INF; b.bmax[a] = ORD_MINUS_INF;
+    }
+    nb[i] = b;
+  }
+  if (i < n_nodes * 3u * kBins) {
+    Bin b;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { b.bmin[a] = ORD_PLUS_INF; b.bmax[a] = ORD_MINUS_INF; }
+    b.count = 0u;
+    b._pad = 0u;
+    bins[i] = b;
+  }
+}
+
+__global__ void __launch_bounds__(FB_THREADS)
+k_bounds(const TriRecord* __restrict__ ref, const uint32_t* __restrict__ idx, const uint32_t* __restrict__ node_of, uint32_t n,
+         NodeBounds* nb) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t nd = node_of[i];
+  if (nd == kNone) return;
+  float mn[3], mx[3];
+  tri_box(ref[idx[i]], mn, mx);
+  NodeBounds* b = nb + nd;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const float c = 0.5f * (mn[a] + mx[a]);
+    atomicMin(&b->cmin[a], ord(c));
+    atomicMax(&b->cmax[a], ord(c));
+    atomicMin(&b->bmin[a], ord(mn[a]));
+    atomicMax(&b->bmax[a], ord(mx[a]));
+  }
+}
+
+__device__ __forceinline__ int bin_of(float c, float base, float scale) {
+  int b = (int)((c - base) * scale);
+  return b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
+}
+
+__global__ void __launch_bounds__(FB_THREADS)
+k_bin(const TriRecord* __restrict__ ref, const uint32_t* __restrict__ idx, const uint32_t* __restrict__ node_of, uint32_t n,
+      const Node* __restrict__ nodes, const NodeBounds* __restrict__ nb, Bin* bins) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t nd = node_of[i];
+  if (nd == kNone) return;
+  if (nodes[nd].hi - nodes[nd].lo <= kLeafMax) return;  // a leaf: no plane is looked for
+  float mn[3], mx[3];
+  tri_box(ref[idx[i]], mn, mx);
+  const NodeBounds b = nb[nd];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const float lo = unord(b.cmin[a]), hi = unord(b.cmax[a]);
+    if (!(hi > lo)) continue;
+    const int k = bin_of(0.5f * (mn[a] + mx[a]), lo, (float)kBins / (hi - lo));
+    Bin* dst = bins + ((size_t)nd * 3u + a) * kBins + k;
+    atomicAdd(&dst->count, 1u);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      atomicMin(&dst->bmin[c], ord(mn[c]));
+      atomicMax(&dst->bmax[c], ord(mx[c]));
+    }
+  }
+}
+
+__device__ __forceinline__ float area_of(const float mn[3], const float mx[3]) {
+  const float dx = mx[0] - mn[0], dy = mx[1] - mn[1], dz = mx[2] - mn[2];
+  return 2.0f * (dx * dy + dy * dz + dz * dx);
+}
+
+__global__ void __launch_bounds__(FB_THREADS)
+k_split(Node* nodes, uint32_t n_nodes, const NodeBounds* __restrict__ nb, const Bin* __restrict__ bins, uint32_t* __restrict__ inner) {
+  const uint32_t nd = blockIdx.x * blockDim.x + threadIdx.x;
+  if (nd > n_nodes) return;
+  if (nd == n_nodes) {  // the scan's last entry is the total
+    inner[nd] = 0u;
+    return;
+  }
+  Node node = nodes[nd];
+  const uint32_t count = node.hi - node.lo;
+  if (count <= kLeafMax) {
+    node.inner = 0u;
+    node.axis = -1;
+    node.bin = -1;
+    node.mid = node.hi;
+    nodes[nd] = node;
+    inner[nd] = 0u;
+    return;
+  }
+  const NodeBounds b = nb[nd];
+  float best_cost = __int_as_float(0x7F800000);
+  int best_axis = -1, best_bin = -1;
+  uint32_t best_left = 0;
+  for (int a = 0; a < 3; ++a) {
+    if (!(unord(b.cmax[a]) > unord(b.cmin[a]))) continue;
+    const Bin* row = bins + ((size_t)nd * 3u + a) * kBins;
+    float ra[kBins];
+    uint32_t rc[kBins];
+    {
+      float mn[3] = {__int_as_float(0x7F800000), __int_as_float(0x7F800000), __int_as_float(0x7F800000)};
+      float mx[3] = {-mn[0], -mn[0], -mn[0]};
+      uint32_t c = 0;
+      for (int k = kBins - 1; k >= 0; --k) {
+        if (row[k].count) {
+          for (int d = 0; d < 3; ++d) {
+            mn[d] = fminf(mn[d], unord(row[k].bmin[d]));
+            mx[d] = fmaxf(mx[d], unord(row[k].bmax[d]));
+          }
+        }
+        c += row[k].count;
+        ra[k] = c ? area_of(mn, mx) : 0.0f;
+        rc[k] = c;
+      }
+    }
+    float mn[3] = {__int_as_float(0x7F800000), __int_as_float(0x7F800000), __int_as_float(0x7F800000)};
+    float mx[3] = {-mn[0], -mn[0], -mn[0]};
+    uint32_t c = 0;
+    for (int k = 0; k + 1 < kBins; ++k) {
+      if (row[k].count) {
+        for (int d = 0; d < 3; ++d) {
+          mn[d] = fminf(mn[d], unord(row[k].bmin[d]));
+          mx[d] = fmaxf(mx[d], unord(row[k].bmax[d]));
+        }
+      }
+      c += row[k].count;
+      if (c == 0u || rc[k + 1] == 0u) continue;
+      const float cost = area_of(mn, mx) * (float)c + ra[k + 1] * (float)rc[k + 1];
+      if (cost < best_cost) {
+        best_cost = cost;
+        best_axis = a;
+        best_bin = k;
+        best_left = c;
+      }
+    }
+  }
+  node.inner = 1u;
+  node.axis = best_axis;
+  node.bin = best_bin;
+  node.mid = best_axis >= 0 ? node.lo + best_left : (node.lo + node.hi) / 2u;  // all centres equal: split by count
+  nodes[nd] = node;
+  inner[nd] = 1u;
+}
+
+// per triangle: 1 when it goes to the left child of its (inner) node
+__global__ void __launch_bounds__(FB_THREADS)
+k_side(const TriRecord* __restrict__ ref, const uint32_t* __restrict__ idx, const uint32_t* __restrict__ node_of, uint32_t n,
+       const Node* __restrict__ nodes, const NodeBounds* __restrict__ nb, uint32_t* __restrict__ left) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > n) return;
+  if (i == n) {
+    left[i] = 0u;
+    return;
+  }
+  const uint32_t nd = node_of[i];
+  uint32_t l = 0u;
+  if (nd != kNone && nodes[nd].inner) {
+    const Node node = nodes[nd];
+    if (node.axis < 0) {
+      l = i < node.mid ? 1u : 0u;
+    } else {
+      float mn[3], mx[3];
+      tri_box(ref[idx[i]], mn, mx);
+      const float lo = unord(nb[nd].cmin[node.axis]), hi = unord(nb[nd].cmax[node.axis]);
+      l = bin_of(0.5f * (mn[node.axis] + mx[node.axis]), lo, (float)kBins / (hi - lo)) <= node.bin ? 1u : 0u;
+    }
+  }
+  left[i] = l;
+}
+
+// per triangle: its place in the next level.  Triangles of a node that became a leaf stay where they are and become the
+// leaf's records (finder-leaf order IS the final order of idx: a leaf's range is never touched again).
+__global__ void __launch_bounds__(FB_THREADS)
+k_scatter(const TriRecord* __restrict__ ref, const uint32_t* __restrict__ idx, const uint32_t* __restrict__ node_of, uint32_t n,
+          const Node* __restrict__ nodes, const uint32_t* __restrict__ left, const uint32_t* __restrict__ left_scan,
+          const uint32_t* __restrict__ inner_scan, uint32_t* __restrict__ idx2, uint32_t* __restrict__ node_of2,
+          TriRecord* __restrict__ ftris) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t nd = node_of[i];
+  const uint32_t t = idx[i];
+  if (nd == kNone) {  // in a leaf made at an earlier level
+    idx2[i] = t;
+    node_of2[i] = kNone;
+    return;
+  }
+  const Node node = nodes[nd];
+  if (!node.inner) {
+    idx2[i] = t;
+    node_of2[i] = kNone;
+    TriRecord r = ref[t];
+    r.v0.w = __uint_as_float(t);                  // where the triangle is in the reference order (its material is looked up there)
+    r.e2.w = __uint_as_float(node.hi - 1u - i);   // triangles that follow in this leaf
+    ftris[i] = r;
+    return;
+  }
+  const uint32_t lefts_before = left_scan[i] - left_scan[node.lo];
+  const uint32_t child = 2u * inner_scan[nd];
+  if (left[i]) {
+    const uint32_t pos = node.lo + lefts_before;
+    idx2[pos] = t;
+    node_of2[pos] = child;
+  } else {
+    const uint32_t pos = node.mid + (i - node.lo - lefts_before);
+    idx2[pos] = t;
+    node_of2[pos] = child + 1u;
+  }
+}
+
+// per node: its reference and padded box into its parent's pair (or the tree's root reference); the child nodes of a split
+__global__ void __launch_bounds__(FB_THREADS)
+k_link(const Node* __restrict__ nodes, uint32_t n_nodes, const NodeBounds* __restrict__ nb, const uint32_t* __restrict__ inner_scan,
+       uint32_t pair_base, const float* __restrict__ pads, NodePair* pairs, uint32_t* __restrict__ roots, Node* __restrict__ next) {
+  const uint32_t nd = blockIdx.x * blockDim.x + threadIdx.x;
+  if (nd >= n_nodes) return;
+  const Node node = nodes[nd];
+  const uint32_t my_pair = pair_base + inner_scan[nd];
+  const uint32_t ref = node.inner ? my_pair : (SRT_LEAF_BIT | node.lo);
+  if (node.parent == kNone) {
+    roots[node.tree] = ref;
+  } else {
+    const float pad = pads[node.tree];
+    const NodeBounds b = nb[nd];
+    const float mn[3] = {unord(b.bmin[0]) - pad, unord(b.bmin[1]) - pad, unord(b.bmin[2]) - pad};
+    const float mx[3] = {unord(b.bmax[0]) + pad, unord(b.bmax[1]) + pad, unord(b.bmax[2]) + pad};
+    NodePair* p = pairs + (node.parent >> 1);
+    if ((node.parent & 1u) == 0u) {
+      p->a = make_float4(mn[0], mn[1], mn[2], mx[0]);
+      p->b.x = mx[1];
+      p->b.y = mx[2];
+      p->d.x = ref;
+      p->d.z = ref;
+    } else {
+      p->b.z = mn[0];
+      p->b.w = mn[1];
+      p->c = make_float4(mn[2], mx[0], mx[1], mx[2]);
+      p->d.y = ref;
+      p->d.w = ref;
+    }
+  }
+  if (node.inner) {
+    const uint32_t c = 2u * inner_scan[nd];
+    Node l, r;
+    l.lo = node.lo; l.hi = node.mid; l.parent = my_pair * 2u; l.mid = 0u; l.axis = -1; l.bin = -1; l.inner = 0u; l.tree = node.tree;
+    r = l;
+    r.lo = node.mid; r.hi = node.hi; r.parent = my_pair * 2u + 1u;
+    next[c] = l;
+    next[c + 1] = r;
+  }
+}
+
+struct Carver {  // 256-byte aligned pieces of one allocation (first pass with base == nullptr: the size)
+  char* base;
+  size_t at = 0;
+  template <class T>
+  T* take(size_t n) {
+    T* p = base ? reinterpret_cast<T*>(base + at) : nullptr;
+    at += ((n ? n : 1) * sizeof(T) + 255) & ~(size_t)255;
+    return p;
+  }
+};
+
+struct Pieces {
+  TriRecord* ref; TriRecord* ftris; NodePair* pairs;
+  uint32_t *idx, *idx2, *node_of, *node_of2, *left, *left_scan, *scan_a, *inner, *inner_scan, *scan_b, *roots;
+  float* pads;
+  Node *nodes_a, *nodes_b;
+  NodeBounds* nb;
+  Bin* bins;
+};
+
+Pieces carve(Carver& c, uint32_t n_ref, uint32_t n, uint32_t max_nodes, uint32_t n_trees) {
+  Pieces p;
+  p.ref = c.take<TriRecord>(n_ref);
+  p.ftris = c.take<TriRecord>(n);
+  p.pairs = c.take<NodePair>(n);
+  p.idx = c.take<uint32_t>(n); p.idx2 = c.take<uint32_t>(n);
+  p.node_of = c.take<uint32_t>(n); p.node_of2 = c.take<uint32_t>(n);
+  p.left = c.take<uint32_t>((size_t)n + 1); p.left_scan = c.take<uint32_t>((size_t)n + 1);
+  p.scan_a = c.take<uint32_t>(device_scan_scratch_entries(n + 1));
+  p.inner = c.take<uint32_t>((size_t)max_nodes + 1); p.inner_scan = c.take<uint32_t>((size_t)max_nodes + 1);
+  p.scan_b = c.take<uint32_t>(device_scan_scratch_entries(max_nodes + 1));
+  p.roots = c.take<uint32_t>(n_trees);
+  p.pads = c.take<float>(n_trees);
+  p.nodes_a = c.take<Node>(max_nodes); p.nodes_b = c.take<Node>(max_nodes);
+  p.nb = c.take<NodeBounds>(max_nodes);
+  p.bins = c.take<Bin>((size_t)max_nodes * 3u * kBins);
+  return p;
+}
+
+}  // namespace
+
+void finder_build_workspace_release(FinderBuildWorkspace* ws) {
+  cudaFree(ws->arena);
+  *ws = FinderBuildWorkspace();
+}
+
+#define FB(call)                                                                            \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) {                                                                \
+      *error = std::string("device finder build: ") + #call + ": " + cudaGetErrorString(e_); \
+      return 1;                                                                             \
+    }                                                                                       \
+  } while (0)
+
+int build_finder_trees_device(const std::vector<TriRecord>& tris_ref, const std::vector<std::vector<uint32_t>>& trees,
+                              const std::vector<float>& pads, FinderBuildWorkspace* ws, cudaStream_t stream,
+                              std::vector<NodePair>* pairs_out, std::vector<TriRecord>* tris_out, std::vector<uint32_t>* roots_out,
+                              int* depth_out, std::string* error) {
+  const uint32_t n_trees = (uint32_t)trees.size();
+  size_t total = 0;
+  for (const auto& t : trees) total += t.size();
+  if (n_trees == 0 || total == 0 || total >= SRT_LEAF_BIT - 1u) return 2;
+  const uint32_t n = (uint32_t)total, n_ref = (uint32_t)tris_ref.size();
+  // every split node has more than kLeafMax triangles, so a level has at most 2 n / (kLeafMax + 1) nodes
+  const uint32_t max_nodes = std::max(n / 2u + 64u, n_trees);
+  auto blocks = [](size_t k) { return (unsigned)((k + FB_THREADS - 1) / FB_THREADS); };
+
+  Carver sizing{nullptr};
+  carve(sizing, n_ref, n, max_nodes, n_trees);
+  if (!ws->arena || ws->bytes < sizing.at || ws->bytes > 2 * sizing.at + 4096) {
+    cudaFree(ws->arena);
+    ws->arena = nullptr;
+    ws->bytes = 0;
+    FB(cudaMalloc(&ws->arena, sizing.at));
+    ws->bytes = sizing.at;
+  }
+  Carver c{static_cast<char*>(ws->arena)};
+  const Pieces w = carve(c, n_ref, n, max_nodes, n_trees);
+
+  // level 0: one node per tree over its triangles, in the order given
+  std::vector<uint32_t> h_idx(n), h_node_of(n);
+  std::vector<Node> h_nodes(n_trees);
+  {
+    uint32_t at = 0;
+    for (uint32_t t = 0; t < n_trees; ++t) {
+      Node nd;
+      memset(&nd, 0, sizeof nd);
+      nd.lo = at;
+      for (uint32_t v : trees[t]) {
+        h_idx[at] = v;
+        h_node_of[at] = t;
+        ++at;
+      }
+      nd.hi = at;
+      nd.parent = kNone;
+      nd.axis = -1;
+      nd.bin = -1;
+      nd.tree = t;
+      h_nodes[t] = nd;
+    }
+  }
+  FB(cudaMemcpyAsync(w.ref, tris_ref.data(), (size_t)n_ref * sizeof(TriRecord), cudaMemcpyHostToDevice, stream));
+  FB(cudaMemcpyAsync(w.idx, h_idx.data(), (size_t)n * 4, cudaMemcpyHostToDevice, stream));
+  FB(cudaMemcpyAsync(w.node_of, h_node_of.data(), (size_t)n * 4, cudaMemcpyHostToDevice, stream));
+  FB(cudaMemcpyAsync(w.nodes_a, h_nodes.data(), (size_t)n_trees * sizeof(Node), cudaMemcpyHostToDevice, stream));
+  FB(cudaMemcpyAsync(w.pads, pads.data(), (size_t)n_trees * 4, cudaMemcpyHostToDevice, stream));
+
+  Node *cur = w.nodes_a, *next = w.nodes_b;
+  uint32_t *idx = w.idx, *idx2 = w.idx2, *node_of = w.node_of, *node_of2 = w.node_of2;
+  uint32_t n_nodes = n_trees, n_pairs = 0;
+  int levels = 0;
+  while (n_nodes > 0) {
+    if (n_nodes > max_nodes || levels > 4096) return 2;
+    k_clear<<<blocks((size_t)n_nodes * 3u * kBins), FB_THREADS, 0, stream>>>(w.nb, w.bins, n_nodes);
+    k_bounds<<<blocks(n), FB_THREADS, 0, stream>>>(w.ref, idx, node_of, n, w.nb);
+    k_bin<<<blocks(n), FB_THREADS, 0, stream>>>(w.ref, idx, node_of, n, cur, w.nb, w.bins);
+    k_split<<<blocks((size_t)n_nodes + 1), FB_THREADS, 0, stream>>>(cur, n_nodes, w.nb, w.bins, w.inner);
+    FB(device_exclusive_scan(w.inner, w.inner_scan, n_nodes + 1, w.scan_b, stream));
+    k_side<<<blocks((size_t)n + 1), FB_THREADS, 0, stream>>>(w.ref, idx, node_of, n, cur, w.nb, w.left);
+    FB(device_exclusive_scan(w.left, w.left_scan, n + 1, w.scan_a, stream));
+    k_scatter<<<blocks(n), FB_THREADS, 0, stream>>>(w.ref, idx, node_of, n, cur, w.left, w.left_scan, w.inner_scan, idx2, node_of2, w.ftris);
+    k_link<<<blocks(n_nodes), FB_THREADS, 0, stream>>>(cur, n_nodes, w.nb, w.inner_scan, n_pairs, w.pads, w.pairs, w.roots, next);
+    uint32_t n_inner = 0;
+    FB(cudaMemcpyAsync(&n_inner, w.inner_scan + n_nodes, 4, cudaMemcpyDeviceToHost, stream));
+    FB(cudaStreamSynchronize(stream));
+    FB(cudaGetLastError());
+    n_pairs += n_inner;
+    if (n_pairs > n) return 2;
+    n_nodes = 2u * n_inner;
+    std::swap(cur, next);
+    std::swap(idx, idx2);
+    std::swap(node_of, node_of2);
+    ++levels;
+  }
+  pairs_out->resize(n_pairs);
+  tris_out->resize(n);
+  roots_out->resize(n_trees);
+  FB(cudaMemcpyAsync(pairs_out->data(), w.pairs, (size_t)n_pairs * sizeof(NodePair), cudaMemcpyDeviceToHost, stream));
+  FB(cudaMemcpyAsync(tris_out->data(), w.ftris, (size_t)n * sizeof(TriRecord), cudaMemcpyDeviceToHost, stream));
+  FB(cudaMemcpyAsync(roots_out->data(), w.roots, (size_t)n_trees * 4, cudaMemcpyDeviceToHost, stream));
+  FB(cudaStreamSynchronize(stream));
+  *depth_out = levels - 1;
+  return 0;
+}
+
+}  // namespace srt
