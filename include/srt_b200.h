@@ -232,7 +232,7 @@ int srt_trace_rays_static(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, ui
                                      which handles or reports it.  Same records up to where a node pair sits in its array: no
                                      ray result depends on it (parity-tested).  srt_get_upload_info says what the last upload did */
 #define SRT_OPT_DEVICE_FINDER_BUILD 17 /* 1 (default) = the hit finder's private trees (SRT_OPT_FINDER) are built by kernels at srt_upload_scene
-                                     time, a tree level per turn (csrc/srt_finder_build.cu); 0 = on host threads.  Either tree gives
+                                     time, a tree level per turn (csrc/srt_finder_build.cu), for scenes of 16 Ki triangles and more; 0 = always on host threads.  Either tree gives
                                      the same pictures: the finder only collects candidates, the replay of the shader's own culls
                                      decides (parity-tested both ways) */
 #define SRT_OPT_SPLIT 14

@@ -488,7 +488,7 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   for (BvhRecord& r : rl.bvhs) r.finder_root = r.root_node = 0u;
   if (ctx->finder_mode != 0) {
     FinderOut fo;
-    if (build_finder(bvhs, n_bvhs, nodes, n_nodes, triangles, vertices, tris, fo, ctx->device_finder_build ? &ctx->finder_ws : nullptr, ctx->stream)) {
+    if (build_finder(bvhs, n_bvhs, nodes, n_nodes, triangles, vertices, tris, fo, (ctx->device_finder_build && (n_triangles >= SRT_FINDER_DEVICE_MIN_TRIS || getenv("SRT_FINDER_DEVICE_ALWAYS"))) ? &ctx->finder_ws : nullptr, ctx->stream)) {
       for (uint32_t b = 0; b < n_bvhs; ++b) {
         rl.bvhs[b].finder_root = fo.root[b];
         rl.bvhs[b].root_node = bvhs[b].first_index;

@@ -74,6 +74,7 @@ struct RefNode {
 #define SRT_CAND_MAX 8          // candidates kept per ray; a ray with more is traced by wf_trace_kernel instead
 #define SRT_CAND_BVH_SHIFT 26   // candidate word: triangle | bvh << 26
 #define SRT_FINDER_MAX_TRIS (1u << 21)
+#define SRT_FINDER_DEVICE_MIN_TRIS (1u << 14)  // below this the host builds the finder's trees faster than ~20 levels of launches (Rubik: 0.3 vs 1.6 ms)
 
 // SRT_OPT_TRAVERSAL values (srt_b200.h)
 enum { TRAV_REFERENCE = 0, TRAV_ORDERED = 1 };

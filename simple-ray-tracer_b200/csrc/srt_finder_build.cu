@@ -21,7 +21,11 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <stdio.h>
+#include <stdlib.h>
+
 #include <algorithm>
+#include <chrono>
 #include <string>
 #include <vector>
 
@@ -97,23 +101,57 @@ k_clear(NodeBounds* nb, Bin* bins, uint32_t n_nodes) {
   }
 }
 
+// Near the root thousands of triangles belong to ONE node: their atomics would queue on the same few words (the first
+// version spent 8 of its 10 ms there).  A block whose triangles all belong to one node reduces in shared memory first and
+// sends one atomic per word; blocks that straddle nodes (the lower levels) go to global memory directly.
+__device__ __forceinline__ bool block_of_one_node(uint32_t nd, bool active, uint32_t& first) {
+  __shared__ uint32_t s_first;
+  if (threadIdx.x == 0) s_first = nd;
+  __syncthreads();
+  first = s_first;
+  return __syncthreads_and((!active || nd == first) && first != kNone) != 0;
+}
+
 __global__ void __launch_bounds__(FB_THREADS)
 k_bounds(const TriRecord* __restrict__ ref, const uint32_t* __restrict__ idx, const uint32_t* __restrict__ node_of, uint32_t n,
          NodeBounds* nb) {
+  __shared__ NodeBounds s_b;
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const uint32_t nd = node_of[i];
-  if (nd == kNone) return;
-  float mn[3], mx[3];
-  tri_box(ref[idx[i]], mn, mx);
-  NodeBounds* b = nb + nd;
+  const bool in_range = i < n;
+  const uint32_t nd = in_range ? node_of[i] : kNone;
+  uint32_t first;
+  const bool one = block_of_one_node(nd, in_range, first);
+  if (one && threadIdx.x == 0) {
 #pragma unroll
-  for (int a = 0; a < 3; ++a) {
-    const float c = 0.5f * (mn[a] + mx[a]);
-    atomicMin(&b->cmin[a], ord(c));
-    atomicMax(&b->cmax[a], ord(c));
-    atomicMin(&b->bmin[a], ord(mn[a]));
-    atomicMax(&b->bmax[a], ord(mx[a]));
+    for (int a = 0; a < 3; ++a) {
+      s_b.cmin[a] = ORD_PLUS_INF; s_b.cmax[a] = ORD_MINUS_INF;
+      s_b.bmin[a] = ORD_PLUS_INF; s_b.bmax[a] = ORD_MINUS_INF;
+    }
+  }
+  if (one) __syncthreads();
+  if (in_range && nd != kNone) {
+    float mn[3], mx[3];
+    tri_box(ref[idx[i]], mn, mx);
+    NodeBounds* b = one ? &s_b : nb + nd;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      const float c = 0.5f * (mn[a] + mx[a]);
+      atomicMin(&b->cmin[a], ord(c));
+      atomicMax(&b->cmax[a], ord(c));
+      atomicMin(&b->bmin[a], ord(mn[a]));
+      atomicMax(&b->bmax[a], ord(mx[a]));
+    }
+  }
+  if (one) {
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      const int a = threadIdx.x;
+      NodeBounds* b = nb + first;
+      atomicMin(&b->cmin[a], s_b.cmin[a]);
+      atomicMax(&b->cmax[a], s_b.cmax[a]);
+      atomicMin(&b->bmin[a], s_b.bmin[a]);
+      atomicMax(&b->bmax[a], s_b.bmax[a]);
+    }
   }
 }
 
@@ -125,25 +163,52 @@ __device__ __forceinline__ int bin_of(float c, float base, float scale) {
 __global__ void __launch_bounds__(FB_THREADS)
 k_bin(const TriRecord* __restrict__ ref, const uint32_t* __restrict__ idx, const uint32_t* __restrict__ node_of, uint32_t n,
       const Node* __restrict__ nodes, const NodeBounds* __restrict__ nb, Bin* bins) {
+  __shared__ Bin s_bins[3 * kBins];
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const uint32_t nd = node_of[i];
-  if (nd == kNone) return;
-  if (nodes[nd].hi - nodes[nd].lo <= kLeafMax) return;  // a leaf: no plane is looked for
-  float mn[3], mx[3];
-  tri_box(ref[idx[i]], mn, mx);
-  const NodeBounds b = nb[nd];
+  const bool in_range = i < n;
+  const uint32_t nd = in_range ? node_of[i] : kNone;
+  uint32_t first;
+  const bool one = block_of_one_node(nd, in_range, first);
+  if (one) {
+    if (threadIdx.x < 3 * kBins) {
+      Bin b;
 #pragma unroll
-  for (int a = 0; a < 3; ++a) {
-    const float lo = unord(b.cmin[a]), hi = unord(b.cmax[a]);
-    if (!(hi > lo)) continue;
-    const int k = bin_of(0.5f * (mn[a] + mx[a]), lo, (float)kBins / (hi - lo));
-    Bin* dst = bins + ((size_t)nd * 3u + a) * kBins + k;
-    atomicAdd(&dst->count, 1u);
+      for (int a = 0; a < 3; ++a) { b.bmin[a] = ORD_PLUS_INF; b.bmax[a] = ORD_MINUS_INF; }
+      b.count = 0u;
+      b._pad = 0u;
+      s_bins[threadIdx.x] = b;
+    }
+    __syncthreads();
+  }
+  if (in_range && nd != kNone && nodes[nd].hi - nodes[nd].lo > kLeafMax) {  // (a leaf: no plane is looked for)
+    float mn[3], mx[3];
+    tri_box(ref[idx[i]], mn, mx);
+    const NodeBounds b = nb[nd];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      atomicMin(&dst->bmin[c], ord(mn[c]));
-      atomicMax(&dst->bmax[c], ord(mx[c]));
+    for (int a = 0; a < 3; ++a) {
+      const float lo = unord(b.cmin[a]), hi = unord(b.cmax[a]);
+      if (!(hi > lo)) continue;
+      const int k = bin_of(0.5f * (mn[a] + mx[a]), lo, (float)kBins / (hi - lo));
+      Bin* dst = one ? &s_bins[a * kBins + k] : bins + ((size_t)nd * 3u + a) * kBins + k;
+      atomicAdd(&dst->count, 1u);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        atomicMin(&dst->bmin[c], ord(mn[c]));
+        atomicMax(&dst->bmax[c], ord(mx[c]));
+      }
+    }
+  }
+  if (one) {
+    __syncthreads();
+    if (threadIdx.x < 3 * kBins && s_bins[threadIdx.x].count != 0u) {
+      const Bin src = s_bins[threadIdx.x];
+      Bin* dst = bins + (size_t)first * 3u * kBins + threadIdx.x;
+      atomicAdd(&dst->count, src.count);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        atomicMin(&dst->bmin[c], src.bmin[c]);
+        atomicMax(&dst->bmax[c], src.bmax[c]);
+      }
     }
   }
 }
@@ -441,6 +506,10 @@ int build_finder_trees_device(const std::vector<TriRecord>& tris_ref, const std:
   FB(cudaMemcpyAsync(w.nodes_a, h_nodes.data(), (size_t)n_trees * sizeof(Node), cudaMemcpyHostToDevice, stream));
   FB(cudaMemcpyAsync(w.pads, pads.data(), (size_t)n_trees * 4, cudaMemcpyHostToDevice, stream));
 
+  const bool log = getenv("SRT_UPLOAD_LOG") != nullptr;
+  const auto t_start = std::chrono::steady_clock::now();
+  if (log) FB(cudaStreamSynchronize(stream));
+  const auto t_up = std::chrono::steady_clock::now();
   Node *cur = w.nodes_a, *next = w.nodes_b;
   uint32_t *idx = w.idx, *idx2 = w.idx2, *node_of = w.node_of, *node_of2 = w.node_of2;
   uint32_t n_nodes = n_trees, n_pairs = 0;
@@ -468,6 +537,7 @@ int build_finder_trees_device(const std::vector<TriRecord>& tris_ref, const std:
     std::swap(node_of, node_of2);
     ++levels;
   }
+  const auto t_levels = std::chrono::steady_clock::now();
   pairs_out->resize(n_pairs);
   tris_out->resize(n);
   roots_out->resize(n_trees);
@@ -476,6 +546,13 @@ int build_finder_trees_device(const std::vector<TriRecord>& tris_ref, const std:
   FB(cudaMemcpyAsync(roots_out->data(), w.roots, (size_t)n_trees * 4, cudaMemcpyDeviceToHost, stream));
   FB(cudaStreamSynchronize(stream));
   *depth_out = levels - 1;
+  if (log) {
+    auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+      return std::chrono::duration<double, std::milli>(b - a).count();
+    };
+    fprintf(stderr, "build_finder_trees_device: %u triangles, %u pairs, %d levels: upload %.2f ms, levels %.2f ms, download %.2f ms\n", n,
+            n_pairs, levels, ms(t_start, t_up), ms(t_up, t_levels), ms(t_levels, std::chrono::steady_clock::now()));
+  }
   return 0;
 }
 

@@ -1,6 +1,7 @@
-"""The hit finder's trees built by kernels (csrc/srt_finder_build.cu, SRT_OPT_DEVICE_FINDER_BUILD = 1, the default)
-against the host builder (0).  The two trees are not the same tree (the host builder samples big nodes), and they need not
-be: the finder collects candidate triangles, the replay of the shader's own culls decides.  So every picture must come
+"""The hit finder's trees built by kernels (csrc/srt_finder_build.cu, SRT_OPT_DEVICE_FINDER_BUILD = 1, the default for
+scenes of 16 Ki triangles and more; the environment variable SRT_FINDER_DEVICE_ALWAYS=1 set below lifts that limit so that
+the small scenes here go through the kernels too) against the host builder (0).  The two trees are not the same tree (the
+host builder samples big nodes), and they need not be: the finder collects candidate triangles, the replay of the shader's own culls decides.  So every picture must come
 out with the same bits either way -- and both must equal the oracle -- with the finder forced on (schedule variant 31:
 waves to the very end through the finder) and with the library's defaults.
 """
@@ -11,6 +12,12 @@ import scenes
 from test_parity_gpu import assert_bit_exact, cpu_render, framed, gpu_render
 
 pytestmark = pytest.mark.gpu
+
+
+
+@pytest.fixture(autouse=True)
+def device_builder_for_small_scenes(monkeypatch):
+    monkeypatch.setenv("SRT_FINDER_DEVICE_ALWAYS", "1")  # read by srt_upload_scene at every call
 
 
 def both_builders(pkg, ctx, scene, W, H, frames, schedule, **kw):
