@@ -201,7 +201,8 @@ struct PathPool {
   float4* ray;   // [2*id]   ray origin.xyz, tmax (initial intersection_distance)
                  // [2*id+1] ray direction.xyz, bits: kind (SRT_WF_KIND_*)
   uint2* hit;    // [id] result: primitive (or SRT_NO_HIT), distance bits.  hit[2*slot+1].x = SRT_WF_NOT_PENDING while the
-                 // slot has no shadow ray in flight (written by whoever decides not to emit one)
+                 // slot has no shadow ray in flight (written by whoever decides not to emit one; not looked at while the
+                 // path has not bounced yet, iter == 0: it cannot have one)
   float4* pst;   // [2*slot]   throughput.xyz, unused
                  // [2*slot+1] colour.xyz, bits: depth | rand_index << 8 | iter << 20
   uint2* path;   // (pixel slot, frame of the launch) of the path in this slot  (8 B)

@@ -377,7 +377,8 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
   // Only the replay of an OUTSIDE ray (finite theta) can add to the overflow list; in any other wave the list is final
   // when the find kernel ends, and the walk over it (a latency-bound launch: a few thousand long rays in lock step,
   // ~0.1 ms whatever its size) runs beside the replay instead of after it.
-  const bool side_by_side = !OUTSIDE && fork != nullptr && fork->aux != nullptr;
+  // (with SRT_WF_SHADOW_EARLY the replay of any wave that holds shadow rays can add to the list too: one after the other then)
+  const bool side_by_side = !SRT_WF_SHADOW_EARLY && !OUTSIDE && fork != nullptr && fork->aux != nullptr;
   if (side_by_side) {
     if ((e = cudaEventRecord(fork->forked, stream)) != cudaSuccess) return e;
     if ((e = cudaStreamWaitEvent(fork->aux, fork->forked, 0)) != cudaSuccess) return e;

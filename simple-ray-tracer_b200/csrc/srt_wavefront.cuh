@@ -91,7 +91,8 @@ __device__ __forceinline__ void wf_store_primary(const PathPool& pool, const Fra
   __stcs(pool.pst + 2 * (size_t)slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
   __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0))));
   __stcs(pool.path + slot, make_uint2(pixel, f));
-  pool.hit[id + 1] = make_uint2(SRT_WF_NOT_PENDING, 0u);
+  // (no "no shadow ray out" mark: a path that has not bounced yet, iter == 0, has none by definition -- one 8-byte write
+  // into a sector of its own per camera path less)
 }
 
 // ---- wave 0: the first pool.cap paths of the launch -----------------------------------------------------------------
@@ -458,7 +459,7 @@ __device__ __forceinline__ V3 wf_zero_term(uint32_t code) {
 }
 // colour after the answer of the shadow ray that was out (hit_s: PathPool::hit[2*slot+1])
 __device__ __forceinline__ V3 wf_add_pending(const PathPool& pool, uint32_t slot, uint2 hit_s, V3 color) {
-  if (hit_s.x == SRT_WF_NOT_PENDING) return color;
+  if (hit_s.x == SRT_WF_NOT_PENDING) return color;  // (callers skip paths that have not bounced yet: their mark is not set)
   const float4 pe = __ldcs(pool.pend + slot);
   return color + (hit_s.x != SRT_NO_HIT ? wf_zero_term(__float_as_uint(pe.w)) : v3(pe.x, pe.y, pe.z));
 }
@@ -587,7 +588,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       rand_index = (int)((packed >> 8) & 0xFFFu);
       iter = (int)(packed >> 20);
       // the direct light of the surface the path left last (:235-246) comes before anything the new segment adds
-      color = wf_add_pending(pool, slot, make_uint2(h.z, h.w), color);
+      if (iter > 0 || !(stashed || region_a)) color = wf_add_pending(pool, slot, make_uint2(h.z, h.w), color);
       if ((stashed || region_a) && primary_ids != nullptr && iter == 0 && path.y == (uint32_t)(fp.n_frames - 1))
         primary_ids[(size_t)y * fp.width + x] = h.x;
     }

@@ -64,6 +64,9 @@ __device__ __forceinline__ bool wf_find_box_t(V3 o, V3 inv, float tmax, float mn
 // culling, as an inside ray does either way); the host uses it for the waves that cannot hold camera rays.
 // COUNT (SRT_OPT_COUNT_TRAVERSAL = 2, bench.py's untimed pass): box and triangle tests this kernel really executes go to
 // counters->nodes / counters->tris -- the work behind the roofline's FP32-issue figure.
+#ifndef SRT_WF_SHADOW_EARLY
+#define SRT_WF_SHADOW_EARLY 1  // shadow rays leave the finder walk at their first candidate (see the leaf loop)
+#endif
 template <bool OUTSIDE, bool COUNT>
 __global__ void __launch_bounds__(SRT_WF_FIND_THREADS, SRT_WF_FIND_MIN_BLOCKS)
 wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity, int refill_threshold,
@@ -297,6 +300,15 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
                     SRT_CHECK(n_cand < SRT_CAND_MAX, SRT_CHK_CAND);
                     wf_sts(cand_base + n_cand * cand_step, __float_as_uint(r0.w) | (bvh_i << SRT_CAND_BVH_SHIFT), __float_as_uint(t));
                     n_cand++;
+                    // A shadow ray (odd ray id) only asks WHETHER the shader accepts some triangle (CheckLightOccluded reads
+                    // rec.hit alone), and the first triangle it accepts is tested against the initial distance: so the ray
+                    // is occluded exactly when SOME candidate's boxes all pass the shader's culls with that distance.  The
+                    // walk stops at its first candidate; the replay checks that one, and hands the ray to the full walk of
+                    // the reference tree in the rare case it fails (a box the shader's slab test misses at a grazing angle).
+                    if (SRT_WF_SHADOW_EARLY && (slot & 1u)) {
+                      trav = false;
+                      pending = true;
+                    }
                   }
                 }
               }
@@ -432,6 +444,9 @@ wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, P
         if (j == n_acc) { a_rank[j] = rank; a_t[j] = t; }
       n_acc++;
     }
+    // a shadow ray whose walk was cut at its first candidate and whose candidate the shader's culls reject: nothing is known
+    // about the triangles the walk did not reach
+    if (SRT_WF_SHADOW_EARLY && any_hit && hit == SRT_NO_HIT) uncertain = true;
     if (uncertain) {  // the long way (wf_trace_kernel over the overflow list, launched after this kernel)
       const uint32_t at = atomicAdd(&pool.fq->over.n_closest[0], 1u);
       SRT_CHECK(at < pool.list_cap, SRT_CHK_OVERFLOW);

@@ -275,7 +275,7 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           depth = (int)(packed & 0xFFu);
           rand_index = (int)((packed >> 8) & 0xFFFu);
           iter = (int)(packed >> 20);
-          const bool shadow_out = is_dying || pool.hit[2 * slot + 1].x != SRT_WF_NOT_PENDING;
+          const bool shadow_out = is_dying || (iter > 0 && pool.hit[2 * slot + 1].x != SRT_WF_NOT_PENDING);  // (a camera path has none)
           // the ray to answer first: the slot's shadow ray if one is out, else its closest-hit ray
           const size_t id = 2 * slot + (shadow_out ? 1u : 0u);
           const float4 a = pool.ray[2 * id], b = pool.ray[2 * id + 1];
