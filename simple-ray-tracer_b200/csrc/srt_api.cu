@@ -1050,6 +1050,9 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     const bool cull = ctx->primary_cull && n_paths <= (unsigned long long)slots;
     ctx->pool.culled = cull ? ctx->d_culled : nullptr;
     int parity = 0;
+    // a scene far beyond L2's reach (126 MB): bounce rays and shadow rays of a wave in launches of their own
+    const bool queue_by_queue = !finder && (((size_t)ctx->n_nodes / 2 * sizeof(NodePair) + (size_t)ctx->n_tris * sizeof(TriRecord)) > ((size_t)256 << 20) ||
+                                            getenv("SRT_QUEUE_BY_QUEUE") != nullptr);  // (the variable: for tests at small sizes)
     // What the host knows about the launch: paths still alive and whether every path has been handed to a slot.  Both
     // are exact before wave 0 and afterwards lag one batch behind the device.
     unsigned long long live = n_paths < (unsigned long long)slots ? n_paths : (unsigned long long)slots;
@@ -1122,11 +1125,11 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
         // camera rays are in the chunk's first wave and, while slots still take new paths, in any later one
         const int finder_kind = !finder ? 0 : ((batch == 0 && w == 0) || !all_out) ? 2 : 1;
         CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
-                               ctx->block_threads, ctx->stream, ev[1], finder_kind, ctx->use_fork ? &ctx->fork : nullptr));
+                               ctx->block_threads, ctx->stream, ev[1], finder_kind, ctx->use_fork ? &ctx->fork : nullptr, queue_by_queue));
         if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], ctx->stream));
         parity ^= 1;
       }
-      ctx->kernel_launches += (finder ? 4 : 2) * n_waves;
+      ctx->kernel_launches += (finder ? 4 : (queue_by_queue ? 3 : 2)) * n_waves;
       ctx->waves += n_waves;
       const int s = batch & 3;
       CU(ctx, cudaMemcpyAsync(&ctx->h_live[s], ctx->pool.q, sizeof(WaveCounters), cudaMemcpyDeviceToHost, ctx->stream));

@@ -178,7 +178,8 @@ struct WaveCounters {
   unsigned int live_slots;    // slots that still carry a path
   unsigned long long next_path;  // next path (frame-major: frame * n_pixels + pixel slot) to hand to a free slot
   unsigned int n_dying[2];    // entries of dlist[parity]
-  unsigned int _pad[2];
+  unsigned int cursor2;       // fetch cursor of a wf_trace_kernel launch that takes the shadow queue alone
+  unsigned int _pad;
 };
 
 // Queues between wf_find_kernel and its two consumers (srt_wf_find.cuh); zeroed by wf_init_kernel / wf_logic_kernel.

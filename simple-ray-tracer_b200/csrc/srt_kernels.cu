@@ -309,7 +309,7 @@ WfGrid g_wf_grid;  // launch geometry is a property of the device + kernel, comp
 
 template <int MODE, bool COUNT>
 cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
-                            DeviceCounters* counters, int /*block*/, cudaStream_t stream) {
+                            DeviceCounters* counters, int /*block*/, cudaStream_t stream, int region = 0) {
   auto k = wf_trace_kernel<MODE, COUNT>;
   const int block = SRT_WF_TRACE_THREADS;  // fixed: the stack stride is a compile-time constant of the kernel
   const size_t smem = (size_t)fp.stack_cap * block * sizeof(uint2);
@@ -335,7 +335,7 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
   long need = ((long)pool.cap / 32 + block / 32 - 1) / (block / 32);
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  k<<<(unsigned)grid, block, smem, stream>>>(sc, fp, pool, parity, refill > 0 ? refill : SRT_WF_TRACE_REFILL, counters);
+  k<<<(unsigned)grid, block, smem, stream>>>(sc, fp, pool, parity, refill > 0 ? refill : SRT_WF_TRACE_REFILL, counters, region);
   return cudaGetLastError();
 }
 }  // namespace
@@ -398,7 +398,7 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
 
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
-                           cudaEvent_t after_trace, int finder, const WaveFork* fork) {
+                           cudaEvent_t after_trace, int finder, const WaveFork* fork, bool queue_by_queue) {
   cudaError_t e;
   if (finder == 2)  // a wave that may hold camera rays
     e = count ? wf_find_launch<true, true>(sc, fp, pool, parity, refill, counters, block, stream, fork)
@@ -406,12 +406,18 @@ cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const P
   else if (finder)
     e = count ? wf_find_launch<false, true>(sc, fp, pool, parity, refill, counters, block, stream, fork)
               : wf_find_launch<false, false>(sc, fp, pool, parity, refill, counters, block, stream, fork);
-  else if (mode == TRAV_REFERENCE)
-    e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, refill, counters, block, stream)
-              : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, refill, counters, block, stream);
-  else
-    e = count ? wf_trace_launch<TRAV_ORDERED, true>(sc, fp, pool, parity, refill, counters, block, stream)
-              : wf_trace_launch<TRAV_ORDERED, false>(sc, fp, pool, parity, refill, counters, block, stream);
+  else {
+    // queue_by_queue: the closest queue, then the shadow queue (a scene far larger than L2; see wf_trace_kernel)
+    e = cudaSuccess;
+    for (int region = queue_by_queue ? 1 : 0; region <= (queue_by_queue ? 2 : 0) && e == cudaSuccess; ++region) {
+      if (mode == TRAV_REFERENCE)
+        e = count ? wf_trace_launch<TRAV_REFERENCE, true>(sc, fp, pool, parity, refill, counters, block, stream, region)
+                  : wf_trace_launch<TRAV_REFERENCE, false>(sc, fp, pool, parity, refill, counters, block, stream, region);
+      else
+        e = count ? wf_trace_launch<TRAV_ORDERED, true>(sc, fp, pool, parity, refill, counters, block, stream, region)
+                  : wf_trace_launch<TRAV_ORDERED, false>(sc, fp, pool, parity, refill, counters, block, stream, region);
+    }
+  }
   if (e != cudaSuccess) return e;
   if (after_trace != nullptr && (e = cudaEventRecord(after_trace, stream)) != cudaSuccess) return e;
   // logic: a fixed grid of warps strides over the wave's 32-entry chunks

@@ -31,7 +31,7 @@ struct WaveFork {
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
                            cudaEvent_t after_trace = nullptr, int finder = 0,  // finder: 0 = walk the reference BVH, 1 = hit finder, 2 = hit finder with its outside-ray walk (waves that may hold camera rays)
-                           const WaveFork* fork = nullptr);
+                           const WaveFork* fork = nullptr, bool queue_by_queue = false);  // queue_by_queue (finder off): one trace launch per queue
 // SRT_OPT_SORT_RAYS: both queues of wave `parity` regrouped by the cell their rays start in (pool.sort_* must be allocated)
 cudaError_t launch_wf_sort(const DeviceScene& sc, const PathPool& pool, int parity, cudaStream_t stream);
 #define SRT_SORT_BINS_HOST 32768u

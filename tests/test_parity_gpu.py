@@ -240,6 +240,21 @@ def test_soup_depth8_bit_exact(pkg, ctx, oracle, tmp_path, schedule):
     assert ocnt["capped_paths"] == 0
 
 
+def test_one_trace_launch_per_queue_changes_no_bit(pkg, ctx, oracle, tmp_path, monkeypatch):
+    """Scenes far larger than L2 are traced queue by queue (closest-hit rays, then shadow rays, a launch each with its own
+    cursor); SRT_QUEUE_BY_QUEUE forces that at a size the oracle finishes.  Waves to the very end on the reference BVH."""
+    monkeypatch.setenv("SRT_QUEUE_BY_QUEUE", "1")
+    scene, info = scenes.soup_scene(20000, str(tmp_path))
+    cam = scenes.reset_camera(True, origin=(0.0, 0.0, 120.0))
+    for schedule in (30, 32):
+        acc, out, ids, cnt = gpu_render(pkg, ctx, 256, 144, True, 2, pkg.TRAV_REFERENCE, scene=scene, cam=cam, max_depth=8,
+                                        schedule=schedule)
+        oacc, oout, oids, ocnt = cpu_render(oracle, 256, 144, True, 2, scene=scene, cam=cam, max_depth=8)
+        assert np.array_equal(ids, oids)
+        assert_bit_exact(acc, oacc)
+        assert cnt["segments"] == ocnt["segments"] and cnt["shadow_rays"] == ocnt["shadow_rays"]
+
+
 @pytest.mark.parametrize("schedule", [3, 30, 31])
 def test_rubik_inside_view_and_depth8(pkg, ctx, oracle, schedule):
     """Camera inside the model's bounds looking around (many bounces), maxDepth 8 as C5 uses."""
