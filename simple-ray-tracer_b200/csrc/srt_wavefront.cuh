@@ -470,6 +470,11 @@ __device__ __forceinline__ V3 wf_add_pending(const PathPool& pool, uint32_t slot
   return color + (hit_s.x != SRT_NO_HIT ? wf_zero_term(__float_as_uint(pe.w)) : v3(pe.x, pe.y, pe.z));
 }
 
+#ifndef SRT_WF_LOGIC_PREFETCH
+#define SRT_WF_LOGIC_PREFETCH 1
+#endif
+__device__ __forceinline__ void wf_prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // ---- logic: everything GetRayColor does between two CheckHit calls (raytrace_compute.glsl:225-292) -----------------
 // TEX: the textured-albedo option (SRT_OPT_TEXTURES with a texture set); its 9 KB of code stay out of the other instance.
 //
@@ -573,6 +578,13 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         base = __shfl_sync(FULL, base, leader);
         SRT_CHECK(base + (uint32_t)__popc(m_p) <= 2u * SRT_WF_LOGIC_THREADS, SRT_CHK_STASH);
         if (put_aside) s_stash[base + __popc(m_p & lt_mask)] = slot;
+      }
+      if (SRT_WF_LOGIC_PREFETCH && put_aside) {
+        // the records phase B will gather for this slot, asked for now: by then they are in L2 instead of in DRAM
+        wf_prefetch_l2(pool.ray + 4 * (size_t)slot);
+        wf_prefetch_l2(pool.pst + 2 * (size_t)slot);
+        wf_prefetch_l2(pool.path + slot);
+        if (h.z != SRT_WF_NOT_PENDING) wf_prefetch_l2(pool.pend + slot);
       }
     }
     shade = valid && stashed;
