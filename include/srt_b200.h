@@ -227,7 +227,8 @@ int srt_trace_rays_static(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, ui
 #define SRT_OPT_DEVICE_RELAYOUT 15 /* where srt_upload_scene turns the reference's arrays into this library's records: 0 = a serial walk
                                      on the host, 1 = kernels on the device (the raw arrays are copied over as they are: DMA
                                      when the caller's arrays are page-locked), 2 (default) = on the device for scenes of more
-                                     than 2 Mi triangles.  The device version needs the reference's node numbering (children
+                                     than 2 Mi triangles, and for scenes whose hit finder is built on the device (SRT_OPT_DEVICE_FINDER_BUILD,
+                                     16 Ki triangles and more: the finder build goes on from the re-layout's sweeps, nothing comes back).  The device version needs the reference's node numbering (children
                                      after their parent, bvh.h:96-131) and valid indices; anything else goes to the host walk,
                                      which handles or reports it.  Same records up to where a node pair sits in its array: no
                                      ray result depends on it (parity-tested).  srt_get_upload_info says what the last upload did */

@@ -412,11 +412,21 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   bool on_device = false;
   ctx->relayout_on_device = false;
   ctx->relayout_device_ms = 0.0f;
-  if (ctx->device_relayout == 1 || (ctx->device_relayout == 2 && n_triangles > SRT_FINDER_MAX_TRIS)) {
+  // Mid-size scenes whose hit finder is built on the device take the same way in, and the finder build goes on from the
+  // re-layout's own sweeps (parents, first ranks, depths, the BVH of every triangle) without the arrays coming back.
+  bool finder_on_device = false;
+  const bool finder_wanted = ctx->finder_mode != 0 && n_triangles > 0 && n_triangles <= SRT_FINDER_MAX_TRIS;
+  const bool device_pipeline = finder_wanted && ctx->device_finder_build && ctx->device_relayout != 0 &&
+                               (n_triangles >= SRT_FINDER_DEVICE_MIN_TRIS || getenv("SRT_FINDER_DEVICE_ALWAYS"));
+  if (ctx->device_relayout == 1 || (ctx->device_relayout == 2 && n_triangles > SRT_FINDER_MAX_TRIS) || device_pipeline) {
     DeviceRelayoutIO io;
     io.d_pairs = &ctx->d_pairs;   io.cap_pairs = &ctx->dev_capacity[(void**)&ctx->d_pairs];
     io.d_leaves = &ctx->d_leaves; io.cap_leaves = &ctx->dev_capacity[(void**)&ctx->d_leaves];
     io.d_tris = &ctx->d_tris;     io.cap_tris = &ctx->dev_capacity[(void**)&ctx->d_tris];
+    if (device_pipeline) {
+      io.d_rnodes = &ctx->d_rnodes;     io.cap_rnodes = &ctx->dev_capacity[(void**)&ctx->d_rnodes];
+      io.d_tri_leaf = &ctx->d_tri_leaf; io.cap_tri_leaf = &ctx->dev_capacity[(void**)&ctx->d_tri_leaf];
+    }
     std::string why;
     const int rc = relayout_on_device(bvhs, n_bvhs, nodes, n_nodes, triangles, n_triangles, vertices, n_vertices, n_materials,
                                       SRT_STACK_SIZE - 1, &ctx->relayout_ws, &io, any_textured ? &rl.tri_bvh : nullptr,
@@ -430,7 +440,36 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
       rl.bvhs = io.bvh_records;
       rl.depth = io.depth;
       rl.top_pairs = 0;  // the pairs are in the reference's node order, not breadth-first: nothing to pin
-      if (ctx->finder_mode != 0 && n_triangles > 0 && n_triangles <= SRT_FINDER_MAX_TRIS) {  // the finder build reads the records
+      if (device_pipeline) {
+        DeviceFinderIn fin;
+        fin.d_tris_ref = ctx->d_tris; fin.n_tris = n_triangles;
+        fin.d_tri_bvh = io.ws_tri_bvh; fin.d_tri_leaf = ctx->d_tri_leaf;
+        fin.d_nodes = io.ws_nodes; fin.d_node_depth = io.ws_node_depth;
+        fin.n_bvhs = n_bvhs; fin.h_bvhs = bvhs; fin.h_records = rl.bvhs.data();
+        DeviceFinderOut fout;
+        fout.d_fpairs = &ctx->d_fpairs; fout.cap_fpairs = &ctx->dev_capacity[(void**)&ctx->d_fpairs];
+        fout.d_ftris = &ctx->d_ftris;   fout.cap_ftris = &ctx->dev_capacity[(void**)&ctx->d_ftris];
+        ctx->finder_ready = false;
+        const int frc = build_finder_on_device(fin, &ctx->finder_ws, ctx->stream, &fout, &why);
+        if (frc == 1) {
+          ctx->have_scene = false;
+          return fail(ctx, "srt_upload_scene: %s", why.c_str());
+        }
+        if (frc == 0) {
+          for (uint32_t b = 0; b < n_bvhs; ++b) {
+            rl.bvhs[b].finder_root = fout.roots[b];
+            rl.bvhs[b].root_node = bvhs[b].first_index;
+            rl.bvhs[b].finder_pad = fout.pads[b];
+          }
+          ctx->finder_ready = true;
+          ctx->finder_worthwhile = fout.cost_finder < 0.9 * fout.cost_reference;  // build_finder's rule (srt_finder.cu)
+          ctx->finder_depth = fout.depth;
+          ctx->finder_cost = fout.cost_finder;
+          ctx->reference_cost = fout.cost_reference;
+          finder_on_device = true;
+        }
+      }
+      if (finder_wanted && !finder_on_device) {  // the host's finder build reads the records
         tris.resize(n_triangles);
         CU(ctx, cudaMemcpyAsync(tris.data(), ctx->d_tris, (size_t)n_triangles * sizeof(TriRecord), cudaMemcpyDeviceToHost, ctx->stream));
         CU(ctx, cudaStreamSynchronize(ctx->stream));
@@ -483,10 +522,12 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   }
   const auto t_relayout = now();
   // hit finder: a private tree over the same triangles + what a replay of the shader's culls needs (srt_finder.h)
-  ctx->finder_ready = false;
-  ctx->finder_worthwhile = false;
-  for (BvhRecord& r : rl.bvhs) r.finder_root = r.root_node = 0u;
-  if (ctx->finder_mode != 0) {
+  if (!finder_on_device) {
+    ctx->finder_ready = false;
+    ctx->finder_worthwhile = false;
+    for (BvhRecord& r : rl.bvhs) r.finder_root = r.root_node = 0u;
+  }
+  if (ctx->finder_mode != 0 && !finder_on_device) {
     FinderOut fo;
     if (build_finder(bvhs, n_bvhs, nodes, n_nodes, triangles, vertices, tris, fo, (ctx->device_finder_build && (n_triangles >= SRT_FINDER_DEVICE_MIN_TRIS || getenv("SRT_FINDER_DEVICE_ALWAYS"))) ? &ctx->finder_ws : nullptr, ctx->stream)) {
       for (uint32_t b = 0; b < n_bvhs; ++b) {

@@ -127,7 +127,8 @@ k_check_triangles(const srt_triangle* __restrict__ tris_in, uint32_t n_tris, uin
 // breadth-first expansion of one level: every inner node of the level appends its two children to the next one
 __global__ void __launch_bounds__(RL_THREADS)
 k_expand(const srt_bvh_node* __restrict__ nodes, uint32_t n_nodes, uint32_t* __restrict__ frontier, uint32_t* __restrict__ bvh_of,
-         uint32_t* __restrict__ seen, uint32_t level_begin, uint32_t level_count, RlStatus* st) {
+         uint32_t* __restrict__ seen, uint32_t level_begin, uint32_t level_count, RlStatus* st, uint32_t* __restrict__ parent,
+         uint32_t* __restrict__ depth, uint32_t level) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= level_count) return;
   const uint32_t n = frontier[level_begin + j];
@@ -148,6 +149,12 @@ k_expand(const srt_bvh_node* __restrict__ nodes, uint32_t n_nodes, uint32_t* __r
   frontier[at + 1] = c + 1;
   bvh_of[c] = bvh_of[n];
   bvh_of[c + 1] = bvh_of[n];
+  if (parent != nullptr) {  // the hit finder's reference-side tables (RefNode, costing)
+    parent[c] = n;
+    parent[c + 1] = n;
+    depth[c] = level + 1u;
+    depth[c + 1] = level + 1u;
+  }
 }
 
 // bottom-up: triangles below every node of one level (the levels below are done)
@@ -176,7 +183,7 @@ __global__ void k_root_offsets(const uint32_t* __restrict__ roots, uint32_t n_bv
 __global__ void __launch_bounds__(RL_THREADS)
 k_ranks(const srt_bvh_node* __restrict__ nodes, const uint32_t* __restrict__ frontier, uint32_t level_begin, uint32_t level_count,
         const uint32_t* __restrict__ count, uint32_t* __restrict__ start, const uint32_t* __restrict__ bvh_of,
-        TriRecord* __restrict__ tris, uint32_t* __restrict__ tri_bvh) {
+        TriRecord* __restrict__ tris, uint32_t* __restrict__ tri_bvh, uint32_t* __restrict__ tri_leaf) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= level_count) return;
   const uint32_t n = frontier[level_begin + j];
@@ -188,12 +195,27 @@ k_ranks(const srt_bvh_node* __restrict__ nodes, const uint32_t* __restrict__ fro
       t->e1.w = __uint_as_float(s + k);
       t->e2.w = __uint_as_float(nd.prim_count - 1u - k);
       if (tri_bvh != nullptr) tri_bvh[nd.first_child_or_prim_index + k] = bvh_of[n];
+      if (tri_leaf != nullptr) tri_leaf[nd.first_child_or_prim_index + k] = n;
     }
     return;
   }
   const uint32_t c = nd.first_child_or_prim_index;
   start[c + 1] = s;
   start[c] = s + count[c + 1];
+}
+
+// per reference node what the replay needs (srt_finder.h): box, parent, first visiting rank of its subtree -- which is
+// the rank offset the top-down sweep gave the node
+__global__ void __launch_bounds__(RL_THREADS)
+k_refnodes(const srt_bvh_node* __restrict__ nodes, uint32_t n_nodes, const uint32_t* __restrict__ parent,
+           const uint32_t* __restrict__ start, RefNode* __restrict__ out) {
+  const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= n_nodes) return;
+  const srt_bvh_node nd = nodes[n];
+  RefNode r;
+  r.a = make_float4(nd.min_bounds[0], nd.min_bounds[1], nd.min_bounds[2], __uint_as_float(parent[n]));
+  r.b = make_float4(nd.max_bounds[0], nd.max_bounds[1], nd.max_bounds[2], __uint_as_float(start[n]));
+  out[n] = r;
 }
 
 __global__ void k_bvh_records(const srt_bvh* __restrict__ bvhs, uint32_t n_bvhs, const srt_bvh_node* __restrict__ nodes,
@@ -243,11 +265,11 @@ struct Carver {  // hands out 256-byte aligned pieces of the arena (first pass: 
 
 struct Pieces {
   srt_bvh_node* nodes; srt_triangle* tin; srt_vertex* vin;
-  uint32_t *inner, *rank, *scan, *frontier, *bvh_of, *seen_count, *start, *roots, *tri_bvh;
+  uint32_t *inner, *rank, *scan, *frontier, *bvh_of, *seen_count, *start, *roots, *tri_bvh, *parent, *depth;
   RlStatus* status; srt_bvh* bvhs; BvhRecord* records;
 };
 
-Pieces carve(Carver& c, uint32_t n_bvhs, uint32_t n_nodes, uint32_t n_tris, uint32_t n_verts, bool want_tri_bvh) {
+Pieces carve(Carver& c, uint32_t n_bvhs, uint32_t n_nodes, uint32_t n_tris, uint32_t n_verts, bool want_tri_bvh, bool want_finder) {
   Pieces p;
   p.nodes = c.take<srt_bvh_node>(n_nodes);
   p.tin = c.take<srt_triangle>(n_tris);
@@ -260,7 +282,9 @@ Pieces carve(Carver& c, uint32_t n_bvhs, uint32_t n_nodes, uint32_t n_tris, uint
   p.seen_count = c.take<uint32_t>(n_nodes);  // `seen` marks while the levels are found, triangle counts afterwards
   p.start = c.take<uint32_t>(n_nodes);
   p.roots = c.take<uint32_t>(n_bvhs);
-  p.tri_bvh = want_tri_bvh ? c.take<uint32_t>(n_tris) : nullptr;
+  p.tri_bvh = (want_tri_bvh || want_finder) ? c.take<uint32_t>(n_tris) : nullptr;
+  p.parent = want_finder ? c.take<uint32_t>(n_nodes) : nullptr;
+  p.depth = want_finder ? c.take<uint32_t>(n_nodes) : nullptr;
   p.status = c.take<RlStatus>(1);
   p.bvhs = c.take<srt_bvh>(n_bvhs);
   p.records = c.take<BvhRecord>(n_bvhs);
@@ -300,10 +324,11 @@ int relayout_on_device(const srt_bvh* h_bvhs, uint32_t n_bvhs, const srt_bvh_nod
 
   // ---- workspace: the raw arrays + scratch, kept between uploads ----
   Carver sizing{nullptr};
-  carve(sizing, n_bvhs, n_nodes, n_triangles, n_vertices, tri_bvh != nullptr);
+  const bool want_finder = io->d_rnodes != nullptr;
+  carve(sizing, n_bvhs, n_nodes, n_triangles, n_vertices, tri_bvh != nullptr, want_finder);
   RL(ensure(&ws->arena, &ws->arena_bytes, sizing.at));
   Carver c{static_cast<char*>(ws->arena)};
-  const Pieces w = carve(c, n_bvhs, n_nodes, n_triangles, n_vertices, tri_bvh != nullptr);
+  const Pieces w = carve(c, n_bvhs, n_nodes, n_triangles, n_vertices, tri_bvh != nullptr, want_finder);
   if (!ws->h_status) RL(cudaHostAlloc(&ws->h_status, sizeof(RlStatus), cudaHostAllocDefault));
   for (cudaEvent_t& e : ws->ev)
     if (!e) RL(cudaEventCreate(&e));
@@ -344,12 +369,18 @@ int relayout_on_device(const srt_bvh* h_bvhs, uint32_t n_bvhs, const srt_bvh_nod
     ordinal[b] = b;
     RL(cudaMemcpyAsync(w.bvh_of + roots[b], &ordinal[b], sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
   }
+  if (want_finder) {  // roots: no parent, depth 0; nodes no tree reaches keep these too
+    RL(cudaMemsetAsync(w.parent, 0xFF, (size_t)n_nodes * sizeof(uint32_t), stream));
+    RL(cudaMemsetAsync(w.depth, 0, (size_t)n_nodes * sizeof(uint32_t), stream));
+    RL(cudaMemsetAsync(w.tri_bvh, 0xFF, ((size_t)n_triangles ? n_triangles : 1) * sizeof(uint32_t), stream));
+  }
   std::vector<std::pair<uint32_t, uint32_t>> levels;  // (first entry of the frontier array, entries)
   levels.push_back({0u, n_bvhs});
   for (;;) {
     const uint32_t begin = levels.back().first, count = levels.back().second;
     RL(cudaMemsetAsync(&w.status->next_count, 0, sizeof(unsigned int), stream));
-    k_expand<<<blocks(count), RL_THREADS, 0, stream>>>(w.nodes, n_nodes, w.frontier, w.bvh_of, w.seen_count, begin, count, w.status);
+    k_expand<<<blocks(count), RL_THREADS, 0, stream>>>(w.nodes, n_nodes, w.frontier, w.bvh_of, w.seen_count, begin, count, w.status, w.parent,
+                                                       w.depth, (uint32_t)levels.size() - 1u);
     RL(cudaMemcpyAsync(h_status, w.status, sizeof(RlStatus), cudaMemcpyDeviceToHost, stream));
     RL(cudaStreamSynchronize(stream));
     io->launches += 1;
@@ -366,6 +397,11 @@ int relayout_on_device(const srt_bvh* h_bvhs, uint32_t n_bvhs, const srt_bvh_nod
   RL(ensure(reinterpret_cast<void**>(io->d_pairs), io->cap_pairs, (size_t)n_inner * sizeof(NodePair)));
   RL(ensure(reinterpret_cast<void**>(io->d_leaves), io->cap_leaves, (size_t)io->n_leaves * sizeof(uint2)));
   RL(ensure(reinterpret_cast<void**>(io->d_tris), io->cap_tris, (size_t)n_triangles * sizeof(TriRecord)));
+  if (want_finder) {
+    RL(ensure(reinterpret_cast<void**>(io->d_rnodes), io->cap_rnodes, (size_t)n_nodes * sizeof(RefNode)));
+    RL(ensure(reinterpret_cast<void**>(io->d_tri_leaf), io->cap_tri_leaf, (size_t)n_triangles * sizeof(uint32_t)));
+    RL(cudaMemsetAsync(*io->d_tri_leaf, 0xFF, ((size_t)n_triangles ? n_triangles : 1) * sizeof(uint32_t), stream));
+  }
   RL(cudaEventRecord(ws->ev[2], stream));
   k_records<<<blocks(n_nodes), RL_THREADS, 0, stream>>>(w.nodes, n_nodes, w.rank, *io->d_pairs, *io->d_leaves);
   if (n_triangles)
@@ -377,7 +413,12 @@ int relayout_on_device(const srt_bvh* h_bvhs, uint32_t n_bvhs, const srt_bvh_nod
   k_root_offsets<<<1, 32, 0, stream>>>(w.roots, n_bvhs, w.seen_count, w.start);
   for (size_t l = 0; l < levels.size(); ++l)
     k_ranks<<<blocks(levels[l].second), RL_THREADS, 0, stream>>>(w.nodes, w.frontier, levels[l].first, levels[l].second, w.seen_count,
-                                                                 w.start, w.bvh_of, *io->d_tris, w.tri_bvh);
+                                                                 w.start, w.bvh_of, *io->d_tris, w.tri_bvh,
+                                                                 want_finder ? *io->d_tri_leaf : nullptr);
+  if (want_finder) {
+    k_refnodes<<<blocks(n_nodes), RL_THREADS, 0, stream>>>(w.nodes, n_nodes, w.parent, w.start, *io->d_rnodes);
+    io->launches += 1;
+  }
   io->launches += 2 * levels.size() + 4;
   RL(cudaGetLastError());
   RL(cudaEventRecord(ws->ev[3], stream));
@@ -394,6 +435,10 @@ int relayout_on_device(const srt_bvh* h_bvhs, uint32_t n_bvhs, const srt_bvh_nod
   cudaEventElapsedTime(&build_ms, ws->ev[2], ws->ev[3]);
   io->copy_ms = copy_ms;
   io->device_ms = check_ms + build_ms;
+  // what a finder build on the device goes on with (valid until the workspace is used again)
+  io->ws_nodes = w.nodes;
+  io->ws_node_depth = w.depth;
+  io->ws_tri_bvh = w.tri_bvh;
   return 0;
 }
 

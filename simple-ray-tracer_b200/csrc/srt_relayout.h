@@ -27,6 +27,10 @@ struct DeviceRelayoutIO {
   NodePair** d_pairs = nullptr;   size_t* cap_pairs = nullptr;
   uint2** d_leaves = nullptr;     size_t* cap_leaves = nullptr;
   TriRecord** d_tris = nullptr;   size_t* cap_tris = nullptr;
+  // optional (all or none): the hit finder's reference-side tables, built from the same sweeps -- per node box / parent /
+  // first visiting rank, per triangle its leaf
+  RefNode** d_rnodes = nullptr;      size_t* cap_rnodes = nullptr;
+  uint32_t** d_tri_leaf = nullptr;   size_t* cap_tri_leaf = nullptr;
   // out
   uint32_t n_pairs = 0, n_leaves = 0;
   int depth = 0;                       // edges on the longest root-to-leaf chain
@@ -34,6 +38,11 @@ struct DeviceRelayoutIO {
   uint64_t launches = 0;
   float copy_ms = 0.0f;                // the raw arrays' way to the device (CUDA events)
   float device_ms = 0.0f;              // checks + sweeps
+  // with the finder tables: pieces of the workspace a finder build on the device reads next (raw nodes, depth of every
+  // node in its tree, the BVH of every triangle or 0xFFFFFFFF for a triangle no leaf holds)
+  const srt_bvh_node* ws_nodes = nullptr;
+  const uint32_t* ws_node_depth = nullptr;
+  const uint32_t* ws_tri_bvh = nullptr;
 };
 
 // h_*: the reference-layout arrays on the host (DMA when page-locked).  tri_bvh: where to put, per triangle, the BVH whose

@@ -24,7 +24,10 @@ def emulator(tmp_path_factory):
     out = str(tmp_path_factory.mktemp("finder") / "finder_emulation")
     csrc = os.path.join(ROOT, "simple-ray-tracer_b200", "csrc")
     subprocess.run([nvcc, "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-I" + os.path.join(ROOT, "include"), "-I" + csrc,
-                    "-o", out, os.path.join(ROOT, "tests", "native", "finder_emulation.cu"), os.path.join(csrc, "srt_finder.cu")],
+                    "-o", out, os.path.join(ROOT, "tests", "native", "finder_emulation.cu"), os.path.join(csrc, "srt_finder.cu"),
+                    # build_finder can hand its trees to the device builder (not here: no workspace is passed), which links
+                    # against these two
+                    os.path.join(csrc, "srt_finder_build.cu"), os.path.join(csrc, "srt_bvh_build.cu")],
                    check=True)
     return out
 
