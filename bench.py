@@ -241,6 +241,8 @@ def run_gpu(args):
         ctx.set_option(pkg.OPT_PRIMARY_CULL, args.primary_cull)
     if args.finder_build >= 0:
         ctx.set_option(pkg.OPT_DEVICE_FINDER_BUILD, args.finder_build)
+    if args.overlap >= 0:
+        ctx.set_option(pkg.OPT_OVERLAP, args.overlap)
     if args.sort_rays >= 0:
         ctx.set_option(pkg.OPT_SORT_RAYS, args.sort_rays)
 
@@ -565,6 +567,7 @@ def main():
                     help="<objects dir>/<NAME>/<NAME>.obj: render this model instead of the workload's scene (size, spp and depth stay "
                          "the workload's), e.g. the Airplane OBJ of BASELINE.json configs[2] where someone supplies it")
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
+    ap.add_argument("--overlap", type=int, default=-1, help="0/1: SRT_OPT_OVERLAP (default: library default, 1)")
     ap.add_argument("--finder-build", type=int, default=-1, help="0/1: SRT_OPT_DEVICE_FINDER_BUILD (default: library default, 1 = on the device)")
     ap.add_argument("--device-relayout", type=int, default=-1, help="0/1/2: SRT_OPT_DEVICE_RELAYOUT (default: library default, 2)")
     ap.add_argument("--l2-persist", type=int, default=-1, help="1/0: pin the BVH top levels in L2 (default: library default, on)")

@@ -236,6 +236,11 @@ int srt_trace_rays_static(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, ui
                                      time, a tree level per turn (csrc/srt_finder_build.cu), for scenes of 16 Ki triangles and more; 0 = always on host threads.  Either tree gives
                                      the same pictures: the finder only collects candidates, the replay of the shader's own culls
                                      decides (parity-tested both ways) */
+#define SRT_OPT_OVERLAP 18          /* wavefront schedule: 1 (default) = two sets of path slots; a chunk's waves run on an internal stream and
+                                     its tail kernel + resolve on the context's stream, so the tail of one chunk -- or of one srt_render
+                                     call -- runs beside the waves of the next.  The accumulation image and the output are only ever
+                                     touched on the context's stream, in call order: same bits.  0 = everything on the context's stream,
+                                     one chunk after the other.  Off by itself while primary ids are recorded or tests are counted */
 #define SRT_OPT_SPLIT 14
 #define SRT_SPLIT_BANDS 0
 #define SRT_SPLIT_SAMPLES 1

@@ -22,6 +22,7 @@ OPT_SPLIT = 14
 OPT_SORT_RAYS = 16
 OPT_DEVICE_RELAYOUT = 15
 OPT_DEVICE_FINDER_BUILD = 17
+OPT_OVERLAP = 18
 SPLIT_BANDS, SPLIT_SAMPLES = 0, 1
 GROUP_ID_BYTES = 128
 TRACE_STATIC_MAX_RAYS = 65536

@@ -77,6 +77,14 @@ static void free_pool(srt_ctx* ctx) {
   p.cap = 0;
   ctx->pool_slots = 0;
   ctx->sample_entries = 0;
+  PathPool& b = ctx->pool_b;  // its own slot records, queues and samples; the finder / sort arrays are pool's
+  dfree(b.ray); dfree(b.hit); dfree(b.pst); dfree(b.path); dfree(b.pend);
+  dfree(b.list[0]); dfree(b.list[1]); dfree(b.dlist[0]); dfree(b.dlist[1]); dfree(b.q); dfree(b.samples);
+  dfree(ctx->d_culled_b);
+  memset(&b, 0, sizeof b);
+  ctx->pool_b_slots = 0;
+  ctx->sample_entries_b = 0;
+  ctx->pool_busy[0] = ctx->pool_busy[1] = false;
 }
 
 #ifdef SRT_CHECKED
@@ -105,6 +113,7 @@ extern "C" int srt_create(srt_ctx** out, int device) {
   srt_ctx* ctx = new srt_ctx();
   ctx->device = device;
   memset(&ctx->pool, 0, sizeof ctx->pool);
+  memset(&ctx->pool_b, 0, sizeof ctx->pool_b);
   memset(&ctx->params, 0, sizeof ctx->params);
   memset(ctx->lights, 0, sizeof ctx->lights);
   if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -140,6 +149,12 @@ extern "C" void srt_destroy(srt_ctx* ctx) {
   for (cudaEvent_t& e : ctx->wave_events)
     if (e) cudaEventDestroy(e);
   if (ctx->fork.aux) { cudaStreamDestroy(ctx->fork.aux); cudaEventDestroy(ctx->fork.forked); cudaEventDestroy(ctx->fork.joined); }
+  if (ctx->wave_stream) cudaStreamDestroy(ctx->wave_stream);
+  if (ctx->ev_inputs) cudaEventDestroy(ctx->ev_inputs);
+  for (int k = 0; k < 2; ++k) {
+    if (ctx->ev_waves_done[k]) cudaEventDestroy(ctx->ev_waves_done[k]);
+    if (ctx->ev_pool_free[k]) cudaEventDestroy(ctx->ev_pool_free[k]);
+  }
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -149,6 +164,7 @@ extern "C" int srt_set_stream(srt_ctx* ctx, void* cuda_stream) {
   CU(ctx, cudaSetDevice(ctx->device));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+  ctx->inputs_dirty = true;
   return 0;
 }
 
@@ -201,6 +217,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_SORT_RAYS) {
     if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_SORT_RAYS: 0 (off) or 1 (on)");
     ctx->sort_rays = value;
+    return 0;
+  }
+  if (key == SRT_OPT_OVERLAP) {
+    if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_OVERLAP: 0 (off) or 1 (on)");
+    ctx->overlap = value;
     return 0;
   }
   if (key == SRT_OPT_DEVICE_FINDER_BUILD) {
@@ -396,6 +417,7 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
   if (!bvhs || !nodes || !materials || !triangles || !vertices) return fail(ctx, "srt_upload_scene: NULL array");
   if (n_bvhs == 0 || n_bvhs > SRT_MAX_BVHS) return fail(ctx, "srt_upload_scene: n_bvhs must be 1..%d", SRT_MAX_BVHS);
   CU(ctx, cudaSetDevice(ctx->device));
+  ctx->inputs_dirty = true;  // (uploads go through the context's stream; wave_stream waits for them at the next render)
   const bool log = getenv("SRT_UPLOAD_LOG") != nullptr;
   auto now = [] { return std::chrono::steady_clock::now(); };
   auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
@@ -613,6 +635,7 @@ extern "C" int srt_update_frame(srt_ctx* ctx, uint32_t index, const float* m) {
   FANOUT(ctx, false, srt_update_frame(c, index, m));
   if (!ctx->have_scene || index >= ctx->h_bvhs.size()) return fail(ctx, "srt_update_frame: index %u out of range", index);
   CU(ctx, cudaSetDevice(ctx->device));
+  ctx->inputs_dirty = true;
   memcpy(ctx->h_bvhs[index].frame, m, 64);
   memcpy(ctx->h_bvh_records[index].frame, m, 64);
   CU(ctx, cudaMemcpyAsync(ctx->d_bvhs + index, &ctx->h_bvh_records[index], 64, cudaMemcpyHostToDevice, ctx->stream));
@@ -626,6 +649,7 @@ extern "C" int srt_upload_noise(srt_ctx* ctx, const float* unit_vec3, const floa
   FANOUT(ctx, false, srt_upload_noise(c, unit_vec3, uniform_vec3, count));
   if (!unit_vec3 || !uniform_vec3 || count == 0) return fail(ctx, "srt_upload_noise: NULL table or count 0");
   CU(ctx, cudaSetDevice(ctx->device));
+  ctx->inputs_dirty = true;
   // the shader reads noiseTex.xy (raytrace_utils.glsl:15) and noiseUniformTex.x (:52) only: keep those, packed.
   const size_t bytes = (size_t)count * 12;
   const auto t0 = std::chrono::steady_clock::now();
@@ -789,6 +813,7 @@ extern "C" int srt_enable_primary_ids(srt_ctx* ctx, int enable) {
 namespace {
 int flush_textures(srt_ctx* ctx) {
   if (!ctx->textures_dirty) return 0;
+  ctx->inputs_dirty = true;
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   if (upload_vec(ctx, ctx->d_texels, ctx->h_texels) || upload_vec(ctx, ctx->d_tex_info, ctx->h_tex_info)) return 1;
   std::vector<MatRecord> mats = ctx->h_mats;
@@ -981,6 +1006,48 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
   return 0;
 }
 
+// the second set (SRT_OPT_OVERLAP): as many slots as the first one, its own records, queues and samples
+int ensure_pool_b(srt_ctx* ctx, size_t sample_entries) {
+  PathPool& a = ctx->pool;
+  PathPool& b = ctx->pool_b;
+  const uint32_t slots = ctx->pool_slots;
+  if (ctx->pool_b_slots != slots || !b.q) {
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    dfree(b.ray); dfree(b.hit); dfree(b.pst); dfree(b.path); dfree(b.pend);
+    dfree(b.list[0]); dfree(b.list[1]); dfree(b.dlist[0]); dfree(b.dlist[1]); dfree(b.q);
+    ctx->pool_b_slots = 0;
+    CU(ctx, cudaMalloc(&b.ray, (size_t)slots * 64)); CU(ctx, cudaMalloc(&b.hit, (size_t)slots * 16));
+    CU(ctx, cudaMalloc(&b.pst, (size_t)slots * 32)); CU(ctx, cudaMalloc(&b.path, (size_t)slots * 8));
+    CU(ctx, cudaMalloc(&b.pend, (size_t)slots * 16));
+    CU(ctx, cudaMalloc(&b.list[0], ctx->pool_list_cap * 4)); CU(ctx, cudaMalloc(&b.list[1], ctx->pool_list_cap * 4));
+    CU(ctx, cudaMalloc(&b.dlist[0], (size_t)slots * 4)); CU(ctx, cudaMalloc(&b.dlist[1], (size_t)slots * 4));
+    CU(ctx, cudaMalloc(&b.q, sizeof(WaveCounters)));
+    ctx->pool_b_slots = slots;
+    ctx->pool_busy[1] = false;
+  }
+  if (ctx->sample_entries_b < sample_entries) {
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    dfree(b.samples);
+    dfree(ctx->d_culled_b);
+    CU(ctx, cudaMalloc(&b.samples, sample_entries * sizeof(float4)));
+    CU(ctx, cudaMalloc(&ctx->d_culled_b, (sample_entries / 32 + 1) * sizeof(uint32_t)));
+    ctx->sample_entries_b = sample_entries;
+  }
+  // what the two sets share: the finder's and the sort's arrays (used by the waves alone, which run one after the other)
+  b.cand = a.cand; b.rlist = a.rlist; b.olist = a.olist; b.fq = a.fq;
+  b.sort_bins = a.sort_bins; b.sort_keys = a.sort_keys; b.sort_tmp = a.sort_tmp;
+  b.cap = a.cap; b.ray_cap = a.ray_cap; b.list_cap = a.list_cap;
+  if (!ctx->wave_stream) {
+    CU(ctx, cudaStreamCreateWithFlags(&ctx->wave_stream, cudaStreamNonBlocking));
+    CU(ctx, cudaEventCreateWithFlags(&ctx->ev_inputs, cudaEventDisableTiming));
+    for (int k = 0; k < 2; ++k) {
+      CU(ctx, cudaEventCreateWithFlags(&ctx->ev_waves_done[k], cudaEventDisableTiming));
+      CU(ctx, cudaEventCreateWithFlags(&ctx->ev_pool_free[k], cudaEventDisableTiming));
+    }
+  }
+  return 0;
+}
+
 // SRT_OPT_L2_PERSIST: the top levels of the BVH (every ray walks them) are pinned in L2 with an access-policy window on
 // the launching stream; the rest of the scene streams through the remaining L2.  Matters when the scene is far larger
 // than the 126 MB L2 (the 10 M-triangle soup); a scene that fits L2 entirely is resident anyway.
@@ -1083,13 +1150,41 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     slots = (slots + 31u) & ~31u;
     if (finder && slots >= (1u << 27)) return fail(ctx, "SRT_OPT_FINDER: at most 2^27 - 1 path slots (SRT_OPT_WAVE_SLOTS)");
     if (ensure_pool(ctx, slots, (size_t)n_pixels * (size_t)chunk_frames, finder)) return 1;
-    ctx->pool.n_pixels = n_pixels;
-    ctx->pool.n_paths = n_paths;
+    // SRT_OPT_OVERLAP: this chunk's init + waves on wave_stream with one set of slot records, its tail + resolve on the
+    // context's stream; the next chunk (of this call or of the next one) takes the other set and starts its waves while
+    // this one's tail still runs.  Not with primary ids (both would write them) or while counting.
+    const bool overlap = ctx->overlap != 0 && ids == nullptr && !ctx->count_traversal;
+    int which = 0;
+    if (overlap) {
+      if (ensure_pool_b(ctx, (size_t)n_pixels * (size_t)chunk_frames)) return 1;
+      which = ctx->pool_turn;
+      ctx->pool_turn ^= 1;
+    }
+    PathPool& P = which ? ctx->pool_b : ctx->pool;
+    cudaStream_t S1 = overlap ? ctx->wave_stream : ctx->stream;
+    if (overlap) {
+      if (ctx->inputs_dirty) {  // scene / noise / texture uploads were queued on the context's stream
+        CU(ctx, cudaEventRecord(ctx->ev_inputs, ctx->stream));
+        CU(ctx, cudaStreamWaitEvent(S1, ctx->ev_inputs, 0));
+        ctx->inputs_dirty = false;
+      }
+      if (ctx->pool_busy[which]) CU(ctx, cudaStreamWaitEvent(S1, ctx->ev_pool_free[which], 0));
+    }
+    bool joined = !overlap;  // whether the context's stream already waits for this chunk's waves
+    auto join = [&]() -> int {
+      if (joined) return 0;
+      CU(ctx, cudaEventRecord(ctx->ev_waves_done[which], S1));
+      CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_waves_done[which], 0));
+      joined = true;
+      return 0;
+    };
+    P.n_pixels = n_pixels;
+    P.n_paths = n_paths;
     // primary ids are those of the launch's LAST frame
     uint32_t* chunk_ids = (done + fp.n_frames == fp_all.n_frames) ? ids : nullptr;
     // every path of the chunk starts in wave 0: primary rays that miss every root box end in the init kernel
     const bool cull = ctx->primary_cull && n_paths <= (unsigned long long)slots;
-    ctx->pool.culled = cull ? ctx->d_culled : nullptr;
+    P.culled = cull ? (which ? ctx->d_culled_b : ctx->d_culled) : nullptr;
     int parity = 0;
     // a scene far beyond L2's reach (126 MB): bounce rays and shadow rays of a wave in launches of their own
     const bool queue_by_queue = !finder && (((size_t)ctx->n_nodes / 2 * sizeof(NodePair) + (size_t)ctx->n_tris * sizeof(TriRecord)) > ((size_t)256 << 20) ||
@@ -1118,12 +1213,12 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
       const bool timed = ctx->time_kernels && cull;
       if (timed) {
         if (timing_events(ev)) return 1;
-        CU(ctx, cudaEventRecord(ev[0], ctx->stream));
+        CU(ctx, cudaEventRecord(ev[0], S1));
       }
-      CU(ctx, launch_wf_init(sc, fp, ctx->pool, cull, chunk_ids, ctx->count_traversal, ctx->d_counters, ctx->stream));
+      CU(ctx, launch_wf_init(sc, fp, P, cull, chunk_ids, ctx->count_traversal, ctx->d_counters, S1));
       if (timed) {
-        CU(ctx, cudaEventRecord(ev[1], ctx->stream));
-        CU(ctx, cudaEventRecord(ev[2], ctx->stream));
+        CU(ctx, cudaEventRecord(ev[1], S1));
+        CU(ctx, cudaEventRecord(ev[2], S1));
       }
       ctx->kernel_launches++;
     }
@@ -1132,15 +1227,16 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
         // the rest of the launch in one kernel (srt_wf_tail.cuh); with SRT_OPT_TIME_KERNELS it is reported as one more
         // trace launch (its shading included: the trace figure can only get worse by it)
         cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+        if (join()) return 1;
         if (ctx->time_kernels) {
           if (timing_events(ev)) return 1;
           CU(ctx, cudaEventRecord(ev[0], ctx->stream));
         }
         if (sort && batch > 0) {  // the paths the tail starts from, grouped like a wave's (inside the timed bracket)
-          CU(ctx, launch_wf_sort(sc, ctx->pool, parity, ctx->stream));
+          CU(ctx, launch_wf_sort(sc, P, parity, ctx->stream));
           ctx->kernel_launches += 8;
         }
-        CU(ctx, launch_wf_tail(sc, fp, ctx->pool, parity, traversal, chunk_ids, ctx->d_counters, ctx->stream));
+        CU(ctx, launch_wf_tail(sc, fp, P, parity, traversal, chunk_ids, ctx->d_counters, ctx->stream));
         if (ctx->time_kernels) {
           CU(ctx, cudaEventRecord(ev[1], ctx->stream));
           CU(ctx, cudaEventRecord(ev[2], ctx->stream));
@@ -1156,25 +1252,25 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
         cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
         if (ctx->time_kernels) {
           if (timing_events(ev)) return 1;
-          CU(ctx, cudaEventRecord(ev[0], ctx->stream));
+          CU(ctx, cudaEventRecord(ev[0], S1));
         }
         // every wave but the camera rays' (one origin): queues regrouped by the cell the rays start in (srt_wf_sort.cuh)
         if (sort && !(batch == 0 && w == 0)) {
-          CU(ctx, launch_wf_sort(sc, ctx->pool, parity, ctx->stream));
+          CU(ctx, launch_wf_sort(sc, P, parity, S1));
           ctx->kernel_launches += 8;
         }
         // camera rays are in the chunk's first wave and, while slots still take new paths, in any later one
         const int finder_kind = !finder ? 0 : ((batch == 0 && w == 0) || !all_out) ? 2 : 1;
-        CU(ctx, launch_wf_wave(sc, fp, ctx->pool, parity, traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
-                               ctx->block_threads, ctx->stream, ev[1], finder_kind, ctx->use_fork ? &ctx->fork : nullptr, queue_by_queue));
-        if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], ctx->stream));
+        CU(ctx, launch_wf_wave(sc, fp, P, parity, traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
+                               ctx->block_threads, S1, ev[1], finder_kind, ctx->use_fork ? &ctx->fork : nullptr, queue_by_queue));
+        if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], S1));
         parity ^= 1;
       }
       ctx->kernel_launches += (finder ? 4 : (queue_by_queue ? 3 : 2)) * n_waves;
       ctx->waves += n_waves;
       const int s = batch & 3;
-      CU(ctx, cudaMemcpyAsync(&ctx->h_live[s], ctx->pool.q, sizeof(WaveCounters), cudaMemcpyDeviceToHost, ctx->stream));
-      CU(ctx, cudaEventRecord(ctx->wave_events[s], ctx->stream));
+      CU(ctx, cudaMemcpyAsync(&ctx->h_live[s], P.q, sizeof(WaveCounters), cudaMemcpyDeviceToHost, S1));
+      CU(ctx, cudaEventRecord(ctx->wave_events[s], S1));
       if (batch >= 1) {
         const int prev = (batch - 1) & 3;
         CU(ctx, cudaEventSynchronize(ctx->wave_events[prev]));
@@ -1183,8 +1279,13 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
         if (live == 0) break;
       }
     }
-    CU(ctx, launch_wf_resolve(fp, ctx->pool, ctx->d_accum, ctx->d_out, ctx->stream));
+    if (join()) return 1;
+    CU(ctx, launch_wf_resolve(fp, P, ctx->d_accum, ctx->d_out, ctx->stream));
     ctx->kernel_launches++;
+    if (overlap) {
+      CU(ctx, cudaEventRecord(ctx->ev_pool_free[which], ctx->stream));
+      ctx->pool_busy[which] = true;
+    }
   }
   return 0;
 }

@@ -98,6 +98,22 @@ struct srt_ctx {
   PathPool pool;
   uint32_t pool_slots = 0;
   size_t pool_list_cap = 0;
+  // A second set of slot records, queues and samples (SRT_OPT_OVERLAP): the chunks of the wavefront schedule alternate
+  // between the two, a chunk's init + waves run on wave_stream, its tail kernel and resolve on `stream` -- so the tail of
+  // one chunk (a third of a rank's step at 8 GPUs, whatever the rank's share) runs beside the waves of the next one, of the
+  // same srt_render call or of the next call.  Images (accum, out) are only ever touched on `stream`, in call order.
+  PathPool pool_b;
+  uint32_t* d_culled_b = nullptr;
+  uint32_t pool_b_slots = 0;
+  size_t sample_entries_b = 0;
+  int overlap = 1;                               // SRT_OPT_OVERLAP
+  int pool_turn = 0;                             // which set the next chunk takes
+  cudaStream_t wave_stream = nullptr;
+  cudaEvent_t ev_inputs = nullptr;               // recorded on `stream` after uploads; wave_stream waits for it
+  cudaEvent_t ev_waves_done[2] = {nullptr, nullptr};
+  cudaEvent_t ev_pool_free[2] = {nullptr, nullptr};
+  bool pool_busy[2] = {false, false};
+  bool inputs_dirty = true;                      // an upload since the last wave_stream launch
   WaveCounters* h_live = nullptr;  // pinned ring the device reports its wave counters into (live slots, paths handed out)
   cudaEvent_t wave_events[4] = {nullptr, nullptr, nullptr, nullptr};
   WaveFork fork = {nullptr, nullptr, nullptr};  // second stream of the finder waves (launch_wf_wave); SRT_NO_FORK=1 in the environment keeps it unused
