@@ -307,9 +307,6 @@ def run_gpu(args):
     ctx.reset_counters()
     launches[0] = 0
     wavefront = show_model and args.schedule == "wavefront"
-    if wavefront:
-        ctx.set_option(pkg.OPT_TIME_KERNELS, 1)  # CUDA events around every trace / logic launch, on the launching stream
-        ctx.kernel_times()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     evk = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     sampler = ClockSampler(local) if rank == 0 else None
@@ -325,12 +322,27 @@ def run_gpu(args):
     clocks = sampler.stop() if sampler else None
     step_ms = [a.elapsed_time(b) for a, b in ev]
     kern_ms = [a.elapsed_time(b) for a, b in evk]
+    cnt = ctx.counters()
+    # ---- per-launch durations for the roofline: the same steps again with every launch bracketed by CUDA events on the
+    # stream it is launched on (SRT_OPT_TIME_KERNELS) and with SRT_OPT_OVERLAP off, so that each launch is timed ALONE -- in
+    # the timed region above a chunk's tail kernel runs beside the next step's waves, and the sum of two overlapping
+    # launches' durations is not the time either of them needs
     trace_ms = logic_ms = 0.0
     n_waves = 0
+    roof_steps = 0
     if wavefront:
+        roof_steps = min(args.steps, 3)
+        ctx.set_option(pkg.OPT_OVERLAP, 0)
+        ctx.set_option(pkg.OPT_TIME_KERNELS, 1)
+        ctx.kernel_times()
+        barrier()
+        for k in range(roof_steps):
+            flush.fill_(k & 0xFF)
+            step()
+        barrier()
         trace_ms, logic_ms, n_waves = ctx.kernel_times()
         ctx.set_option(pkg.OPT_TIME_KERNELS, 0)
-    cnt = ctx.counters()
+        ctx.set_option(pkg.OPT_OVERLAP, 1 if args.overlap < 0 else args.overlap)
     coll_ms, coll_n = ctx.collective_ms() if world > 1 else (0.0, 0)
     gpu_launches = cnt["kernel_launches"]  # every kernel this context launched in the timed region (clear, init, waves, resolve, tonemap)
 
@@ -422,6 +434,7 @@ def run_gpu(args):
     # ---- roofline of the kernels that answer rays: which roof binds depends on where the scene lives
     peaks, which = measured_peaks()
     rays = segments + shadow
+    roof_rays = rays * (roof_steps / args.steps) if wavefront else rays  # the rays of the steps whose launches were bracketed
     finder_on = bool(show_model and wavefront and ctx.finder_info()[0])
     if wavefront:
         # SRT_OPT_TIME_KERNELS brackets every launch that answers rays: wf_init_kernel's cull, wf_find_kernel,
@@ -451,8 +464,8 @@ def run_gpu(args):
         # one-thread-per-pixel kernel's whole duration (traversal + shading) is the denominator
         exe_flops_per_ray, exe_bytes_per_ray = 5.0 * 30.0, 0.0
     ref_bytes_per_ray = 32.0 * ref_nodes_per_ray + 52.0 * ref_tris_per_ray
-    achieved_tflops = rays * exe_flops_per_ray / k_s / 1e12
-    achieved_gbs = rays * exe_bytes_per_ray / k_s / 1e9
+    achieved_tflops = roof_rays * exe_flops_per_ray / k_s / 1e12
+    achieved_gbs = roof_rays * exe_bytes_per_ray / k_s / 1e9
     issue_peak_tflops = roofs["issue_fmul_fadd_Gop_s"] * world / 1e3
     level = "l1" if scene_mb <= 0.2 else ("l2" if scene_mb <= 100.0 else "hbm")
     mem_peak = {"l1": roofs["l1_gather_GBps"], "l2": roofs["l2_gather_GBps"], "hbm": peaks["hbm_gbs"]}[level] * world
@@ -465,7 +478,7 @@ def run_gpu(args):
     if wavefront and world == 1 and os.path.exists(tf):
         t = json.load(open(tf))
         traffic = t["dram_bytes_per_launch"]
-        algorithmic_dram = (12.0 * W * H + 36.0 * W * H) * spp / max(k_launches / args.steps, 1.0)  # noise gathers + accumulate/output streaming
+        algorithmic_dram = (12.0 * W * H + 36.0 * W * H) * spp / max(k_launches / max(roof_steps, 1), 1.0)  # noise gathers + accumulate/output streaming
         traffic_extra = {"traffic_source": "profiles/%s (dram__bytes_read.sum + dram__bytes_write.sum over the launches of one "
                                            "step from an ncu pass of this command, divided by the ray-answering launches)" % os.path.basename(tf),
                          "traffic_per_step": t.get("dram_bytes_per_step"), "traffic_build": t.get("build"),
@@ -484,16 +497,18 @@ def run_gpu(args):
         "logic_kernel_ms_total": logic_ms,
         "frac_issue": frac_issue, "frac_memory": frac_mem, "memory_level": level,
         "achieved_tflops": achieved_tflops, "achieved_GBps": achieved_gbs,
-        "flops_per_launch": rays * exe_flops_per_ray / k_launches, "bytes_per_launch": rays * exe_bytes_per_ray / k_launches,
+        "flops_per_launch": roof_rays * exe_flops_per_ray / k_launches, "bytes_per_launch": roof_rays * exe_bytes_per_ray / k_launches,
+        "timed_alone_steps": roof_steps,
         "executed_per_ray": {"box_tests": exe_nodes_per_ray, "triangle_tests": exe_tris_per_ray, "sphere_tests": 0.0 if show_model else 5.0,
                              "flops": exe_flops_per_ray, "bytes": exe_bytes_per_ray},
         "reference_walk_per_ray": {"box_tests": ref_nodes_per_ray, "triangle_tests": ref_tris_per_ray, "bytes": ref_bytes_per_ray,
-                                   "answered_GBps": rays * ref_bytes_per_ray / k_s / 1e9},
+                                   "answered_GBps": roof_rays * ref_bytes_per_ray / k_s / 1e9},
         "rays_per_step": rays / args.steps, "scene_mb": scene_mb, "roofs": roofs,
         "note": "achieved = rays x algorithmic work of the box and triangle tests the kernels EXECUTE (28 fp32 ops / 32 B per "
                 "box test, 50 ops / 52 B per triangle test, counted by an untimed pass over the same frames with "
                 "SRT_OPT_COUNT_TRAVERSAL = 2) / sum of CUDA-event durations around every ray-answering launch on the "
-                "launching stream (max over ranks).  Both fractions are reported; the larger names the bound.  frac_issue "
+                "stream it is launched on (max over ranks), taken over `timed_alone_steps` further steps with SRT_OPT_OVERLAP off so "
+                "that no two bracketed launches run at the same time.  Both fractions are reported; the larger names the bound.  frac_issue "
                 "counts only the tests' own arithmetic against the issue rate of un-fused FP32 instructions: address, "
                 "stack, queue and control instructions use the other slots (ncu: profiles/).  reference_walk_per_ray is "
                 "what the shader's own traversal does for the same rays (answered_GBps: reference work answered per "

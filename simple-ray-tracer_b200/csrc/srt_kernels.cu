@@ -455,8 +455,16 @@ cudaError_t wf_tail_launch(const DeviceScene& sc, const FrameParams& fp, const P
     if (per_sm < 1) per_sm = 1;
     smem_set = smem;
   }
-  // persistent warps: every resident slot of all SMs once; a small tail is spread over them one path per warp
-  k<<<(unsigned)(sms * per_sm), block, smem, stream>>>(sc, fp, pool, parity, ids, counters);
+  // persistent warps: every resident slot of all SMs once; a small tail is spread over them one path per warp.
+  // SRT_TAIL_BLOCKS_PER_SM (environment, experiments): fewer blocks per SM leave shared memory and registers to the next
+  // chunk's waves, which run beside this kernel (SRT_OPT_OVERLAP).
+  static int cap_per_sm = -1;
+  if (cap_per_sm < 0) {
+    const char* v = getenv("SRT_TAIL_BLOCKS_PER_SM");
+    cap_per_sm = v ? atoi(v) : 0;
+  }
+  const int use_per_sm = (cap_per_sm > 0 && cap_per_sm < per_sm) ? cap_per_sm : per_sm;
+  k<<<(unsigned)(sms * use_per_sm), block, smem, stream>>>(sc, fp, pool, parity, ids, counters);
   return cudaGetLastError();
 }
 }  // namespace
