@@ -1186,6 +1186,11 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     const bool cull = ctx->primary_cull && n_paths <= (unsigned long long)slots;
     P.culled = cull ? (which ? ctx->d_culled_b : ctx->d_culled) : nullptr;
     int parity = 0;
+    // The tail takes over at SRT_OPT_TAIL_PATHS live paths.  (Lowering that in proportion when the launch is a fraction of
+    // the full frame -- a rank of an 8-GPU group: 16.6 M paths, threshold 130 k -- was measured: the stand-in, whose
+    // reference tree is slow to walk, went from 13.3 to 8.6 ms per rank, Rubik from 5.3 to 5.7: with SRT_OPT_OVERLAP its
+    // tail is hidden behind the next waves and the more it takes off them the better.  Scene-dependent; left to the option.)
+    const unsigned long long tail_at = ctx->tail_paths;
     // a scene far beyond L2's reach (126 MB): bounce rays and shadow rays of a wave in launches of their own
     const bool queue_by_queue = !finder && (((size_t)ctx->n_nodes / 2 * sizeof(NodePair) + (size_t)ctx->n_tris * sizeof(TriRecord)) > ((size_t)256 << 20) ||
                                             getenv("SRT_QUEUE_BY_QUEUE") != nullptr);  // (the variable: for tests at small sizes)
@@ -1223,7 +1228,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
       ctx->kernel_launches++;
     }
     for (int batch = 0;; ++batch) {
-      if (tail_ok && all_out && live <= (unsigned long long)ctx->tail_paths) {
+      if (tail_ok && all_out && live <= tail_at) {
         // the rest of the launch in one kernel (srt_wf_tail.cuh); with SRT_OPT_TIME_KERNELS it is reported as one more
         // trace launch (its shading included: the trace figure can only get worse by it)
         cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
