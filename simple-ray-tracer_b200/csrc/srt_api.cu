@@ -1038,7 +1038,16 @@ int ensure_pool_b(srt_ctx* ctx, size_t sample_entries) {
   b.sort_bins = a.sort_bins; b.sort_keys = a.sort_keys; b.sort_tmp = a.sort_tmp;
   b.cap = a.cap; b.ray_cap = a.ray_cap; b.list_cap = a.list_cap;
   if (!ctx->wave_stream) {
-    CU(ctx, cudaStreamCreateWithFlags(&ctx->wave_stream, cudaStreamNonBlocking));
+    {
+      // SRT_WAVE_PRIORITY (environment, experiments): 1 = the waves' stream gets the device's highest priority, so that
+      // their blocks are placed before the tail kernel's when both wait for an SM
+      int lo = 0, hi = 0;
+      const char* v = getenv("SRT_WAVE_PRIORITY");
+      if (v && atoi(v) == 1 && cudaDeviceGetStreamPriorityRange(&lo, &hi) == cudaSuccess)
+        CU(ctx, cudaStreamCreateWithPriority(&ctx->wave_stream, cudaStreamNonBlocking, hi));
+      else
+        CU(ctx, cudaStreamCreateWithFlags(&ctx->wave_stream, cudaStreamNonBlocking));
+    }
     CU(ctx, cudaEventCreateWithFlags(&ctx->ev_inputs, cudaEventDisableTiming));
     for (int k = 0; k < 2; ++k) {
       CU(ctx, cudaEventCreateWithFlags(&ctx->ev_waves_done[k], cudaEventDisableTiming));
