@@ -75,8 +75,9 @@ typedef struct srt_counters {
 
 #define SRT_OPT_TAIL_PATHS 11     /* wavefront schedule: once no more than this many paths are alive (and none is left to start),
                                      ONE kernel runs them all to their last bounce instead of ~50 ever smaller waves; the same
-                                     per-path arithmetic, the same bits (default 1 Mi; 0 = waves to the end).  Not used with
-                                     SRT_OPT_TEXTURES or SRT_OPT_COUNT_TRAVERSAL. */
+                                     per-path arithmetic, the same bits (default 1 Mi -- 128 Ki for a scene whose reference tree has
+                                     leaves of more than 64 triangles, which the tail's lock-step walk is slow on, unless the
+                                     option is set; 0 = waves to the end).  Not used with SRT_OPT_TEXTURES or SRT_OPT_COUNT_TRAVERSAL. */
 
 #define SRT_OPT_FINDER 12         /* wavefront schedule: how Intersects (ray_intersects.glsl:99-133) is evaluated.
                                      0 = walk the reference BVH as the shader does

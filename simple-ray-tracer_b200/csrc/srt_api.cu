@@ -237,6 +237,7 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
   if (key == SRT_OPT_TAIL_PATHS) {
     if (value < 0) return fail(ctx, "SRT_OPT_TAIL_PATHS: 0 (off) or a number of paths");
     ctx->tail_paths = (uint32_t)value;
+    ctx->tail_paths_set = true;
     return 0;
   }
   if (key == SRT_OPT_WAVE_SLOTS) {
@@ -608,6 +609,9 @@ extern "C" int srt_upload_scene(srt_ctx* ctx, const srt_bvh* bvhs, uint32_t n_bv
     return 1;
   if (upload_vec(ctx, ctx->d_mats, mats) || upload_vec(ctx, ctx->d_bvhs, rl.bvhs)) return 1;
   CU(ctx, cudaStreamSynchronize(ctx->stream));  // host vectors go out of scope
+  ctx->max_leaf = 0;
+  if (n_triangles <= SRT_FINDER_MAX_TRIS)  // (above that the finder is off and the number is not used)
+    for (uint32_t i = 0; i < n_nodes; ++i) ctx->max_leaf = std::max(ctx->max_leaf, nodes[i].prim_count);
   ctx->h_bvhs.assign(bvhs, bvhs + n_bvhs);
   ctx->h_bvh_records = rl.bvhs;
   ctx->n_nodes = n_nodes;
@@ -1199,7 +1203,10 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
     // the full frame -- a rank of an 8-GPU group: 16.6 M paths, threshold 130 k -- was measured: the stand-in, whose
     // reference tree is slow to walk, went from 13.3 to 8.6 ms per rank, Rubik from 5.3 to 5.7: with SRT_OPT_OVERLAP its
     // tail is hidden behind the next waves and the more it takes off them the better.  Scene-dependent; left to the option.)
-    const unsigned long long tail_at = ctx->tail_paths;
+    // Unless the caller chose a threshold: a reference tree with leaves of more than 64 triangles (the stand-in: 165) makes
+    // the tail's lock-step leaf loop slow, and waves through the hit finder are worth more there -- 128 Ki instead of 1 Mi
+    // (stand-in, ms per step at 1 Mi / 256 Ki / 64 Ki: 40.2 / 39.2 / 41.1 on one GPU, 13.3 / 8.8 / 8.8 per rank of 8).
+    const unsigned long long tail_at = (!ctx->tail_paths_set && finder && ctx->max_leaf > 64u) ? (128ull << 10) : ctx->tail_paths;
     // a scene far beyond L2's reach (126 MB): bounce rays and shadow rays of a wave in launches of their own
     const bool queue_by_queue = !finder && (((size_t)ctx->n_nodes / 2 * sizeof(NodePair) + (size_t)ctx->n_tris * sizeof(TriRecord)) > ((size_t)256 << 20) ||
                                             getenv("SRT_QUEUE_BY_QUEUE") != nullptr);  // (the variable: for tests at small sizes)

@@ -136,6 +136,8 @@ struct srt_ctx {
   bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
   uint32_t* d_culled = nullptr;                 // bit map of the paths the cull ended (one bit per sample entry)
   uint32_t tail_paths = 1u << 20;               // live paths at which the tail kernel takes over (SRT_OPT_TAIL_PATHS, 0 = never)
+  bool tail_paths_set = false;                  // the caller chose it; otherwise scenes with big leaves get a lower one (max_leaf)
+  uint32_t max_leaf = 0;                        // most triangles in one leaf of the uploaded reference tree
   size_t sample_entries = 0;                   // float4 entries allocated in pool.samples
   size_t sample_budget_bytes = (size_t)4 << 30;  // sample buffer budget per frame chunk (SRT_OPT_SAMPLE_BUDGET_MB)
 
