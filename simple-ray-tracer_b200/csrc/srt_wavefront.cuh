@@ -102,7 +102,9 @@ __device__ __forceinline__ void wf_store_primary(const PathPool& pool, const Fra
 // the sky term of GetRayColor's miss branch (raytrace_compute.glsl:287-292) and is written here.  The paths that are
 // left take consecutive slots (one pair of atomics per block), so wave 0 is as wide as the model on the screen and not
 // as the screen.
+#ifndef SRT_WF_INIT_THREADS
 #define SRT_WF_INIT_THREADS 256
+#endif
 template <bool CULL>
 __global__ void __launch_bounds__(SRT_WF_INIT_THREADS)
 wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool,

@@ -35,6 +35,15 @@ def test_library_exports_every_declared_symbol(pkg):
     assert b"sm_100a" in lib.srt_version()
 
 
+def test_option_numbers_match_the_header(pkg):
+    """Every SRT_OPT_* of the header has the same number in the Python view, and no two options share one."""
+    src = open(HEADER).read()
+    opts = {k: int(v) for k, v in re.findall(r"#define\s+SRT_OPT_([A-Z0-9_]+)\s+(\d+)", src)}
+    assert len(opts) >= 17 and len(set(opts.values())) == len(opts), opts
+    for name, number in opts.items():
+        assert getattr(pkg, "OPT_" + name) == number, name
+
+
 def test_struct_mirrors_match_the_c_layouts(pkg, tmp_path):
     src = tmp_path / "sizes.c"
     src.write_text('#include <stdio.h>\n#include "srt_b200.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
