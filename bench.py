@@ -243,6 +243,8 @@ def run_gpu(args):
         ctx.set_option(pkg.OPT_DEVICE_FINDER_BUILD, args.finder_build)
     if args.overlap >= 0:
         ctx.set_option(pkg.OPT_OVERLAP, args.overlap)
+    if args.fused_primary >= 0:
+        ctx.set_option(pkg.OPT_FUSED_PRIMARY, args.fused_primary)
     if args.sort_rays >= 0:
         ctx.set_option(pkg.OPT_SORT_RAYS, args.sort_rays)
 
@@ -582,6 +584,7 @@ def main():
                     help="<objects dir>/<NAME>/<NAME>.obj: render this model instead of the workload's scene (size, spp and depth stay "
                          "the workload's), e.g. the Airplane OBJ of BASELINE.json configs[2] where someone supplies it")
     ap.add_argument("--soup-tris", type=int, default=10_000_000, help="triangles of the soup workload")
+    ap.add_argument("--fused-primary", type=int, default=-1, help="0/1: SRT_OPT_FUSED_PRIMARY (default: library default, 0 = init kernel; 1 = the first find kernel makes the camera rays)")
     ap.add_argument("--overlap", type=int, default=-1, help="0/1: SRT_OPT_OVERLAP (default: library default, 1)")
     ap.add_argument("--finder-build", type=int, default=-1, help="0/1: SRT_OPT_DEVICE_FINDER_BUILD (default: library default, 1 = on the device)")
     ap.add_argument("--device-relayout", type=int, default=-1, help="0/1/2: SRT_OPT_DEVICE_RELAYOUT (default: library default, 2)")

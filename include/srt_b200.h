@@ -242,6 +242,15 @@ int srt_trace_rays_static(srt_ctx* ctx, const srt_ray* rays, uint32_t n_rays, ui
                                      call -- runs beside the waves of the next.  The accumulation image and the output are only ever
                                      touched on the context's stream, in call order: same bits.  0 = everything on the context's stream,
                                      one chunk after the other.  Off by itself while primary ids are recorded or tests are counted */
+#define SRT_OPT_FUSED_PRIMARY 19    /* wavefront schedule with the hit finder: 1 = no separate init kernel where every path of a launch starts
+                                     in its first wave; that wave's find kernel makes the camera rays itself and only a ray that comes back
+                                     with candidate triangles becomes a path in a slot -- any other ends there with the sky sample, one bit
+                                     instead of slot records and a trip through the logic kernel.  Same bits (parity-tested both ways).
+                                     0 (default) = init kernel, then the waves: measured FASTER (Rubik 1080p x 64 spp 26.3 against 29.3 ms,
+                                     an eighth of the frame 5.24 against 5.43): the two thirds of the camera rays that miss the root box
+                                     cost the persistent find kernel 2.5x what they cost the init kernel (half the occupancy, its fetch /
+                                     flush loop per 32 paths), more than the saved records give back.  Kept as the measured alternative.
+                                     Off by itself while tests are counted or rays sorted */
 #define SRT_OPT_SPLIT 14
 #define SRT_SPLIT_BANDS 0
 #define SRT_SPLIT_SAMPLES 1

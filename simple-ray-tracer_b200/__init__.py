@@ -23,6 +23,7 @@ OPT_SORT_RAYS = 16
 OPT_DEVICE_RELAYOUT = 15
 OPT_DEVICE_FINDER_BUILD = 17
 OPT_OVERLAP = 18
+OPT_FUSED_PRIMARY = 19
 SPLIT_BANDS, SPLIT_SAMPLES = 0, 1
 GROUP_ID_BYTES = 128
 TRACE_STATIC_MAX_RAYS = 65536

@@ -219,6 +219,11 @@ extern "C" int srt_set_option(srt_ctx* ctx, int key, int value) {
     ctx->sort_rays = value;
     return 0;
   }
+  if (key == SRT_OPT_FUSED_PRIMARY) {
+    if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_FUSED_PRIMARY: 0 (init kernel) or 1 (camera rays made by the first find kernel)");
+    ctx->fused_primary = value;
+    return 0;
+  }
   if (key == SRT_OPT_OVERLAP) {
     if (value != 0 && value != 1) return fail(ctx, "SRT_OPT_OVERLAP: 0 (off) or 1 (on)");
     ctx->overlap = value;
@@ -1227,7 +1232,14 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
       ctx->timing_used += 3;
       return 0;
     };
-    {
+    // SRT_OPT_FUSED_PRIMARY: no init kernel -- the first wave's find kernel makes the camera rays and only those that come back
+    // with candidates become paths in slots (srt_wf_find.cuh, PRIMARY).  Needs the cull's conditions (every path starts in
+    // wave 0) and a first wave at all; not while counting or sorting (both look at the queue the init kernel writes).
+    const bool fused = ctx->fused_primary && finder && cull && !ctx->count_traversal && !sort && !(tail_ok && all_out && live <= tail_at);
+    if (fused) {
+      CU(ctx, launch_wf_begin_fused(P, ctx->d_counters, S1));
+      ctx->kernel_launches++;
+    } else {
       // with the cull the init kernel answers rays (root-box tests): SRT_OPT_TIME_KERNELS reports it as one more trace
       // launch, like the tail kernel
       cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
@@ -1281,7 +1293,7 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
           ctx->kernel_launches += 8;
         }
         // camera rays are in the chunk's first wave and, while slots still take new paths, in any later one
-        const int finder_kind = !finder ? 0 : ((batch == 0 && w == 0) || !all_out) ? 2 : 1;
+        const int finder_kind = !finder ? 0 : (fused && batch == 0 && w == 0) ? 3 : ((batch == 0 && w == 0) || !all_out) ? 2 : 1;
         CU(ctx, launch_wf_wave(sc, fp, P, parity, traversal, ctx->count_traversal, ctx->refill_threshold, chunk_ids, ctx->d_counters,
                                ctx->block_threads, S1, ev[1], finder_kind, ctx->use_fork ? &ctx->fork : nullptr, queue_by_queue));
         if (ctx->time_kernels) CU(ctx, cudaEventRecord(ev[2], S1));

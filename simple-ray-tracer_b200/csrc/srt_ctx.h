@@ -132,6 +132,7 @@ struct srt_ctx {
   int device_finder_build = 1;                  // SRT_OPT_DEVICE_FINDER_BUILD: the hit finder's trees are built by kernels (srt_finder_build.cu)
   FinderBuildWorkspace finder_ws;
   RelayoutWorkspace relayout_ws;                // raw arrays + scratch of the device re-layout, kept between uploads
+  int fused_primary = 0;                        // SRT_OPT_FUSED_PRIMARY: the first wave's find kernel makes the camera rays (no init kernel); measured slower, off
   int sort_rays = 0;                            // SRT_OPT_SORT_RAYS: 0 off (default: measured slower, see srt_b200.h), 1 on
   bool primary_cull = true;                     // SRT_OPT_PRIMARY_CULL
   uint32_t* d_culled = nullptr;                 // bit map of the paths the cull ended (one bit per sample entry)

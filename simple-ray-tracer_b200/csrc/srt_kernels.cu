@@ -284,6 +284,23 @@ cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const P
   return cudaGetLastError();
 }
 
+// SRT_OPT_FUSED_PRIMARY: what wf_init_kernel<true> leaves behind besides the slots -- empty queues, every path of the launch
+// handed out, no bit of the culled map set -- for a first wave whose find kernel makes the camera rays (finder = 3 below)
+__global__ void wf_begin_fused_kernel(PathPool pool, DeviceCounters* __restrict__ counters) {
+  pool.q->next_path = pool.n_paths;
+  atomicAdd(&counters->segments, pool.n_paths);
+  atomicAdd(&counters->paths, pool.n_paths);
+}
+
+cudaError_t launch_wf_begin_fused(const PathPool& pool, DeviceCounters* counters, cudaStream_t stream) {
+  cudaError_t e;
+  if ((e = cudaMemsetAsync(pool.q, 0, sizeof(WaveCounters), stream)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(pool.fq, 0, sizeof(FinderQueues), stream)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(pool.culled, 0, (size_t)(pool.n_paths / 32 + 1) * sizeof(uint32_t), stream)) != cudaSuccess) return e;
+  wf_begin_fused_kernel<<<1, 1, 0, stream>>>(pool, counters);
+  return cudaGetLastError();
+}
+
 uint32_t launch_wf_max_logic_warps() {
   int dev = 0, sms = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
@@ -343,12 +360,12 @@ cudaError_t wf_trace_launch(const DeviceScene& sc, const FrameParams& fp, const 
 namespace {
 // the trace step through the hit finder (srt_wf_find.cuh): candidates, then the replay of the shader's culls, then the
 // rays with too many candidates (or a replay that could not be sure) the long way
-template <bool OUTSIDE, bool COUNT>
+template <bool OUTSIDE, bool COUNT, bool PRIMARY = false>
 cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int refill,
-                           DeviceCounters* counters, int block, cudaStream_t stream, const WaveFork* fork) {
+                           DeviceCounters* counters, int block, cudaStream_t stream, const WaveFork* fork, uint32_t* ids = nullptr) {
   static int per_sm = 0, sms = 0;
   static size_t smem_set = 0;
-  auto k = wf_find_kernel<OUTSIDE, COUNT>;
+  auto k = wf_find_kernel<OUTSIDE, COUNT, PRIMARY>;
   const size_t smem = (size_t)fp.stack_cap * SRT_WF_FIND_THREADS * 4u + (size_t)SRT_CAND_MAX * SRT_WF_FIND_THREADS * 8u;
   cudaError_t e;
   if (per_sm == 0 || smem_set != smem) {
@@ -366,7 +383,7 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
   long need = ((long)pool.cap / 32 + 1) / 2;
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  k<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill > 0 ? refill : SRT_WF_FIND_REFILL, counters);
+  k<<<(unsigned)grid, SRT_WF_FIND_THREADS, smem, stream>>>(sc, fp, pool, parity, refill > 0 ? refill : SRT_WF_FIND_REFILL, counters, ids);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   long blocks = ((long)pool.cap + 127) / 128;
   if (blocks > (long)sms * 16) blocks = (long)sms * 16;
@@ -385,7 +402,7 @@ cudaError_t wf_find_launch(const DeviceScene& sc, const FrameParams& fp, const P
     if ((e = wf_trace_launch<TRAV_REFERENCE, COUNT>(sc, fp, over, 0, refill, counters, block, fork->aux)) != cudaSuccess) return e;
     if ((e = cudaEventRecord(fork->joined, fork->aux)) != cudaSuccess) return e;
   }
-  wf_replay_kernel<COUNT><<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool, counters);
+  wf_replay_kernel<COUNT><<<(unsigned)blocks, 128, 0, stream>>>(sc, fp, pool, counters, PRIMARY ? 1 : 0);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   if (side_by_side) {
     if ((e = cudaStreamWaitEvent(stream, fork->joined, 0)) != cudaSuccess) return e;
@@ -400,7 +417,9 @@ cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const P
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
                            cudaEvent_t after_trace, int finder, const WaveFork* fork, bool queue_by_queue) {
   cudaError_t e;
-  if (finder == 2)  // a wave that may hold camera rays
+  if (finder == 3)  // the launch's camera rays, made by the find kernel itself (launch_wf_begin_fused came before)
+    e = wf_find_launch<true, false, true>(sc, fp, pool, parity, refill, counters, block, stream, fork, ids);
+  else if (finder == 2)  // a wave that may hold camera rays
     e = count ? wf_find_launch<true, true>(sc, fp, pool, parity, refill, counters, block, stream, fork)
               : wf_find_launch<true, false>(sc, fp, pool, parity, refill, counters, block, stream, fork);
   else if (finder)

@@ -22,6 +22,9 @@ cudaError_t launch_pack_noise(const float* unit3, const float* uniform3, float2*
                               cudaStream_t stream);
 cudaError_t launch_wf_init(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, bool cull,
                            uint32_t* primary_ids, bool count_nodes, DeviceCounters* counters, cudaStream_t stream);
+// SRT_OPT_FUSED_PRIMARY: instead of launch_wf_init, before a first wave launched with finder = 3 (the find kernel makes the
+// camera rays itself and gives slots only to those that come back with candidates; needs pool.culled and pool.fq)
+cudaError_t launch_wf_begin_fused(const PathPool& pool, DeviceCounters* counters, cudaStream_t stream);
 // A second stream + two events: in a finder wave without camera rays the overflow walk (rays with too many candidates) and
 // the replay are independent -- only an OUTSIDE ray's replay can add to the overflow list -- and run side by side.
 struct WaveFork {
@@ -30,7 +33,7 @@ struct WaveFork {
 };
 cudaError_t launch_wf_wave(const DeviceScene& sc, const FrameParams& fp, const PathPool& pool, int parity, int mode,
                            bool count, int refill, uint32_t* ids, DeviceCounters* counters, int block, cudaStream_t stream,
-                           cudaEvent_t after_trace = nullptr, int finder = 0,  // finder: 0 = walk the reference BVH, 1 = hit finder, 2 = hit finder with its outside-ray walk (waves that may hold camera rays)
+                           cudaEvent_t after_trace = nullptr, int finder = 0,  // finder: 0 = walk the reference BVH, 1 = hit finder, 2 = hit finder with its outside-ray walk (waves that may hold camera rays), 3 = as 2 and the find kernel makes the camera rays (after launch_wf_begin_fused)
                            const WaveFork* fork = nullptr, bool queue_by_queue = false);  // queue_by_queue (finder off): one trace launch per queue
 // SRT_OPT_SORT_RAYS: both queues of wave `parity` regrouped by the cell their rays start in (pool.sort_* must be allocated)
 cudaError_t launch_wf_sort(const DeviceScene& sc, const PathPool& pool, int parity, cudaStream_t stream);

@@ -67,10 +67,19 @@ __device__ __forceinline__ bool wf_find_box_t(V3 o, V3 inv, float tmax, float mn
 #ifndef SRT_WF_SHADOW_EARLY
 #define SRT_WF_SHADOW_EARLY 1  // shadow rays leave the finder walk at their first candidate (see the leaf loop)
 #endif
-template <bool OUTSIDE, bool COUNT>
+// PRIMARY (SRT_OPT_FUSED_PRIMARY; the first wave of a launch whose paths all start there, OUTSIDE, not COUNT): the kernel
+// takes PATHS of the launch instead of queue entries.  A lane makes the path's camera ray itself (GetRay, as wf_init_kernel)
+// and walks the finder with it; only a ray that comes back with candidates (or with too many) is given a slot -- its
+// records are written then, at the position the replay will read them from -- and a ray without any candidate, whose
+// CheckHit cannot find anything either, ends here as wf_init_kernel's culled paths do: one bit in PathPool::culled, the sky
+// sample never stored.  Against init + find that is one launch less, no slot records for the half of the surviving
+// camera rays that miss the model, and no trip of theirs through the logic kernel.  Until its flush a lane's `slot`
+// holds the path number; a path's slot is its position in the replay list (the replay kernel that follows publishes the
+// count as wave 0's queue length and as the launch's live paths).
+template <bool OUTSIDE, bool COUNT, bool PRIMARY = false>
 __global__ void __launch_bounds__(SRT_WF_FIND_THREADS, SRT_WF_FIND_MIN_BLOCKS)
 wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, int parity, int refill_threshold,
-               DeviceCounters* __restrict__ counters) {
+               DeviceCounters* __restrict__ counters, uint32_t* __restrict__ primary_ids) {
   extern __shared__ uint32_t s_find[];  // [stack_cap][64] node references, then [SRT_CAND_MAX][64] candidates (8 B)
   const uint32_t sp_base = (uint32_t)__cvta_generic_to_shared(s_find + threadIdx.x);
   constexpr uint32_t sp_step = SRT_WF_FIND_THREADS * 4u;
@@ -81,9 +90,9 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   const unsigned lt_mask = (1u << lane) - 1u;
   WaveCounters* q = pool.q;
   FinderQueues* fq = pool.fq;
-  const uint32_t n_front = q->n_closest[parity];
-  const uint32_t n_total = n_front + q->n_shadow[parity];
-  const uint32_t* __restrict__ list = parity ? pool.list[1] : pool.list[0];
+  const uint32_t n_front = PRIMARY ? (uint32_t)pool.n_paths : q->n_closest[parity];
+  const uint32_t n_total = PRIMARY ? n_front : n_front + q->n_shadow[parity];
+  const uint32_t* list = parity ? pool.list[1] : pool.list[0];
   if (blockIdx.x == 0 && threadIdx.x == 0) {  // the logic kernel of this wave fills the other list from empty
     q->n_closest[parity ^ 1] = 0;
     q->n_shadow[parity ^ 1] = 0;
@@ -106,6 +115,12 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   const int refill_at = refill_threshold < (lane_cap + 1) / 2 ? refill_threshold : (lane_cap + 1) / 2;
   uint32_t r_next = 0, r_end = 0, seen_cursor = 0;
 
+  // PRIMARY: the camera ray of path p (raytrace_compute.glsl:78-90), the values wf_init_kernel would have stored
+  auto camera_ray = [&](uint32_t p, uint32_t& pixel, uint32_t& f, int& x, int& y) -> V3 {
+    wf_path_id(pool, p, pixel, f);
+    tile_pixel(fp, pixel >> 5, pixel & 31, x, y);
+    return wf_primary_dir(sc, fp, x, y, y * fp.height + x, (int)f);  // Q4
+  };
   auto enter = [&]() {  // next BVH whose (padded) root box the ray meets, or the end of the ray
     for (;;) {
       if (bvh_i >= fp.bvh_count) {
@@ -114,9 +129,19 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
         return;
       }
       const BvhRecord* bvh = sc.bvhs + bvh_i;
-      const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1];
-      to = mat4_mul_(bvh->frame, v3(a.x, a.y, a.z), 1.0f);
-      td = mat4_mul_(bvh->frame, v3(b.x, b.y, b.z), 0.0f);
+      V3 ray_o, ray_d;
+      if (PRIMARY) {
+        uint32_t pixel, f;
+        int x, y;
+        ray_d = camera_ray(slot, pixel, f, x, y);
+        ray_o = fp.center;
+      } else {
+        const float4 a = pool.ray[2 * (size_t)slot], b = pool.ray[2 * (size_t)slot + 1];
+        ray_o = v3(a.x, a.y, a.z);
+        ray_d = v3(b.x, b.y, b.z);
+      }
+      to = mat4_mul_(bvh->frame, ray_o, 1.0f);
+      td = mat4_mul_(bvh->frame, ray_d, 0.0f);
       inv = v3(div_(1.0f, td.x), div_(1.0f, td.y), div_(1.0f, td.z));
       const float pad = bvh->finder_pad;
       tcull = tmax;
@@ -155,25 +180,62 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
     {
       const bool to_replay = pending && !overflow && n_cand > 0;
       const bool to_over = pending && overflow;
-      if (pending && !overflow && n_cand == 0) pool.hit[slot] = make_uint2(SRT_NO_HIT, __float_as_uint(tmax));
-      const unsigned m_r = __ballot_sync(FULL, to_replay);
+      const bool is_miss = pending && !overflow && n_cand == 0;
+      uint32_t rid = slot;  // the ray id the two lists get
+      if (PRIMARY) {
+        // a camera ray nothing can stop: the path's sample is the sky term (as a path wf_init_kernel culls).  Lanes that
+        // were handed paths together hold bits of one word of the map: one atomic for those, one each for stragglers.
+        const unsigned m_miss = __ballot_sync(FULL, is_miss);
+        if (m_miss) {
+          const int first_lane = __ffs(m_miss) - 1;
+          const uint32_t word = __shfl_sync(FULL, slot >> 5, first_lane);
+          const bool here = is_miss && (slot >> 5) == word;
+          const unsigned bits = __reduce_or_sync(FULL, here ? 1u << (slot & 31u) : 0u);
+          if (lane == first_lane) atomicOr(pool.culled + word, bits);
+          if (is_miss && !here) atomicOr(pool.culled + (slot >> 5), 1u << (slot & 31u));
+          if (is_miss && primary_ids != nullptr) {
+            uint32_t pixel, f;
+            int x, y;
+            (void)camera_ray(slot, pixel, f, x, y);
+            if (f == (uint32_t)(fp.n_frames - 1)) primary_ids[(size_t)y * fp.width + x] = SRT_NO_HIT;
+          }
+        }
+      } else if (is_miss) {
+        pool.hit[slot] = make_uint2(SRT_NO_HIT, __float_as_uint(tmax));
+      }
+      // PRIMARY: a camera ray that goes on becomes a path, and the path's slot IS its position in the replay list (one
+      // counter, one atomic per flush as without PRIMARY; a second same-address atomic per flush cost 4 ms per Rubik step) --
+      // so a ray bound for the overflow list takes a position too, with an entry the replay skips (no candidates).
+      const bool takes_entry = PRIMARY ? (to_replay || to_over) : to_replay;
+      const unsigned m_r = __ballot_sync(FULL, takes_entry);
       if (m_r) {
         uint32_t base = 0;
         const int leader = __ffs(m_r) - 1;
         if (lane == leader) base = atomicAdd(&fq->n_replay, (unsigned int)__popc(m_r));
         base = __shfl_sync(FULL, base, leader);
-        if (to_replay) {
+        if (takes_entry) {
           // the replay's input goes where the replay reads it in order: candidates and list entry by position in
           // the replay list, not by slot (scattered 64 B records cost 4-5x a sequential read, profiles/r01k_gather_probe)
           const uint32_t pos = base + (uint32_t)__popc(m_r & lt_mask);
           SRT_CHECK(pos < pool.ray_cap && n_cand <= SRT_CAND_MAX, SRT_CHK_CAND);
-          uint2* dst = pool.cand + (size_t)pos * SRT_CAND_MAX;
-          uint32_t w = 0;
-          for (uint32_t k = 0; k < n_cand; ++k) {  // an OUTSIDE ray keeps the candidates within its final theta
-            const uint2 c = wf_lds(cand_base + k * cand_step);
-            if (!OUTSIDE || !outside || __uint_as_float(c.y) <= tcull) dst[w++] = c;
+          if (PRIMARY) {  // the records wf_init_kernel would have written (wf_store_primary), for the paths that need them
+            SRT_CHECK(pos < pool.cap && pos < pool.list_cap, SRT_CHK_SLOT);
+            uint32_t pixel, f;
+            int x, y;
+            const V3 d = camera_ray(slot, pixel, f, x, y);
+            wf_store_primary(pool, fp, pos, d, pixel, f);
+            pool.list[0][pos] = 2u * pos;
+            rid = 2u * pos;
           }
-          pool.rlist[pos] = make_uint2(slot | (w << 28), __float_as_uint((OUTSIDE && outside) ? tcull : inf_()));  // .y: theta
+          uint32_t w = 0;
+          if (to_replay) {
+            uint2* dst = pool.cand + (size_t)pos * SRT_CAND_MAX;
+            for (uint32_t k = 0; k < n_cand; ++k) {  // an OUTSIDE ray keeps the candidates within its final theta
+              const uint2 c = wf_lds(cand_base + k * cand_step);
+              if (!OUTSIDE || !outside || __uint_as_float(c.y) <= tcull) dst[w++] = c;
+            }
+          }
+          pool.rlist[pos] = make_uint2(rid | (w << 28), __float_as_uint((OUTSIDE && outside) ? tcull : inf_()));  // .y: theta
         }
       }
       const unsigned m_o = __ballot_sync(FULL, to_over);
@@ -183,7 +245,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
         if (lane == leader) base = atomicAdd(&fq->over.n_closest[0], (unsigned int)__popc(m_o));
         base = __shfl_sync(FULL, base, leader);
         SRT_CHECK(base + (uint32_t)__popc(m_o) <= pool.list_cap, SRT_CHK_OVERFLOW);
-        if (to_over) pool.olist[base + __popc(m_o & lt_mask)] = slot;
+        if (to_over) pool.olist[base + __popc(m_o & lt_mask)] = rid;
       }
       pending = false;
     }
@@ -196,6 +258,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
         uint32_t chunk = (n_total - seen_cursor) / (total_warps * 4u);
         chunk = chunk > SRT_WF_FETCH_MAX ? SRT_WF_FETCH_MAX : chunk;
         chunk = chunk < (uint32_t)lane_cap ? (uint32_t)lane_cap : chunk;
+        if (PRIMARY) chunk = (chunk + 31u) & ~31u;  // a whole warp's paths: one word of the culled map
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(&fq->cursor, chunk);
         base = __shfl_sync(FULL, base, 0);
@@ -211,12 +274,12 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
       const int my_rank = __popc(idle & lt_mask);
       if (!trav && !pending && my_rank < n_take) {
         const uint32_t idx = r_next + my_rank;
-        SRT_CHECK((idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)) < pool.list_cap, SRT_CHK_LIST_READ);
-        const uint32_t entry = __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
-        if (entry != SRT_WF_HOLE) {
+        SRT_CHECK(PRIMARY || (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)) < pool.list_cap, SRT_CHK_LIST_READ);
+        const uint32_t entry = PRIMARY ? idx : __ldg(list + (idx < n_front ? idx : pool.list_cap - 1u - (idx - n_front)));
+        if (PRIMARY || entry != SRT_WF_HOLE) {
           slot = entry;
           SRT_CHECK(slot < pool.ray_cap, SRT_CHK_SLOT);
-          tmax = pool.ray[2 * (size_t)slot].w;
+          tmax = PRIMARY ? inf_() : pool.ray[2 * (size_t)slot].w;
           n_cand = 0;
           overflow = false;
           bvh_i = 0;
@@ -305,7 +368,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
                     // is occluded exactly when SOME candidate's boxes all pass the shader's culls with that distance.  The
                     // walk stops at its first candidate; the replay checks that one, and hands the ray to the full walk of
                     // the reference tree in the rare case it fails (a box the shader's slab test misses at a grazing angle).
-                    if (SRT_WF_SHADOW_EARLY && (slot & 1u)) {
+                    if (SRT_WF_SHADOW_EARLY && !PRIMARY && (slot & 1u)) {
                       trav = false;
                       pending = true;
                     }
@@ -342,14 +405,22 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
 #endif
 template <bool COUNT>
 __global__ void __launch_bounds__(128, SRT_WF_REPLAY_MIN_BLOCKS)
-wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, DeviceCounters* __restrict__ counters) {
+wf_replay_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, PathPool pool, DeviceCounters* __restrict__ counters,
+                 int after_primary) {
   const uint32_t n = pool.fq->n_replay;
+  // after wf_find_kernel<.., PRIMARY>: the slots it handed out are the launch's live paths (and wave 0's queue)
+  // (a slot is a position in this list, srt_wf_find.cuh PRIMARY; entries without candidates belong to rays on the overflow list)
+  if (after_primary && blockIdx.x == 0 && threadIdx.x == 0) {
+    pool.q->n_closest[0] = n;
+    pool.q->live_slots = n;
+  }
   unsigned int n_nodes = 0;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint2 entry = pool.rlist[i];
     const uint32_t slot = entry.x & 0x0FFFFFFFu, n_cand = entry.x >> 28;
     SRT_CHECK(slot < pool.ray_cap, SRT_CHK_SLOT);
     SRT_CHECK(n_cand <= SRT_CAND_MAX && i < pool.ray_cap, SRT_CHK_CAND);
+    if (n_cand == 0) continue;  // only after wf_find_kernel<.., PRIMARY>: a ray the overflow walk answers
     const float4 ra = pool.ray[2 * (size_t)slot], rb = pool.ray[2 * (size_t)slot + 1];
     const V3 ray_o = v3(ra.x, ra.y, ra.z), ray_d = v3(rb.x, rb.y, rb.z);
     const bool any_hit = (__float_as_uint(rb.w) & 0xFFu) == SRT_WF_KIND_SHADOW;
