@@ -60,6 +60,11 @@ __device__ __forceinline__ bool wf_find_box_t(V3 o, V3 inv, float tmax, float mn
   return (tn <= tf) && (tf >= 0.0f) && (tn <= tmax);
 }
 
+// (One fma per slab plane -- mn * inv - o * inv, the second product made once per ray -- takes 12 of the descent loop's 58
+// instructions away and was measured SLOWER, Rubik 26.0 -> 28.8 ms, stand-in 38.9 -> 45.9: that form's error is 2^-24 of
+// |o * inv| where the difference form's is 2^-23 of |(mn - o) * inv|, and a bounce ray starts ON a surface, next to the planes
+// of the boxes around it: with a small direction component the slab distances come out wrong by whole units of t, boxes
+// that should be culled are walked, and nothing bounds the error the other way either.  Not kept.)
 // OUTSIDE = false: the kernel without the outside-ray handling (every ray walks the finder tree without distance
 // culling, as an inside ray does either way); the host uses it for the waves that cannot hold camera rays.
 // COUNT (SRT_OPT_COUNT_TRAVERSAL = 2, bench.py's untimed pass): box and triangle tests this kernel really executes go to
