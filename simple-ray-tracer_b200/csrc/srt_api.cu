@@ -68,7 +68,7 @@ static void dfree(T*& p) {
 
 static void free_pool(srt_ctx* ctx) {
   PathPool& p = ctx->pool;
-  dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.path); dfree(p.pend);
+  dfree(p.ray); dfree(p.hit); dfree(p.pst); dfree(p.pend);
   dfree(p.list[0]); dfree(p.list[1]); dfree(p.dlist[0]); dfree(p.dlist[1]); dfree(p.q); dfree(p.samples);
   dfree(p.cand); dfree(p.rlist); dfree(p.olist); dfree(p.fq);
   dfree(p.sort_bins); dfree(p.sort_keys); dfree(p.sort_tmp);
@@ -78,7 +78,7 @@ static void free_pool(srt_ctx* ctx) {
   ctx->pool_slots = 0;
   ctx->sample_entries = 0;
   PathPool& b = ctx->pool_b;  // its own slot records, queues and samples; the finder / sort arrays are pool's
-  dfree(b.ray); dfree(b.hit); dfree(b.pst); dfree(b.path); dfree(b.pend);
+  dfree(b.ray); dfree(b.hit); dfree(b.pst); dfree(b.pend);
   dfree(b.list[0]); dfree(b.list[1]); dfree(b.dlist[0]); dfree(b.dlist[1]); dfree(b.q); dfree(b.samples);
   dfree(ctx->d_culled_b);
   memset(&b, 0, sizeof b);
@@ -968,7 +968,7 @@ int ensure_pool(srt_ctx* ctx, uint32_t slots, size_t sample_entries, bool want_f
     // per slot: two rays (closest-hit + shadow, 32 B each) and their two answers (8 B each), path state, pixel/frame, the
     // direct-light term put aside for the shadow ray
     CU(ctx, cudaMalloc(&p.ray, (size_t)slots * 64)); CU(ctx, cudaMalloc(&p.hit, (size_t)slots * 16));
-    CU(ctx, cudaMalloc(&p.pst, (size_t)slots * 32)); CU(ctx, cudaMalloc(&p.path, (size_t)slots * 8));
+    CU(ctx, cudaMalloc(&p.pst, (size_t)slots * 32));
     CU(ctx, cudaMalloc(&p.pend, (size_t)slots * 16));
     // a wave holds up to two rays per slot; every logic warp can leave one partly used reservation per queue: room for
     // those holes beside the rays
@@ -1022,11 +1022,11 @@ int ensure_pool_b(srt_ctx* ctx, size_t sample_entries) {
   const uint32_t slots = ctx->pool_slots;
   if (ctx->pool_b_slots != slots || !b.q) {
     CU(ctx, cudaStreamSynchronize(ctx->stream));
-    dfree(b.ray); dfree(b.hit); dfree(b.pst); dfree(b.path); dfree(b.pend);
+    dfree(b.ray); dfree(b.hit); dfree(b.pst); dfree(b.pend);
     dfree(b.list[0]); dfree(b.list[1]); dfree(b.dlist[0]); dfree(b.dlist[1]); dfree(b.q);
     ctx->pool_b_slots = 0;
     CU(ctx, cudaMalloc(&b.ray, (size_t)slots * 64)); CU(ctx, cudaMalloc(&b.hit, (size_t)slots * 16));
-    CU(ctx, cudaMalloc(&b.pst, (size_t)slots * 32)); CU(ctx, cudaMalloc(&b.path, (size_t)slots * 8));
+    CU(ctx, cudaMalloc(&b.pst, (size_t)slots * 32));
     CU(ctx, cudaMalloc(&b.pend, (size_t)slots * 16));
     CU(ctx, cudaMalloc(&b.list[0], ctx->pool_list_cap * 4)); CU(ctx, cudaMalloc(&b.list[1], ctx->pool_list_cap * 4));
     CU(ctx, cudaMalloc(&b.dlist[0], (size_t)slots * 4)); CU(ctx, cudaMalloc(&b.dlist[1], (size_t)slots * 4));
@@ -1144,6 +1144,8 @@ int render_wavefront(srt_ctx* ctx, const FrameParams& fp_all) {
   const size_t budget_entries = ctx->sample_budget_bytes / sizeof(float4);
   int chunk_frames = (int)(budget_entries / n_pixels);
   if (chunk_frames < 1) chunk_frames = 1;
+  // a path's number in its chunk (frame * n_pixels + pixel slot) is kept in 32 bits (PathPool::pst)
+  if ((unsigned long long)chunk_frames * n_pixels > 0xFFFFFFFFull) chunk_frames = (int)(0xFFFFFFFFull / n_pixels);
   // a chunk whose paths all fit the pool starts them all in wave 0, where the primary cull applies
   if (ctx->primary_cull && ctx->wave_slots / n_pixels >= 1u && (uint32_t)chunk_frames > ctx->wave_slots / n_pixels)
     chunk_frames = (int)(ctx->wave_slots / n_pixels);

@@ -204,9 +204,8 @@ struct PathPool {
   uint2* hit;    // [id] result: primitive (or SRT_NO_HIT), distance bits.  hit[2*slot+1].x = SRT_WF_NOT_PENDING while the
                  // slot has no shadow ray in flight (written by whoever decides not to emit one; not looked at while the
                  // path has not bounced yet, iter == 0: it cannot have one)
-  float4* pst;   // [2*slot]   throughput.xyz, unused
+  float4* pst;   // [2*slot]   throughput.xyz, bits: the path's number in the launch (frame * n_pixels + pixel slot, < 2^32)
                  // [2*slot+1] colour.xyz, bits: depth | rand_index << 8 | iter << 20
-  uint2* path;   // (pixel slot, frame of the launch) of the path in this slot  (8 B)
   float4* pend;  // while a shadow ray is out: the term `throughput * SampleDirect * weight` for an unoccluded light (.xyz), and
                  // in .w two bits per channel saying what the occluded term is (+0, -0 or NaN: 0 * anything)
   uint32_t* dlist[2];  // cap entries each: SLOTS whose path ends as soon as its last shadow ray is answered (no closest-hit

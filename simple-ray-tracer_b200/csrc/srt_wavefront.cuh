@@ -84,13 +84,14 @@ __device__ __forceinline__ void wf_path_id(const PathPool& pool, unsigned long l
 }
 
 // a new path moves into `slot`: its camera ray, unit throughput, no colour, no shadow ray in flight
-__device__ __forceinline__ void wf_store_primary(const PathPool& pool, const FrameParams& fp, uint32_t slot, V3 d, uint32_t pixel, uint32_t f) {
+// (the path's number in the launch -- frame * n_pixels + pixel slot, below 2^32 per chunk -- rides in the free word of the
+// throughput record: a record of its own was 8 bytes in a 32-byte sector, one more sector per logic visit)
+__device__ __forceinline__ void wf_store_primary(const PathPool& pool, const FrameParams& fp, uint32_t slot, V3 d, uint32_t path_number) {
   const size_t id = 2 * (size_t)slot;
   __stcs(pool.ray + 2 * id, make_float4(fp.center.x, fp.center.y, fp.center.z, inf_()));
   __stcs(pool.ray + 2 * id + 1, make_float4(d.x, d.y, d.z, __uint_as_float(SRT_WF_KIND_CLOSEST)));
-  __stcs(pool.pst + 2 * (size_t)slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
+  __stcs(pool.pst + 2 * (size_t)slot, make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(path_number)));
   __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_pack(fp.max_depth, 0, 0))));
-  __stcs(pool.path + slot, make_uint2(pixel, f));
   // (no "no shadow ray out" mark: a path that has not bounced yet, iter == 0, has none by definition -- one 8-byte write
   // into a sector of its own per camera path less)
 }
@@ -198,7 +199,7 @@ wf_init_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
   }
   SRT_CHECK(slot < pool.cap && slot < pool.list_cap, SRT_CHK_SLOT);
   SRT_CHECK(x >= 0 && x < fp.width && y >= 0 && y < fp.height, SRT_CHK_PIXEL);
-  wf_store_primary(pool, fp, slot, d, pixel, f);
+  wf_store_primary(pool, fp, slot, d, p);
   pool.list[0][slot] = 2u * slot;  // ray id of the slot's closest-hit ray
 }
 
@@ -585,23 +586,25 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         // the records phase B will gather for this slot, asked for now: by then they are in L2 instead of in DRAM
         wf_prefetch_l2(pool.ray + 4 * (size_t)slot);
         wf_prefetch_l2(pool.pst + 2 * (size_t)slot);
-        wf_prefetch_l2(pool.path + slot);
         if (h.z != SRT_WF_NOT_PENDING) wf_prefetch_l2(pool.pend + slot);
       }
     }
     shade = valid && stashed;
 
     uint2 path = make_uint2(0u, 0u);  // (pixel slot, frame of the launch)
+    uint32_t path_number = 0;         // frame * n_pixels + pixel slot: also the path's entry of the sample buffer
     int x = 0, y = 0, pix = 0;
     V3 throughput = v3(0.0f), color = v3(0.0f);
     int depth = 0, rand_index = 0, iter = 0;
     if (shade || finish) {
       // slot records stream through once per wave (gigabytes, no reuse within L2's reach): evict-first loads and stores
-      path = __ldcs(pool.path + slot);
+      const float4 t0 = __ldcs(pool.pst + 2 * (size_t)slot), c1 = __ldcs(pool.pst + 2 * (size_t)slot + 1);
+      path_number = __float_as_uint(t0.w);
+      path.y = path_number / pool.n_pixels;
+      path.x = path_number - path.y * pool.n_pixels;
       tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
       pix = y * fp.height + x;  // Q4
       SRT_CHECK(x >= 0 && x < fp.width && y >= 0 && y < fp.height, SRT_CHK_PIXEL);
-      const float4 t0 = __ldcs(pool.pst + 2 * (size_t)slot), c1 = __ldcs(pool.pst + 2 * (size_t)slot + 1);
       throughput = v3(t0.x, t0.y, t0.z);
       color = v3(c1.x, c1.y, c1.z);
       const uint32_t packed = __float_as_uint(c1.w);
@@ -693,7 +696,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
         finish = true;
       }
       if (goes_on || emit_dying) {
-        __stcs(pool.pst + 2 * (size_t)slot, make_float4(throughput.x, throughput.y, throughput.z, 0.0f));
+        __stcs(pool.pst + 2 * (size_t)slot, make_float4(throughput.x, throughput.y, throughput.z, __uint_as_float(path_number)));
         __stcs(pool.pst + 2 * (size_t)slot + 1, make_float4(color.x, color.y, color.z, __uint_as_float(wf_pack(depth, rand_index, iter))));
       }
     }
@@ -713,8 +716,8 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
       if (finish) {
         color = color + throughput * sky;  // Q19
         const V3 pixel_color = v3(0.0f) + color;  // main(): pixelColor = vec3(0) + GetRayColor(...)
-        SRT_CHECK((unsigned long long)path.y * pool.n_pixels + path.x < pool.n_paths && path.x < pool.n_pixels, SRT_CHK_SAMPLE);
-        __stcs(pool.samples + (size_t)path.y * pool.n_pixels + path.x, make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f));
+        SRT_CHECK((unsigned long long)path_number < pool.n_paths && path.x < pool.n_pixels, SRT_CHK_SAMPLE);
+        __stcs(pool.samples + path_number, make_float4(pixel_color.x, pixel_color.y, pixel_color.z, 0.0f));
         const unsigned long long next = base + (unsigned long long)__popc(m_f & lt_mask);
         if (next < pool.n_paths) {
           uint32_t pixel, f;
@@ -722,7 +725,7 @@ wf_logic_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pa
           int nx, ny;
           tile_pixel(fp, pixel >> 5, pixel & 31, nx, ny);
           const V3 d = wf_primary_dir(sc, fp, nx, ny, ny * fp.height + nx, (int)f);
-          wf_store_primary(pool, fp, slot, d, pixel, f);
+          wf_store_primary(pool, fp, slot, d, (uint32_t)next);
           emit_closest = true;
           n_seg++;
         } else {

@@ -228,7 +228,7 @@ wf_find_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
             uint32_t pixel, f;
             int x, y;
             const V3 d = camera_ray(slot, pixel, f, x, y);
-            wf_store_primary(pool, fp, pos, d, pixel, f);
+            wf_store_primary(pool, fp, pos, d, slot);
             pool.list[0][pos] = 2u * pos;
             rid = 2u * pos;
           }

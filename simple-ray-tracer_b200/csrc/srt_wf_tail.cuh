@@ -265,7 +265,9 @@ wf_tail_kernel(const DeviceScene sc, const __grid_constant__ FrameParams fp, Pat
           const size_t slot = my_slot;
           SRT_CHECK(slot < pool.cap, SRT_CHK_SLOT);
           const float4 t0 = pool.pst[2 * slot], c1 = pool.pst[2 * slot + 1];
-          path = pool.path[slot];
+          const uint32_t path_number = __float_as_uint(t0.w);  // frame * n_pixels + pixel slot (wf_store_primary)
+          path.y = path_number / pool.n_pixels;
+          path.x = path_number - path.y * pool.n_pixels;
           int x, y;
           tile_pixel(fp, path.x >> 5, path.x & 31, x, y);
           pix = y * fp.height + x;  // Q4
