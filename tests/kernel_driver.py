@@ -7,7 +7,7 @@ compute-sanitizer is closed on the pool this was developed on ("runs under it ha
 kernels' own bounds checks (csrc/srt_device.cuh SRT_CHECK, compiled in with -DSRT_CHECKED) stand in for memcheck: every
 traversal-stack push, every queue / list / slot / sample / candidate index.  The driver is small enough to run under a
 sanitizer where one is available.  Kernels reached: clear_accum, wf_init
-(<cull> and plain), wf_find (<outside> and plain), wf_replay, wf_trace (overflow walk, and the plain walk with the finder
+(<cull> and plain), wf_find (<outside>, <primary> and plain), wf_replay, wf_trace (overflow walk, and the plain walk with the finder
 off), wf_logic, wf_tail, wf_resolve, pathtrace (spheres, per-path and regeneration), pathtrace_persistent, tonemap,
 trace_rays (allocating and static-scratch entry points), pack_noise (pinned tables), detmath, the BVH builder's kernels,
 the probes.
@@ -65,6 +65,8 @@ def main():
     variants = [
         ("wavefront defaults (finder, cull, tail)", {}),
         ("wavefront, waves to the end through the finder", {pkg.OPT_TAIL_PATHS: 0, pkg.OPT_FINDER: 1}),
+        ("wavefront, camera rays made by the find kernel", {pkg.OPT_FUSED_PRIMARY: 1, pkg.OPT_TAIL_PATHS: 0, pkg.OPT_FINDER: 1}),
+        ("wavefront, same, tail at 1 Ki paths", {pkg.OPT_FUSED_PRIMARY: 1, pkg.OPT_TAIL_PATHS: 1024, pkg.OPT_FINDER: 1}),
         ("wavefront, plain walk, no cull, no tail", {pkg.OPT_TAIL_PATHS: 0, pkg.OPT_FINDER: 0, pkg.OPT_PRIMARY_CULL: 0}),
         ("wavefront, small pool (slots regenerate)", {pkg.OPT_WAVE_SLOTS: 2048, pkg.OPT_TAIL_PATHS: 256}),
         ("wavefront, ordered traversal, finder off", {pkg.OPT_FINDER: 0, pkg.OPT_TRAVERSAL: pkg.TRAV_ORDERED}),
@@ -88,6 +90,10 @@ def main():
     good &= check("rubik from inside, depth 8 (overflow rays)", ctx, True, rubik, cam=inside, max_depth=8)
     good &= check("soup 3 k, depth 8, finder forced", ctx, True, soup, cam=scenes.reset_camera(True, origin=(0.0, 0.0, 120.0)), max_depth=8)
     good &= check("spheres", ctx, False, None)
+    ctx.set_option(pkg.OPT_FUSED_PRIMARY, 1)
+    ctx.set_option(pkg.OPT_TAIL_PATHS, 0)
+    good &= check("rubik from inside, camera rays by the find kernel", ctx, True, rubik, cam=inside, max_depth=8)
+    ctx.set_option(pkg.OPT_FUSED_PRIMARY, 0)
     # the ray entry points, the probes, the decree kernel, the device BVH builder
     ctx.upload_scene(rubik)
     rays = np.zeros(777, pkg.RAY_DT)

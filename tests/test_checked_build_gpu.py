@@ -42,7 +42,7 @@ def test_checked_build_sees_no_out_of_bounds_access(pkg):
     assert m.group(1).endswith("checked")
     assert int(m.group(2), 16) == 0, "bounds checks fired: 0x%s\n%s" % (m.group(2), text)
     assert int(m.group(3), 16) == 1 << 31  # the checks are live in this build
-    assert len(re.findall(r"check_flags 0x0\b", text)) >= 11  # every rendered case reported its flag word
+    assert len(re.findall(r"check_flags 0x0\b", text)) >= 14  # every rendered case reported its flag word
 
 
 def test_normal_build_compiles_the_checks_away(pkg):
