@@ -33,7 +33,7 @@ namespace srt {
 #define SRT_WF_FIND_THREADS 64
 #define SRT_WF_FIND_REFILL 16  // idle lanes that send a find warp back to the queue (4 / 8 / 12 / 16 / 20 / 24 measured: 36.93 / 36.14 / 35.27 / 34.62 / 34.61 / 34.70 ms per Rubik step)
 #ifndef SRT_WF_FIND_MIN_BLOCKS
-#define SRT_WF_FIND_MIN_BLOCKS 16  // 64 registers
+#define SRT_WF_FIND_MIN_BLOCKS 16  // 64 registers, 24-64 B of spills outside the walk's loops; 12 (75-80 registers, none) measured 27.5 vs 26.0 ms per Rubik step, stand-in 38.3 vs 38.6
 #endif
 
 __device__ __forceinline__ void wf_sts1(uint32_t addr, uint32_t x) {
